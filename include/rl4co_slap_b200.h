@@ -1,0 +1,226 @@
+/*
+ * rl4co_slap_b200 - C ABI of the B200-native (sm_100a) rollout path.
+ *
+ * Drop-in boundary for the batched environment + Attention-Model decode rollout of
+ * j4n1k/rl4co-slap.  The reference is pure Python, so "the reference's FFI" for this path
+ * is a ctypes binding (INTEGRATION.md shows the stub a maintainer adds); each entry point
+ * below names the reference interface (file:line under rl4co/) it replaces.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller (torch caching allocator);
+ *    the library allocates nothing and frees nothing;
+ *  - `stream` is a cudaStream_t passed as void*; calls are asynchronous and stream ordered,
+ *    no host synchronisation inside;
+ *  - return value: 0 = launched, non-zero = host-side argument / launch error, message via
+ *    rl4co_last_error() (thread local);
+ *  - device-side conditions the reference raises as AssertionError ("Invalid tour",
+ *    "Used more than capacity", "infeasible action selected", "Logits contain NaNs",
+ *    "Logprobs should not be -inf") are OR-ed into the caller's int32 `status` word; the
+ *    host wrapper reads it once per call and raises with the reference's message;
+ *  - dtypes/shapes are the reference's: int64 actions and node ids, bool (1 byte) masks,
+ *    uint8 `visited`, float32 coordinates / demands / capacities.
+ */
+#ifndef RL4CO_SLAP_B200_H
+#define RL4CO_SLAP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RL4CO_ABI_VERSION 1
+
+/* status bits (device int32 word) */
+#define RL4CO_ST_INVALID_TOUR      1   /* tsp/env.py:173, cvrp/env.py:175 */
+#define RL4CO_ST_OVER_CAPACITY     2   /* cvrp/env.py:190 */
+#define RL4CO_ST_INFEASIBLE_ACTION 4   /* utils/decoding.py:379,395 */
+#define RL4CO_ST_NAN_LOGITS        8   /* models/nn/attention.py:285 */
+#define RL4CO_ST_NEG_INF_LOGP      16  /* utils/decoding.py:59 */
+#define RL4CO_ST_ACTION_RANGE      32  /* action outside [0,N): torch gather/scatter would raise */
+
+typedef void *rl4co_stream_t;
+
+int rl4co_abi_version(void);
+const char *rl4co_last_error(void);
+
+/* ------------------------------------------------------------------ TSP (K1) ------- */
+
+/* TSPEnv._reset, envs/routing/tsp/env.py:95-120 (+ done/terminated of EnvBase.reset,
+ * envs/common/base.py:143).  Any output pointer may be NULL. */
+int rl4co_tsp_reset(int64_t B, int32_t N, int64_t *first_node, int64_t *current_node,
+                    int64_t *i, uint8_t *action_mask, float *reward, uint8_t *done,
+                    uint8_t *terminated, rl4co_stream_t stream);
+
+/* TSPEnv._step, envs/routing/tsp/env.py:67-93.  In place on i / first_node / action_mask.
+ * `flag_ws` is a caller-provided int32 scratch word used for the reference's batch-global
+ * first-step test (`td["i"].all() == 0`, :70).  done is [B]. */
+int rl4co_tsp_step(int64_t B, int32_t N, const int64_t *action, int64_t *i,
+                   int64_t *first_node, int64_t *current_node, uint8_t *action_mask,
+                   uint8_t *done, int32_t *flag_ws, int32_t *status, rl4co_stream_t stream);
+
+/* Fused reset + T x _step + get_reward (tsp/env.py:67-93,157-173; utils/ops.py:65-101).
+ * actions [B,T] int64.  Outputs (each may be NULL): final first_node/current_node [B],
+ * i [B], action_mask [B,N], done [B], reward [B] (= -closed tour length of the T actions).
+ * check_validity != 0 ORs RL4CO_ST_INVALID_TOUR when sort(actions) != arange(N). */
+int rl4co_tsp_replay(int64_t B, int32_t N, int32_t T, const float *locs,
+                     const int64_t *actions, int64_t *first_node, int64_t *current_node,
+                     int64_t *i, uint8_t *action_mask, uint8_t *done, float *reward,
+                     int32_t check_validity, int32_t *status, rl4co_stream_t stream);
+
+/* ------------------------------------------------------------------ CVRP (K1) ------ */
+/* N counts the depot (node 0).  demand [B,N-1] is already divided by capacity. */
+
+/* CVRPEnv.get_action_mask, envs/routing/cvrp/env.py:137-149. */
+int rl4co_cvrp_action_mask(int64_t B, int32_t N, const float *demand,
+                           const float *used_capacity, const float *vehicle_capacity,
+                           const uint8_t *visited, const int64_t *current_node,
+                           uint8_t *action_mask, rl4co_stream_t stream);
+
+/* CVRPEnv._step, envs/routing/cvrp/env.py:73-105 (includes the mask update). */
+int rl4co_cvrp_step(int64_t B, int32_t N, const int64_t *action, const float *demand,
+                    const float *vehicle_capacity, float *used_capacity,
+                    int64_t *current_node, uint8_t *visited, uint8_t *action_mask,
+                    uint8_t *done, int32_t *status, rl4co_stream_t stream);
+
+/* Fused reset + T x _step + get_reward + check_solution_validity
+ * (cvrp/env.py:73-190).  locs [B,N,2] includes the depot at row 0. */
+int rl4co_cvrp_replay(int64_t B, int32_t N, int32_t T, const float *locs,
+                      const float *demand, const float *vehicle_capacity,
+                      const int64_t *actions, int64_t *current_node, float *used_capacity,
+                      uint8_t *visited, uint8_t *action_mask, uint8_t *done, float *reward,
+                      int32_t check_validity, int32_t *status, rl4co_stream_t stream);
+
+/* ------------------------------------------------------------------ SLAP (K1) ------ */
+/* N storage locations (node 0 = depot, never assignable), P products. */
+
+/* SLAPEnv._step, envs/warehousing/slap/env.py:38-93.  `product` = to_choose[:,0] as the
+ * reference stores it (float32, element stride `product_stride`); the to_choose slice
+ * itself is a view operation done by the host wrapper.  done is [B,1] = (i == P-1). */
+int rl4co_slap_step(int64_t B, int32_t N, int32_t P, const int64_t *action,
+                    const float *product, int64_t product_stride, int64_t *i,
+                    int32_t *assignment, uint8_t *action_mask, uint8_t *done,
+                    int32_t *status, rl4co_stream_t stream);
+
+/* SLAPEnv._get_reward, slap/env.py:131-143: sum over O orders of minus the closed
+ * Euclidean tour through locs[assignment[picklist[b,o,:]]].  picklist [B,O,K] int64. */
+int rl4co_slap_reward(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
+                      const float *locs, const int32_t *assignment, const int64_t *picklist,
+                      float *reward, rl4co_stream_t stream);
+
+/* Fused reset + P x _step + _get_reward.  actions [B,P] int64 (storage location of
+ * product t at step t).  Outputs may be NULL. */
+int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
+                      const float *locs, const int64_t *picklist, const int64_t *actions,
+                      int32_t *assignment, uint8_t *action_mask, int64_t *i, uint8_t *done,
+                      float *reward, int32_t *status, rl4co_stream_t stream);
+
+/* ------------------------------------------------------- AM decoder (K3, K2) ------- */
+
+#define RL4CO_ENV_TSP  0
+#define RL4CO_ENV_CVRP 1
+#define RL4CO_ENV_SLAP 2
+
+#define RL4CO_MODE_GREEDY   0  /* utils/decoding.py:371-381,410-418 */
+#define RL4CO_MODE_SAMPLING 1  /* utils/decoding.py:383-397,475-483 (Philox instead of torch.multinomial) */
+#define RL4CO_MODE_EVALUATE 2  /* utils/decoding.py:486-499 */
+
+#define RL4CO_EMBED_DIM 128
+#define RL4CO_NUM_HEADS 8
+
+/* K3 - one-off projection of the encoder's node embeddings into the per-node tables the
+ * rollout kernel consumes.  Replaces AttentionModelDecoder._precompute_cache
+ * (models/zoo/am/decoder.py:208-237) plus the per-node halves of the context projection
+ * (models/nn/env_embeddings/context.py:67-71).
+ *   tables[t][m][j] = sum_e h[m][e] * W[t*E + j][e]      m in [0,M), M = B*N, E = 128
+ * W is [n_tables*E, E] row-major (nn.Linear layout).  fp32 in, fp32 out, fp32-accurate. */
+int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
+                     float *tables, rl4co_stream_t stream);
+
+/* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */
+int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
+                           float *gctx, rl4co_stream_t stream);
+
+/* K2 - persistent rollout: encoder-output caches -> tours, log-likelihoods, rewards in ONE
+ * launch.  Replaces the hot loop ConstructivePolicy.forward
+ * (models/common/constructive/base.py:229-265): AttentionModelDecoder.forward
+ * (am/decoder.py:162-200), PointerAttention.forward (nn/attention.py:263-309),
+ * DecodingStrategy.step / process_logits (utils/decoding.py:141-191,327-369), the multistart
+ * pre_decoder_hook (utils/decoding.py:265-313), Env._step and Env.get_reward.
+ *
+ * Rollout r in [0,R), R = max(S,1)*B, is start s = r / B of instance b = r % B (the
+ * reference's batchify order, utils/ops.py:11-34).
+ *
+ * tables (from rl4co_am_project, [n_tables][B*N][E]):
+ *   0: glimpse keys  h.Wk^T (the 1/sqrt(16) score scale is applied in the kernel)
+ *   1: glimpse values h.Wv^T
+ *   2: folded logit keys h.(Wout^T Wl)^T  (project_out folded: <Wout o, l> = <o, Wout^T l>)
+ *   3: (tsp, cvrp) per-node context h.Wctx[:, cur-half]^T
+ *   4: (tsp) first-node context h.Wctx[:, first-half]^T
+ */
+typedef struct rl4co_am_rollout_args {
+    int32_t env;            /* RL4CO_ENV_* */
+    int32_t mode;           /* RL4CO_MODE_* */
+    int64_t B;              /* instances */
+    int32_t S;              /* starts per instance; <=1 means single start */
+    int32_t multistart;     /* !=0: first action forced to the POMO start node, log-prob 0 */
+    int32_t num_loc;        /* generator.num_loc for select_start_nodes (utils/ops.py:158-163) */
+    int32_t N;              /* nodes (incl. depot for cvrp / slap) */
+    int32_t T;              /* second dim of actions / logp (step capacity) */
+    int32_t P;              /* slap: products (= steps) */
+    int32_t O, K;           /* slap: orders, SKUs per order */
+    int32_t n_tables;
+    float temperature;
+    float tanh_clipping;    /* <=0: no clipping */
+    int32_t mask_logits;
+    const float *tables;
+    const float *gctx;      /* [B,E] or NULL (use_graph_context=False) */
+    const float *q0;        /* [E] tsp: Wctx . W_placeholder (step-0 context), else NULL */
+    const float *wcap;      /* [E] cvrp: Wctx[:, E] (remaining-capacity column), else NULL */
+    const float *locs;      /* [B,N,2] */
+    const float *demand;    /* cvrp [B,N-1] */
+    const float *vehicle_capacity; /* cvrp [B] */
+    const int64_t *picklist;/* slap [B,O,K] */
+    const int64_t *actions_in; /* evaluate: [R,T] */
+    uint64_t seed, offset;  /* Philox key / counter base for sampling */
+    int64_t *actions;       /* [R,T] out (padded with 0 after done) */
+    float *logp;            /* [R,T] chosen log-probs, may be NULL */
+    float *logp_all;        /* [R,T,N] all log-probs (store_all_logp / entropy), may be NULL */
+    float *ll;              /* [R] sum of chosen log-probs */
+    float *reward;          /* [R] */
+    int32_t *steps;         /* [R] steps until done, may be NULL */
+    int32_t *assignment;    /* slap [R,P] out, may be NULL */
+    int32_t *status;
+} rl4co_am_rollout_args;
+
+int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);
+
+/* Standalone decode step on given logits: process_logits + greedy / sampling / evaluate +
+ * chosen log-prob (utils/decoding.py:141-191,327-397).  logits [B,N] f32 (not modified),
+ * mask [B,N] bool.  Outputs: action [B] i64, logp [B] f32, logp_all [B,N] (may be NULL). */
+int rl4co_decode_step(int64_t B, int32_t N, const float *logits, const uint8_t *mask,
+                      int32_t mode, float temperature, float tanh_clipping,
+                      int32_t mask_logits, const int64_t *action_in, uint64_t seed,
+                      uint64_t offset, int64_t *action, float *logp, float *logp_all,
+                      int32_t *status, rl4co_stream_t stream);
+
+/* ------------------------------------------------------- reductions (K4) ----------- */
+
+/* Local partial of the reward statistics that are all-reduced across ranks (NCCL sum):
+ * stats[0] += sum(reward), stats[1] += sum(reward^2), stats[2] += n   (float64).
+ * Feeds RolloutBaseline mean / t-test and the logged reward mean
+ * (models/rl/reinforce/baselines.py:186-224, models/rl/common/base.py:224-240). */
+int rl4co_reward_stats(int64_t n, const float *reward, double *stats, rl4co_stream_t stream);
+
+/* POMO shared baseline + REINFORCE loss partials (baselines.py:57-61, reinforce.py:103-106).
+ * reward / ll are [S*B] start-major.  baseline[b] = mean_s reward; advantage [S*B];
+ * loss_partial[0] += sum((reward-baseline)*ll), loss_partial[1] += S*B  (float64);
+ * max_reward[b] = max_s reward (pomo/model.py:117-141).  Outputs may be NULL. */
+int rl4co_shared_baseline(int64_t B, int32_t S, const float *reward, const float *ll,
+                          float *baseline, float *advantage, float *max_reward,
+                          int64_t *best_start, double *loss_partial, rl4co_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RL4CO_SLAP_B200_H */

@@ -1,0 +1,136 @@
+// K3 - one-off projection of encoder node embeddings into the rollout tables, and the
+// graph context.  Reference: rl4co/models/zoo/am/decoder.py:208-237 (_precompute_cache),
+// rl4co/models/nn/env_embeddings/context.py:67-71 (the per-node halves of project_context).
+//
+// v1: fp32 SIMT register-tiled GEMM (128x128 CTA tile, 8x8 per thread, K staged in 32-wide
+// slabs), exact fp32 FMA accumulation in k order so the tables match torch's fp32 Linear to
+// ~1 ulp-level differences.  [the tcgen05 3xTF32 version replaces this in a later step]
+#include "common.cuh"
+
+namespace rl4co {
+
+constexpr int PE = RL4CO_EMBED_DIM;   // K dimension = 128
+constexpr int BM = 128, BN = 128, BK = 32;
+constexpr int PLD = BM + 4;
+
+__global__ void __launch_bounds__(256)
+am_project_kernel(int64_t M, const float *__restrict__ h, const float *__restrict__ W,
+                  float *__restrict__ tables) {
+    __shared__ __align__(16) float As[BK][PLD];
+    __shared__ __align__(16) float Ws[BK][PLD];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int64_t m0 = (int64_t)blockIdx.x * BM;
+    const int tab = blockIdx.y;                         // one table (128 output features) per y
+    const float *Wt = W + (size_t)tab * BN * PE;
+
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    for (int k0 = 0; k0 < PE; k0 += BK) {
+        // stage A[m0..m0+127][k0..k0+31] and W[0..127][k0..k0+31], transposed to k-major
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            int idx = tid + it * 256;
+            int row = idx >> 3, kq = idx & 7;
+            float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (m0 + row < M) av = __ldg(reinterpret_cast<const float4 *>(h + (m0 + row) * PE + k0) + kq);
+            As[kq * 4 + 0][row] = av.x; As[kq * 4 + 1][row] = av.y;
+            As[kq * 4 + 2][row] = av.z; As[kq * 4 + 3][row] = av.w;
+            float4 wv = __ldg(reinterpret_cast<const float4 *>(Wt + (size_t)row * PE + k0) + kq);
+            Ws[kq * 4 + 0][row] = wv.x; Ws[kq * 4 + 1][row] = wv.y;
+            Ws[kq * 4 + 2][row] = wv.z; Ws[kq * 4 + 3][row] = wv.w;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            float4 a0 = *reinterpret_cast<const float4 *>(&As[k][ty * 4]);
+            float4 a1 = *reinterpret_cast<const float4 *>(&As[k][64 + ty * 4]);
+            float4 b0 = *reinterpret_cast<const float4 *>(&Ws[k][tx * 4]);
+            float4 b1 = *reinterpret_cast<const float4 *>(&Ws[k][64 + tx * 4]);
+            float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float *out = tables + (size_t)tab * M * PE;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        int64_t m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (m < M) {
+            *reinterpret_cast<float4 *>(out + m * PE + tx * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            *reinterpret_cast<float4 *>(out + m * PE + 64 + tx * 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+        }
+    }
+}
+
+// gctx[b] = Wfixed . mean_n h[b,n,:]   (am/decoder.py:225-228)
+__global__ void __launch_bounds__(256)
+am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
+                        const float *__restrict__ Wfixed, float *__restrict__ gctx) {
+    extern __shared__ __align__(16) float gsm[];
+    float *Wt = gsm;                         // [e][j] transposed, stride PE+1
+    float *mean = gsm + PE * (PE + 1);       // [2][PE]
+    float *part = mean + 2 * PE;             // [2][PE]
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < PE * PE; idx += 256) {
+        int j = idx / PE, e = idx % PE;
+        Wt[e * (PE + 1) + j] = Wfixed[idx];
+    }
+    __syncthreads();
+    const int e = tid & (PE - 1), half = tid >> 7;
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+        const float *hb = h + b * (int64_t)N * PE;
+        float s = 0.f;
+        for (int n = half; n < N; n += 2) s += hb[(size_t)n * PE + e];
+        mean[half * PE + e] = s;
+        __syncthreads();
+        if (half == 0) mean[e] = (mean[e] + mean[PE + e]) / (float)N;
+        __syncthreads();
+        float d = 0.f;
+        for (int k = half * 64; k < half * 64 + 64; ++k) d = fmaf(mean[k], Wt[k * (PE + 1) + e], d);
+        part[half * PE + e] = d;
+        __syncthreads();
+        if (half == 0) gctx[b * PE + e] = part[e] + part[PE + e];
+        __syncthreads();
+    }
+}
+
+}  // namespace rl4co
+
+using namespace rl4co;
+
+extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
+                                float *tables, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_tables >= 1 && n_tables <= 16, "am_project: bad sizes M=%lld n_tables=%d", (long long)M, n_tables);
+    RL4CO_REQUIRE(h && W && tables, "am_project: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)W & 15) == 0 && ((uintptr_t)tables & 15) == 0,
+                  "am_project: pointers must be 16-byte aligned");
+    if (M == 0) return 0;
+    int64_t gx = (M + BM - 1) / BM;
+    RL4CO_REQUIRE(gx < (1ll << 31), "am_project: M too large");
+    dim3 grid((unsigned)gx, (unsigned)n_tables);
+    am_project_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(M, h, W, tables);
+    RL4CO_CHECK_LAUNCH("am_project");
+    return 0;
+}
+
+extern "C" int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
+                                      float *gctx, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(B >= 0 && N >= 1, "am_graph_context: bad sizes");
+    RL4CO_REQUIRE(h && Wfixed && gctx, "am_graph_context: null pointer");
+    if (B == 0) return 0;
+    size_t smem = (size_t)(PE * (PE + 1) + 4 * PE) * sizeof(float);
+    cudaFuncSetAttribute(am_graph_context_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int64_t grid = B < 148 * 3 ? B : 148 * 3;
+    am_graph_context_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(B, N, h, Wfixed, gctx);
+    RL4CO_CHECK_LAUNCH("am_graph_context");
+    return 0;
+}
