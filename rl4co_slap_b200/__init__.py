@@ -1,0 +1,18 @@
+"""rl4co_slap_b200 - B200-native (sm_100a) environment + Attention-Model decode rollout.
+
+Drop-in for ONE path of j4n1k/rl4co-slap: RL4COEnvBase-style TSP / CVRP / SLAP envs and
+AttentionModelPolicy.forward(decode_type=greedy|sampling|multistart_*|evaluate), backed by
+hand-written CUDA kernels behind a C ABI (include/rl4co_slap_b200.h).  No CPU fallback.
+"""
+from . import _lib  # noqa: F401
+from .baselines import (RolloutBaseline, SharedBaseline, global_reward_mean, reinforce_loss,  # noqa: F401
+                        reward_stats, shard_bounds)
+from .decoding import decode_step, get_log_likelihood, random_policy, rollout  # noqa: F401
+from .envs import ENV_REGISTRY, CVRPEnv, RL4COEnvBase, SLAPEnv, TSPEnv, get_env  # noqa: F401
+from .generators import CVRPGenerator, SLAPGenerator, TSPGenerator  # noqa: F401
+from .ops import (batchify, gather_by_index, get_num_starts, get_tour_length,  # noqa: F401
+                  select_start_nodes, unbatchify)
+from .policy import AttentionModelDecoder, AttentionModelPolicy, POMOPolicy  # noqa: F401
+from .tensordict_compat import TensorDict  # noqa: F401
+
+__version__ = "0.1.0"

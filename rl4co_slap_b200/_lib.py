@@ -120,6 +120,35 @@ def new_status(device) -> torch.Tensor:
     return torch.zeros(1, dtype=torch.int32, device=device)
 
 
+_deferred = {}
+
+
+def deferred_status(device) -> torch.Tensor:
+    """Per-device status word the single-step env kernels OR into; it is read (one sync) by
+    ``raise_deferred`` at the next get_reward, not after every step."""
+    key = torch.device(device)
+    if key.index is None:
+        key = torch.device("cuda", torch.cuda.current_device())
+    t = _deferred.get(key)
+    if t is None:
+        t = _deferred[key] = torch.zeros(1, dtype=torch.int32, device=key)
+    return t
+
+
+def raise_deferred(device) -> None:
+    key = torch.device(device)
+    if key.type != "cuda":
+        return
+    if key.index is None:
+        key = torch.device("cuda", torch.cuda.current_device())
+    t = _deferred.get(key)
+    if t is not None:
+        try:
+            raise_for_status(t)
+        finally:
+            t.zero_()
+
+
 def raise_for_status(status: torch.Tensor) -> None:
     """One device->host read per call; raises AssertionError with the reference's text."""
     bits = int(status.item())

@@ -1,0 +1,190 @@
+"""Instance generators with the reference's names, kwargs and output keys.
+
+Follows rl4co/envs/common/utils.py:11-92 (Generator, get_sampler),
+rl4co/envs/routing/tsp/generator.py:14-60, rl4co/envs/routing/cvrp/generator.py:15-143,
+rl4co/envs/warehousing/slap/generator.py:21-155.
+
+Generators are data preparation, not the hot path: they are vectorised torch code that
+runs on whatever ``device`` is asked for (the reference always samples on the CPU; its
+SLAP generator is O(B*N) python loops, here it is one broadcast).
+"""
+from __future__ import annotations
+
+import abc
+from typing import Callable, Union
+
+import torch
+from torch.distributions import Exponential, Normal, Poisson, Uniform
+
+from .tensordict_compat import TensorDict
+
+# Kool et al. 2019 capacities (cvrp/generator.py:15-30)
+CAPACITIES = {10: 20.0, 15: 25.0, 20: 30.0, 30: 33.0, 40: 37.0, 50: 40.0, 60: 43.0, 75: 45.0,
+              100: 50.0, 125: 55.0, 150: 60.0, 200: 70.0, 500: 100.0, 1000: 150.0}
+
+
+class Generator(metaclass=abc.ABCMeta):
+    """envs/common/utils.py:11-24: called as ``env.generator(batch_size)``."""
+
+    device = None
+
+    def __init__(self, **kwargs):
+        self.kwargs = kwargs
+
+    def __call__(self, batch_size) -> TensorDict:
+        batch_size = [batch_size] if isinstance(batch_size, int) else list(batch_size)
+        return self._generate(batch_size)
+
+    @abc.abstractmethod
+    def _generate(self, batch_size, **kwargs) -> TensorDict:
+        raise NotImplementedError
+
+
+class _DeviceUniform:
+    """Uniform(low, high) sampled directly on a device (same distribution as
+    torch.distributions.Uniform.sample: low + rand * (high - low))."""
+
+    def __init__(self, low, high, device=None):
+        self.low, self.high, self.device = float(low), float(high), device
+
+    def sample(self, shape):
+        u = torch.rand(tuple(shape), dtype=torch.float32, device=self.device)
+        return self.low + u * (self.high - self.low)
+
+
+def get_sampler(val_name: str, distribution: Union[int, float, str, type, Callable],
+                low: float = 0, high: float = 1.0, device=None, **kwargs):
+    """envs/common/utils.py:27-92 (uniform / constant / normal / exponential / poisson /
+    center / corner / callable; the cluster / mixture samplers are out of scope)."""
+    if isinstance(distribution, (int, float)):
+        return _DeviceUniform(distribution, distribution, device)
+    if distribution == Uniform or distribution == "uniform":
+        return _DeviceUniform(low, high, device)
+    if distribution == Normal or distribution in ("normal", "gaussian"):
+        assert kwargs.get(val_name + "_mean") is not None, "mean is required for Normal distribution"
+        assert kwargs.get(val_name + "_std") is not None, "std is required for Normal distribution"
+        return Normal(loc=kwargs[val_name + "_mean"], scale=kwargs[val_name + "_std"])
+    if distribution == Exponential or distribution == "exponential":
+        assert kwargs.get(val_name + "_rate") is not None, "rate is required for Exponential/Poisson distribution"
+        return Exponential(rate=kwargs[val_name + "_rate"])
+    if distribution == Poisson or distribution == "poisson":
+        assert kwargs.get(val_name + "_rate") is not None, "rate is required for Exponential/Poisson distribution"
+        return Poisson(rate=kwargs[val_name + "_rate"])
+    if distribution == "center":
+        return _DeviceUniform((high - low) / 2, (high - low) / 2, device)
+    if distribution == "corner":
+        return _DeviceUniform(low, low, device)
+    if callable(distribution):
+        return distribution(**kwargs)
+    raise ValueError(f"Invalid distribution type of {distribution}")
+
+
+class TSPGenerator(Generator):
+    """tsp/generator.py:14-60 -> td{"locs" [B, num_loc, 2] f32}."""
+
+    def __init__(self, num_loc: int = 20, min_loc: float = 0.0, max_loc: float = 1.0,
+                 init_sol_type: str = "random", loc_distribution=Uniform, device=None, **kwargs):
+        self.num_loc, self.min_loc, self.max_loc = num_loc, min_loc, max_loc
+        self.init_sol_type = init_sol_type
+        self.device = device
+        if kwargs.get("loc_sampler") is not None:
+            self.loc_sampler = kwargs["loc_sampler"]
+        else:
+            self.loc_sampler = get_sampler("loc", loc_distribution, min_loc, max_loc, device=device, **kwargs)
+
+    def _generate(self, batch_size) -> TensorDict:
+        locs = self.loc_sampler.sample((*batch_size, self.num_loc, 2))
+        return TensorDict({"locs": locs}, batch_size=batch_size)
+
+
+class CVRPGenerator(Generator):
+    """cvrp/generator.py:33-143 -> td{"locs" [B,n,2], "depot" [B,2], "demand" [B,n]
+    (already / capacity), "capacity" [B,1]}."""
+
+    def __init__(self, num_loc: int = 20, min_loc: float = 0.0, max_loc: float = 1.0,
+                 loc_distribution=Uniform, depot_distribution=None, min_demand: int = 1,
+                 max_demand: int = 10, demand_distribution=Uniform, vehicle_capacity: float = 1.0,
+                 capacity: float = None, device=None, **kwargs):
+        self.num_loc, self.min_loc, self.max_loc = num_loc, min_loc, max_loc
+        self.min_demand, self.max_demand = min_demand, max_demand
+        self.vehicle_capacity = vehicle_capacity
+        self.device = device
+        self.loc_sampler = kwargs.get("loc_sampler") or get_sampler(
+            "loc", loc_distribution, min_loc, max_loc, device=device, **kwargs)
+        if kwargs.get("depot_sampler") is not None:
+            self.depot_sampler = kwargs["depot_sampler"]
+        else:
+            self.depot_sampler = (get_sampler("depot", depot_distribution, min_loc, max_loc, device=device, **kwargs)
+                                  if depot_distribution is not None else None)
+        self.demand_sampler = kwargs.get("demand_sampler") or get_sampler(
+            "demand", demand_distribution, min_demand - 1, max_demand - 1, device=device, **kwargs)
+        if capacity is None:
+            capacity = CAPACITIES.get(num_loc)
+        if capacity is None:  # closest table entry (cvrp/generator.py:103-112)
+            closest = min(CAPACITIES.keys(), key=lambda x: abs(x - num_loc))
+            capacity = CAPACITIES[closest]
+        self.capacity = capacity
+
+    def _generate(self, batch_size) -> TensorDict:
+        if self.depot_sampler is not None:
+            depot = self.depot_sampler.sample((*batch_size, 2))
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc, 2))
+        else:  # depot = first sampled location (cvrp/generator.py:121-124)
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc + 1, 2))
+            depot = locs[..., 0, :]
+            locs = locs[..., 1:, :]
+        demand = self.demand_sampler.sample((*batch_size, self.num_loc))
+        demand = (demand.int() + 1).float()
+        capacity = torch.full((*batch_size, 1), self.capacity, device=demand.device)
+        return TensorDict({"locs": locs, "depot": depot, "demand": demand / self.capacity,
+                           "capacity": capacity}, batch_size=batch_size)
+
+
+class SLAPGenerator(Generator):
+    """slap/generator.py:21-155.  Grid warehouse: location i sits in aisle i // n_locs at
+    x = aisle * inter_aisle_dist, y = (i % n_locs) * inter_loc_dist (:67-80); Manhattan
+    distance matrix (:51-65); freq ~ U(min_freq, max_freq) [B,P,1] (:138); picklist =
+    max_orders x max_products_in_order uniform SKUs (:99-111); assignment = -1 int32."""
+
+    def __init__(self, n_products: int = 20, n_aisles: int = 10, n_locs: int = 10,
+                 inter_loc_dist: float = 1, inter_aisle_dist: float = 2.4, min_freq: int = 1,
+                 max_freq: int = 20, max_orders: int = 20, max_products_in_order: int = 5,
+                 device=None):
+        self.n_products, self.n_aisles, self.n_locs = n_products, n_aisles, n_locs
+        self.max_orders, self.max_products_in_order = max_orders, max_products_in_order
+        self.inter_loc_dist, self.inter_aisle_dist = inter_loc_dist, inter_aisle_dist
+        self.min_freq, self.max_freq = min_freq, max_freq
+        self.device = device
+        self.freq_sampler = _DeviceUniform(min_freq, max_freq, device)
+
+    @staticmethod
+    def _get_distance_matrix(locs: torch.Tensor) -> torch.Tensor:
+        if locs.dtype not in (torch.float32, torch.float64):
+            locs = locs.to(torch.float32)
+        return (locs[..., :, None, :] - locs[..., None, :, :]).abs().sum(-1)
+
+    def _calc_coordinates(self, batch_size) -> torch.Tensor:
+        total = self.n_aisles * self.n_locs
+        idx = torch.arange(total, device=self.device)
+        # python-float (double) products rounded once to fp32, like the reference's loop (:76-79)
+        x = ((idx // self.n_locs).to(torch.float64) * self.inter_aisle_dist).to(torch.float32)
+        y = ((idx % self.n_locs).to(torch.float64) * self.inter_loc_dist).to(torch.float32)
+        return torch.stack((x, y), -1).expand(*batch_size, total, 2).contiguous()
+
+    def _create_picklist(self, freq) -> torch.Tensor:
+        B = freq.shape[0]
+        return torch.randint(0, self.n_products, (B, self.max_orders, self.max_products_in_order),
+                             dtype=torch.int64, device=freq.device)
+
+    def _generate(self, batch_size) -> TensorDict:
+        freq = self.freq_sampler.sample((*batch_size, self.n_products, 1))
+        locs = self._calc_coordinates(batch_size)
+        # every instance shares the grid, so the [B,N,N] matrix is a stride-0 view of one [N,N]
+        # matrix (the reference materialises it: 40 GB at B = 1 Mi)
+        lead = (0,) * len(batch_size)
+        dist_mat = self._get_distance_matrix(locs[lead]).expand(*batch_size, -1, -1)
+        assignment = torch.full((*batch_size, self.n_products), -1, dtype=torch.int32, device=locs.device)
+        picklist = self._create_picklist(freq)
+        return TensorDict({"freq": freq, "locs": locs, "dist_mat": dist_mat, "assignment": assignment,
+                           "picklist": picklist, "depot_loc_dist": dist_mat[..., 0, :]},
+                          batch_size=batch_size)

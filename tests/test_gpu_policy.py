@@ -1,0 +1,235 @@
+"""GPU parity: projection (K3) + persistent rollout kernel (K2) + reductions (K4) through
+AttentionModelPolicy.forward vs the reference fixtures and the oracle port.
+Tolerances (BASELINE.json north_star): tours bit-exact given identical logits; rewards and
+log-likelihoods within 1e-5 relative (fp32); sampling matches in distribution."""
+import numpy as np
+import pytest
+import torch
+
+import rl4co_slap_b200 as R
+from oracle import port
+from tests.helpers import (env_of, fixture, gen_td, load_policy, oracle_reset, oracle_weights, t)
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def _run(case, dev, variant=None, **kw):
+    fx, name = fixture(case), env_of(case)
+    pol = load_policy(name, dev, variant)
+    env = R.get_env(name, device=dev)
+    td = env.reset(gen_td(name, fx, dev))
+    return fx, pol, env, td, pol(td, env, return_actions=True, hidden=t(fx["hidden"], dev), **kw)
+
+
+@pytest.mark.parametrize("case", ("tsp5", "tsp20", "tsp50", "tsp100", "cvrp10", "cvrp20", "cvrp50", "cvrp100",
+                                  "slap50", "slap100"))
+def test_greedy_matches_reference_fixture(case, dev):
+    fx, pol, env, td, out = _run(case, dev, decode_type="greedy", return_sum_log_likelihood=False)
+    assert out["actions"].dtype == torch.int64
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["greedy.actions"]), "tours differ from the reference"
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["greedy.reward"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["greedy.logprobs"], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(out["log_likelihood"].sum(1).cpu().numpy(), fx["greedy.ll"], rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", ("tsp20", "tsp50", "cvrp20", "cvrp50"))
+def test_multistart_greedy_matches_reference_fixture(case, dev):
+    S = int(fixture(case)["ms_greedy.num_starts"])
+    fx, pol, env, td, out = _run(case, dev, decode_type="multistart_greedy", num_starts=S)
+    assert out["reward"].shape == (fx["gen.locs"].shape[0] * S,)      # tests/test_policy.py:37-51
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["ms_greedy.actions"])
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["ms_greedy.reward"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["ms_greedy.ll"], rtol=RTOL, atol=1e-5)
+
+
+def test_pomo_policy_multistart_default_starts(dev):
+    fx, pol, env, td, out = _run("cvrp20_pomo", dev, variant="cvrp_pomo", decode_type="multistart_greedy")
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["ms_greedy.actions"])
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["ms_greedy.ll"], rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", ("tsp50", "cvrp50", "slap100"))
+def test_evaluate_given_actions(case, dev):
+    """ll of the reference's tours (no argmax divergence possible), constructive/base.py:206-207"""
+    fx, name = fixture(case), env_of(case)
+    pol, env = load_policy(name, dev), R.get_env(name, device=dev)
+    td = env.reset(gen_td(name, fx, dev))
+    out = pol(td, env, actions=t(fx["greedy.actions"], dev), hidden=t(fx["hidden"], dev), return_actions=True)
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["greedy.actions"])
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["greedy.ll"], rtol=RTOL, atol=1e-5)
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["greedy.reward"], rtol=RTOL, atol=1e-6)
+    # a random feasible tour against the oracle
+    acts = t(fx["replay.actions"], dev)
+    out = pol(td, env, actions=acts, hidden=t(fx["hidden"], dev))
+    ref = port.am_rollout(name, oracle_reset(name, fx), t(fx["hidden"]), oracle_weights(name), actions=acts.cpu())
+    torch.testing.assert_close(out["log_likelihood"].cpu(), ref["log_likelihood"], rtol=RTOL, atol=1e-5)
+    torch.testing.assert_close(out["reward"].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+
+
+def test_evaluate_invalid_tour_raises(dev):
+    fx = fixture("tsp20")
+    pol, env = load_policy("tsp", dev), R.TSPEnv(device=dev)
+    td = env.reset(gen_td("tsp", fx, dev))
+    bad = t(fx["greedy.actions"], dev).clone()
+    bad[0, 3] = bad[0, 2]
+    with pytest.raises(AssertionError, match="Invalid tour"):
+        pol(td, env, actions=bad, hidden=t(fx["hidden"], dev))
+
+
+def test_full_policy_with_pytorch_encoder(dev):
+    """encoder (PyTorch on GPU) + kernels end to end; larger random batch vs the oracle fed
+    with the same GPU-computed embeddings"""
+    torch.manual_seed(5)
+    for name, g in (("tsp", R.TSPGenerator(num_loc=30)), ("cvrp", R.CVRPGenerator(num_loc=30))):
+        pol, env = load_policy(name, dev), R.get_env(name, device=dev)
+        td0 = g(96)
+        td = env.reset(td0.to(dev))
+        with torch.inference_mode():
+            out = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True)
+        h = out["hidden"].node_embeddings.cpu()
+        o0 = port.tsp_reset(td0["locs"]) if name == "tsp" else port.cvrp_reset(td0["depot"], td0["locs"], td0["demand"])
+        ref = port.am_rollout(name, o0, h, oracle_weights(name), "greedy")
+        ga, ra = out["actions"].cpu(), ref["actions"]
+        Tm = max(ga.shape[1], ra.shape[1])      # cvrp: a near-tie flip may change the padded length
+        ga = torch.nn.functional.pad(ga, (0, Tm - ga.shape[1]))
+        ra = torch.nn.functional.pad(ra, (0, Tm - ra.shape[1]))
+        same = (ga == ra).all(1)
+        assert same.float().mean() > 0.97, "greedy tours diverge beyond near-tie flips"
+        torch.testing.assert_close(out["reward"].cpu()[same], ref["reward"][same], rtol=RTOL, atol=1e-6)
+        torch.testing.assert_close(out["log_likelihood"].cpu()[same], ref["log_likelihood"][same], rtol=RTOL, atol=2e-5)
+        ev = pol(td, env, actions=ref["actions"].to(dev), hidden=h.to(dev))
+        torch.testing.assert_close(ev["log_likelihood"].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
+
+
+def test_chunked_equals_unchunked(dev):
+    fx = fixture("tsp50")
+    pol, env = load_policy("tsp", dev), R.TSPEnv(device=dev)
+    td = env.reset(gen_td("tsp", fx, dev))
+    a = pol(td, env, decode_type="greedy", return_actions=True)
+    pol.rollout_chunk = 4
+    b = pol(td, env, decode_type="greedy", return_actions=True)
+    assert torch.equal(a["actions"], b["actions"]) and torch.equal(a["reward"], b["reward"])
+    assert torch.equal(a["log_likelihood"], b["log_likelihood"])
+
+
+def test_sampling_distribution(dev):
+    """Philox sampling vs the reference distribution: (1) every sampled tour is feasible and
+    its ll equals the evaluate-mode ll of the same tour; (2) first-step action frequencies
+    match the oracle's step-0 probabilities (chi-square); (3) mean reward of samples equals
+    the oracle's own multinomial sampling within 4 standard errors."""
+    fx = fixture("tsp20")
+    pol, env = load_policy("tsp", dev), R.TSPEnv(device=dev)
+    h1 = t(fx["hidden"], dev)[:1]
+    reps = 4096
+    locs = t(fx["gen.locs"], dev)[:1].expand(reps, -1, -1).contiguous()
+    td = env.reset(R.TensorDict({"locs": locs}, batch_size=[reps]))
+    hid = h1.expand(reps, -1, -1).contiguous()
+    torch.manual_seed(11)
+    out = pol(td, env, decode_type="sampling", return_actions=True, hidden=hid)
+    env.check_solution_validity(td, out["actions"])
+    ev = pol(td, env, actions=out["actions"], hidden=hid)
+    torch.testing.assert_close(ev["log_likelihood"], out["log_likelihood"], rtol=1e-6, atol=1e-6)
+    again = pol(td, env, decode_type="sampling", return_actions=True, hidden=hid)
+    assert not torch.equal(again["actions"], out["actions"])          # fresh seed per call
+    # step-0 distribution from the oracle
+    W = oracle_weights("tsp")
+    o0 = port.tsp_reset(t(fx["gen.locs"])[:1])
+    cache = port.precompute_cache(t(fx["hidden"])[:1], W)
+    logits, mask = port.decoder_forward("tsp", o0, cache, W, 0)
+    p0 = port.process_logits(logits, mask).exp()[0].double()
+    counts = torch.bincount(out["actions"][:, 0].cpu(), minlength=20).double()
+    chi2 = (((counts - reps * p0) ** 2) / (reps * p0).clamp_min(1e-9))[p0 * reps > 5].sum().item()
+    assert chi2 < 60.0, chi2                                           # dof <= 19, p ~ 1e-6
+    torch.manual_seed(3)
+    o = port.tsp_reset(t(fx["gen.locs"])[:1].expand(1024, -1, -1).contiguous())
+    ref = port.am_rollout("tsp", o, t(fx["hidden"])[:1].expand(1024, -1, -1), W, "sampling")
+    a, b = out["reward"].double().cpu(), ref["reward"].double()
+    se = (a.var() / a.numel() + b.var() / b.numel()).sqrt().item()
+    assert abs(a.mean().item() - b.mean().item()) < 4 * se
+
+
+def test_multistart_sampling_cvrp_pomo(dev):
+    """BASELINE config 4 shape: CVRP POMO multistart sampling + shared baseline"""
+    fx = fixture("cvrp20_pomo")
+    pol, env = load_policy("cvrp", dev, "cvrp_pomo"), R.CVRPEnv(device=dev)
+    td = env.reset(gen_td("cvrp", fx, dev))
+    B, S = fx["gen.locs"].shape[0], 20
+    torch.manual_seed(2)
+    out = pol(td, env, decode_type="multistart_sampling", return_actions=True, hidden=t(fx["hidden"], dev))
+    assert out["reward"].shape == (B * S,)
+    first = out["actions"][:, 0].view(S, B)
+    assert torch.equal(first, torch.arange(1, S + 1, device=dev)[:, None].expand(S, B))
+    env.check_solution_validity(R.batchify(td, S), out["actions"])
+    ref_r = port.cvrp_reward(R.batchify(td["locs"], S).cpu(), out["actions"].cpu())
+    torch.testing.assert_close(out["reward"].cpu(), ref_r, rtol=RTOL, atol=1e-6)
+    bl, part = R.SharedBaseline().eval(td, out["reward"], out["log_likelihood"], num_starts=S)
+    r2 = R.unbatchify(out["reward"], S)
+    torch.testing.assert_close(bl, r2.mean(1, keepdim=True), rtol=1e-6, atol=1e-6)
+    loss = R.reinforce_loss(part)
+    want = -((r2 - r2.mean(1, keepdim=True)) * R.unbatchify(out["log_likelihood"], S)).double().mean()
+    torch.testing.assert_close(loss, want, rtol=1e-5, atol=1e-6)
+
+
+def test_select_best_and_entropy(dev):
+    fx = fixture("tsp20")
+    pol, env = load_policy("tsp", dev), R.TSPEnv(device=dev)
+    td = env.reset(gen_td("tsp", fx, dev))
+    h = t(fx["hidden"], dev)
+    full = pol(td, env, decode_type="multistart_greedy", num_starts=8, return_actions=True, hidden=h)
+    best = pol(td, env, decode_type="multistart_greedy", num_starts=8, return_actions=True, hidden=h,
+               select_best=True, return_entropy=True)
+    torch.testing.assert_close(best["reward"], R.unbatchify(full["reward"], 8).max(1)[0])
+    assert best["actions"].shape == (8, 20) and best["entropy"].shape == (8,)
+    ent = pol(td, env, decode_type="greedy", return_entropy=True, hidden=h)["entropy"]
+    ref = port.am_rollout("tsp", oracle_reset("tsp", fx), t(fx["hidden"]), oracle_weights("tsp"), "greedy",
+                          return_all_logp=True)
+    lp = torch.nan_to_num(ref["logprobs"], nan=0.0)
+    want = -(lp.exp() * lp).nan_to_num(0.0).sum(-1).sum(1)
+    torch.testing.assert_close(ent.cpu(), want, rtol=1e-4, atol=1e-4)
+
+
+def test_decode_step_vs_torch(dev):
+    torch.manual_seed(0)
+    logits = torch.randn(300, 77, device=dev) * 3
+    mask = torch.rand(300, 77, device=dev) > 0.4
+    mask[:, 0] = True
+    lp, a = R.decode_step(logits, mask, "greedy", tanh_clipping=10.0, store_all_logp=True)
+    ref = port.process_logits(logits.cpu(), mask.cpu(), 1.0, 10.0)
+    torch.testing.assert_close(lp.cpu(), ref, rtol=1e-5, atol=1e-5)
+    assert torch.equal(a.cpu(), ref.argmax(-1))
+    lp2, a2 = R.decode_step(logits, mask, "sampling", temperature=2.0)
+    assert mask.gather(1, a2[:, None]).all()
+    ref2 = port.process_logits(logits.cpu(), mask.cpu(), 2.0, 0.0)
+    torch.testing.assert_close(lp2.cpu(), ref2.gather(1, a2.cpu()[:, None]).squeeze(1), rtol=1e-5, atol=1e-5)
+
+
+def test_reward_stats_and_global_mean(dev):
+    torch.manual_seed(1)
+    r = -torch.rand(100_003, device=dev) * 30
+    s = R.reward_stats(r)
+    assert s[2].item() == 100_003
+    torch.testing.assert_close(s[0], r.double().sum(), rtol=1e-12, atol=1e-9)
+    torch.testing.assert_close(s[1], (r.double() ** 2).sum(), rtol=1e-12, atol=1e-9)
+    torch.testing.assert_close(R.global_reward_mean(r), r.double().mean(), rtol=1e-12, atol=1e-12)
+
+
+def test_large_batch_greedy_properties(dev):
+    """size-independent checks at a large batch: every tour is a permutation, reward equals
+    the env's own replay of the returned tours, evaluate(ll) reproduces ll, and a sub-sample
+    matches the oracle."""
+    B, N = 8192, 100
+    torch.manual_seed(1234)
+    pol, env = load_policy("tsp", dev), R.TSPEnv(generator_params=dict(num_loc=N), device=dev)
+    td = env.reset(batch_size=[B])
+    with torch.inference_mode():
+        out = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True)
+    _, r = env.replay(td, out["actions"], check=True)
+    assert torch.equal(r, out["reward"])
+    h = out["hidden"].node_embeddings
+    ev = pol(td, env, actions=out["actions"], hidden=h)
+    torch.testing.assert_close(ev["log_likelihood"], out["log_likelihood"], rtol=1e-6, atol=1e-6)
+    idx = torch.arange(0, B, B // 32, device=dev)
+    ref = port.am_rollout("tsp", port.tsp_reset(td["locs"][idx].cpu()), h[idx].cpu(), oracle_weights("tsp"),
+                          actions=out["actions"][idx].cpu())
+    torch.testing.assert_close(out["log_likelihood"][idx].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
