@@ -1,6 +1,5 @@
 """GPU parity: env kernels (K1) through the reference-shaped API vs the reference fixtures
-and the oracle port.  Masks / states / tours bit-exact; rewards within 1e-5 relative (they
-are in fact bit-exact on the replay path: same fp32 op order, no FMA contraction)."""
+and the oracle port.  Masks / states / tours bit-exact; rewards within 1e-5 relative."""
 import numpy as np
 import pytest
 import torch
@@ -14,6 +13,13 @@ pytestmark = pytest.mark.gpu
 
 def _keys(fx, prefix):
     return [k[len(prefix) + 1:] for k in fx.files if k.startswith(prefix + ".")]
+
+
+def _close(got, want, what):
+    """rewards: 1e-5 relative (north_star); the kernels sum the legs warp-parallel, torch
+    sums them in its own vectorised order, so the last ulp may differ"""
+    np.testing.assert_allclose(got.cpu().numpy(), want, rtol=1e-5, atol=1e-6, err_msg=str(what))
+    assert got.cpu().numpy().dtype == want.dtype and got.shape == want.shape, what
 
 
 def _same(got, want, what):
@@ -40,7 +46,7 @@ def test_step_by_step_replay_bit_exact(case, dev):
             _same(td[k], fx[f"step{step}.{k}"], (case, step, k))
     assert bool(td["done"].all())
     reward = env.get_reward(td, acts)
-    _same(reward, fx["replay.reward"], (case, "reward"))
+    _close(reward, fx["replay.reward"], (case, "reward"))
 
 
 @pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES)
@@ -50,7 +56,7 @@ def test_fused_replay_matches_fixture(case, dev):
     td = env.reset(gen_td(name, fx, dev))
     acts = t(fx["replay.actions"], dev)
     final, reward = env.replay(td, acts)
-    _same(reward, fx["replay.reward"], (case, "reward"))
+    _close(reward, fx["replay.reward"], (case, "reward"))
     last = int(fx["replay.steps"]) - 1
     for k in _keys(fx, f"step{last}"):
         if k in final and k != "reward":
@@ -98,11 +104,11 @@ def test_fused_replay_vs_oracle_random(name, size, B, dev):
     env = R.get_env(name, device=dev)
     td = env.reset(td0.to(dev))
     final, reward = env.replay(td, acts.to(dev))
-    assert torch.equal(reward.cpu(), want)
+    torch.testing.assert_close(reward.cpu(), want, rtol=1e-5, atol=1e-6)
     for k in ("action_mask", "visited", "used_capacity", "current_node", "assignment", "done"):
         if k in final and k in fin:
             assert torch.equal(final[k].cpu().view(fin[k].shape), fin[k]), k
-    torch.testing.assert_close(env.get_reward(final if name == "slap" else td, acts.to(dev)).cpu(), want, rtol=0, atol=0)
+    torch.testing.assert_close(env.get_reward(final if name == "slap" else td, acts.to(dev)).cpu(), want, rtol=1e-5, atol=1e-6)
 
 
 def test_invalid_tours_raise_reference_messages(dev):
@@ -194,5 +200,5 @@ def test_full_size_replay_properties(dev):
     torch.testing.assert_close(r_rev, r, rtol=1e-5, atol=1e-5)
     idx = torch.randint(0, B, (512,), device=dev)
     want = port.tsp_reward(locs[idx].cpu(), acts[idx].cpu())
-    assert torch.equal(r[idx].cpu(), want)
+    torch.testing.assert_close(r[idx].cpu(), want, rtol=1e-5, atol=1e-6)
     assert abs(r.double().mean().item() + 52.14) < 0.05   # theory: N * 0.5214

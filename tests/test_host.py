@@ -114,7 +114,7 @@ def test_state_dict_names_and_folded_weights():
     """reference checkpoints load unchanged; folded tables reproduce the reference algebra"""
     for name in ("tsp", "cvrp", "slap"):
         pol = load_policy(name, "cpu")
-        W, q0, wcap = pol.decoder.folded_weights()
+        W, q0, wcap, _ = pol.decoder.folded_weights()
         ow = oracle_weights(name)
         E = 128
         h = torch.randn(6, E)
