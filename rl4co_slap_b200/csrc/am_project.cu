@@ -110,10 +110,10 @@ using namespace rl4co;
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
                                 float *tables, rl4co_stream_t stream) {
     RL4CO_REQUIRE(M >= 0 && n_tables >= 1 && n_tables <= 16, "am_project: bad sizes M=%lld n_tables=%d", (long long)M, n_tables);
+    if (M == 0) return 0;
     RL4CO_REQUIRE(h && W && tables, "am_project: null pointer");
     RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)W & 15) == 0 && ((uintptr_t)tables & 15) == 0,
                   "am_project: pointers must be 16-byte aligned");
-    if (M == 0) return 0;
     int64_t gx = (M + BM - 1) / BM;
     RL4CO_REQUIRE(gx < (1ll << 31), "am_project: M too large");
     dim3 grid((unsigned)gx, (unsigned)n_tables);
@@ -125,8 +125,8 @@ extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, con
 extern "C" int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
                                       float *gctx, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N >= 1, "am_graph_context: bad sizes");
-    RL4CO_REQUIRE(h && Wfixed && gctx, "am_graph_context: null pointer");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(h && Wfixed && gctx, "am_graph_context: null pointer");
     size_t smem = (size_t)(PE * (PE + 1) + 4 * PE) * sizeof(float);
     cudaFuncSetAttribute(am_graph_context_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int64_t grid = B < 148 * 3 ? B : 148 * 3;

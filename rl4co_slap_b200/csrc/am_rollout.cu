@@ -569,6 +569,7 @@ static int launch_rollout(const rl4co_am_rollout_args &a, int n_smem_tab, size_t
 extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream) {
     RL4CO_REQUIRE(args != nullptr, "am_rollout: null args");
     const rl4co_am_rollout_args &a = *args;
+    if (a.B == 0) return 0;
     RL4CO_REQUIRE(a.env >= RL4CO_ENV_TSP && a.env <= RL4CO_ENV_SLAP, "am_rollout: unknown env %d", a.env);
     RL4CO_REQUIRE(a.mode >= RL4CO_MODE_GREEDY && a.mode <= RL4CO_MODE_EVALUATE, "am_rollout: unknown mode %d", a.mode);
     RL4CO_REQUIRE(a.B >= 0 && a.N >= 2 && a.T >= 1, "am_rollout: bad sizes B=%lld N=%d T=%d", (long long)a.B, a.N, a.T);
@@ -584,7 +585,6 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     if (a.env == RL4CO_ENV_SLAP)
         RL4CO_REQUIRE(a.picklist && a.P >= 1 && a.O >= 0 && a.K >= 1 && a.T >= a.P, "am_rollout: slap needs picklist and T>=P");
     if (a.multistart) RL4CO_REQUIRE(a.num_loc >= 1 && a.env != RL4CO_ENV_SLAP, "am_rollout: bad multistart setup");
-    if (a.B == 0) return 0;
 
     int n_smem_tab = a.env == RL4CO_ENV_SLAP ? 3 : 4;
     const size_t limit = 227 * 1024;

@@ -177,11 +177,11 @@ extern "C" int rl4co_decode_step(int64_t B, int32_t N, const float *logits, cons
                                  uint64_t offset, int64_t *action, float *logp, float *logp_all,
                                  int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N >= 1, "decode_step: bad sizes");
+    if (B == 0) return 0;
     RL4CO_REQUIRE(logits && mask && action, "decode_step: null pointer");
     RL4CO_REQUIRE(mode >= RL4CO_MODE_GREEDY && mode <= RL4CO_MODE_EVALUATE, "decode_step: unknown mode %d", mode);
     RL4CO_REQUIRE(mode != RL4CO_MODE_EVALUATE || action_in, "decode_step: evaluate needs action_in");
     RL4CO_REQUIRE(temperature > 0.f, "decode_step: temperature must be > 0");
-    if (B == 0) return 0;
     int64_t blocks = (B + 7) / 8;
     RL4CO_REQUIRE(blocks < (1ll << 31), "decode_step: batch too large");
     decode_step_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(

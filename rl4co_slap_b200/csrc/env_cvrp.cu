@@ -171,9 +171,9 @@ extern "C" int rl4co_cvrp_action_mask(int64_t B, int32_t N, const float *demand,
                                       const uint8_t *visited, const int64_t *current_node,
                                       uint8_t *action_mask, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 1, "cvrp_action_mask: bad sizes B=%lld N=%d", (long long)B, N);
+    if (B == 0) return 0;
     RL4CO_REQUIRE(demand && used_capacity && vehicle_capacity && visited && current_node && action_mask,
                   "cvrp_action_mask: null pointer");
-    if (B == 0) return 0;
     unsigned g;
     RL4CO_REQUIRE(cvrp_blocks(B, &g) == 0, "cvrp_action_mask: batch too large");
     cvrp_mask_kernel<<<g, kCvrpWarps * 32, 0, (cudaStream_t)stream>>>(
@@ -187,9 +187,9 @@ extern "C" int rl4co_cvrp_step(int64_t B, int32_t N, const int64_t *action, cons
                                int64_t *current_node, uint8_t *visited, uint8_t *action_mask,
                                uint8_t *done, int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 1, "cvrp_step: bad sizes B=%lld N=%d", (long long)B, N);
+    if (B == 0) return 0;
     RL4CO_REQUIRE(action && demand && vehicle_capacity && used_capacity && current_node && visited &&
                       action_mask && done, "cvrp_step: null pointer");
-    if (B == 0) return 0;
     unsigned g;
     RL4CO_REQUIRE(cvrp_blocks(B, &g) == 0, "cvrp_step: batch too large");
     cvrp_step_kernel<<<g, kCvrpWarps * 32, 0, (cudaStream_t)stream>>>(
@@ -206,8 +206,8 @@ extern "C" int rl4co_cvrp_replay(int64_t B, int32_t N, int32_t T, const float *l
                                  uint8_t *done, float *reward, int32_t check_validity,
                                  int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 1 && T >= 0, "cvrp_replay: bad sizes B=%lld N=%d T=%d", (long long)B, N, T);
-    RL4CO_REQUIRE(locs && demand && vehicle_capacity && actions, "cvrp_replay: null input");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(locs && demand && vehicle_capacity && actions, "cvrp_replay: null input");
     int Tp = (T + 3) & ~3, Np = (N + 3) & ~3;
     int per_warp = (N * 8 + Np * 4 + Tp * 4 + Np + 15) & ~15;
     size_t smem = (size_t)per_warp * kCvrpWarps;

@@ -116,8 +116,8 @@ extern "C" int rl4co_slap_step(int64_t B, int32_t N, int32_t P, const int64_t *a
                                int32_t *assignment, uint8_t *action_mask, uint8_t *done,
                                int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 0 && P > 0, "slap_step: bad sizes B=%lld N=%d P=%d", (long long)B, N, P);
-    RL4CO_REQUIRE(action && product && i && assignment && action_mask && done, "slap_step: null pointer");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(action && product && i && assignment && action_mask && done, "slap_step: null pointer");
     int64_t blocks = (B + 255) / 256;
     RL4CO_REQUIRE(blocks < (1ll << 31), "slap_step: batch too large");
     slap_step_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
@@ -130,8 +130,8 @@ extern "C" int rl4co_slap_reward(int64_t B, int32_t N, int32_t P, int32_t O, int
                                  const float *locs, const int32_t *assignment,
                                  const int64_t *picklist, float *reward, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 0 && P > 0 && O >= 0 && K > 0, "slap_reward: bad sizes");
-    RL4CO_REQUIRE(locs && assignment && picklist && reward, "slap_reward: null pointer");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(locs && assignment && picklist && reward, "slap_reward: null pointer");
     int64_t blocks = (B + kSlapWarps - 1) / kSlapWarps;
     RL4CO_REQUIRE(blocks < (1ll << 31), "slap_reward: batch too large");
     slap_reward_kernel<<<(unsigned)blocks, kSlapWarps * 32, 0, (cudaStream_t)stream>>>(
@@ -146,8 +146,8 @@ extern "C" int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int
                                  uint8_t *action_mask, int64_t *i, uint8_t *done, float *reward,
                                  int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 0 && P > 0 && O >= 0 && K > 0, "slap_replay: bad sizes");
-    RL4CO_REQUIRE(locs && picklist && actions, "slap_replay: null input");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(locs && picklist && actions, "slap_replay: null input");
     size_t smem = (size_t)P * 4 * kSlapWarps;
     RL4CO_REQUIRE(smem <= 48 * 1024, "slap_replay: P=%d too large", P);
     int64_t blocks = (B + kSlapWarps - 1) / kSlapWarps;

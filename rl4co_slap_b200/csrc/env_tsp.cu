@@ -194,9 +194,9 @@ extern "C" int rl4co_tsp_step(int64_t B, int32_t N, const int64_t *action, int64
                               uint8_t *done, int32_t *flag_ws, int32_t *status,
                               rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 0, "tsp_step: bad sizes B=%lld N=%d", (long long)B, N);
+    if (B == 0) return 0;
     RL4CO_REQUIRE(action && i && first_node && current_node && action_mask && done && flag_ws,
                   "tsp_step: null pointer");
-    if (B == 0) return 0;
     cudaStream_t s = (cudaStream_t)stream;
     cudaMemsetAsync(flag_ws, 0, sizeof(int32_t), s);
     any_zero_kernel<<<grid_for(B, 256), 256, 0, s>>>(B, i, flag_ws);
@@ -214,8 +214,8 @@ extern "C" int rl4co_tsp_replay(int64_t B, int32_t N, int32_t T, const float *lo
                                 uint8_t *done, float *reward, int32_t check_validity,
                                 int32_t *status, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N > 0 && T >= 0, "tsp_replay: bad sizes B=%lld N=%d T=%d", (long long)B, N, T);
-    RL4CO_REQUIRE(locs && actions, "tsp_replay: null input");
     if (B == 0) return 0;
+    RL4CO_REQUIRE(locs && actions, "tsp_replay: null input");
     int words = (N + 31) / 32;
     int per_warp = N * 8 + ((T + 1) & ~1) * 4 + ((words + 3) & ~3) * 4;
     size_t smem = (size_t)per_warp * kWarpsPerCta;
