@@ -195,6 +195,12 @@ typedef struct rl4co_am_rollout_args {
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);
 
+/* rl4co_am_rollout picks between two kernels with identical semantics: register-file
+ * resident tables (single start, N <= 128) and shared-memory resident tables (multistart,
+ * or anything the first cannot hold).  impl = 1 forces the second one (parity tests run
+ * both against the oracle); impl = 0 restores the automatic choice. */
+int rl4co_set_rollout_impl(int impl);
+
 /* Standalone decode step on given logits: process_logits + greedy / sampling / evaluate +
  * chosen log-prob (utils/decoding.py:141-191,327-397).  logits [B,N] f32 (not modified),
  * mask [B,N] bool.  Outputs: action [B] i64, logp [B] f32, logp_all [B,N] (may be NULL). */

@@ -1,0 +1,85 @@
+// PTX / RNG / reward helpers shared by the two rollout kernels (am_rollout.cu: shared-memory
+// resident tables, any number of starts; am_rollout_rf.cu: register-file resident tables,
+// single start).
+#pragma once
+#include <math.h>
+
+#include "common.cuh"
+
+namespace rl4co {
+
+// ---------------------------------------------------------------- PTX helpers ------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, unsigned bytes,
+                                            uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+// ---------------------------------------------------------------- Philox4x32-10 ----
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+        uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += W0;
+        key.y += W1;
+    }
+    return ctr;
+}
+__device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, uint64_t r, uint32_t t) {
+    uint4 c = make_uint4((uint32_t)(offset + t), (uint32_t)((offset + t) >> 32), (uint32_t)r, (uint32_t)(r >> 32));
+    uint4 o = philox4x32_10(c, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    return (float)(o.x >> 8) * (1.0f / 16777216.0f);   // [0,1)
+}
+
+// closed tour through the K storage locations of one order (slap/env.py:136-142)
+__device__ __forceinline__ float slap_order_len(const float2 *locs, const int *assign,
+                                                const int64_t *order, int K) {
+    float2 first = locs[assign[(int)order[0]]], prev = first;
+    float len = 0.f;
+    for (int k = 1; k < K; ++k) {
+        float2 cur = locs[assign[(int)order[k]]];
+        len += leg(prev.x, prev.y, cur.x, cur.y);
+        prev = cur;
+    }
+    return len + leg(prev.x, prev.y, first.x, first.y);
+}
+
+
+// host-side launchers of the register-file resident single-start kernel (am_rollout_rf.cu)
+int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream);
+bool rollout_rf_supports(const rl4co_am_rollout_args &a);
+
+}  // namespace rl4co
