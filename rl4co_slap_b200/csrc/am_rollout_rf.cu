@@ -11,23 +11,22 @@
 // fp32 pairs, so that every mat-vec is FFMA2 (fma.rn.f32x2) work on registers - measured on
 // B200: ~85 FMA/clk/SM for FFMA2 against ~64 for three-register FFMA (tools/probe_sm.cu).
 //
-// One decode step = 2 block barriers:
+// One decode step = ONE block barrier:
 //   every warp, its own head, no block-level communication:
 //     q       = (gctx + ctx_first) + C[cur]      C = per-node context table (the one table
 //               gathered by row; staged in shared memory by a TMA bulk copy, double buffered)
 //     s[n]    = <q_h, K[n]_h> * 0.25*log2(e)     halves combined with one shuffle per node
 //     p[n]    = 2^(s[n] - max_n s[n])            masked nodes -> 0      (attention.py:289-306)
-//     o_h     = sum_n p[n] V[n]_h / sum_n p[n]   16-lane butterfly, 8 shuffles
-//     pl_h[n] = <o_h, L[n]_h>                    project_out folded into L -> shared memory
-//   barrier 1
-//   warp w finishes nodes 16w..16w+15: logit = sum_h pl_h / sqrt(E), tanh clip, mask,
-//     temperature (utils/decoding.py:141-191); warp max / argmax / sum of exponentials
-//   barrier 2
-//   every warp (8 candidates): global argmax / Philox inverse-CDF sample / given action, then
-//     the env transition and the new mask on its own copy of the state bits.
-// The chosen log-probability needs a log-sum-exp; its ingredients (per-warp max and sum,
-// chosen logit) are kept per step in shared memory and turned into log-probs after the loop,
-// one thread per step, so no transcendental sits on the step's critical path.
+//     o_h     = sum_n p[n] V[n]_h                16-lane butterfly, 8 shuffles
+//     pl_h[n] = <o_h, L[n]_h> / sum_n p[n]       project_out folded into L -> shared memory
+//   barrier (partial logits double buffered, so one barrier per step is enough)
+//   every warp, redundantly, lane l = nodes 4l..4l+3: logit = sum_h pl_h / sqrt(E), tanh clip,
+//     mask, temperature (utils/decoding.py:141-191); argmax / Philox inverse-CDF sample / given
+//     action; env transition and new mask on its own copy of the state bits.
+// The chosen log-probability needs a log-sum-exp; its ingredients (max, sum of exponentials -
+// each warp contributes the 16 nodes 16w..16w+15 -, chosen logit) are kept per step in shared
+// memory and turned into log-probs after the loop, one thread per step, so no logarithm sits
+// on the step's critical path.
 //
 // Reference op order being reproduced (all fp32): SURVEY.md appendix A;
 // rl4co/models/zoo/am/decoder.py:134-200, rl4co/models/nn/attention.py:263-309,
@@ -45,31 +44,36 @@ constexpr int kThreads = 256;
 constexpr int kWarps = 8;
 constexpr float kScoreScale = 0.25f * 1.4426950408889634f;   // 1/sqrt(16) * log2(e)
 constexpr float kInvSqrtE = 0.08838834764831845f;             // 1/sqrt(128)
+constexpr float kLog2e = 1.4426950408889634f;
 
-// row stride of the partial-logit matrix: = 16 (mod 32) so the two lane halves hit disjoint banks
-__host__ __device__ constexpr int pl_stride(int M) { return 16 * M + ((M & 1) ? 0 : 16); }
+constexpr int PLS = 144;              // row stride of the partial-logit matrix [head][node], = 16 (mod 32)
 
 struct Layout {
-    size_t off_c, off_pl, off_o, off_xs, off_cand, off_pref, off_ring, off_xa, off_act, off_ain,
-        off_lp, off_locs, off_dem, off_part, off_bar, total;
+    int xs_rows;        // T: every step keeps its logits (log-probs are formed after the loop); 1: per-step sums
+    size_t off_c, off_pl, off_xs, off_o, off_ring, off_mw, off_xa, off_act, off_ain, off_lp, off_locs,
+        off_dem, off_part, off_bar, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline Layout make_layout(int N, int T, int M, bool has_c) {
+__host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     Layout L;
+    // everything except the logits: does a [T][128] ring of them still fit next to it?
+    const size_t fixed = (has_c ? (size_t)2 * N * E * 4 : 0) + (size_t)kWarps * PLS * 4 + E * 4 +
+                         up16((size_t)T * kWarps * 4) + 5 * up16((size_t)T * 4) + up16((size_t)N * 8) +
+                         128 * 4 + 64 * 4 + 16;
+    L.xs_rows = (fixed + (size_t)T * 128 * 4 <= (size_t)227 * 1024) ? T : 1;
     size_t o = 0;
     L.off_c = o;    o += has_c ? (size_t)2 * N * E * 4 : 0;     // double-buffered context table
-    L.off_pl = o;   o += (size_t)16 * pl_stride(M) * 4;         // [2*head + half][node]
+    L.off_pl = o;   o += (size_t)kWarps * PLS * 4;              // partial logits [head][node]
+    L.off_xs = o;   o += (size_t)L.xs_rows * 128 * 4;           // processed logits, one row per step (or one in all)
     L.off_o = o;    o += E * 4;                                 // glimpse heads (warp private)
-    L.off_xs = o;   o += (size_t)16 * M * 4;                    // processed logits of the step
-    L.off_cand = o; o += kWarps * 8;                            // (max, argmax | sum) per warp
-    L.off_pref = o; o += kWarps * 16 * 4;                       // sampling: prefix sums per warp
-    L.off_ring = o; o += up16((size_t)T * kWarps * 8);          // per step, per warp (max, sum)
+    L.off_ring = o; o += up16((size_t)T * kWarps * 4);          // per step, per warp: sum of exponentials
+    L.off_mw = o;   o += up16((size_t)T * 4);                   // per step max logit
     L.off_xa = o;   o += up16((size_t)T * 4);                   // per step chosen logit
     L.off_act = o;  o += up16((size_t)T * 4);
     L.off_ain = o;  o += up16((size_t)T * 4);
     L.off_lp = o;   o += up16((size_t)T * 4);
     L.off_locs = o; o += up16((size_t)N * 8);
-    L.off_dem = o;  o += up16((size_t)16 * M * 4);
+    L.off_dem = o;  o += 128 * 4;
     L.off_part = o; o += 64 * 4;
     L.off_bar = o;  o += 16;
     L.total = o;
@@ -81,9 +85,25 @@ __device__ __forceinline__ float ex2f(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+// tanh(x) = 1 - 2 / (2^(2 log2(e) x) + 1): two MUFU ops; absolute error ~2e-7 (the libm tanhf
+// costs ~60 cycles of latency on the step's critical path)
+__device__ __forceinline__ float fast_tanh(float x) {
+    const float t = ex2f(x * 2.8853900817779268f);
+    return 1.f - __fdividef(2.f, t + 1.f);
+}
+__device__ __forceinline__ float rcpf(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 __device__ __forceinline__ float redux_max(float v) {       // all 32 lanes
     float r;
     asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ unsigned redux_min_u32(unsigned v) {
+    unsigned r;
+    asm volatile("redux.sync.min.u32 %0, %1, 0xffffffff;" : "=r"(r) : "r"(v));
     return r;
 }
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {  // SASS: FFMA2
@@ -108,22 +128,27 @@ __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
 
+// -DRF_TRACE: thread 0 of CTA 0 writes clock64() at eight points of every step of its first
+// instance into a.logp_all (reused as a [T][8] int64 buffer by tools/trace_rollout.py)
+#ifdef RF_TRACE
+#define RF_TRACE_AT(k) do { if (tid == 0 && blockIdx.x == 0 && it == 0) reinterpret_cast<long long *>(a.logp_all)[t * 8 + (k)] = clock64(); } while (0)
+#else
+#define RF_TRACE_AT(k) do { } while (0)
+#endif
+
 template <int ENV, int M>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
-    constexpr int NS = 16 * M;                      // node slots
-    constexpr int PLS = pl_stride(M);
     constexpr bool HAS_C = ENV != RL4CO_ENV_SLAP;
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T;
-    const Layout L = make_layout(N, T, M, HAS_C);
+    const Layout L = make_layout(N, T, HAS_C);
     float *cbuf = reinterpret_cast<float *>(smem + L.off_c);
     float *spl = reinterpret_cast<float *>(smem + L.off_pl);
-    float *so = reinterpret_cast<float *>(smem + L.off_o);
     float *sxs = reinterpret_cast<float *>(smem + L.off_xs);
-    float2 *scand = reinterpret_cast<float2 *>(smem + L.off_cand);
-    float *spref = reinterpret_cast<float *>(smem + L.off_pref);
-    float2 *sring = reinterpret_cast<float2 *>(smem + L.off_ring);
+    float *so = reinterpret_cast<float *>(smem + L.off_o);
+    float *sring = reinterpret_cast<float *>(smem + L.off_ring);
+    float *s_mw = reinterpret_cast<float *>(smem + L.off_mw);
     float *s_xa = reinterpret_cast<float *>(smem + L.off_xa);
     int *s_act = reinterpret_cast<int *>(smem + L.off_act);
     int *s_ain = reinterpret_cast<int *>(smem + L.off_ain);
@@ -139,7 +164,10 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
     const int64_t Mrows = a.B * (int64_t)N;         // rows per table
     const size_t c_bytes = (size_t)N * E * 4;
     const u64 scale2 = pack2(kScoreScale, kScoreScale);
-    const bool sampling = a.mode == RL4CO_MODE_SAMPLING;
+    // the usual decoding configuration gets a branch-free logit path
+    const bool xring = L.xs_rows > 1;
+    const bool std_logits = a.tanh_clipping > 0.f && a.temperature == 1.f && a.mask_logits != 0;
+    const float clip = a.tanh_clipping;
 
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -147,7 +175,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         fence_barrier_init();
     }
     __syncthreads();
-    unsigned parity[2] = {0u, 0u};
+    unsigned par0 = 0u, par1 = 0u;
     auto stage_context = [&](int64_t b, int buf) {  // thread 0: TMA the context table of instance b
         mbar_expect_tx(&bar[buf], (unsigned)c_bytes);
         const char *src = reinterpret_cast<const char *>(a.tables + ((size_t)3 * Mrows + b * (int64_t)N) * E);
@@ -217,11 +245,9 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         }
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
-        if (tid < NS) {
-            sxs[tid] = -INFINITY;
+        for (int q = tid; q < L.xs_rows * 128; q += kThreads) sxs[q] = -INFINITY;
+        if (tid < 128)
             s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
-        }
-        if (tid < kWarps) scand[tid] = make_float2(-INFINITY, 0.f);
         {
             const float2 *lrow = reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2);
             for (int n = tid; n < N; n += kThreads) s_locs[n] = lrow[n];
@@ -248,42 +274,84 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         __syncthreads();
 
         // ------------------------------------------------ env state, replicated in every warp
-        // bit j of a word <-> node g + 16 j.  tsp/env.py:95-120, cvrp/env.py:107-135, slap/env.py:95-129
-        unsigned own = 0;
+        // tsp/env.py:95-120, cvrp/env.py:107-135, slap/env.py:95-129.  Two copies of the mask:
+        //   owner layout  - bit j of a word <-> node g + 16 j   (glimpse mask of the mat-vec phase)
+        //   reader layout - bit k of a word <-> node 4 lane + k (logit mask of the selection phase)
+        unsigned own = 0, rown = 0;
 #pragma unroll
         for (int j = 0; j < M; ++j) own |= (g + 16 * j < N) ? (1u << j) : 0u;
-        unsigned alive = own, vis = 0;
-        if (ENV == RL4CO_ENV_SLAP && g == 0) alive &= ~1u;      // slap: depot never assignable
-        float dm[M];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
+        unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
+        if (ENV == RL4CO_ENV_SLAP) {                // slap: depot never assignable
+            if (g == 0) alive &= ~1u;
+            if (lane == 0) ralive &= ~1u;
+        }
+        float dm[M], rdm[4];
 #pragma unroll
         for (int j = 0; j < M; ++j) dm[j] = (ENV == RL4CO_ENV_CVRP) ? s_dem[g + 16 * j] : 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rdm[k] = (ENV == RL4CO_ENV_CVRP) ? s_dem[4 * lane + k] : 0.f;
         const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b] : 0.f;
         float used = 0.f;
-        auto cvrp_mask = [&](int at) {              // cvrp/env.py:137-149
-            unsigned f = 0;
+        auto cvrp_masks = [&](int at) {             // cvrp/env.py:137-149, both layouts
+            unsigned f = 0, rf = 0;
 #pragma unroll
             for (int j = 0; j < M; ++j) {
                 const bool exceeds = __fadd_rn(dm[j], used) > cap;
                 if (!exceeds && !((vis >> j) & 1u)) f |= 1u << j;
             }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const bool exceeds = __fadd_rn(rdm[k], used) > cap;
+                if (!exceeds && !((rvis >> k) & 1u)) rf |= 1u << k;
+            }
             f &= own;
+            rf &= rown;
             if (g == 0) f &= ~1u;
-            const bool any = __any_sync(kFull, f != 0);
-            if (g == 0 && !(at == 0 && any)) f |= 1u;
-            return f;
+            if (lane == 0) rf &= ~1u;
+            const bool depot = !(at == 0 && __any_sync(kFull, rf != 0));
+            if (g == 0 && depot) f |= 1u;
+            if (lane == 0 && depot) rf |= 1u;
+            alive = f;
+            ralive = rf;
         };
-        if (ENV == RL4CO_ENV_CVRP) alive = cvrp_mask(0);
+        if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
         int cur = 0, t = 0, status = 0;
         bool done = false, use_c = (ENV == RL4CO_ENV_CVRP);
         const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);
 
         if (HAS_C) {                                // context table landed?
-            mbar_wait(&bar[buf], parity[buf]);
-            parity[buf] ^= 1;
+            if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }
+            else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
         }
+
+        // log-prob ingredients of step tp (its logits px, their max pgm, its action pact): this warp's
+        // share of the sum of exponentials = nodes 16w..16w+15 = lanes 4w..4w+3, chosen logit, action
+        float px[4] = {0.f, 0.f, 0.f, 0.f}, pgm = 0.f;
+        int pact = 0;
+        auto book = [&](int tp) {
+            float e[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) e[k] = (px[k] == -INFINITY) ? 0.f : ex2f((px[k] - pgm) * kLog2e);
+            float esum = (e[0] + e[1]) + (e[2] + e[3]);
+            esum += __shfl_xor_sync(kFull, esum, 1);
+            esum += __shfl_xor_sync(kFull, esum, 2);
+            if (lane == 4 * warp) sring[tp * kWarps + warp] = esum;
+            if (warp == 0) {
+                float xa = pgm;
+                if (a.mode != RL4CO_MODE_GREEDY) {
+                    const int ak = pact & 3;
+                    const float mine = ak == 0 ? px[0] : ak == 1 ? px[1] : ak == 2 ? px[2] : px[3];
+                    xa = __shfl_sync(kFull, mine, pact >> 2);
+                }
+                if (lane == 0) { s_act[tp] = pact; s_xa[tp] = xa; s_mw[tp] = pgm; }
+            }
+        };
 
         // ================================================== decode loop ==================
         while (!done && t < t_end) {
+            RF_TRACE_AT(0);
             // ---- query of this half head (decoder.py:141-142), pre-scaled
             u64 q2[4];
             if (HAS_C && use_c) {
@@ -313,6 +381,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int j = 0; j < M; ++j) acc[j] = ffma2(K2[j][i], q2[i], acc[j]);
+                if (!xring && t > 0) book(t - 1);       // overlaps with the FFMA2 latency above
 #pragma unroll
                 for (int j = 0; j < M; ++j) s[j] = hsum2(acc[j]);
 #pragma unroll
@@ -325,6 +394,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 mx = fmaxf(mx, s[j]);
             }
             mx = redux_max(mx);
+            RF_TRACE_AT(1);
             float psum = 0.f;
             u64 oacc[4] = {0ull, 0ull, 0ull, 0ull};
 #pragma unroll
@@ -359,12 +429,13 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                     w1 = keep + __shfl_xor_sync(kFull, send, 2);
                 }
                 w1 += __shfl_xor_sync(kFull, w1, 1);
-                // this lane now holds head dim (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0) of its half
-                const int d = (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
-                so[dim0 + d] = __fdividef(w1, psum);
+                // this lane now holds head dim (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0) of its half,
+                // un-normalised; 1/psum is applied to the partial logits
+                so[dim0 + (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0)] = w1;
             }
             __syncwarp();
-            // ---- partial pointer logits over this half head, project_out folded (attention.py:276-282)
+            RF_TRACE_AT(2);
+            // ---- partial pointer logits of this head, project_out folded (attention.py:276-282)
             {
                 const ulonglong2 o0 = *reinterpret_cast<const ulonglong2 *>(so + dim0);
                 const ulonglong2 o1 = *(reinterpret_cast<const ulonglong2 *>(so + dim0) + 1);
@@ -376,102 +447,111 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int j = 0; j < M; ++j) acc[j] = ffma2(L2[j][i], o2[i], acc[j]);
-                float *row = spl + (2 * warp + hh) * PLS + g;
+                const float inv = __fdividef(1.f, psum);    // softmax normaliser of this head
+                float pl[M];
 #pragma unroll
-                for (int j = 0; j < M; ++j) row[16 * j] = hsum2(acc[j]);
+                for (int j = 0; j < M; ++j) pl[j] = hsum2(acc[j]) * inv;
+#pragma unroll
+                for (int j = 0; j < M; ++j) pl[j] += __shfl_xor_sync(kFull, pl[j], 16);
+                float *row = spl + warp * PLS + g;
+                if (hh == 0) {
+#pragma unroll
+                    for (int j = 0; j < M; ++j) row[16 * j] = pl[j];
+                }
             }
+            RF_TRACE_AT(3);
             __syncthreads();
+            RF_TRACE_AT(4);
 
-            // ---- warp w < M finishes nodes 16w .. 16w+15: process_logits (utils/decoding.py:141-191)
-            float x = -INFINITY;
+            float *sxrow = sxs + (xring ? t * 128 : 0);
+            // ---- warp w < M finishes nodes 16w .. 16w+15 (lane half hh sums heads hh, hh+2, hh+4, hh+6):
+            //      logit = sum_h pl_h / sqrt(E), then process_logits (utils/decoding.py:141-191)
             if (warp < M) {
                 const float *col = spl + hh * PLS + 16 * warp + g;
-                float sum = 0.f;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) sum += col[2 * k * PLS];
+                float sum = (col[0] + col[2 * PLS]) + (col[4 * PLS] + col[6 * PLS]);
                 sum += __shfl_xor_sync(kFull, sum, 16);
                 const bool exists = (own >> warp) & 1u, feasible = (alive >> warp) & 1u;
-                if (exists && (feasible || !a.mask_logits)) {
-                    x = sum * kInvSqrtE;
-                    if (x != x) status |= RL4CO_ST_NAN_LOGITS;
-                    if (a.tanh_clipping > 0.f) x = tanhf(x) * a.tanh_clipping;
-                    if (a.temperature != 1.f) x = __fdiv_rn(x, a.temperature);
-                }
-                const float mw = redux_max(x);
-                if (a.mode != RL4CO_MODE_GREEDY && hh == 0) sxs[16 * warp + g] = x;
-                float e = (x == -INFINITY) ? 0.f : expf(x - mw);
-                if (!sampling) {
-                    const unsigned eq = __ballot_sync(kFull, x == mw) & 0xffffu;
-                    const int arg = 16 * warp + (eq ? __ffs(eq) - 1 : 0);
-                    if (lane == 0) scand[warp] = make_float2(mw, __int_as_float(arg));
-#pragma unroll
-                    for (int o = 8; o > 0; o >>= 1) e += __shfl_xor_sync(kFull, e, o);
+                float xv;
+                if (std_logits) {
+                    // clip * tanh(z) = clip - 2 clip / (2^(2 log2(e) z) + 1), z = sum / sqrt(E)
+                    const float e2 = ex2f(sum * (kInvSqrtE * 2.f * kLog2e));
+                    xv = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
+                    if (exists && sum != sum) status |= RL4CO_ST_NAN_LOGITS;
+                    xv = feasible ? xv : -INFINITY;
                 } else {
-                    // inclusive prefix over the 16 nodes (both halves hold the same values)
-#pragma unroll
-                    for (int o = 1; o < 16; o <<= 1) {
-                        const float up = __shfl_up_sync(kFull, e, o, 16);
-                        if (g >= o) e += up;
-                    }
-                    if (hh == 0) spref[16 * warp + g] = e;
-                    e = __shfl_sync(kFull, e, 15);
-                    if (lane == 0) scand[warp] = make_float2(mw, e);
+                    xv = sum * kInvSqrtE;
+                    if (exists && xv != xv) status |= RL4CO_ST_NAN_LOGITS;
+                    if (clip > 0.f) xv = fast_tanh(xv) * clip;
+                    xv = __fdiv_rn(xv, a.temperature);
+                    xv = (exists && (feasible || !a.mask_logits)) ? xv : -INFINITY;
                 }
-                if (lane == 0) sring[(size_t)t * kWarps + warp] = make_float2(mw, e);
-            } else if (lane == 0) {
-                sring[(size_t)t * kWarps + warp] = make_float2(-INFINITY, 0.f);
+                if (hh == 0) sxrow[16 * warp + g] = xv;
             }
+            RF_TRACE_AT(5);
             __syncthreads();
-
-            // ---- every warp: combine the candidates, select (utils/decoding.py:371-397,410-499)
-            const float2 cd = scand[lane & 7];
-            const float gm = redux_max(cd.x);
+            RF_TRACE_AT(6);
+            // ---- every warp: all logits, lane = nodes 4 lane .. 4 lane + 3
+            float x[4];
+            {
+                const float4 xv = *reinterpret_cast<const float4 *>(sxrow + 4 * lane);
+                x[0] = xv.x; x[1] = xv.y; x[2] = xv.z; x[3] = xv.w;
+            }
+            const float gm = redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
+            // ---- selection (utils/decoding.py:371-397,410-499)
             int act;
-            float xa;
             if (a.mode == RL4CO_MODE_GREEDY) {
                 // argmax, lowest index on ties (the log-softmax shift is common to all nodes)
-                const unsigned eq = __ballot_sync(kFull, cd.x == gm) & 0xffu;
-                act = __float_as_int(__shfl_sync(kFull, cd.y, eq ? __ffs(eq) - 1 : 0));
-                xa = gm;
+                const unsigned cand = x[0] == gm ? 4u * lane : x[1] == gm ? 4u * lane + 1u
+                                    : x[2] == gm ? 4u * lane + 2u : x[3] == gm ? 4u * lane + 3u : 0x7fffffffu;
+                const unsigned win = redux_min_u32(cand);
+                act = win < (unsigned)N ? (int)win : 0;
+            } else if (a.mode == RL4CO_MODE_EVALUATE) {
+                act = s_ain[t];
+                if (act < 0) { status |= RL4CO_ST_ACTION_RANGE; act = 0; }
             } else {
-                if (a.mode == RL4CO_MODE_EVALUATE) {
-                    act = s_ain[t];
-                    if (act < 0) { status |= RL4CO_ST_ACTION_RANGE; act = 0; }
-                } else {
-                    // inverse-CDF sample of Categorical(exp(logp)) with one Philox uniform
-                    const float sc = (cd.x == -INFINITY) ? 0.f : expf(cd.x - gm);
-                    const float tw = cd.y * sc;
-                    float cum = tw;
+                // inverse-CDF sample of Categorical(exp(logp)) with one Philox uniform; every warp
+                // does the same arithmetic, so all of them agree on the action
+                float e[4];
 #pragma unroll
-                    for (int o = 1; o < 8; o <<= 1) {
-                        const float up = __shfl_up_sync(kFull, cum, o, 8);
-                        if ((lane & 7) >= o) cum += up;
-                    }
-                    const float total = __shfl_sync(kFull, cum, 7);
-                    const float u = philox_uniform(a.seed, a.offset, (uint64_t)r, (uint32_t)t) * total;
-                    const unsigned over = __ballot_sync(kFull, cum > u && tw > 0.f) & 0xffu;
-                    const unsigned nz = __ballot_sync(kFull, tw > 0.f) & 0xffu;
-                    const int ws = over ? __ffs(over) - 1 : (nz ? 31 - __clz(nz) : 0);
-                    const float before = __shfl_sync(kFull, cum - tw, ws), scw = __shfl_sync(kFull, sc, ws);
-                    const float pf = spref[16 * ws + g];
-                    const float prev = __shfl_up_sync(kFull, pf, 1, 16);
-                    const bool nonzero = pf > (g == 0 ? 0.f : prev);
-                    const unsigned hit = __ballot_sync(kFull, nonzero && fmaf(pf, scw, before) > u) & 0xffffu;
-                    const unsigned any = __ballot_sync(kFull, nonzero) & 0xffffu;
-                    act = 16 * ws + (hit ? __ffs(hit) - 1 : (any ? 31 - __clz(any) : 0));
+                for (int k = 0; k < 4; ++k) e[k] = (x[k] == -INFINITY) ? 0.f : ex2f((x[k] - gm) * kLog2e);
+                const float ls = (e[0] + e[1]) + (e[2] + e[3]);
+                float incl = ls;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const float up = __shfl_up_sync(kFull, incl, o);
+                    if (lane >= o) incl += up;
                 }
-                xa = sxs[act];
+                const float total = __shfl_sync(kFull, incl, 31);
+                const float u = philox_uniform(a.seed, a.offset, (uint64_t)r, (uint32_t)t) * total;
+                float run = incl - ls;
+                int pick = -1, lastf = -1;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (e[k] > 0.f) {
+                        lastf = 4 * lane + k;
+                        run += e[k];
+                        if (pick < 0 && run > u) pick = 4 * lane + k;
+                    }
+                }
+                const unsigned has = __ballot_sync(kFull, pick >= 0);
+                const unsigned any = __ballot_sync(kFull, lastf >= 0);
+                act = has ? __shfl_sync(kFull, pick, __ffs(has) - 1)
+                          : (any ? __shfl_sync(kFull, lastf, 31 - __clz(any)) : 0);
             }
-            // feasibility of the chosen action (utils/decoding.py:377-379,393-395)
-            {
-                const unsigned fb = __shfl_sync(kFull, alive, act & 15);
-                if (!((fb >> (act >> 4)) & 1u)) status |= RL4CO_ST_INFEASIBLE_ACTION;
-            }
-            if (tid == 0) { s_act[t] = act; s_xa[t] = xa; }
-            // ---- transition
+            // feasibility of the chosen action (utils/decoding.py:377-379,393-395): its owner lane checks
+            if (lane == (act >> 2) && !((ralive >> (act & 3)) & 1u)) status |= RL4CO_ST_INFEASIBLE_ACTION;
+            // the step's log-prob ingredients are recorded during the next step's mat-vecs (book())
+#pragma unroll
+            for (int k = 0; k < 4; ++k) px[k] = x[k];
+            pgm = gm;
+            pact = act;
+            if (xring && tid == 0) { s_act[t] = act; s_mw[t] = gm; }
+            // ---- transition, both mask layouts
             const unsigned abit = (g == (act & 15)) ? (1u << (act >> 4)) : 0u;
+            const unsigned rbit = (lane == (act >> 2)) ? (1u << (act & 3)) : 0u;
             if (ENV == RL4CO_ENV_TSP) {                 // tsp/env.py:67-93
                 alive &= ~abit;
+                ralive &= ~rbit;
                 if (t == 0) {
                     // from step 1 on: ctx = Wc [h_first ; h_cur] (context.py:123-131); the
                     // first-node half is constant for the rest of the trajectory
@@ -482,33 +562,48 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 const float sel = s_dem[act == 0 ? 1 : act];
                 used = __fmul_rn(__fadd_rn(used, sel), act != 0 ? 1.f : 0.f);
                 vis |= abit;
-                alive = cvrp_mask(act);
-                done = __all_sync(kFull, vis == own);
+                rvis |= rbit;
+                cvrp_masks(act);
+                done = __all_sync(kFull, rvis == rown);
             } else {                                    // slap/env.py:38-93
                 alive &= ~abit;
+                ralive &= ~rbit;
             }
             cur = act;
+            RF_TRACE_AT(7);
             ++t;
         }
 
         // ================================================== epilogue =====================
+        if (!xring && t > 0) book(t - 1);
         __syncthreads();
         const int nact = t;
-        // chosen log-probs from the per-step ingredients: logp = (x_a - m) - log(sum exp(x - m))
-        for (int q = tid; q < nact; q += kThreads) {
-            const float2 *rg = sring + (size_t)q * kWarps;
-            float m = -INFINITY;
-#pragma unroll
-            for (int w = 0; w < kWarps; ++w) m = fmaxf(m, rg[w].x);
-            float tot = 0.f;
-#pragma unroll
-            for (int w = 0; w < kWarps; ++w) {
-                const float2 c = rg[w];
-                tot += (c.x == -INFINITY) ? 0.f : c.y * expf(c.x - m);
+        // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368)
+        if (xring) {
+            for (int q = warp; q < nact; q += kWarps) {      // one warp per step, from the kept logits
+                const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
+                const float m = s_mw[q];
+                float es = 0.f;
+                es += (xv.x == -INFINITY) ? 0.f : expf(xv.x - m);
+                es += (xv.y == -INFINITY) ? 0.f : expf(xv.y - m);
+                es += (xv.z == -INFINITY) ? 0.f : expf(xv.z - m);
+                es += (xv.w == -INFINITY) ? 0.f : expf(xv.w - m);
+                es = warp_sum(es);
+                if (lane == 0) {
+                    const float lpa = (sxs[q * 128 + s_act[q]] - m) - logf(es);
+                    s_lp[q] = lpa;
+                    if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
+                }
             }
-            const float lpa = (s_xa[q] - m) - logf(tot);
-            s_lp[q] = lpa;
-            if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
+        } else {
+            for (int q = tid; q < nact; q += kThreads) {
+                const float4 r0 = *reinterpret_cast<const float4 *>(sring + q * kWarps);
+                const float4 r1 = *reinterpret_cast<const float4 *>(sring + q * kWarps + 4);
+                const float tot = ((r0.x + r0.y) + (r0.z + r0.w)) + ((r1.x + r1.y) + (r1.z + r1.w));
+                const float lpa = (s_xa[q] - s_mw[q]) - logf(tot);
+                s_lp[q] = lpa;
+                if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
+            }
         }
         float part = 0.f;
         if (ENV == RL4CO_ENV_TSP) {              // tsp/env.py:157-163
@@ -564,7 +659,7 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    const Layout L = make_layout(a.N, a.T, M, ENV != RL4CO_ENV_SLAP);
+    const Layout L = make_layout(a.N, a.T, ENV != RL4CO_ENV_SLAP);
     if (L.total > (size_t)227 * 1024) {
         set_error("am_rollout(rf): N=%d T=%d needs %zu B shared memory", a.N, a.T, L.total);
         return 1;
@@ -596,8 +691,11 @@ static int launch_env(const rl4co_am_rollout_args &a, cudaStream_t stream) {
 }  // namespace rf
 
 bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
-    if (a.S > 1 || a.multistart || a.N > 128 || a.logp_all != nullptr) return false;
-    return rf::make_layout(a.N, a.T, rf::nodes_per_thread(a.N), a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
+#ifndef RF_TRACE
+    if (a.logp_all != nullptr) return false;
+#endif
+    if (a.S > 1 || a.multistart || a.N > 128) return false;
+    return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
 }
 
 int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream) {
