@@ -137,6 +137,15 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
 int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
                      float *tables, rl4co_stream_t stream);
 
+/* K3 on the tensor cores (tcgen05.mma kind::tf32, 3-term hi/lo split, fp32 accumulation in TMEM;
+ * same result as rl4co_am_project to fp32 rounding level).  The weights are first packed once per
+ * weight update into the shared-memory image the MMA reads:
+ *   image: rl4co_am_weight_image_floats(n_tables) floats (128 KB per table), caller owned. */
+int64_t rl4co_am_weight_image_floats(int32_t n_tables);
+int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *image, rl4co_stream_t stream);
+int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
+                        float *tables, rl4co_stream_t stream);
+
 /* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */
 int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
                            float *gctx, rl4co_stream_t stream);

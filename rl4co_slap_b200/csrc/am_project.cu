@@ -105,7 +105,31 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
 
 }  // namespace rl4co
 
+namespace rl4co {
+int launch_pack_weights(int n_tables, const float *W, float *image, cudaStream_t stream);
+int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables, cudaStream_t stream);
+}  // namespace rl4co
+
 using namespace rl4co;
+
+extern "C" int64_t rl4co_am_weight_image_floats(int32_t n_tables) { return (int64_t)n_tables * 32768; }
+
+extern "C" int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *image, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(n_tables >= 1 && n_tables <= 16, "am_pack_weights: bad n_tables=%d", n_tables);
+    RL4CO_REQUIRE(W && image, "am_pack_weights: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)W & 15) == 0 && ((uintptr_t)image & 15) == 0, "am_pack_weights: pointers must be 16-byte aligned");
+    return launch_pack_weights(n_tables, W, image, (cudaStream_t)stream);
+}
+
+extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
+                                   float *tables, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_tables >= 1 && n_tables <= 16, "am_project_tc: bad sizes M=%lld n_tables=%d", (long long)M, n_tables);
+    if (M == 0) return 0;
+    RL4CO_REQUIRE(h && image && tables, "am_project_tc: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)tables & 15) == 0,
+                  "am_project_tc: pointers must be 16-byte aligned");
+    return launch_project_tc(M, n_tables, h, image, tables, (cudaStream_t)stream);
+}
 
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
                                 float *tables, rl4co_stream_t stream) {

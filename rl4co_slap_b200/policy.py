@@ -77,7 +77,20 @@ class AttentionModelDecoder(nn.Module):
         if getattr(self, "_fold_key", None) != key:
             self._fold = self._fold_weights() + (self.project_fixed_context.weight.detach().float().contiguous(),)
             self._fold_key = key
+            self._image = None
         return self._fold
+
+    def weight_image(self):
+        """The folded table weights as the pre-split (TF32 hi / lo), pre-swizzled shared-memory image
+        the tensor-core projection reads (csrc/am_project_tc.cu); packed once per weight update."""
+        W = self.folded_weights()[0]
+        if getattr(self, "_image", None) is None:
+            n_tables = W.shape[0] // 128
+            image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(n_tables)), dtype=torch.float32,
+                                device=W.device)
+            _lib.call("rl4co_am_pack_weights", n_tables, _lib.ptr(W), _lib.ptr(image), _lib.stream_ptr(W.device))
+            self._image = image
+        return self._image
 
     @torch.no_grad()
     def _fold_weights(self):
@@ -144,6 +157,7 @@ class AttentionModelPolicy(nn.Module):
         self.val_decode_type = val_decode_type
         self.test_decode_type = test_decode_type
         self.rollout_chunk = rollout_chunk
+        self.projection = "tensor"      # "tensor" | "simt": which K3 kernel builds the rollout tables
         self.unused_kwargs = unused_kwargs
         self.last_launches = 0  # rl4co_* kernel launches of the most recent forward()
         self.profile = None     # set to a list to collect (rollouts, [ev0, ev1, ev2]) per chunk
@@ -220,6 +234,7 @@ class AttentionModelPolicy(nn.Module):
         assign = torch.empty(R, P, dtype=torch.int32, device=dev) if name == "slap" else None
         status = _lib.new_status(dev)
         W, q0, wcap, Wfixed = self.decoder.folded_weights()
+        W_image = self.decoder.weight_image() if self.projection == "tensor" else None
         n_tables = W.shape[0] // 128
         prof = self.profile  # optional CUDA-event timing of the K3 / K2 launches (bench.py)
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if mode == _lib.MODE_SAMPLING else 0
@@ -240,7 +255,10 @@ class AttentionModelPolicy(nn.Module):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if prof is not None else None
             if ev:
                 ev[0].record()
-            _lib.call("rl4co_am_project", Bc * N, n_tables, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
+            if self.projection == "tensor":     # tcgen05 3xTF32, fp32-accurate
+                _lib.call("rl4co_am_project_tc", Bc * N, n_tables, _lib.ptr(h), _lib.ptr(W_image), _lib.ptr(tables), stream)
+            else:                               # fp32 SIMT kernel (kept as the in-library cross-check)
+                _lib.call("rl4co_am_project", Bc * N, n_tables, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
             launches += 1
             gctx = None
             if self.decoder.use_graph_context:
