@@ -38,6 +38,16 @@ N_NODES, EMBED = 100, 128
 ALGO_BYTES_PER_ROLLOUT = 16 * N_NODES * EMBED + 4 * EMBED + 16 * N_NODES + 8   # 206 920 B
 
 
+def profile_summary():
+    """ncu-derived per-launch numbers of the dominant kernel (profiles/r01_summary.json, written
+    from the committed ncu capture by tools/summarize_profile.py); None when absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_summary.json")) as f:
+            return json.load(f)
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -245,6 +255,10 @@ def run_ours(args):
         return
 
     peak, peak_src = measured_peaks()
+    prof_sum = profile_summary()
+    traffic = None
+    if prof_sum and prof_sum.get("k2_dram_bytes_per_rollout"):
+        traffic = prof_sum["k2_dram_bytes_per_rollout"] * min(B, pol.rollout_chunk)   # per launch, like `achieved`
     achieved = k2_rollouts * ALGO_BYTES_PER_ROLLOUT / (k2_ms * 1e-3) / 1e9 if k2_ms > 0 else 0.0
     value = B * world / (ms_step * 1e-3)
     line = {
@@ -258,11 +272,17 @@ def run_ours(args):
                    "encoder output resident in HBM", "l2": "inputs larger than L2 (encoder output "
                    f"{B * N_NODES * EMBED * 4 / 1e9:.1f} GB per GPU)", "rollout_chunk": pol.rollout_chunk,
                    "mean_reward": mean_reward},
-        "roofline": {"bound": "hbm", "kernel": "am_rollout_kernel<TSP>", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "roofline": {"bound": "hbm", "kernel": "am_rollout_rf_kernel<TSP,7> (K2, one launch per chunk)",
+                     "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_rollout": ALGO_BYTES_PER_ROLLOUT,
+                     "algorithmic_bytes_per_launch": ALGO_BYTES_PER_ROLLOUT * min(B, pol.rollout_chunk),
                      "kernel_ms_per_step": k2_ms / args.steps, "projection_ms_per_step": k3_ms / args.steps,
-                     "kernel_share_of_step": (k2_ms / args.steps) / ms_step},
+                     "kernel_share_of_step": (k2_ms / args.steps) / ms_step,
+                     # second ceiling: the folded decode step is 3*N*E fp32 MACs; FFMA2 sustains
+                     # ~85 MAC/clk/SM on this part (tools/probe_sm.cu), the kernel is latency bound below that
+                     "fma_frac_of_measured_ffma2_peak": (k2_rollouts * N_NODES * 3 * N_NODES * EMBED) /
+                                                        (k2_ms * 1e-3) / (85.0 * 148 * 1.965e9) if k2_ms > 0 else None},
         "clocks": clk.summary(),
         "gpu_launches": launches_per_step * args.steps,
     }
@@ -270,10 +290,10 @@ def run_ours(args):
         line["e2e"] = e2e
     if not args.no_cpu_baseline and world >= 1:
         threads = os.cpu_count() or 1
-        v, sec = cpu_reference(build_policy("cpu"), args.ref_batch, 1, 1, threads)
+        v, sec = cpu_reference(build_policy("cpu"), args.ref_batch, args.ref_steps, 1, threads)
         line["cpu_baseline"] = {"value": v, "unit": "rollouts/s", "cores": threads, "kind": "port",
-                                "sample": f"TSP100 greedy AM (3-layer encoder + decode), batch {args.ref_batch}, "
-                                          f"1 warm-up + 1 timed pass, {sec:.2f} s"}
+                                "sample": f"TSP100 greedy AM (3-layer encoder + decode), {args.ref_steps} timed passes of "
+                                          f"batch {args.ref_batch} after 1 warm-up, {sec:.2f} s per pass"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -286,7 +306,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--batch", type=int, default=1 << 20, help="instances per GPU")
-    ap.add_argument("--ref-batch", type=int, default=1024, help="host-side sample batch")
+    ap.add_argument("--ref-batch", type=int, default=4096, help="host-side sample batch")
+    ap.add_argument("--ref-steps", type=int, default=4, help="timed host-side passes of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

@@ -279,7 +279,7 @@ def context_embedding(env_name: str, cache, td: State, W):
         return F.linear(x, W["Wctx"])
     if env_name == "cvrp":
         cur = gather_by_index(h, td["current_node"])
-        state = td["vehicle_capacity"] - td["used_capacity"]
+        state = (td["vehicle_capacity"] - td["used_capacity"]).to(cur.dtype)   # (no-op in fp32; fp64 decoder checks)
         return F.linear(torch.cat([cur, state], -1), W["Wctx"])
     if env_name == "slap":
         return h.new_zeros(B, h.size(-1))
