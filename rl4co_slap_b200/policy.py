@@ -73,7 +73,12 @@ class AttentionModelDecoder(nn.Module):
               self.context_embedding.project_context.weight, self.project_fixed_context.weight]
         if hasattr(self.context_embedding, "W_placeholder"):
             ps.append(self.context_embedding.W_placeholder)
-        key = tuple((p.data_ptr(), p._version, str(p.device)) for p in ps)
+        def version(p):     # inference tensors (module built under torch.inference_mode) carry no counter
+            try:
+                return p._version
+            except RuntimeError:
+                return -1
+        key = tuple((p.data_ptr(), version(p), str(p.device)) for p in ps)
         if getattr(self, "_fold_key", None) != key:
             self._fold = self._fold_weights() + (self.project_fixed_context.weight.detach().float().contiguous(),)
             self._fold_key = key
