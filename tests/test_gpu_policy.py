@@ -264,3 +264,38 @@ def test_large_batch_greedy_properties(dev):
     ref = port.am_rollout("tsp", port.tsp_reset(td["locs"][idx].cpu()), h[idx].cpu(), oracle_weights("tsp"),
                           actions=out["actions"][idx].cpu())
     torch.testing.assert_close(out["log_likelihood"][idx].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
+
+
+@pytest.mark.parametrize("M,nt", ((1, 1), (100, 3), (128 * 7 + 5, 5), (148 * 128 * 3 + 17, 4)))
+def test_tensor_core_projection_matches_fp64(M, nt, dev):
+    """K3 on tcgen05 (3xTF32 split, TMEM accumulation) vs an fp64 matmul and the fp32 SIMT kernel:
+    ragged last tile, several tiles per CTA, every table count the policies use."""
+    from rl4co_slap_b200 import _lib
+    torch.manual_seed(M + nt)
+    h = (torch.randn(M, 128, device=dev) * 3).contiguous()
+    W = (torch.randn(nt * 128, 128, device=dev) * 0.1).contiguous()
+    s = _lib.stream_ptr(dev)
+    image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(nt)), device=dev)
+    _lib.call("rl4co_am_pack_weights", nt, _lib.ptr(W), _lib.ptr(image), s)
+    out_tc = torch.full((nt, M, 128), float("nan"), device=dev)
+    out_simt = torch.empty(nt, M, 128, device=dev)
+    _lib.call("rl4co_am_project_tc", M, nt, _lib.ptr(h), _lib.ptr(image), _lib.ptr(out_tc), s)
+    _lib.call("rl4co_am_project", M, nt, _lib.ptr(h), _lib.ptr(W), _lib.ptr(out_simt), s)
+    ref = (h.double() @ W.double().t()).view(M, nt, 128).permute(1, 0, 2)
+    bound = 4e-6 * (h.double().abs() @ W.double().abs().t()).view(M, nt, 128).permute(1, 0, 2) + 1e-7
+    assert not torch.isnan(out_tc).any()
+    assert ((out_tc.double() - ref).abs() <= bound).all()          # fp32-level: ~1e-6 of sum |a||w|
+    assert ((out_simt.double() - ref).abs() <= bound).all()
+
+
+def test_policy_projection_paths_agree(dev):
+    """the rollout through the tensor-core tables and through the fp32 SIMT tables: same tours, ll within 1e-5"""
+    fx = fixture("tsp100")
+    pol, env = load_policy("tsp", dev), R.TSPEnv(device=dev)
+    td = env.reset(gen_td("tsp", fx, dev))
+    h = t(fx["hidden"], dev)
+    a = pol(td, env, decode_type="greedy", return_actions=True, hidden=h)
+    pol.projection = "simt"
+    b = pol(td, env, decode_type="greedy", return_actions=True, hidden=h)
+    assert torch.equal(a["actions"], b["actions"])
+    torch.testing.assert_close(a["log_likelihood"], b["log_likelihood"], rtol=RTOL, atol=1e-5)
