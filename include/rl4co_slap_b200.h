@@ -146,6 +146,13 @@ int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *image, rl4co_
 int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
                         float *tables, rl4co_stream_t stream);
 
+/* The same tensor-core kernel with a linear-layer epilogue, for the K = 128 linears of the PyTorch
+ * encoder that feeds the path (models/nn/graph/attnnet.py:16-63: Wqkv, out_proj, feed-forward in):
+ *   y[m][b*128 + j] = act(sum_e x[m][e] * W[b*128 + j][e] + bias[b*128 + j]),  act = ReLU if relu != 0.
+ * x [M,128], y [M, n_blocks*128] row-major, image = rl4co_am_pack_weights(n_blocks, W), bias may be NULL. */
+int rl4co_linear128_tc(int64_t M, int32_t n_blocks, const float *x, const float *image, const float *bias,
+                       int32_t relu, float *y, rl4co_stream_t stream);
+
 /* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */
 int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
                            float *gctx, rl4co_stream_t stream);

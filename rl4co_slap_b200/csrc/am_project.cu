@@ -107,7 +107,8 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
 
 namespace rl4co {
 int launch_pack_weights(int n_tables, const float *W, float *image, cudaStream_t stream);
-int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables, cudaStream_t stream);
+int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables, int64_t table_stride,
+                      int64_t ldo, const float *bias, int relu, cudaStream_t stream);
 }  // namespace rl4co
 
 using namespace rl4co;
@@ -128,7 +129,17 @@ extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, 
     RL4CO_REQUIRE(h && image && tables, "am_project_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)tables & 15) == 0,
                   "am_project_tc: pointers must be 16-byte aligned");
-    return launch_project_tc(M, n_tables, h, image, tables, (cudaStream_t)stream);
+    return launch_project_tc(M, n_tables, h, image, tables, M * 128, 128, nullptr, 0, (cudaStream_t)stream);
+}
+
+extern "C" int rl4co_linear128_tc(int64_t M, int32_t n_blocks, const float *x, const float *image, const float *bias,
+                                  int32_t relu, float *y, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_blocks >= 1 && n_blocks <= 16, "linear128_tc: bad sizes M=%lld n_blocks=%d", (long long)M, n_blocks);
+    if (M == 0) return 0;
+    RL4CO_REQUIRE(x && image && y, "linear128_tc: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)y & 15) == 0,
+                  "linear128_tc: pointers must be 16-byte aligned");
+    return launch_project_tc(M, n_blocks, x, image, y, 128, (int64_t)n_blocks * 128, bias, relu, (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,

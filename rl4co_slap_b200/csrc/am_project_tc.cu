@@ -37,7 +37,7 @@ constexpr int A_STAGE_BYTES = 2 * KB_BYTES;          // hi + lo
 constexpr int kProducerWarps = 8;
 constexpr int kThreads = (1 + kProducerWarps + 4) * 32;
 constexpr int OUT_BYTES = BM * 128;                    // staging of one 32-column block of the accumulator
-constexpr int SMEM_BYTES = 1024 + W_BYTES + A_STAGES * A_STAGE_BYTES + 2 * OUT_BYTES + 256;
+constexpr int SMEM_BYTES = 1024 + W_BYTES + A_STAGES * A_STAGE_BYTES + 2 * OUT_BYTES + 256 + 512;
 constexpr uint32_t kTmemCols = 256;      // two 128-column accumulators
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = F32 (bits 4-5 = 1),
 // A = B = TF32 (bits 7-9, 10-12 = 2), both K-major, N/8 at bit 17, M/16 at bit 24
@@ -115,7 +115,8 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const f
 
 __global__ void __launch_bounds__(kThreads, 1)
 am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restrict__ h,
-                     const float *__restrict__ image, float *__restrict__ tables) {
+                     const float *__restrict__ image, float *__restrict__ tables, int64_t table_stride, int64_t ldo,
+                     const float *__restrict__ bias, int relu) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char *sW = smem;                                   // 128 KB weight image
@@ -125,6 +126,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
     uint64_t *w_full = bars, *a_full = bars + 1, *a_empty = bars + 1 + A_STAGES;
     uint64_t *acc_full = bars + 1 + 2 * A_STAGES, *acc_empty = acc_full + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+    float *s_bias = reinterpret_cast<float *>(sO + 2 * OUT_BYTES + 256);   // this table's 128 bias values (zeros if none)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int table = blockIdx.x % n_tables, group = blockIdx.x / n_tables;
@@ -136,6 +138,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
         for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); }
         fence_barrier_init();
     }
+    if (tid < BN) s_bias[tid] = bias ? bias[table * BN + tid] : 0.f;
     if (warp == 0) {                                            // TMEM: 256 columns for this CTA
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(kTmemCols)
@@ -231,7 +234,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
         // ================================================= epilogue: TMEM -> registers -> table rows
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
         const int row = 32 * q + lane;
-        float *out = tables + (size_t)table * M * E;
+        float *out = tables + (size_t)table * table_stride;
         unsigned acc_phase[2] = {0u, 0u};
         int it = 0;
         for (int64_t tile = group; tile < n_tiles; tile += n_groups, ++it) {
@@ -258,6 +261,13 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[ab]);
                 }
+                if (bias != nullptr || relu) {                  // linear-layer epilogue: + bias, optional ReLU
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) {
+                        float y = __uint_as_float(v[k]) + s_bias[cb * 32 + k];
+                        v[k] = __float_as_uint(relu ? fmaxf(y, 0.f) : y);
+                    }
+                }
                 // registers (one row, 32 columns per thread) -> swizzled staging -> coalesced row stores
                 unsigned char *st = sO + (cb & 1) * OUT_BYTES;
 #pragma unroll
@@ -270,7 +280,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                     const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
                     const int64_t mm = tile * BM + rr;
                     if (mm < M)
-                        *reinterpret_cast<uint4 *>(out + mm * E + cb * 32 + ch * 4) =
+                        *reinterpret_cast<uint4 *>(out + mm * ldo + cb * 32 + ch * 4) =
                             *reinterpret_cast<const uint4 *>(st + swz(rr, ch));
                 }
             }
@@ -294,7 +304,7 @@ int launch_pack_weights(int n_tables, const float *W, float *image, cudaStream_t
 }
 
 int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables,
-                      cudaStream_t stream) {
+                      int64_t table_stride, int64_t ldo, const float *bias, int relu, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -313,7 +323,7 @@ int launch_project_tc(int64_t M, int n_tables, const float *h, const float *imag
     if (groups < 1) groups = 1;
     if (groups > n_tiles) groups = n_tiles;
     tc::am_project_tc_kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
-        M, n_tables, (int)groups, h, image, tables);
+        M, n_tables, (int)groups, h, image, tables, table_stride, ldo, bias, relu);
     RL4CO_CHECK_LAUNCH("am_project(tc)");
     return 0;
 }

@@ -54,6 +54,38 @@ class SLAPInitEmbedding(nn.Module):
 INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding}
 
 
+# ---- K = 128 linears on the tensor cores ----------------------------------------------
+def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tensor:
+    """``act(lin(x))``.  On a CUDA device, outside autograd, a Linear with 128 inputs and a multiple of
+    128 outputs runs on the library's fp32-accurate tensor-core kernel (rl4co_linear128_tc: tcgen05,
+    3-term TF32 split, fp32 accumulation - the K3 projection kernel with a bias / ReLU epilogue);
+    everything else is the plain PyTorch op.  The packed weight image is cached on the module."""
+    w = lin.weight
+    use_tc = (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
+              and w.shape[1] == 128 and w.shape[0] % 128 == 0 and w.shape[0] <= 2048
+              and getattr(lin, "tensor_core", True))
+    if not use_tc:
+        y = F.linear(x, w, lin.bias)
+        return F.relu(y) if relu else y
+    from . import _lib
+    try:
+        ver = w._version
+    except RuntimeError:        # inference tensor
+        ver = -1
+    key = (w.data_ptr(), ver, str(w.device))
+    if getattr(lin, "_tc_key", None) != key:
+        nb = w.shape[0] // 128
+        image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(nb)), dtype=torch.float32, device=w.device)
+        _lib.call("rl4co_am_pack_weights", nb, _lib.ptr(w.detach().contiguous()), _lib.ptr(image), _lib.stream_ptr(w.device))
+        lin._tc_image, lin._tc_key = image, key
+    x2 = x.reshape(-1, 128).contiguous()
+    y = torch.empty(x2.shape[0], w.shape[0], dtype=torch.float32, device=x.device)
+    bias = lin.bias.detach().contiguous() if lin.bias is not None else None
+    _lib.call("rl4co_linear128_tc", x2.shape[0], w.shape[0] // 128, _lib.ptr(x2), _lib.ptr(lin._tc_image),
+              _lib.ptr(bias), int(relu), _lib.ptr(y), _lib.stream_ptr(x.device))
+    return y.view(*x.shape[:-1], w.shape[0])
+
+
 # ---- encoder blocks -------------------------------------------------------------------
 class _Skip(nn.Module):
     def __init__(self, module):
@@ -73,10 +105,10 @@ class _SelfAttention(nn.Module):
 
     def forward(self, x):
         B, N, E = x.shape
-        qkv = self.Wqkv(x).view(B, N, 3, self.num_heads, E // self.num_heads)
+        qkv = linear128(x, self.Wqkv).view(B, N, 3, self.num_heads, E // self.num_heads)
         q, k, v = qkv.permute(2, 0, 3, 1, 4).unbind(0)
         o = F.scaled_dot_product_attention(q, k, v)
-        return self.out_proj(o.transpose(1, 2).reshape(B, N, E))
+        return linear128(o.transpose(1, 2).reshape(B, N, E), self.out_proj)
 
 
 class _FeedForward(nn.Module):
@@ -87,8 +119,8 @@ class _FeedForward(nn.Module):
 
     def forward(self, x):
         for lin in self.lins[:-1]:
-            x = F.relu(lin(x))
-        return self.lins[-1](x)
+            x = linear128(x, lin, relu=True)
+        return linear128(x, self.lins[-1])
 
 
 class _Norm(nn.Module):

@@ -299,3 +299,33 @@ def test_policy_projection_paths_agree(dev):
     b = pol(td, env, decode_type="greedy", return_actions=True, hidden=h)
     assert torch.equal(a["actions"], b["actions"])
     torch.testing.assert_close(a["log_likelihood"], b["log_likelihood"], rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("name", ("tsp", "cvrp"))
+def test_encoder_tensor_core_linears_match_pytorch(name, dev):
+    """the encoder's K = 128 linears through rl4co_linear128_tc (bias / ReLU epilogue) vs torch fp32 F.linear"""
+    torch.manual_seed(3)
+    pol = load_policy(name, dev)
+    g = R.TSPGenerator(num_loc=50) if name == "tsp" else R.CVRPGenerator(num_loc=50)
+    td = R.get_env(name, device=dev).reset(g(300).to(dev))
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        with torch.inference_mode():
+            h_tc = pol.encoder(td)[0]
+            for m in pol.encoder.modules():
+                if isinstance(m, torch.nn.Linear):
+                    m.tensor_core = False
+            h_pt = pol.encoder(td)[0]
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    scale = h_pt.abs().max().item()
+    assert (h_tc - h_pt).abs().max().item() <= 2e-5 * scale, ((h_tc - h_pt).abs().max().item(), scale)
+    # and the fixture's reference embeddings (CPU fp32 reference encoder) through the tensor-core path
+    fx = fixture(f"{name}50")
+    pol2 = load_policy(name, dev)
+    td2 = R.get_env(name, device=dev).reset(gen_td(name, fx, dev))
+    with torch.inference_mode():
+        h2 = pol2.encoder(td2)[0]
+    ref = t(fx["hidden"], dev)
+    assert (h2 - ref).abs().max().item() <= 2e-5 * ref.abs().max().item()
