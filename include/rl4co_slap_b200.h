@@ -153,6 +153,11 @@ int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float
 int rl4co_linear128_tc(int64_t M, int32_t n_blocks, const float *x, const float *image, const float *bias,
                        int32_t relu, float *y, rl4co_stream_t stream);
 
+/* Self-attention of the PyTorch encoder's layers for the path's graph sizes (N <= 128, 8 heads x 16,
+ * no mask, fp32): replaces the F.scaled_dot_product_attention call of MultiHeadAttention
+ * (models/nn/attention.py:65-135).  qkv [B,N,3,8,16] = the fused Wqkv output, out [B,N,128]. */
+int rl4co_encoder_attention(int64_t B, int32_t N, const float *qkv, float *out, rl4co_stream_t stream);
+
 /* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */
 int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
                            float *gctx, rl4co_stream_t stream);

@@ -105,7 +105,16 @@ class _SelfAttention(nn.Module):
 
     def forward(self, x):
         B, N, E = x.shape
-        qkv = linear128(x, self.Wqkv).view(B, N, 3, self.num_heads, E // self.num_heads)
+        qkv = linear128(x, self.Wqkv)
+        if (qkv.is_cuda and not torch.is_grad_enabled() and qkv.dtype == torch.float32 and E == 128
+                and self.num_heads == 8 and N <= 128 and getattr(self, "fused_attention", True)):
+            # fp32 attention kernel of the library for the path's graph sizes (csrc/encoder_attention.cu)
+            from . import _lib
+            qkv = qkv.contiguous()
+            o = torch.empty(B, N, E, dtype=torch.float32, device=x.device)
+            _lib.call("rl4co_encoder_attention", B, N, _lib.ptr(qkv), _lib.ptr(o), _lib.stream_ptr(x.device))
+            return linear128(o, self.out_proj)
+        qkv = qkv.view(B, N, 3, self.num_heads, E // self.num_heads)
         q, k, v = qkv.permute(2, 0, 3, 1, 4).unbind(0)
         o = F.scaled_dot_product_attention(q, k, v)
         return linear128(o.transpose(1, 2).reshape(B, N, E), self.out_proj)

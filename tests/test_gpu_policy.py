@@ -316,6 +316,8 @@ def test_encoder_tensor_core_linears_match_pytorch(name, dev):
             for m in pol.encoder.modules():
                 if isinstance(m, torch.nn.Linear):
                     m.tensor_core = False
+                if hasattr(m, "Wqkv"):
+                    m.fused_attention = False
             h_pt = pol.encoder(td)[0]
     finally:
         torch.backends.cuda.matmul.allow_tf32 = prev
