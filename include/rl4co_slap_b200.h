@@ -146,12 +146,15 @@ int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *image, rl4co_
 int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
                         float *tables, rl4co_stream_t stream);
 
-/* The same tensor-core kernel with a linear-layer epilogue, for the K = 128 linears of the PyTorch
- * encoder that feeds the path (models/nn/graph/attnnet.py:16-63: Wqkv, out_proj, feed-forward in):
- *   y[m][b*128 + j] = act(sum_e x[m][e] * W[b*128 + j][e] + bias[b*128 + j]),  act = ReLU if relu != 0.
- * x [M,128], y [M, n_blocks*128] row-major, image = rl4co_am_pack_weights(n_blocks, W), bias may be NULL. */
-int rl4co_linear128_tc(int64_t M, int32_t n_blocks, const float *x, const float *image, const float *bias,
-                       int32_t relu, float *y, rl4co_stream_t stream);
+/* The same tensor-core kernel with a linear-layer epilogue, for the linears of the PyTorch encoder that
+ * feeds the path (models/nn/graph/attnnet.py:16-63: Wqkv, out_proj, feed-forward):
+ *   y[m][j] = act(sum_e x[m][e] * W[j][e] + bias[j]),  act = ReLU if relu != 0,
+ * n_in and n_out multiples of 128 (<= 2048); n_in > 128 runs as 128-wide K chunks accumulated through y.
+ * x [M,n_in], W [n_out,n_in], y [M,n_out] row-major; bias may be NULL.
+ * image = rl4co_linear_pack(W): (n_in/128) * rl4co_am_weight_image_floats(n_out/128) floats. */
+int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream);
+int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
+                    const float *bias, int32_t relu, float *y, rl4co_stream_t stream);
 
 /* Self-attention of the PyTorch encoder's layers for the path's graph sizes (N <= 128, 8 heads x 16,
  * no mask, fp32): replaces the F.scaled_dot_product_attention call of MultiHeadAttention

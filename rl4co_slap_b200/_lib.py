@@ -63,7 +63,8 @@ _SIGNATURES = {
     "rl4co_am_weight_image_floats": ([_i32], C.c_int64),
     "rl4co_am_pack_weights": ([_i32, _p, _p, _p], C.c_int),
     "rl4co_am_project_tc": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
-    "rl4co_linear128_tc": ([_i64, _i32, _p, _p, _p, _i32, _p, _p], C.c_int),
+    "rl4co_linear_pack": ([_i32, _i32, _p, _p, _p], C.c_int),
+    "rl4co_linear_tc": ([_i64, _i32, _i32, _p, _p, _p, _i32, _p, _p], C.c_int),
     "rl4co_encoder_attention": ([_i64, _i32, _p, _p, _p], C.c_int),
     "rl4co_am_graph_context": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_am_rollout": ([C.POINTER(AmRolloutArgs), _p], C.c_int),

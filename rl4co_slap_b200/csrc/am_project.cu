@@ -106,9 +106,9 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
 }  // namespace rl4co
 
 namespace rl4co {
-int launch_pack_weights(int n_tables, const float *W, float *image, cudaStream_t stream);
+int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream);
 int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables, int64_t table_stride,
-                      int64_t ldo, const float *bias, int relu, cudaStream_t stream);
+                      int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate, cudaStream_t stream);
 }  // namespace rl4co
 
 using namespace rl4co;
@@ -119,7 +119,7 @@ extern "C" int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *im
     RL4CO_REQUIRE(n_tables >= 1 && n_tables <= 16, "am_pack_weights: bad n_tables=%d", n_tables);
     RL4CO_REQUIRE(W && image, "am_pack_weights: null pointer");
     RL4CO_REQUIRE(((uintptr_t)W & 15) == 0 && ((uintptr_t)image & 15) == 0, "am_pack_weights: pointers must be 16-byte aligned");
-    return launch_pack_weights(n_tables, W, image, (cudaStream_t)stream);
+    return launch_pack_weights(n_tables, W, 128, image, (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
@@ -129,17 +129,37 @@ extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, 
     RL4CO_REQUIRE(h && image && tables, "am_project_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)tables & 15) == 0,
                   "am_project_tc: pointers must be 16-byte aligned");
-    return launch_project_tc(M, n_tables, h, image, tables, M * 128, 128, nullptr, 0, (cudaStream_t)stream);
+    return launch_project_tc(M, n_tables, h, image, tables, M * 128, 128, nullptr, 0, 128, 0, (cudaStream_t)stream);
 }
 
-extern "C" int rl4co_linear128_tc(int64_t M, int32_t n_blocks, const float *x, const float *image, const float *bias,
-                                  int32_t relu, float *y, rl4co_stream_t stream) {
-    RL4CO_REQUIRE(M >= 0 && n_blocks >= 1 && n_blocks <= 16, "linear128_tc: bad sizes M=%lld n_blocks=%d", (long long)M, n_blocks);
+extern "C" int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(n_out >= 128 && n_out % 128 == 0 && n_out <= 2048 && n_in >= 128 && n_in % 128 == 0 && n_in <= 2048,
+                  "linear_pack: sizes must be multiples of 128 (<= 2048), got %d x %d", n_out, n_in);
+    RL4CO_REQUIRE(W && image, "linear_pack: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)W & 15) == 0 && ((uintptr_t)image & 15) == 0, "linear_pack: pointers must be 16-byte aligned");
+    const int nb = n_out / 128;
+    for (int kc = 0; kc < n_in / 128; ++kc) {       // one image set per 128-wide K chunk
+        int rc = launch_pack_weights(nb, W + kc * 128, n_in, image + (size_t)kc * nb * 32768, (cudaStream_t)stream);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+extern "C" int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
+                               const float *bias, int32_t relu, float *y, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_out >= 128 && n_out % 128 == 0 && n_out <= 2048 && n_in >= 128 && n_in % 128 == 0 && n_in <= 2048,
+                  "linear_tc: sizes must be multiples of 128 (<= 2048), got M=%lld %d x %d", (long long)M, n_out, n_in);
     if (M == 0) return 0;
-    RL4CO_REQUIRE(x && image && y, "linear128_tc: null pointer");
+    RL4CO_REQUIRE(x && image && y, "linear_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)y & 15) == 0,
-                  "linear128_tc: pointers must be 16-byte aligned");
-    return launch_project_tc(M, n_blocks, x, image, y, 128, (int64_t)n_blocks * 128, bias, relu, (cudaStream_t)stream);
+                  "linear_tc: pointers must be 16-byte aligned");
+    const int nb = n_out / 128, nk = n_in / 128;
+    for (int kc = 0; kc < nk; ++kc) {               // K chunks accumulate through y; bias first, ReLU last
+        int rc = launch_project_tc(M, nb, x + kc * 128, image + (size_t)kc * nb * 32768, y, 128, n_out,
+                                   kc == 0 ? bias : nullptr, (kc == nk - 1) ? relu : 0, n_in, kc > 0, (cudaStream_t)stream);
+        if (rc) return rc;
+    }
+    return 0;
 }
 
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,

@@ -95,14 +95,14 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // weights -> the shared-memory image of one table: [hi|lo][kb][row j = output feature][32 k], swizzled
-__global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const float *__restrict__ W,
+__global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const float *__restrict__ W, int64_t ldw,
                                                            float *__restrict__ image) {
     const int t = blockIdx.x;
-    const float *Wt = W + (size_t)t * BN * E;
+    const float *Wt = W + (size_t)t * BN * ldw;
     char *img = reinterpret_cast<char *>(image) + (size_t)t * W_BYTES;
     for (int idx = threadIdx.x; idx < BN * (E / 4); idx += blockDim.x) {
         const int j = idx / (E / 4), c4 = idx % (E / 4);        // row j, float4 chunk c4 of the row
-        const float4 w = *reinterpret_cast<const float4 *>(Wt + (size_t)j * E + 4 * c4);
+        const float4 w = *reinterpret_cast<const float4 *>(Wt + (size_t)j * ldw + 4 * c4);
         const int kb = c4 / 8, c = c4 % 8;
         uint4 hi, lo;
         hi.x = to_tf32(w.x); hi.y = to_tf32(w.y); hi.z = to_tf32(w.z); hi.w = to_tf32(w.w);
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const f
 __global__ void __launch_bounds__(kThreads, 1)
 am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restrict__ h,
                      const float *__restrict__ image, float *__restrict__ tables, int64_t table_stride, int64_t ldo,
-                     const float *__restrict__ bias, int relu) {
+                     const float *__restrict__ bias, int relu, int64_t ldx, int accumulate) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char *sW = smem;                                   // 128 KB weight image
@@ -201,7 +201,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
 #pragma unroll
             for (int i = 0; i < RPT; ++i) {
                 const int64_t m = tile * BM + r0 + 32 * i;
-                v[kb][i] = (tile < n_tiles && m < M) ? __ldg(reinterpret_cast<const float4 *>(h + m * E + kb * KB) + c)
+                v[kb][i] = (tile < n_tiles && m < M) ? __ldg(reinterpret_cast<const float4 *>(h + m * ldx + kb * KB) + c)
                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
@@ -235,6 +235,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
         const int row = 32 * q + lane;
         float *out = tables + (size_t)table * table_stride;
+        const bool epi = bias != nullptr || relu || accumulate;
         unsigned acc_phase[2] = {0u, 0u};
         int it = 0;
         for (int64_t tile = group; tile < n_tiles; tile += n_groups, ++it) {
@@ -261,13 +262,6 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[ab]);
                 }
-                if (bias != nullptr || relu) {                  // linear-layer epilogue: + bias, optional ReLU
-#pragma unroll
-                    for (int k = 0; k < 32; ++k) {
-                        float y = __uint_as_float(v[k]) + s_bias[cb * 32 + k];
-                        v[k] = __float_as_uint(relu ? fmaxf(y, 0.f) : y);
-                    }
-                }
                 // registers (one row, 32 columns per thread) -> swizzled staging -> coalesced row stores
                 unsigned char *st = sO + (cb & 1) * OUT_BYTES;
 #pragma unroll
@@ -279,9 +273,17 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                 for (int j = 0; j < 8; ++j) {
                     const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
                     const int64_t mm = tile * BM + rr;
-                    if (mm < M)
-                        *reinterpret_cast<uint4 *>(out + mm * ldo + cb * 32 + ch * 4) =
-                            *reinterpret_cast<const uint4 *>(st + swz(rr, ch));
+                    if (mm < M) {
+                        float4 y = *reinterpret_cast<const float4 *>(st + swz(rr, ch));
+                        float4 *dst = reinterpret_cast<float4 *>(out + mm * ldo + cb * 32 + ch * 4);
+                        if (epi) {                              // linear-layer epilogue: (+ previous K chunks) + bias, ReLU
+                            const float4 bb = *reinterpret_cast<const float4 *>(s_bias + cb * 32 + ch * 4);
+                            y.x += bb.x; y.y += bb.y; y.z += bb.z; y.w += bb.w;
+                            if (accumulate) { const float4 o = *dst; y.x += o.x; y.y += o.y; y.z += o.z; y.w += o.w; }
+                            if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+                        }
+                        *dst = y;
+                    }
                 }
             }
         }
@@ -297,14 +299,15 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
 
 }  // namespace tc
 
-int launch_pack_weights(int n_tables, const float *W, float *image, cudaStream_t stream) {
-    tc::pack_weights_kernel<<<n_tables, 256, 0, stream>>>(n_tables, W, image);
+int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream) {
+    tc::pack_weights_kernel<<<n_tables, 256, 0, stream>>>(n_tables, W, ldw, image);
     RL4CO_CHECK_LAUNCH("am_pack_weights");
     return 0;
 }
 
 int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables,
-                      int64_t table_stride, int64_t ldo, const float *bias, int relu, cudaStream_t stream) {
+                      int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
+                      cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -323,7 +326,7 @@ int launch_project_tc(int64_t M, int n_tables, const float *h, const float *imag
     if (groups < 1) groups = 1;
     if (groups > n_tiles) groups = n_tiles;
     tc::am_project_tc_kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
-        M, n_tables, (int)groups, h, image, tables, table_stride, ldo, bias, relu);
+        M, n_tables, (int)groups, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate);
     RL4CO_CHECK_LAUNCH("am_project(tc)");
     return 0;
 }

@@ -56,14 +56,15 @@ INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SL
 
 # ---- K = 128 linears on the tensor cores ----------------------------------------------
 def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tensor:
-    """``act(lin(x))``.  On a CUDA device, outside autograd, a Linear with 128 inputs and a multiple of
-    128 outputs runs on the library's fp32-accurate tensor-core kernel (rl4co_linear128_tc: tcgen05,
+    """``act(lin(x))``.  On a CUDA device, outside autograd, a Linear whose input and output widths are
+    multiples of 128 runs on the library's fp32-accurate tensor-core kernel (rl4co_linear_tc: tcgen05,
     3-term TF32 split, fp32 accumulation - the K3 projection kernel with a bias / ReLU epilogue);
     everything else is the plain PyTorch op.  The packed weight image is cached on the module."""
     w = lin.weight
     use_tc = (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
-              and w.shape[1] == 128 and w.shape[0] % 128 == 0 and w.shape[0] <= 2048
-              and getattr(lin, "tensor_core", True))
+              and w.shape[1] % 128 == 0 and w.shape[0] % 128 == 0 and max(w.shape) <= 2048
+              and getattr(lin, "tensor_core", w.shape[1] == 128))   # wider inputs run as K chunks through y and
+                                                                     # lose to cuBLAS (tools/bench_linear.py): opt-in
     if not use_tc:
         y = F.linear(x, w, lin.bias)
         return F.relu(y) if relu else y
@@ -72,18 +73,20 @@ def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tens
         ver = w._version
     except RuntimeError:        # inference tensor
         ver = -1
+    n_out, n_in = w.shape
     key = (w.data_ptr(), ver, str(w.device))
     if getattr(lin, "_tc_key", None) != key:
-        nb = w.shape[0] // 128
-        image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(nb)), dtype=torch.float32, device=w.device)
-        _lib.call("rl4co_am_pack_weights", nb, _lib.ptr(w.detach().contiguous()), _lib.ptr(image), _lib.stream_ptr(w.device))
+        n_img = (n_in // 128) * int(_lib.load().rl4co_am_weight_image_floats(n_out // 128))
+        image = torch.empty(n_img, dtype=torch.float32, device=w.device)
+        _lib.call("rl4co_linear_pack", n_out, n_in, _lib.ptr(w.detach().contiguous()), _lib.ptr(image),
+                  _lib.stream_ptr(w.device))
         lin._tc_image, lin._tc_key = image, key
-    x2 = x.reshape(-1, 128).contiguous()
-    y = torch.empty(x2.shape[0], w.shape[0], dtype=torch.float32, device=x.device)
+    x2 = x.reshape(-1, n_in).contiguous()
+    y = torch.empty(x2.shape[0], n_out, dtype=torch.float32, device=x.device)
     bias = lin.bias.detach().contiguous() if lin.bias is not None else None
-    _lib.call("rl4co_linear128_tc", x2.shape[0], w.shape[0] // 128, _lib.ptr(x2), _lib.ptr(lin._tc_image),
+    _lib.call("rl4co_linear_tc", x2.shape[0], n_out, n_in, _lib.ptr(x2), _lib.ptr(lin._tc_image),
               _lib.ptr(bias), int(relu), _lib.ptr(y), _lib.stream_ptr(x.device))
-    return y.view(*x.shape[:-1], w.shape[0])
+    return y.view(*x.shape[:-1], n_out)
 
 
 # ---- encoder blocks -------------------------------------------------------------------

@@ -331,3 +331,23 @@ def test_encoder_tensor_core_linears_match_pytorch(name, dev):
         h2 = pol2.encoder(td2)[0]
     ref = t(fx["hidden"], dev)
     assert (h2 - ref).abs().max().item() <= 2e-5 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("M,n_out,n_in,relu", ((257, 128, 512, False), (1000, 512, 128, True), (130, 256, 256, True)))
+def test_linear_tc_k_chunks_bias_relu(M, n_out, n_in, relu, dev):
+    """rl4co_linear_tc: 128-wide K chunks accumulated through y, bias on the first, ReLU on the last"""
+    from rl4co_slap_b200 import _lib
+    torch.manual_seed(n_out + n_in)
+    x = torch.randn(M, n_in, device=dev)
+    W = torch.randn(n_out, n_in, device=dev) * 0.1
+    b = torch.randn(n_out, device=dev)
+    s = _lib.stream_ptr(dev)
+    image = torch.empty((n_in // 128) * int(_lib.load().rl4co_am_weight_image_floats(n_out // 128)), device=dev)
+    _lib.call("rl4co_linear_pack", n_out, n_in, _lib.ptr(W), _lib.ptr(image), s)
+    y = torch.full((M, n_out), float("nan"), device=dev)
+    _lib.call("rl4co_linear_tc", M, n_out, n_in, _lib.ptr(x), _lib.ptr(image), _lib.ptr(b), int(relu), _lib.ptr(y), s)
+    ref = x.double() @ W.double().t() + b.double()
+    if relu:
+        ref = ref.clamp_min(0)
+    bound = 4e-6 * (x.double().abs() @ W.double().abs().t() + b.double().abs()) + 1e-6
+    assert ((y.double() - ref).abs() <= bound).all()
