@@ -107,8 +107,9 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
 
 namespace rl4co {
 int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream);
-int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables, int64_t table_stride,
-                      int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate, cudaStream_t stream);
+int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, const float *image, float *tables,
+                      int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
+                      cudaStream_t stream);
 }  // namespace rl4co
 
 using namespace rl4co;
@@ -129,7 +130,7 @@ extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, 
     RL4CO_REQUIRE(h && image && tables, "am_project_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)tables & 15) == 0,
                   "am_project_tc: pointers must be 16-byte aligned");
-    return launch_project_tc(M, n_tables, h, image, tables, M * 128, 128, nullptr, 0, 128, 0, (cudaStream_t)stream);
+    return launch_project_tc(M, n_tables, 1, h, image, tables, M * 128, 128, nullptr, 0, 128, 0, (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream) {
@@ -153,13 +154,8 @@ extern "C" int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const flo
     RL4CO_REQUIRE(x && image && y, "linear_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)y & 15) == 0,
                   "linear_tc: pointers must be 16-byte aligned");
-    const int nb = n_out / 128, nk = n_in / 128;
-    for (int kc = 0; kc < nk; ++kc) {               // K chunks accumulate through y; bias first, ReLU last
-        int rc = launch_project_tc(M, nb, x + kc * 128, image + (size_t)kc * nb * 32768, y, 128, n_out,
-                                   kc == 0 ? bias : nullptr, (kc == nk - 1) ? relu : 0, n_in, kc > 0, (cudaStream_t)stream);
-        if (rc) return rc;
-    }
-    return 0;
+    // the K chunks of a row tile accumulate in TMEM; bias and ReLU ride the single epilogue
+    return launch_project_tc(M, n_out / 128, n_in / 128, x, image, y, 128, n_out, bias, relu, n_in, 0, (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,

@@ -38,7 +38,8 @@ constexpr int kProducerWarps = 8;
 constexpr int kThreads = (1 + kProducerWarps + 4) * 32;
 constexpr int OUT_BYTES = BM * 128;                    // staging of one 32-column block of the accumulator
 constexpr int SMEM_BYTES = 1024 + W_BYTES + A_STAGES * A_STAGE_BYTES + 2 * OUT_BYTES + 256 + 512;
-constexpr uint32_t kTmemCols = 256;      // two 128-column accumulators
+constexpr int TB = 4;                    // tiles per block = accumulators resident in TMEM
+constexpr uint32_t kTmemCols = TB * BN;  // 512 columns: four 128-column accumulators
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = F32 (bits 4-5 = 1),
 // A = B = TF32 (bits 7-9, 10-12 = 2), both K-major, N/8 at bit 17, M/16 at bit 24
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((BN >> 3) << 17) | ((BM >> 4) << 24);
@@ -56,13 +57,32 @@ __host__ __device__ __forceinline__ uint32_t swz(int r, int c) { return (uint32_
 __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
+// descriptors travel as their low words (start address in 16-byte units | LBO); the high word is one constant.
+// Everything the instruction reads must sit in uniform registers: keep the operands provably warp-uniform
+// (shared-window addresses, constants, a shuffled TMEM base) or the compiler wraps every MMA in an
+// elect / broadcast loop that costs more issue time than the MMA takes to execute.
+__device__ __forceinline__ bool elect_one() {                  // one lane of a converged warp
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "elect.sync _|P1, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
+constexpr uint32_t kDescHi = (uint32_t)((64ull << 32 | 1ull << 46 | 2ull << 61) >> 32);
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint32_t a_lo32, uint32_t b_lo32, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(kIdesc), "r"(accumulate)
+        "mov.b64 da, {%1, %5};\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(a_lo32), "r"(b_lo32), "r"(kIdesc), "r"(accumulate), "r"(kDescHi)
         : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {    // arrives when all prior MMAs are done
@@ -114,32 +134,39 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const f
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restrict__ h,
+am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb, const float *__restrict__ h,
                      const float *__restrict__ image, float *__restrict__ tables, int64_t table_stride, int64_t ldo,
                      const float *__restrict__ bias, int relu, int64_t ldx, int accumulate) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    unsigned char *sW = smem;                                   // 128 KB weight image
+    unsigned char *sW = smem;                                   // 128 KB weight image (of the current K chunk)
     unsigned char *sA = smem + W_BYTES;                         // A ring
     unsigned char *sO = sA + A_STAGES * A_STAGE_BYTES;          // epilogue staging, 2 x 16 KB
     uint64_t *bars = reinterpret_cast<uint64_t *>(sO + 2 * OUT_BYTES);
-    uint64_t *w_full = bars, *a_full = bars + 1, *a_empty = bars + 1 + A_STAGES;
-    uint64_t *acc_full = bars + 1 + 2 * A_STAGES, *acc_empty = acc_full + 2;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+    uint64_t *w_full = bars, *w_empty = bars + 1, *a_full = bars + 2, *a_empty = a_full + A_STAGES;
+    uint64_t *acc_full = a_empty + A_STAGES, *acc_empty = acc_full + TB;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + TB);
     float *s_bias = reinterpret_cast<float *>(sO + 2 * OUT_BYTES + 256);   // this table's 128 bias values (zeros if none)
+    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 <= 256, "barrier block");
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int table = blockIdx.x % n_tables, group = blockIdx.x / n_tables;
     const int64_t n_tiles = (M + BM - 1) / BM;
+    // Every role walks the same order: block of `tb` consecutive tiles -> K chunk -> tile -> k-block.
+    // A block's accumulators stay in TMEM across the K chunks; with one chunk (K = 128) the weight
+    // image is loaded once and the accumulators are simply a tb-deep ring.
+    const int64_t n_blocks = (n_tiles + tb - 1) / tb;
+    auto tiles_in = [&](int64_t blk) { const int64_t left = n_tiles - blk * tb; return (int)(left < tb ? left : tb); };
 
     if (tid == 0) {
         mbar_init(w_full, 1);
+        mbar_init(w_empty, 1);
         for (int s = 0; s < A_STAGES; ++s) { mbar_init(&a_full[s], kProducerWarps); mbar_init(&a_empty[s], 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); }
+        for (int s = 0; s < TB; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); }
         fence_barrier_init();
     }
     if (tid < BN) s_bias[tid] = bias ? bias[table * BN + tid] : 0.f;
-    if (warp == 0) {                                            // TMEM: 256 columns for this CTA
+    if (warp == 0) {                                            // TMEM: all 512 columns (one CTA per SM)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(kTmemCols)
                      : "memory");
@@ -152,40 +179,61 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
 
     if (warp == 0) {
         // ================================================= MMA issuer (one lane)
-        if (lane == 0) {
-            mbar_expect_tx(w_full, (unsigned)W_BYTES);
-            const char *src = reinterpret_cast<const char *>(image) + (size_t)table * W_BYTES;
-            for (int off = 0; off < W_BYTES; off += KB_BYTES) tma_load_1d(sW + off, src + off, KB_BYTES, w_full);
-            mbar_wait_bounded(w_full, 0);
-            // descriptors differ only in the start-address field (16-byte units, low word): one add each,
-            // so that this single thread can keep the tensor pipe fed (48 MMAs of ~64 clk per tile)
-            const uint64_t dA = smem_desc(smem_u32(sA)), dW = smem_desc(smem_u32(sW));
-            static_assert(A_STAGES == 2 && NKB % A_STAGES == 0, "stage of k-block kb is kb & 1");
-            unsigned a_phase = 0, acc_phase0 = 0, acc_phase1 = 0;
-            int it = 0;
-            for (int64_t tile = group; tile < n_tiles; tile += n_groups, ++it) {
-                const int ab = it & 1;
-                if (ab == 0) { mbar_wait_bounded(&acc_empty[0], acc_phase0 ^ 1u); acc_phase0 ^= 1u; }
-                else         { mbar_wait_bounded(&acc_empty[1], acc_phase1 ^ 1u); acc_phase1 ^= 1u; }
-                tc_fence_after();
-                const uint32_t d = tmem_base + (uint32_t)(ab * BN);
-#pragma unroll
-                for (int kb = 0; kb < NKB; ++kb) {
-                    const int stage = kb & 1;
-                    mbar_wait_bounded(&a_full[stage], a_phase);
-                    tc_fence_after();
-                    const uint64_t a_hi = dA + (uint64_t)((stage * A_STAGE_BYTES) >> 4), a_lo = a_hi + (KB_BYTES >> 4);
-                    const uint64_t b_hi = dW + (uint64_t)((kb * KB_BYTES) >> 4), b_lo = b_hi + ((NKB * KB_BYTES) >> 4);
-#pragma unroll
-                    for (int k8 = 0; k8 < KB / 8; ++k8) {       // K = 8 tf32 = 32 bytes = 2 address units per instruction
-                        umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, (kb | k8) != 0);
-                        umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, 1u);
-                        umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, 1u);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);     // same value, now provably uniform
+        // The whole warp walks the pipeline (converged), one elected lane issues: an MMA under elect.sync
+        // compiles to a single predicated UTCHMMA, under `lane == 0` to an elect / retry loop per instruction.
+        // descriptors differ only in the start-address field (16-byte units, low word): one add each
+        const uint32_t dA = (uint32_t)smem_desc(smem_u32(sA)), dW = (uint32_t)smem_desc(smem_u32(sW));
+        static_assert(A_STAGES == 2 && NKB % A_STAGES == 0, "stage of k-block kb is kb & 1");
+        unsigned a_phase = 0, w_phase = 0, we_phase = 0;
+        int bi = 0;
+        for (int64_t blk = group; blk < n_blocks; blk += n_groups, ++bi) {
+            const int nt = tiles_in(blk);
+            for (int kc = 0; kc < n_chunks; ++kc) {
+                if (n_chunks > 1 || bi == 0) {                  // (re)load the weight image of this K chunk
+                    if (bi != 0 || kc != 0) {                   // ... once the previous chunk's MMAs have read theirs
+                        mbar_wait_bounded(w_empty, we_phase);
+                        we_phase ^= 1u;
                     }
-                    umma_commit(&a_empty[stage]);               // smem slot free once these MMAs have read it
-                    if (stage == A_STAGES - 1) a_phase ^= 1u;
+                    if (lane == 0) {
+                        mbar_expect_tx(w_full, (unsigned)W_BYTES);
+                        const char *src = reinterpret_cast<const char *>(image) + ((size_t)kc * n_tables + table) * W_BYTES;
+                        for (int off = 0; off < W_BYTES; off += KB_BYTES) tma_load_1d(sW + off, src + off, KB_BYTES, w_full);
+                    }
+                    __syncwarp();
+                    mbar_wait_bounded(w_full, w_phase);
+                    w_phase ^= 1u;
                 }
-                umma_commit(&acc_full[ab]);                     // accumulator complete
+                for (int t = 0; t < nt; ++t) {
+                    if (kc == 0) mbar_wait_bounded(&acc_empty[t], (unsigned)(bi & 1) ^ 1u);   // drained by the epilogue
+                    tc_fence_after();
+                    const uint32_t d = tmem_u + (uint32_t)(t * BN);
+                    const bool last = kc == n_chunks - 1;
+#pragma unroll
+                    for (int kb = 0; kb < NKB; ++kb) {
+                        const int stage = kb & 1;
+                        mbar_wait_bounded(&a_full[stage], a_phase);
+                        tc_fence_after();
+                        const uint32_t a_hi = dA + (uint32_t)((stage * A_STAGE_BYTES) >> 4), a_lo = a_hi + (KB_BYTES >> 4);
+                        const uint32_t b_hi = dW + (uint32_t)((kb * KB_BYTES) >> 4), b_lo = b_hi + ((NKB * KB_BYTES) >> 4);
+                        if (elect_one()) {
+#pragma unroll
+                            for (int k8 = 0; k8 < KB / 8; ++k8) {   // K = 8 tf32 = 32 bytes = 2 address units per instruction
+                                umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, (unsigned)((kb | k8) != 0 || kc != 0));
+                                umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, 1u);
+                                umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, 1u);
+                            }
+                            umma_commit(&a_empty[stage]);           // smem slot free once these MMAs have read it
+                            if (kb == NKB - 1 && last) umma_commit(&acc_full[t]);   // accumulator complete
+                        }
+                        __syncwarp();
+                        if (stage == A_STAGES - 1) a_phase ^= 1u;
+                    }
+                }
+                if (n_chunks > 1) {                             // this chunk's image may be overwritten
+                    if (elect_one()) umma_commit(w_empty);
+                    __syncwarp();
+                }
             }
         }
         __syncwarp();
@@ -197,17 +245,28 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
         int stage = 0;
         unsigned phase = 0;
         float4 v[NKB][RPT];                                     // one tile of h: 16 LDG.128 per thread in flight
-        auto load_kb = [&](int64_t tile, int kb) {
+        auto load_kb = [&](int64_t blk, int kc, int t, int kb) {
 #pragma unroll
             for (int i = 0; i < RPT; ++i) {
-                const int64_t m = tile * BM + r0 + 32 * i;
-                v[kb][i] = (tile < n_tiles && m < M) ? __ldg(reinterpret_cast<const float4 *>(h + m * ldx + kb * KB) + c)
-                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+                const int64_t m = (blk * tb + t) * BM + r0 + 32 * i;
+                v[kb][i] = (blk < n_blocks && m < M)
+                               ? __ldg(reinterpret_cast<const float4 *>(h + m * ldx + kc * E + kb * KB) + c)
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
+        auto advance = [&](int64_t &blk, int &kc, int &t) {     // next (block, chunk, tile) of the walk
+            if (blk >= n_blocks) return;
+            if (++t >= tiles_in(blk)) {
+                t = 0;
+                if (++kc >= n_chunks) { kc = 0; blk += n_groups; }
+            }
+        };
+        int64_t blk = group, nblk = group;
+        int kc = 0, t = 0, nkc = 0, ntl = 0;
+        advance(nblk, nkc, ntl);
 #pragma unroll
-        for (int kb = 0; kb < NKB; ++kb) load_kb(group, kb);
-        for (int64_t tile = group; tile < n_tiles; tile += n_groups) {
+        for (int kb = 0; kb < NKB; ++kb) load_kb(blk, kc, t, kb);
+        while (blk < n_blocks) {
 #pragma unroll
             for (int kb = 0; kb < NKB; ++kb) {
                 mbar_wait_bounded(&a_empty[stage], phase ^ 1u);
@@ -223,12 +282,16 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                     *reinterpret_cast<uint4 *>(hi_img + swz(r, c)) = hi;
                     *reinterpret_cast<uint4 *>(lo_img + swz(r, c)) = lo;
                 }
-                load_kb(tile + n_groups, kb);           // same registers, next tile: a whole tile time to land
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&a_full[stage]);
+                // refill the same registers for the next tile AFTER the fence: the fence's MEMBAR waits for every
+                // load in flight, so loads issued before it would put the full HBM latency into each k-block
+                load_kb(nblk, nkc, ntl, kb);
                 if (++stage == A_STAGES) { stage = 0; phase ^= 1u; }
             }
+            blk = nblk; kc = nkc; t = ntl;
+            advance(nblk, nkc, ntl);
         }
     } else {
         // ================================================= epilogue: TMEM -> registers -> table rows
@@ -236,17 +299,16 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
         const int row = 32 * q + lane;
         float *out = tables + (size_t)table * table_stride;
         const bool epi = bias != nullptr || relu || accumulate;
-        unsigned acc_phase[2] = {0u, 0u};
-        int it = 0;
-        for (int64_t tile = group; tile < n_tiles; tile += n_groups, ++it) {
-            const int ab = it & 1;
-            mbar_wait_bounded(&acc_full[ab], acc_phase[ab]);
-            acc_phase[ab] ^= 1u;
+        int bi = 0;
+        for (int64_t blk = group; blk < n_blocks; blk += n_groups, ++bi)
+        for (int t = 0, nt = tiles_in(blk); t < nt; ++t) {
+            const int64_t tile = blk * tb + t;
+            mbar_wait_bounded(&acc_full[t], (unsigned)(bi & 1));
             tc_fence_after();
 #pragma unroll
             for (int cb = 0; cb < BN / 32; ++cb) {
                 uint32_t v[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(ab * BN + cb * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * BN + cb * 32);
                 asm volatile(
                     "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                     "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -260,7 +322,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                 if (cb == BN / 32 - 1) {                        // accumulator drained: hand it back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&acc_empty[ab]);
+                    if (lane == 0) mbar_arrive(&acc_empty[t]);
                 }
                 // registers (one row, 32 columns per thread) -> swizzled staging -> coalesced row stores
                 unsigned char *st = sO + (cb & 1) * OUT_BYTES;
@@ -269,21 +331,39 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, const float *__restr
                     *reinterpret_cast<uint4 *>(st + swz(row, k)) = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
                 asm volatile("bar.sync 1, 128;" ::: "memory");     // the four epilogue warps
                 const int et = tid - (1 + kProducerWarps) * 32;     // 0..127
+                // all eight staged chunks first (shared-space loads the compiler may not reorder against the
+                // global stores on its own), then the row stores: one latency per column block, not eight
+                float4 y[8];
+                const uint32_t st_addr = smem_u32(st);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(y[j].x), "=f"(y[j].y), "=f"(y[j].z), "=f"(y[j].w)
+                                 : "r"(st_addr + (uint32_t)swz(rr, ch)));
+                }
+                if (epi) {                                      // linear-layer epilogue: (+ previous K chunks) + bias, ReLU
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
+                        const int64_t mm = tile * BM + rr;
+                        const float4 bb = *reinterpret_cast<const float4 *>(s_bias + cb * 32 + ch * 4);
+                        y[j].x += bb.x; y[j].y += bb.y; y[j].z += bb.z; y[j].w += bb.w;
+                        if (accumulate && mm < M) {
+                            const float4 o = __ldg(reinterpret_cast<const float4 *>(out + mm * ldo + cb * 32 + ch * 4));
+                            y[j].x += o.x; y[j].y += o.y; y[j].z += o.z; y[j].w += o.w;
+                        }
+                        if (relu) {
+                            y[j].x = fmaxf(y[j].x, 0.f); y[j].y = fmaxf(y[j].y, 0.f);
+                            y[j].z = fmaxf(y[j].z, 0.f); y[j].w = fmaxf(y[j].w, 0.f);
+                        }
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
                     const int64_t mm = tile * BM + rr;
-                    if (mm < M) {
-                        float4 y = *reinterpret_cast<const float4 *>(st + swz(rr, ch));
-                        float4 *dst = reinterpret_cast<float4 *>(out + mm * ldo + cb * 32 + ch * 4);
-                        if (epi) {                              // linear-layer epilogue: (+ previous K chunks) + bias, ReLU
-                            const float4 bb = *reinterpret_cast<const float4 *>(s_bias + cb * 32 + ch * 4);
-                            y.x += bb.x; y.y += bb.y; y.z += bb.z; y.w += bb.w;
-                            if (accumulate) { const float4 o = *dst; y.x += o.x; y.y += o.y; y.z += o.z; y.w += o.w; }
-                            if (relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
-                        }
-                        *dst = y;
-                    }
+                    if (mm < M) *reinterpret_cast<float4 *>(out + mm * ldo + cb * 32 + ch * 4) = y[j];
                 }
             }
         }
@@ -305,7 +385,8 @@ int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image,
     return 0;
 }
 
-int launch_project_tc(int64_t M, int n_tables, const float *h, const float *image, float *tables,
+// n_chunks K chunks of 128 (x row stride ldx >= 128 * n_chunks; image = [chunk][table][W image]) accumulate in TMEM
+int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, const float *image, float *tables,
                       int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
                       cudaStream_t stream) {
     static int sm_count = 0;
@@ -325,8 +406,12 @@ int launch_project_tc(int64_t M, int n_tables, const float *h, const float *imag
     int64_t groups = sm_count / n_tables;                       // persistent: one CTA per SM
     if (groups < 1) groups = 1;
     if (groups > n_tiles) groups = n_tiles;
+    // tiles per block: up to four accumulators, but never fewer blocks than CTA groups
+    int64_t tb = n_tiles / groups;
+    if (tb > tc::TB) tb = tc::TB;
+    if (tb < 1) tb = 1;
     tc::am_project_tc_kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
-        M, n_tables, (int)groups, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate);
+        M, n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate);
     RL4CO_CHECK_LAUNCH("am_project(tc)");
     return 0;
 }

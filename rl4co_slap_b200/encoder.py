@@ -54,7 +54,7 @@ class SLAPInitEmbedding(nn.Module):
 INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding}
 
 
-# ---- K = 128 linears on the tensor cores ----------------------------------------------
+# ---- linears (widths multiples of 128) on the tensor cores ----------------------------------------------
 def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tensor:
     """``act(lin(x))``.  On a CUDA device, outside autograd, a Linear whose input and output widths are
     multiples of 128 runs on the library's fp32-accurate tensor-core kernel (rl4co_linear_tc: tcgen05,
@@ -63,8 +63,7 @@ def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tens
     w = lin.weight
     use_tc = (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
               and w.shape[1] % 128 == 0 and w.shape[0] % 128 == 0 and max(w.shape) <= 2048
-              and getattr(lin, "tensor_core", w.shape[1] == 128))   # wider inputs run as K chunks through y and
-                                                                     # lose to cuBLAS (tools/bench_linear.py): opt-in
+              and getattr(lin, "tensor_core", True))     # wider inputs: K chunks of 128 accumulate in TMEM
     if not use_tc:
         y = F.linear(x, w, lin.bias)
         return F.relu(y) if relu else y
