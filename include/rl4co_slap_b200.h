@@ -149,12 +149,19 @@ int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float
 /* The same tensor-core kernel with a linear-layer epilogue, for the linears of the PyTorch encoder that
  * feeds the path (models/nn/graph/attnnet.py:16-63: Wqkv, out_proj, feed-forward):
  *   y[m][j] = act(sum_e x[m][e] * W[j][e] + bias[j]),  act = ReLU if relu != 0,
- * n_in and n_out multiples of 128 (<= 2048); n_in > 128 runs as 128-wide K chunks accumulated through y.
+ * n_in and n_out multiples of 128 (<= 2048); n_in > 128 runs as 128-wide K chunks that accumulate in TMEM.
  * x [M,n_in], W [n_out,n_in], y [M,n_out] row-major; bias may be NULL.
- * image = rl4co_linear_pack(W): (n_in/128) * rl4co_am_weight_image_floats(n_out/128) floats. */
+ * image = rl4co_linear_pack(W): (n_in/128) * rl4co_am_weight_image_floats(n_out/128) floats.
+ * rl4co_linear_tc_ex adds the skip connection and the eval-mode batch norm that follow out_proj and the
+ * feed-forward in the encoder layer (attnnet.py:44-58, SkipConnection + Normalization) to the epilogue:
+ *   y = (act(x W^T + bias) + residual) * scale + shift
+ * residual [M,n_out] (must not alias y), scale / shift [n_out]; each may be NULL (0, 1, 0). */
 int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream);
 int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
                     const float *bias, int32_t relu, float *y, rl4co_stream_t stream);
+int rl4co_linear_tc_ex(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
+                       const float *bias, int32_t relu, const float *residual, const float *scale,
+                       const float *shift, float *y, rl4co_stream_t stream);
 
 /* Self-attention of the PyTorch encoder's layers for the path's graph sizes (N <= 128, 8 heads x 16,
  * no mask, fp32): replaces the F.scaled_dot_product_attention call of MultiHeadAttention

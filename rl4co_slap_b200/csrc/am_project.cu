@@ -109,7 +109,7 @@ namespace rl4co {
 int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream);
 int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, const float *image, float *tables,
                       int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
-                      cudaStream_t stream);
+                      const float *residual, const float *scale, const float *shift, cudaStream_t stream);
 }  // namespace rl4co
 
 using namespace rl4co;
@@ -130,7 +130,8 @@ extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, 
     RL4CO_REQUIRE(h && image && tables, "am_project_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)h & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)tables & 15) == 0,
                   "am_project_tc: pointers must be 16-byte aligned");
-    return launch_project_tc(M, n_tables, 1, h, image, tables, M * 128, 128, nullptr, 0, 128, 0, (cudaStream_t)stream);
+    return launch_project_tc(M, n_tables, 1, h, image, tables, M * 128, 128, nullptr, 0, 128, 0, nullptr, nullptr, nullptr,
+                             (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream) {
@@ -146,16 +147,30 @@ extern "C" int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, fl
     return 0;
 }
 
+static int linear_tc_impl(const char *who, int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
+                          const float *bias, int32_t relu, const float *residual, const float *scale,
+                          const float *shift, float *y, rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_out >= 128 && n_out % 128 == 0 && n_out <= 2048 && n_in >= 128 && n_in % 128 == 0 && n_in <= 2048,
+                  "%s: sizes must be multiples of 128 (<= 2048), got M=%lld %d x %d", who, (long long)M, n_out, n_in);
+    if (M == 0) return 0;
+    RL4CO_REQUIRE(x && image && y, "%s: null pointer", who);
+    RL4CO_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)y & 15) == 0 &&
+                      ((uintptr_t)residual & 15) == 0,
+                  "%s: pointers must be 16-byte aligned", who);
+    // the K chunks of a row tile accumulate in TMEM; bias, ReLU, residual and the affine ride the single epilogue
+    return launch_project_tc(M, n_out / 128, n_in / 128, x, image, y, 128, n_out, bias, relu, n_in, 0, residual, scale,
+                             shift, (cudaStream_t)stream);
+}
+
 extern "C" int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
                                const float *bias, int32_t relu, float *y, rl4co_stream_t stream) {
-    RL4CO_REQUIRE(M >= 0 && n_out >= 128 && n_out % 128 == 0 && n_out <= 2048 && n_in >= 128 && n_in % 128 == 0 && n_in <= 2048,
-                  "linear_tc: sizes must be multiples of 128 (<= 2048), got M=%lld %d x %d", (long long)M, n_out, n_in);
-    if (M == 0) return 0;
-    RL4CO_REQUIRE(x && image && y, "linear_tc: null pointer");
-    RL4CO_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)image & 15) == 0 && ((uintptr_t)y & 15) == 0,
-                  "linear_tc: pointers must be 16-byte aligned");
-    // the K chunks of a row tile accumulate in TMEM; bias and ReLU ride the single epilogue
-    return launch_project_tc(M, n_out / 128, n_in / 128, x, image, y, 128, n_out, bias, relu, n_in, 0, (cudaStream_t)stream);
+    return linear_tc_impl("linear_tc", M, n_out, n_in, x, image, bias, relu, nullptr, nullptr, nullptr, y, stream);
+}
+
+extern "C" int rl4co_linear_tc_ex(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
+                                  const float *bias, int32_t relu, const float *residual, const float *scale,
+                                  const float *shift, float *y, rl4co_stream_t stream) {
+    return linear_tc_impl("linear_tc_ex", M, n_out, n_in, x, image, bias, relu, residual, scale, shift, y, stream);
 }
 
 extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,

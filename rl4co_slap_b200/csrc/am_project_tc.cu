@@ -37,7 +37,7 @@ constexpr int A_STAGE_BYTES = 2 * KB_BYTES;          // hi + lo
 constexpr int kProducerWarps = 8;
 constexpr int kThreads = (1 + kProducerWarps + 4) * 32;
 constexpr int OUT_BYTES = BM * 128;                    // staging of one 32-column block of the accumulator
-constexpr int SMEM_BYTES = 1024 + W_BYTES + A_STAGES * A_STAGE_BYTES + 2 * OUT_BYTES + 256 + 512;
+constexpr int SMEM_BYTES = 1024 + W_BYTES + A_STAGES * A_STAGE_BYTES + 2 * OUT_BYTES + 256 + 3 * 512;
 constexpr int TB = 4;                    // tiles per block = accumulators resident in TMEM
 constexpr uint32_t kTmemCols = TB * BN;  // 512 columns: four 128-column accumulators
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = F32 (bits 4-5 = 1),
@@ -136,7 +136,9 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const f
 __global__ void __launch_bounds__(kThreads, 1)
 am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb, const float *__restrict__ h,
                      const float *__restrict__ image, float *__restrict__ tables, int64_t table_stride, int64_t ldo,
-                     const float *__restrict__ bias, int relu, int64_t ldx, int accumulate) {
+                     const float *__restrict__ bias, int relu, int64_t ldx, int accumulate,
+                     const float *__restrict__ residual, const float *__restrict__ scale,
+                     const float *__restrict__ shift) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char *sW = smem;                                   // 128 KB weight image (of the current K chunk)
@@ -165,7 +167,11 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
         for (int s = 0; s < TB; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); }
         fence_barrier_init();
     }
-    if (tid < BN) s_bias[tid] = bias ? bias[table * BN + tid] : 0.f;
+    if (tid < BN) {                                             // per-column epilogue vectors of this table
+        s_bias[tid] = bias ? bias[table * BN + tid] : 0.f;
+        s_bias[BN + tid] = scale ? scale[table * BN + tid] : 1.f;
+        s_bias[2 * BN + tid] = shift ? shift[table * BN + tid] : 0.f;
+    }
     if (warp == 0) {                                            // TMEM: all 512 columns (one CTA per SM)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(kTmemCols)
@@ -220,8 +226,10 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
 #pragma unroll
                             for (int k8 = 0; k8 < KB / 8; ++k8) {   // K = 8 tf32 = 32 bytes = 2 address units per instruction
                                 umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, (unsigned)((kb | k8) != 0 || kc != 0));
+#ifndef TC_EXP_ONE_MMA
                                 umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, 1u);
                                 umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, 1u);
+#endif
                             }
                             umma_commit(&a_empty[stage]);           // smem slot free once these MMAs have read it
                             if (kb == NKB - 1 && last) umma_commit(&acc_full[t]);   // accumulator complete
@@ -287,6 +295,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                 if (lane == 0) mbar_arrive(&a_full[stage]);
                 // refill the same registers for the next tile AFTER the fence: the fence's MEMBAR waits for every
                 // load in flight, so loads issued before it would put the full HBM latency into each k-block
+                // (refilling all four k-blocks once per tile instead was measured slower: 1.49 vs 1.19 ms, 512->128)
                 load_kb(nblk, nkc, ntl, kb);
                 if (++stage == A_STAGES) { stage = 0; phase ^= 1u; }
             }
@@ -295,18 +304,52 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
         }
     } else {
         // ================================================= epilogue: TMEM -> registers -> table rows
+        // Per 32-column block: tcgen05.ld (thread = row) -> swizzled staging -> thread = (row group, 16-byte
+        // chunk) -> 512-byte coalesced row stores.  All addresses are hoisted: a thread's eight staging reads
+        // are 2 KB apart (same swizzle phase) and its eight rows 16 * ldo apart.
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
         const int row = 32 * q + lane;
         float *out = tables + (size_t)table * table_stride;
         const bool epi = bias != nullptr || relu || accumulate;
+        const bool post = residual != nullptr || scale != nullptr || shift != nullptr;
+        const int et = tid - (1 + kProducerWarps) * 32;         // 0..127
+        const int rr0 = et >> 3, ch = et & 7;                   // first of this thread's 8 rows, its 16-byte chunk
+        const uint32_t sO_addr = smem_u32(sO);
+        const uint32_t st_w = sO_addr + (uint32_t)row * 128u;   // + ((k ^ (row & 7)) << 4) per chunk k
+        const uint32_t st_r = sO_addr + swz(rr0, ch);           // + 2048 * j
+        const int r7 = row & 7;
+        const int64_t row_step = 16 * ldo;
+        auto prefetch_rows = [&](int64_t tl) {                  // 128 rows x 512 B of the residual, one row per thread
+            const int64_t mm = tl * BM + et;
+            if (tl < 0 || mm >= M) return;
+            const char *row_ptr = reinterpret_cast<const char *>(residual + mm * ldo + table * BN);
+#pragma unroll
+            for (int l = 0; l < 4; ++l) asm volatile("prefetch.global.L2 [%0];" ::"l"(row_ptr + 128 * l));
+        };
         int bi = 0;
         for (int64_t blk = group; blk < n_blocks; blk += n_groups, ++bi)
         for (int t = 0, nt = tiles_in(blk); t < nt; ++t) {
             const int64_t tile = blk * tb + t;
+            if (residual) {                                     // next tile's skip rows -> L2, a tile time ahead of their loads
+                const int64_t nxt = (t + 1 < nt) ? tile + 1 : (blk + n_groups) * tb;
+                prefetch_rows(bi == 0 && t == 0 ? tile : -1);   // (and the first tile's own)
+                prefetch_rows(nxt);
+            }
+            const int64_t m0 = tile * BM + rr0;                 // this thread's rows: m0 + 16 j
+            const int rows_ok = (int)((M - m0 + 15) / 16 < 8 ? (M - m0 + 15) / 16 : 8);    // 8 on all but a ragged tile
+            float *o_ptr = out + m0 * ldo + ch * 4;
+            const float *r_ptr = residual ? residual + m0 * ldo + table * BN + ch * 4 : nullptr;
             mbar_wait_bounded(&acc_full[t], (unsigned)(bi & 1));
             tc_fence_after();
 #pragma unroll
             for (int cb = 0; cb < BN / 32; ++cb) {
+                float4 rs[8];
+                if (r_ptr) {                                    // skip rows of this column block: in flight under the drain
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        rs[j] = j < rows_ok ? __ldg(reinterpret_cast<const float4 *>(r_ptr + j * row_step + cb * 32))
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
                 uint32_t v[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(t * BN + cb * 32);
                 asm volatile(
@@ -324,33 +367,30 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[t]);
                 }
-                // registers (one row, 32 columns per thread) -> swizzled staging -> coalesced row stores
-                unsigned char *st = sO + (cb & 1) * OUT_BYTES;
+#ifdef TC_EXP_NO_EPI
+                if (v[0] == 0x7fc12345u) out[0] = 1.f;
+                continue;
+#endif
+                const uint32_t so = (uint32_t)(cb & 1) * OUT_BYTES;
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
-                    *reinterpret_cast<uint4 *>(st + swz(row, k)) = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st_w + so + (uint32_t)((k ^ r7) << 4)),
+                                 "r"(v[4 * k]), "r"(v[4 * k + 1]), "r"(v[4 * k + 2]), "r"(v[4 * k + 3])
+                                 : "memory");
                 asm volatile("bar.sync 1, 128;" ::: "memory");     // the four epilogue warps
-                const int et = tid - (1 + kProducerWarps) * 32;     // 0..127
-                // all eight staged chunks first (shared-space loads the compiler may not reorder against the
-                // global stores on its own), then the row stores: one latency per column block, not eight
                 float4 y[8];
-                const uint32_t st_addr = smem_u32(st);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
+                for (int j = 0; j < 8; ++j)
                     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                                  : "=f"(y[j].x), "=f"(y[j].y), "=f"(y[j].z), "=f"(y[j].w)
-                                 : "r"(st_addr + (uint32_t)swz(rr, ch)));
-                }
+                                 : "r"(st_r + so + 2048u * j));
                 if (epi) {                                      // linear-layer epilogue: (+ previous K chunks) + bias, ReLU
+                    const float4 bb = *reinterpret_cast<const float4 *>(s_bias + cb * 32 + ch * 4);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
-                        const int64_t mm = tile * BM + rr;
-                        const float4 bb = *reinterpret_cast<const float4 *>(s_bias + cb * 32 + ch * 4);
                         y[j].x += bb.x; y[j].y += bb.y; y[j].z += bb.z; y[j].w += bb.w;
-                        if (accumulate && mm < M) {
-                            const float4 o = __ldg(reinterpret_cast<const float4 *>(out + mm * ldo + cb * 32 + ch * 4));
+                        if (accumulate && j < rows_ok) {
+                            const float4 o = *reinterpret_cast<const float4 *>(o_ptr + j * row_step + cb * 32);
                             y[j].x += o.x; y[j].y += o.y; y[j].z += o.z; y[j].w += o.w;
                         }
                         if (relu) {
@@ -359,11 +399,23 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                         }
                     }
                 }
+                if (post) {                                     // (+ skip row) * scale + shift: skip connection and the
+                    const float4 sc = *reinterpret_cast<const float4 *>(s_bias + BN + cb * 32 + ch * 4);       // eval-mode
+                    const float4 sh = *reinterpret_cast<const float4 *>(s_bias + 2 * BN + cb * 32 + ch * 4);   // batch norm
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int idx = et + 128 * j, rr = idx >> 3, ch = idx & 7;
-                    const int64_t mm = tile * BM + rr;
-                    if (mm < M) *reinterpret_cast<float4 *>(out + mm * ldo + cb * 32 + ch * 4) = y[j];
+                    for (int j = 0; j < 8; ++j) {
+                        if (r_ptr) { y[j].x += rs[j].x; y[j].y += rs[j].y; y[j].z += rs[j].z; y[j].w += rs[j].w; }
+                        y[j].x = fmaf(y[j].x, sc.x, sh.x); y[j].y = fmaf(y[j].y, sc.y, sh.y);
+                        y[j].z = fmaf(y[j].z, sc.z, sh.z); y[j].w = fmaf(y[j].w, sc.w, sh.w);
+                    }
+                }
+                if (rows_ok == 8) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) *reinterpret_cast<float4 *>(o_ptr + j * row_step + cb * 32) = y[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (j < rows_ok) *reinterpret_cast<float4 *>(o_ptr + j * row_step + cb * 32) = y[j];
                 }
             }
         }
@@ -388,7 +440,7 @@ int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image,
 // n_chunks K chunks of 128 (x row stride ldx >= 128 * n_chunks; image = [chunk][table][W image]) accumulate in TMEM
 int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, const float *image, float *tables,
                       int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
-                      cudaStream_t stream) {
+                      const float *residual, const float *scale, const float *shift, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -411,7 +463,8 @@ int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, con
     if (tb > tc::TB) tb = tc::TB;
     if (tb < 1) tb = 1;
     tc::am_project_tc_kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
-        M, n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate);
+        M, n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate,
+        residual, scale, shift);
     RL4CO_CHECK_LAUNCH("am_project(tc)");
     return 0;
 }

@@ -55,18 +55,46 @@ INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SL
 
 
 # ---- linears (widths multiples of 128) on the tensor cores ----------------------------------------------
-def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tensor:
-    """``act(lin(x))``.  On a CUDA device, outside autograd, a Linear whose input and output widths are
-    multiples of 128 runs on the library's fp32-accurate tensor-core kernel (rl4co_linear_tc: tcgen05,
-    3-term TF32 split, fp32 accumulation - the K3 projection kernel with a bias / ReLU epilogue);
-    everything else is the plain PyTorch op.  The packed weight image is cached on the module."""
+def _tc_ok(x: torch.Tensor, lin: nn.Linear) -> bool:
     w = lin.weight
-    use_tc = (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
-              and w.shape[1] % 128 == 0 and w.shape[0] % 128 == 0 and max(w.shape) <= 2048
-              and getattr(lin, "tensor_core", True))     # wider inputs: K chunks of 128 accumulate in TMEM
-    if not use_tc:
+    return (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
+            and w.shape[1] % 128 == 0 and w.shape[0] % 128 == 0 and max(w.shape) <= 2048
+            and getattr(lin, "tensor_core", True))      # wider inputs: K chunks of 128 accumulate in TMEM
+
+
+def _bn_affine(bn: nn.BatchNorm1d):
+    """Eval-mode batch norm as a per-channel (scale, shift), cached until its buffers change."""
+    tensors = (bn.weight, bn.bias, bn.running_mean, bn.running_var)
+    vers = []
+    for p in tensors:
+        try:
+            vers.append(p._version)
+        except RuntimeError:        # inference tensor
+            vers.append(-1)
+    key = tuple((p.data_ptr(), v) for p, v in zip(tensors, vers))
+    if getattr(bn, "_affine_key", None) != key:
+        scale = bn.weight.detach() * torch.rsqrt(bn.running_var + bn.eps)
+        shift = bn.bias.detach() - bn.running_mean * scale
+        bn._affine, bn._affine_key = (scale.contiguous(), shift.contiguous()), key
+    return bn._affine
+
+
+def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False, residual: torch.Tensor = None,
+              norm: nn.BatchNorm1d = None) -> torch.Tensor:
+    """``norm(act(lin(x)) + residual)`` (residual / norm optional).  On a CUDA device, outside autograd, a
+    Linear whose input and output widths are multiples of 128 runs on the library's fp32-accurate tensor-core
+    kernel (rl4co_linear_tc[_ex]: tcgen05, 3-term TF32 split, fp32 accumulation - the K3 projection kernel
+    with a bias / ReLU / skip / eval-batch-norm epilogue); everything else is the plain PyTorch ops.  The
+    packed weight image is cached on the module.  ``norm`` must be an eval-mode BatchNorm1d."""
+    w = lin.weight
+    if not _tc_ok(x, lin):
         y = F.linear(x, w, lin.bias)
-        return F.relu(y) if relu else y
+        y = F.relu(y) if relu else y
+        if residual is not None:
+            y = y + residual
+        if norm is not None:
+            y = norm(y.reshape(-1, y.size(-1))).view(*y.size())
+        return y
     from . import _lib
     try:
         ver = w._version
@@ -83,8 +111,16 @@ def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False) -> torch.Tens
     x2 = x.reshape(-1, n_in).contiguous()
     y = torch.empty(x2.shape[0], n_out, dtype=torch.float32, device=x.device)
     bias = lin.bias.detach().contiguous() if lin.bias is not None else None
-    _lib.call("rl4co_linear_tc", x2.shape[0], n_out, n_in, _lib.ptr(x2), _lib.ptr(lin._tc_image),
-              _lib.ptr(bias), int(relu), _lib.ptr(y), _lib.stream_ptr(x.device))
+    if residual is None and norm is None:
+        _lib.call("rl4co_linear_tc", x2.shape[0], n_out, n_in, _lib.ptr(x2), _lib.ptr(lin._tc_image),
+                  _lib.ptr(bias), int(relu), _lib.ptr(y), _lib.stream_ptr(x.device))
+    else:
+        assert norm is None or not norm.training, "fused batch norm needs eval mode (running statistics)"
+        scale, shift = _bn_affine(norm) if norm is not None else (None, None)
+        res = residual.reshape(-1, n_out).contiguous() if residual is not None else None
+        _lib.call("rl4co_linear_tc_ex", x2.shape[0], n_out, n_in, _lib.ptr(x2), _lib.ptr(lin._tc_image),
+                  _lib.ptr(bias), int(relu), _lib.ptr(res), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(y),
+                  _lib.stream_ptr(x.device))
     return y.view(*x.shape[:-1], n_out)
 
 
@@ -105,7 +141,8 @@ class _SelfAttention(nn.Module):
         self.Wqkv = nn.Linear(embed_dim, 3 * embed_dim)
         self.out_proj = nn.Linear(embed_dim, embed_dim)
 
-    def forward(self, x):
+    def attend(self, x):
+        """Heads' outputs before the output projection, [B, N, E]."""
         B, N, E = x.shape
         qkv = linear128(x, self.Wqkv)
         if (qkv.is_cuda and not torch.is_grad_enabled() and qkv.dtype == torch.float32 and E == 128
@@ -115,11 +152,14 @@ class _SelfAttention(nn.Module):
             qkv = qkv.contiguous()
             o = torch.empty(B, N, E, dtype=torch.float32, device=x.device)
             _lib.call("rl4co_encoder_attention", B, N, _lib.ptr(qkv), _lib.ptr(o), _lib.stream_ptr(x.device))
-            return linear128(o, self.out_proj)
+            return o
         qkv = qkv.view(B, N, 3, self.num_heads, E // self.num_heads)
         q, k, v = qkv.permute(2, 0, 3, 1, 4).unbind(0)
         o = F.scaled_dot_product_attention(q, k, v)
-        return linear128(o.transpose(1, 2).reshape(B, N, E), self.out_proj)
+        return o.transpose(1, 2).reshape(B, N, E)
+
+    def forward(self, x):
+        return linear128(self.attend(x), self.out_proj)
 
 
 class _FeedForward(nn.Module):
@@ -164,6 +204,21 @@ class _Layer(nn.Sequential):
             _Skip(_FeedForward(embed_dim, hidden)),
             _Norm(embed_dim, normalization),
         )
+
+    def forward(self, x):
+        mha, norm1, ff, norm2 = self[0].module, self[1], self[2].module, self[3]
+        fused = (x.is_cuda and not torch.is_grad_enabled() and not self.training
+                 and norm1.kind == "batch" and norm2.kind == "batch"
+                 and norm1.normalizer.track_running_stats and norm2.normalizer.track_running_stats
+                 and _tc_ok(x, mha.out_proj) and _tc_ok(x, ff.lins[-1]) and getattr(self, "fused_epilogue", True))
+        if not fused:
+            return super().forward(x)
+        # inference: skip connection + eval-mode batch norm ride the epilogue of the linear before them
+        h = linear128(mha.attend(x), mha.out_proj, residual=x, norm=norm1.normalizer)
+        f = h
+        for lin in ff.lins[:-1]:
+            f = linear128(f, lin, relu=True)
+        return linear128(f, ff.lins[-1], residual=h, norm=norm2.normalizer)
 
 
 class GraphAttentionNetwork(nn.Module):

@@ -333,9 +333,42 @@ def test_encoder_tensor_core_linears_match_pytorch(name, dev):
     assert (h2 - ref).abs().max().item() <= 2e-5 * ref.abs().max().item()
 
 
+@pytest.mark.parametrize("name", ("tsp", "cvrp"))
+def test_encoder_fused_skip_batchnorm_epilogue(name, dev):
+    """eval-mode encoder layer: skip connection + batch norm (running statistics) fused into the epilogue of
+    out_proj / the last feed-forward linear (rl4co_linear_tc_ex) vs the unfused PyTorch modules"""
+    torch.manual_seed(11)
+    pol = load_policy(name, dev).eval()
+    for m in pol.encoder.modules():                 # non-trivial running statistics and affine
+        if isinstance(m, torch.nn.BatchNorm1d):
+            m.running_mean.copy_(torch.randn_like(m.running_mean) * 0.3)
+            m.running_var.copy_(torch.rand_like(m.running_var) + 0.5)
+            m.weight.data.copy_(torch.rand_like(m.weight) + 0.5)
+            m.bias.data.copy_(torch.randn_like(m.bias) * 0.2)
+    g = R.TSPGenerator(num_loc=50) if name == "tsp" else R.CVRPGenerator(num_loc=50)
+    td = R.get_env(name, device=dev).reset(g(777).to(dev))       # 777 * 50 rows: a ragged last row tile
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        with torch.inference_mode():
+            h_fused = pol.encoder(td)[0]
+            for m in pol.encoder.modules():
+                if isinstance(m, torch.nn.Linear):
+                    m.tensor_core = False
+                if hasattr(m, "Wqkv"):
+                    m.fused_attention = False
+                if isinstance(m, torch.nn.Sequential) and len(m) == 4:
+                    m.fused_epilogue = False
+            h_pt = pol.encoder(td)[0]
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    scale = h_pt.abs().max().item()
+    assert (h_fused - h_pt).abs().max().item() <= 2e-5 * scale, ((h_fused - h_pt).abs().max().item(), scale)
+
+
 @pytest.mark.parametrize("M,n_out,n_in,relu", ((257, 128, 512, False), (1000, 512, 128, True), (130, 256, 256, True)))
 def test_linear_tc_k_chunks_bias_relu(M, n_out, n_in, relu, dev):
-    """rl4co_linear_tc: 128-wide K chunks accumulated through y, bias on the first, ReLU on the last"""
+    """rl4co_linear_tc: 128-wide K chunks accumulated in TMEM, bias / ReLU in the single epilogue"""
     from rl4co_slap_b200 import _lib
     torch.manual_seed(n_out + n_in)
     x = torch.randn(M, n_in, device=dev)

@@ -20,3 +20,14 @@ with torch.inference_mode():
         lin.tensor_core = False
         t_pt = timed(lambda: linear128(x, lin, relu))
         print(f"{n_in}->{n_out} relu={relu}: tc {t_tc:.3f} ms  torch {t_pt:.3f} ms")
+    # skip + eval batch norm fused into the epilogue vs separate kernels
+    for n_in in (128, 512):
+        lin = nn.Linear(n_in, 128).to(dev)
+        bn = nn.BatchNorm1d(128).to(dev).eval()
+        x = torch.randn(M, n_in, device=dev)
+        res = torch.randn(M, 128, device=dev)
+        t_f = timed(lambda: linear128(x, lin, residual=res, norm=bn))
+        t_s = timed(lambda: bn(linear128(x, lin) + res))
+        t_r = timed(lambda: linear128(x, lin, residual=res))
+        t_n = timed(lambda: linear128(x, lin, norm=bn))
+        print(f"{n_in}->128 + skip + bn: fused {t_f:.3f} ms  separate {t_s:.3f} ms  (residual only {t_r:.3f}, affine only {t_n:.3f})")
