@@ -201,16 +201,20 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, region=False):
         for _ in range(warmup):
             fn()
         barrier()
+        if region:                                            # ncu --profile-from-start off: timed steps only
+            torch.cuda.profiler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         barrier()
+        if region:
+            torch.cuda.profiler.stop()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -220,7 +224,7 @@ def run_ours(args):
         decode_step()                                         # first touch (allocator, lib load)
         pol.profile = []
         with ClockSampler(local) as clk:
-            ms_step = timed(decode_step, args.steps, args.warmup)
+            ms_step = timed(decode_step, args.steps, args.warmup, region=args.profile_region)
         prof = pol.profile[-args.steps * ((B + pol.rollout_chunk - 1) // pol.rollout_chunk):]
         pol.profile = None
         launches_per_step = pol.last_launches + 1             # + reward_stats
@@ -247,7 +251,7 @@ def run_ours(args):
             ms_e2e = timed(e2e_step, args.steps, args.warmup)
             e2e = {"value": B * world / (ms_e2e * 1e-3), "unit": "rollouts/s",
                    "h2d_bytes_per_step": host_locs.numel() * 4, "d2h_bytes_per_step": host_reward.numel() * 4,
-                   "ms_per_step": ms_e2e, "includes": "H2D locs + PyTorch fp32 encoder + K3 + K2 + D2H rewards"}
+                   "ms_per_step": ms_e2e, "includes": "H2D locs + fp32 encoder (PyTorch modules; linears, skip+BN and attention on library kernels) + K3 + K2 + D2H rewards"}
 
     if rank != 0:
         if world > 1:
@@ -310,6 +314,8 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=4, help="timed host-side passes of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile-region", action="store_true",
+                    help="cudaProfilerStart/Stop around the timed decode steps (ncu --profile-from-start off)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -12,7 +12,7 @@
 // (rl4co_am_pack_weights) - resident in shared memory (128 KB, one TMA bulk load), and streams
 // 128-row tiles of h:
 //   warps 1-8  producers: coalesced LDG of a 128 x 32 fp32 k-block, hi / lo split, swizzled
-//              st.shared into a 3-stage ring, mbarrier full / empty;
+//              st.shared into a 2-stage ring, mbarrier full / empty;
 //   warp 0     one elected lane issues 48 tcgen05.mma (M128 N128 K8, kind::tf32) per tile and
 //              commits to the mbarriers;
 //   warps 9-12 epilogue: tcgen05.ld the 128 x 128 fp32 accumulator (double buffered in TMEM,
@@ -295,7 +295,8 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                 if (lane == 0) mbar_arrive(&a_full[stage]);
                 // refill the same registers for the next tile AFTER the fence: the fence's MEMBAR waits for every
                 // load in flight, so loads issued before it would put the full HBM latency into each k-block
-                // (refilling all four k-blocks once per tile instead was measured slower: 1.49 vs 1.19 ms, 512->128)
+                // (measured alternatives, both slower: refilling all four k-blocks once per tile, 1.49 vs 1.19 ms on
+                // 512->128; two producer sets of four warps, one per ring stage, 1.31 vs 1.24 ms on 128->384)
                 load_kb(nblk, nkc, ntl, kb);
                 if (++stage == A_STAGES) { stage = 0; phase ^= 1u; }
             }
@@ -409,6 +410,9 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                         y[j].z = fmaf(y[j].z, sc.z, sh.z); y[j].w = fmaf(y[j].w, sc.w, sh.w);
                     }
                 }
+#ifdef TC_EXP_NO_STG
+                if (y[0].x != 1.2345e-33f) continue;
+#endif
                 if (rows_ok == 8) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) *reinterpret_cast<float4 *>(o_ptr + j * row_step + cb * 32) = y[j];
