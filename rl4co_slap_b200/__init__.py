@@ -7,12 +7,17 @@ hand-written CUDA kernels behind a C ABI (include/rl4co_slap_b200.h).  No CPU fa
 from . import _lib  # noqa: F401
 from .baselines import (RolloutBaseline, SharedBaseline, global_reward_mean, reinforce_loss,  # noqa: F401
                         reward_stats, shard_bounds)
+from .data import (TensorDictDataset, generate_dataset, load_npz_to_tensordict,  # noqa: F401
+                   save_tensordict_to_npz)
 from .decoding import decode_step, get_log_likelihood, random_policy, rollout  # noqa: F401
 from .envs import ENV_REGISTRY, CVRPEnv, RL4COEnvBase, SLAPEnv, TSPEnv, get_env  # noqa: F401
+from .evaluation import (AugmentationEval, GreedyEval, GreedyMultiStartAugmentEval,  # noqa: F401
+                         GreedyMultiStartEval, SamplingEval, evaluate_policy)
 from .generators import CVRPGenerator, SLAPGenerator, TSPGenerator  # noqa: F401
 from .ops import (batchify, gather_by_index, get_num_starts, get_tour_length,  # noqa: F401
                   select_start_nodes, unbatchify)
 from .policy import AttentionModelDecoder, AttentionModelPolicy, POMOPolicy  # noqa: F401
 from .tensordict_compat import TensorDict  # noqa: F401
+from .transforms import StateAugmentation, dihedral_8_augmentation  # noqa: F401
 
 __version__ = "0.1.0"

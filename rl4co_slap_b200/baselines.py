@@ -123,24 +123,76 @@ def reinforce_loss(loss_partial: torch.Tensor, group=None) -> torch.Tensor:
 
 
 class RolloutBaseline:
-    """baselines.py:162-258, the greedy-rollout consumer of the path: ``rollout`` greedy-rolls
-    a dataset shard in batches and ``mean`` is the global mean via one all-reduce."""
+    """baselines.py:162-258, the greedy-rollout consumer of the path, on device-resident datasets.
 
-    def __init__(self, policy, env, batch_size: int = 65536):
-        self.policy, self.env, self.batch_size = policy, env, batch_size
-        self.mean = None
+    Same surface as the reference (``setup`` / ``_update_policy`` / ``eval`` / ``epoch_callback`` /
+    ``rollout`` / ``wrap_dataset``); differences: the evaluation dataset is one device TensorDict sliced
+    in place (no DataLoader / host collate), rewards stay on the device, and with ``group`` (or an
+    initialised default process group) every rank rolls out its own contiguous shard of the dataset while
+    the mean and the paired t-test come from one all-reduce of three fp64 partial sums each."""
 
-    @torch.inference_mode()
-    def rollout(self, td_dataset) -> torch.Tensor:
-        """baselines.py:226-243: rewards [D_local] of greedy rollouts."""
-        D = td_dataset.batch_size[0]
+    def __init__(self, bl_alpha: float = 0.05, **kw):
+        self.bl_alpha = bl_alpha
+        self.policy = self.dataset = self.bl_vals = self.mean = None
+        self.group = kw.get("group")
+
+    def setup(self, *args, **kw):
+        self._update_policy(*args, **kw)
+
+    def _update_policy(self, policy, env, batch_size: int = 65536, device="cuda", dataset_size=None, dataset=None):
+        """baselines.py:176-189: freeze a copy of the policy and greedy-roll it over the evaluation dataset."""
+        import copy
+        self.policy = copy.deepcopy(policy).to(device)
+        if dataset is None:
+            self.dataset = env.dataset(batch_size=[dataset_size])
+        else:       # (the reference ignores a passed dataset here and keeps the old one; accept it)
+            self.dataset = dataset
+        self.bl_vals = self.rollout(self.policy, env, batch_size, device, self.dataset)
+        self.mean = global_reward_mean(self.bl_vals, self.group).item()
+
+    def eval(self, td, reward, env):
+        """baselines.py:191-200: greedy rollout of the frozen policy on the batch."""
+        with torch.inference_mode():
+            reward = self.policy(td, env)["reward"]
+        return reward, 0
+
+    def epoch_callback(self, policy, env, batch_size: int = 65536, device="cuda", epoch=None, dataset_size=None):
+        """baselines.py:202-224: challenge the baseline; replace it if the candidate is better with
+        p < bl_alpha in a one-sided paired t-test.  Returns (candidate_mean, t, p_val, updated)."""
+        candidate_vals = self.rollout(policy, env, batch_size, device)
+        candidate_mean = global_reward_mean(candidate_vals, self.group).item()
+        t = p_val = None
+        updated = False
+        if candidate_mean - self.mean > 0:
+            # ttest_rel(-candidate, -baseline): d = baseline - candidate, t must be negative
+            t, n = paired_ttest_finalize(paired_ttest_partials(self.bl_vals, candidate_vals), self.group)
+            from scipy.stats import t as student_t
+            p_val = float(student_t.sf(abs(t), n - 1))          # = two-sided p / 2
+            assert t < 0, "T-statistic should be negative"
+            if p_val < self.bl_alpha:
+                self._update_policy(policy, env, batch_size, device, dataset_size)
+                updated = True
+        return candidate_mean, t, p_val, updated
+
+    def rollout(self, policy, env, batch_size: int = 65536, device="cuda", dataset=None) -> torch.Tensor:
+        """baselines.py:226-243: rewards [D_local] of greedy rollouts, in dataset order, on the device."""
+        from .data import TensorDictDataset
+        dataset = self.dataset if dataset is None else dataset
+        if not isinstance(dataset, TensorDictDataset):
+            dataset = TensorDictDataset(dataset)
+        policy.eval()
+        policy = policy.to(device)
         out = []
-        for lo in range(0, D, self.batch_size):
-            td = self.env.reset(td_dataset[lo:min(D, lo + self.batch_size)])
-            out.append(self.policy(td, self.env, decode_type="greedy")["reward"])
-        return torch.cat(out)
+        with torch.inference_mode():
+            for batch in dataset.batches(batch_size):
+                td = env.reset(batch.to(device))
+                out.append(policy(td, env, decode_type="greedy")["reward"])
+        return torch.cat(out, 0)
 
-    def setup(self, td_dataset, group=None):
-        rewards = self.rollout(td_dataset)
-        self.mean = global_reward_mean(rewards, group)
-        return rewards
+    def wrap_dataset(self, dataset, env, batch_size: int = 65536, device="cuda", **kw):
+        """baselines.py:245-258: attach the frozen policy's greedy rewards as ``"extra"``."""
+        from .data import TensorDictDataset
+        if not isinstance(dataset, TensorDictDataset):
+            dataset = TensorDictDataset(dataset)
+        rewards = self.rollout(self.policy, env, batch_size, device, dataset=dataset).detach()
+        return dataset.add_key("extra", rewards)

@@ -94,6 +94,35 @@ class RL4COEnvBase:
             self.check_solution_validity(td, actions)
         return self._get_reward(td, actions)
 
+    def dataset(self, batch_size=[], phase: str = "train", filename: Optional[str] = None):
+        """base.py:236-273: a dataset of observations, loaded from ``filename`` / ``{phase}_file`` when one is
+        set (missing file -> generated, as in the reference), else generated - here straight on the env's device."""
+        from .data import TensorDictDataset, generate_dataset
+        f = getattr(self, f"{phase}_file", None) if filename is None else filename
+        if isinstance(batch_size, (list, tuple, torch.Size)):
+            n = int(batch_size[0]) if len(batch_size) else None
+        else:
+            n = int(batch_size)
+        td = None
+        if f is not None:
+            try:
+                td = self.load_data(f, batch_size)
+                if self.device is not None and self.device.type == "cuda":
+                    from .data import to_device
+                    td = to_device(td, self.device)
+            except FileNotFoundError:
+                td = None
+        if td is None:
+            if n is None:
+                raise ValueError("dataset(): batch_size=[n] is needed to generate a dataset")
+            td = generate_dataset(self, n)
+        return TensorDictDataset(td)
+
+    def load_data(self, fpath, batch_size=[]):
+        """base.py:270-273 / cvrp/env.py:192-199."""
+        from .data import load_data
+        return load_data(self.name, fpath)
+
     def get_num_starts(self, td):
         return get_num_starts(td, self.name)
 
