@@ -167,6 +167,9 @@ int rl4co_linear_tc_ex(int64_t M, int32_t n_out, int32_t n_in, const float *x, c
  * no mask, fp32): replaces the F.scaled_dot_product_attention call of MultiHeadAttention
  * (models/nn/attention.py:65-135).  qkv [B,N,3,8,16] = the fused Wqkv output, out [B,N,128]. */
 int rl4co_encoder_attention(int64_t B, int32_t N, const float *qkv, float *out, rl4co_stream_t stream);
+/* Same contract with S = Q K^T on the tensor cores (tcgen05.mma kind::tf32, 3-term split, scores in TMEM);
+ * softmax and P V stay fp32 on the CUDA cores.  The kernel the encoder uses; the one above is the SIMT cross-check. */
+int rl4co_encoder_attention_tc(int64_t B, int32_t N, const float *qkv, float *out, rl4co_stream_t stream);
 
 /* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */
 int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,

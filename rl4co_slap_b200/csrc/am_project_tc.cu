@@ -21,9 +21,11 @@
 // row-major [t][m][128].
 #include "common.cuh"
 #include "rollout_util.cuh"
+#include "tc_util.cuh"
 
 namespace rl4co {
 namespace tc {
+using namespace tcu;
 
 constexpr int E = RL4CO_EMBED_DIM;       // K = 128
 constexpr int BM = 128;                  // rows per tile (= TMEM lanes)
@@ -43,76 +45,6 @@ constexpr uint32_t kTmemCols = TB * BN;  // 512 columns: four 128-column accumul
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = F32 (bits 4-5 = 1),
 // A = B = TF32 (bits 7-9, 10-12 = 2), both K-major, N/8 at bit 17, M/16 at bit 24
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((BN >> 3) << 17) | ((BM >> 4) << 24);
-
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
-// byte offset of 16-byte chunk `c` of row `r` inside a [rows][128 B] image with the 128B swizzle
-// (Swizzle<3,4,3>: chunk index xor row mod 8); images are 1024-byte aligned
-__host__ __device__ __forceinline__ uint32_t swz(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
-
-// shared-memory matrix descriptor (SmemDescriptor): K-major, SWIZZLE_128B, 8-row groups 1024 B apart
-__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
-    return (uint64_t)((saddr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-// descriptors travel as their low words (start address in 16-byte units | LBO); the high word is one constant.
-// Everything the instruction reads must sit in uniform registers: keep the operands provably warp-uniform
-// (shared-window addresses, constants, a shuffled TMEM base) or the compiler wraps every MMA in an
-// elect / broadcast loop that costs more issue time than the MMA takes to execute.
-__device__ __forceinline__ bool elect_one() {                  // one lane of a converged warp
-    uint32_t pred;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "elect.sync _|P1, 0xffffffff;\n\t"
-        "selp.u32 %0, 1, 0, P1;\n\t"
-        "}\n"
-        : "=r"(pred));
-    return pred != 0;
-}
-constexpr uint32_t kDescHi = (uint32_t)((64ull << 32 | 1ull << 46 | 2ull << 61) >> 32);
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint32_t a_lo32, uint32_t b_lo32, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        ".reg .b64 da, db;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "mov.b64 da, {%1, %5};\n\t"
-        "mov.b64 db, {%2, %5};\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "r"(a_lo32), "r"(b_lo32), "r"(kIdesc), "r"(accumulate), "r"(kDescHi)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t *bar) {    // arrives when all prior MMAs are done
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// bounded wait: a pipeline bug must end in a trap, not in a hung GPU
-__device__ __forceinline__ void mbar_wait_bounded(uint64_t *bar, unsigned parity) {
-    const uint32_t addr = smem_u32(bar);
-    const long long t0 = clock64();
-    while (clock64() - t0 < 4000000000ll) {                     // ~2 s
-        uint32_t ok;
-        asm volatile(
-            "{\n\t"
-            ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t"
-            "}\n"
-            : "=r"(ok)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (ok) return;
-    }
-    __trap();
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // weights -> the shared-memory image of one table: [hi|lo][kb][row j = output feature][32 k], swizzled
 __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const float *__restrict__ W, int64_t ldw,
@@ -225,10 +157,10 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                         if (elect_one()) {
 #pragma unroll
                             for (int k8 = 0; k8 < KB / 8; ++k8) {   // K = 8 tf32 = 32 bytes = 2 address units per instruction
-                                umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, (unsigned)((kb | k8) != 0 || kc != 0));
+                                umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, kIdesc, (unsigned)((kb | k8) != 0 || kc != 0));
 #ifndef TC_EXP_ONE_MMA
-                                umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, 1u);
-                                umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, 1u);
+                                umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, kIdesc, 1u);
+                                umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, kIdesc, 1u);
 #endif
                             }
                             umma_commit(&a_empty[stage]);           // smem slot free once these MMAs have read it

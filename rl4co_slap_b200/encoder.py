@@ -147,11 +147,13 @@ class _SelfAttention(nn.Module):
         qkv = linear128(x, self.Wqkv)
         if (qkv.is_cuda and not torch.is_grad_enabled() and qkv.dtype == torch.float32 and E == 128
                 and self.num_heads == 8 and N <= 128 and getattr(self, "fused_attention", True)):
-            # fp32 attention kernel of the library for the path's graph sizes (csrc/encoder_attention.cu)
+            # fp32 attention kernels of the library for the path's graph sizes: Q K^T on the tensor cores
+            # (csrc/encoder_attention_tc.cu) or all-SIMT (csrc/encoder_attention.cu, the cross-check)
             from . import _lib
             qkv = qkv.contiguous()
             o = torch.empty(B, N, E, dtype=torch.float32, device=x.device)
-            _lib.call("rl4co_encoder_attention", B, N, _lib.ptr(qkv), _lib.ptr(o), _lib.stream_ptr(x.device))
+            fn = "rl4co_encoder_attention_tc" if getattr(self, "tensor_core", True) else "rl4co_encoder_attention"
+            _lib.call(fn, B, N, _lib.ptr(qkv), _lib.ptr(o), _lib.stream_ptr(x.device))
             return o
         qkv = qkv.view(B, N, 3, self.num_heads, E // self.num_heads)
         q, k, v = qkv.permute(2, 0, 3, 1, 4).unbind(0)

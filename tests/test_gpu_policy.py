@@ -366,6 +366,22 @@ def test_encoder_fused_skip_batchnorm_epilogue(name, dev):
     assert (h_fused - h_pt).abs().max().item() <= 2e-5 * scale, ((h_fused - h_pt).abs().max().item(), scale)
 
 
+@pytest.mark.parametrize("B,N,amp", ((3, 100, 1.0), (7, 5, 1.0), (300, 50, 3.0), (150, 128, 1.0), (500, 101, 2.0), (1, 1, 1.0)))
+def test_encoder_attention_kernels_match_fp64(B, N, amp, dev):
+    """rl4co_encoder_attention_tc (Q K^T on tcgen05, 3xTF32) and rl4co_encoder_attention (SIMT) vs an fp64 softmax
+    attention on the fused Wqkv layout [B, N, 3, 8, 16] (nn/attention.py:81-126, no mask)"""
+    from rl4co_slap_b200 import _lib
+    torch.manual_seed(B * 131 + N)
+    qkv = torch.randn(B, N, 384, device=dev) * amp
+    q, k, v = qkv.double().view(B, N, 3, 8, 16).permute(2, 0, 3, 1, 4).unbind(0)
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.25, -1) @ v).transpose(1, 2).reshape(B, N, 128)
+    for fn in ("rl4co_encoder_attention_tc", "rl4co_encoder_attention"):
+        out = torch.full((B, N, 128), float("nan"), device=dev)
+        _lib.call(fn, B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev))
+        err = (out.double() - ref).abs().max().item()
+        assert err <= 1e-5 * max(1.0, amp ** 3) * max(1.0, ref.abs().max().item()), (fn, err)
+
+
 @pytest.mark.parametrize("M,n_out,n_in,relu", ((257, 128, 512, False), (1000, 512, 128, True), (130, 256, 256, True)))
 def test_linear_tc_k_chunks_bias_relu(M, n_out, n_in, relu, dev):
     """rl4co_linear_tc: 128-wide K chunks accumulated in TMEM, bias / ReLU in the single epilogue"""
