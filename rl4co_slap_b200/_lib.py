@@ -68,6 +68,7 @@ _SIGNATURES = {
     "rl4co_linear_tc_ex": ([_i64, _i32, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_encoder_attention": ([_i64, _i32, _p, _p, _p], C.c_int),
     "rl4co_encoder_attention_tc": ([_i64, _i32, _p, _p, _p], C.c_int),
+    "rl4co_set_attention_impl": ([_i32], C.c_int),
     "rl4co_am_graph_context": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_am_rollout": ([C.POINTER(AmRolloutArgs), _p], C.c_int),
     "rl4co_set_rollout_impl": ([C.c_int], C.c_int),

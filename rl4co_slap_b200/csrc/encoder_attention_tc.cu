@@ -253,7 +253,319 @@ encoder_attention_tc_kernel(int64_t B, int N, const float *__restrict__ qkv, flo
 
 }  // namespace enctc
 
-int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, cudaStream_t stream) {
+
+// ============================================================================================
+// Both GEMMs on the tensor cores (N <= 112): S = Q K^T as above with N = 112 key columns, then the
+// consumers turn their score row into P = 2^(s - max) IN TMEM (hi / lo TF32 images written back with
+// tcgen05.st: P_hi over the scores, P_lo beside them) and O = P V is a second tcgen05.mma with A = P
+// read from TMEM and B = V^T (hi / lo, K-major swizzled rows of 32 keys) from shared memory:
+// 14 k-steps x 3 terms of M128 N16 K8.  The CUDA cores keep only max / exp2 / sum / split and the
+// final O / l.  TMEM per buffer (256 columns, two buffers): [0,112) S then P_hi, [112,224) P_lo,
+// [224,240) O.  Two consumer groups of four warps, one per buffer; the MMA warp interleaves
+// QK(i) with PV(i-1).
+namespace enctc2 {
+using namespace tcu;
+using enctc::ex2f;
+
+constexpr int H = 8, D = 16, E = 128, NK = 112;         // key columns of the score tile (multiple of 16)
+constexpr int TILE_BYTES = 128 * 128;                   // Q / K operand image: 128 rows x 128 B (64 B used)
+constexpr int VT_TILE = 16 * 128;                       // V^T k-block: 16 dims x 32 keys
+constexpr int VT_BYTES = 4 * VT_TILE;                   // 8 KB per image (hi or lo)
+constexpr int QK_STAGE_BYTES = 4 * TILE_BYTES;          // Qhi Qlo Khi Klo = 64 KB, free again once the scores are in TMEM
+constexpr int QK_STAGES = 2;
+constexpr int VT_SLOT_BYTES = 2 * VT_BYTES;             // VThi VTlo = 16 KB, needed until O = P V is complete
+constexpr int VT_SLOTS = 4;
+constexpr int kProducerWarps = 4, kConsumerWarps = 8;
+constexpr int kThreads = (1 + kProducerWarps + kConsumerWarps) * 32;       // 416
+constexpr int SMEM_BYTES = 1024 + QK_STAGES * QK_STAGE_BYTES + VT_SLOTS * VT_SLOT_BYTES + 256;
+constexpr uint32_t kIdescS = make_idesc_tf32(128, NK);
+constexpr uint32_t kIdescO = make_idesc_tf32(128, D);
+constexpr int COL_PLO = NK, COL_O = 2 * NK, BUF_COLS = 256;
+
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo32, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 db;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], db, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHi)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, float *__restrict__ out) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char *sVT = smem + QK_STAGES * QK_STAGE_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sVT + VT_SLOTS * VT_SLOT_BYTES);
+    uint64_t *in_full = bars, *s_full = bars + 2, *p_full = bars + 4, *o_full = bars + 6, *buf_free = bars + 8;
+    uint64_t *qk_empty = bars + 10, *vt_free = bars + 12;       // [2], [4]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t n_inst = blockIdx.x < B ? (B - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t n_units = n_inst * H;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&in_full[s], kProducerWarps);     // inputs of a unit staged
+            mbar_init(&s_full[s], 1);                   // scores complete (commit)
+            mbar_init(&p_full[s], 4);                   // P written by the buffer's four consumer warps
+            mbar_init(&o_full[s], 1);                   // O complete (commit)
+            mbar_init(&buf_free[s], 4);                 // O read back: the TMEM buffer may be overwritten
+            mbar_init(&qk_empty[s], 1);                 // Q / K stage read by the score MMAs (commit)
+        }
+        for (int s = 0; s < VT_SLOTS; ++s) mbar_init(&vt_free[s], 1);   // V^T slot read by the P V MMAs (commit)
+        fence_barrier_init();
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================================= MMA issue: QK(i), then PV(i - 1)
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
+        for (int64_t i = 0; i <= n_units; ++i) {
+            if (i < n_units) {
+                const int b = (int)(i & 1);
+                const unsigned ph = (unsigned)((i >> 1) & 1);
+                mbar_wait_bounded(&in_full[b], ph);
+                mbar_wait_bounded(&buf_free[b], ph ^ 1u);
+                tc_fence_after();
+                const uint32_t q_hi = d0 + (uint32_t)((b * QK_STAGE_BYTES) >> 4), q_lo = q_hi + (TILE_BYTES >> 4);
+                const uint32_t k_hi = q_hi + 2 * (TILE_BYTES >> 4), k_lo = q_hi + 3 * (TILE_BYTES >> 4);
+                const uint32_t d = tmem_u + (uint32_t)(b * BUF_COLS);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k8 = 0; k8 < D / 8; ++k8) {
+                        umma_tf32(d, q_lo + 2 * k8, k_hi + 2 * k8, kIdescS, (unsigned)(k8 != 0));
+                        umma_tf32(d, q_hi + 2 * k8, k_lo + 2 * k8, kIdescS, 1u);
+                        umma_tf32(d, q_hi + 2 * k8, k_hi + 2 * k8, kIdescS, 1u);
+                    }
+                    umma_commit(&qk_empty[b]);
+                    umma_commit(&s_full[b]);
+                }
+                __syncwarp();
+            }
+            if (i >= 1) {
+                const int64_t u = i - 1;
+                const int b = (int)(u & 1);
+                mbar_wait_bounded(&p_full[b], (unsigned)((u >> 1) & 1));
+                tc_fence_after();
+                const int vs = (int)(u & 3);
+                const uint32_t vt_hi = d0 + (uint32_t)((QK_STAGES * QK_STAGE_BYTES + vs * VT_SLOT_BYTES) >> 4);
+                const uint32_t vt_lo = vt_hi + (VT_BYTES >> 4);
+                const uint32_t p_hi = tmem_u + (uint32_t)(b * BUF_COLS), p_lo = p_hi + COL_PLO;
+                const uint32_t o = tmem_u + (uint32_t)(b * BUF_COLS + COL_O);
+                if (elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < NK / 8; ++ks) {       // 14 k-steps of 8 keys
+                        const uint32_t voff = (uint32_t)(((ks >> 2) * VT_TILE + (ks & 3) * 32) >> 4);
+                        umma_tf32_ts(o, p_lo + 8 * ks, vt_hi + voff, kIdescO, (unsigned)(ks != 0));
+                        umma_tf32_ts(o, p_hi + 8 * ks, vt_lo + voff, kIdescO, 1u);
+                        umma_tf32_ts(o, p_hi + 8 * ks, vt_hi + voff, kIdescO, 1u);
+                    }
+                    umma_commit(&vt_free[vs]);
+                    umma_commit(&o_full[b]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp <= kProducerWarps) {
+        // ================================================= producers: thread = node row
+        const int row = tid - 32;                               // 0..127
+        const float scale = 0.25f * 1.4426950408889634f;        // 1/sqrt(16) * log2(e), folded into Q
+        const uint32_t r7 = (uint32_t)(row & 7);
+        {                                                       // zero what is never written: pad rows, all of V^T
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            if (row >= N)
+                for (int s = 0; s < QK_STAGES; ++s)
+                    for (int img = 0; img < 4; ++img)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            *reinterpret_cast<uint4 *>(smem + s * QK_STAGE_BYTES + img * TILE_BYTES + swz(row, c)) = z;
+            for (int off = row * 16; off < VT_SLOTS * VT_SLOT_BYTES; off += 128 * 16)
+                *reinterpret_cast<uint4 *>(sVT + off) = z;
+            asm volatile("bar.sync 2, 128;" ::: "memory");      // the four producer warps: zeros before any key write
+        }
+        // V^T element (key j = row, dim d): k-block j >> 5, row d, 16-byte chunk ((j & 31) >> 2) ^ (d & 7), word j & 3
+        const uint32_t vt_base = (uint32_t)((row >> 5) * VT_TILE + (row & 3) * 4);
+        const uint32_t vt_chunk = (uint32_t)((row & 31) >> 2);
+        for (int64_t i = 0; i < n_units; ++i) {
+            const int st_i = (int)(i & 1), h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            float4 q[4], k[4], v[4];
+            if (row < N) {                                      // loads first: they fly while we wait for the stage
+                const float4 *p = reinterpret_cast<const float4 *>(qkv + (b * N + row) * (3 * E) + h * D);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { q[c] = __ldg(p + c); k[c] = __ldg(p + E / 4 + c); v[c] = __ldg(p + 2 * E / 4 + c); }
+            }
+            const int vs = (int)(i & 3);
+            mbar_wait_bounded(&qk_empty[st_i], (unsigned)((i >> 1) & 1) ^ 1u);  // scores of unit i - 2 are in TMEM
+            mbar_wait_bounded(&vt_free[vs], (unsigned)((i >> 2) & 1) ^ 1u);     // P V of unit i - 4 is complete
+            if (row < N) {
+                unsigned char *st = smem + st_i * QK_STAGE_BYTES;
+                unsigned char *vt = sVT + vs * VT_SLOT_BYTES;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t off = (uint32_t)row * 128u + (((uint32_t)c ^ r7) << 4);
+                    const float4 a = make_float4(q[c].x * scale, q[c].y * scale, q[c].z * scale, q[c].w * scale);
+                    uint4 hi, lo;
+                    hi.x = to_tf32(a.x); hi.y = to_tf32(a.y); hi.z = to_tf32(a.z); hi.w = to_tf32(a.w);
+                    lo.x = to_tf32(a.x - __uint_as_float(hi.x)); lo.y = to_tf32(a.y - __uint_as_float(hi.y));
+                    lo.z = to_tf32(a.z - __uint_as_float(hi.z)); lo.w = to_tf32(a.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + TILE_BYTES + off) = lo;
+                    const float4 kk = k[c];
+                    hi.x = to_tf32(kk.x); hi.y = to_tf32(kk.y); hi.z = to_tf32(kk.z); hi.w = to_tf32(kk.w);
+                    lo.x = to_tf32(kk.x - __uint_as_float(hi.x)); lo.y = to_tf32(kk.y - __uint_as_float(hi.y));
+                    lo.z = to_tf32(kk.z - __uint_as_float(hi.z)); lo.w = to_tf32(kk.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + 2 * TILE_BYTES + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + 3 * TILE_BYTES + off) = lo;
+                    const float vv[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {               // dim d = 4 c + e of key `row`, transposed
+                        const int d = 4 * c + e;
+                        const uint32_t o2 = vt_base + (uint32_t)d * 128u + ((vt_chunk ^ (uint32_t)(d & 7)) << 4);
+                        const uint32_t vh = to_tf32(vv[e]);
+                        *reinterpret_cast<uint32_t *>(vt + o2) = vh;
+                        *reinterpret_cast<uint32_t *>(vt + VT_BYTES + o2) = to_tf32(vv[e] - __uint_as_float(vh));
+                    }
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&in_full[st_i]);
+        }
+    } else {
+        // ================================================= consumers: thread = query row = TMEM lane
+        const int cw = warp - (1 + kProducerWarps);             // 0..7
+        const int buf = cw >> 2, quarter = warp & 3;
+        const int row = 32 * quarter + lane;
+        const uint32_t t0 = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)(buf * BUF_COLS);
+        const int n_full = N >> 4, tail = N & 15;
+        for (int64_t i = buf; i < n_units; i += 2) {
+            const int h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            const unsigned ph = (unsigned)((i >> 1) & 1);
+            mbar_wait_bounded(&s_full[buf], ph);
+            tc_fence_after();
+            // The loops over 16-column chunks stay rolled (one body for full chunks, one predicated body for
+            // the chunk that holds column N - 1): unrolled per chunk, this code no longer fits the instruction
+            // cache next to the other roles.  P is split by truncation (hi = p & ~0x1fff, lo = p - hi, exact);
+            // p is in [0, 1], so the round-to-nearest conversion's overflow handling buys nothing here.
+            uint32_t sv[16];
+            float m = -INFINITY;                                // pass 1: row maximum over the N real keys
+#pragma unroll 1
+            for (int c = 0; c < n_full; ++c) {
+                tmem_ld16(t0 + c * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) m = fmaxf(m, __uint_as_float(sv[j]));
+            }
+            if (tail) {
+                tmem_ld16(t0 + n_full * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (j < tail) m = fmaxf(m, __uint_as_float(sv[j]));
+            }
+            float l = 0.f;                                      // pass 2: P = 2^(s - m) as hi / lo TF32, in place
+            uint32_t hi[16], lo[16];
+#pragma unroll 1
+            for (int c = 0; c < n_full; ++c) {
+                tmem_ld16(t0 + c * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float p = ex2f(__uint_as_float(sv[j]) - m);
+                    l += p;
+                    hi[j] = __float_as_uint(p) & 0xffffe000u;
+                    lo[j] = __float_as_uint(p - __uint_as_float(hi[j]));
+                }
+                tmem_st16(t0 + c * 16, hi);
+                tmem_st16(t0 + COL_PLO + c * 16, lo);
+            }
+            int c_next = n_full;
+            if (tail) {
+                tmem_ld16(t0 + n_full * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float p = j < tail ? ex2f(__uint_as_float(sv[j]) - m) : 0.f;
+                    l += p;
+                    hi[j] = __float_as_uint(p) & 0xffffe000u;
+                    lo[j] = __float_as_uint(p - __uint_as_float(hi[j]));
+                }
+                tmem_st16(t0 + n_full * 16, hi);
+                tmem_st16(t0 + COL_PLO + n_full * 16, lo);
+                c_next = n_full + 1;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) hi[j] = 0u;
+#pragma unroll 1
+            for (int c = c_next; c < NK / 16; ++c) {            // key columns beyond N: P = 0
+                tmem_st16(t0 + c * 16, hi);
+                tmem_st16(t0 + COL_PLO + c * 16, hi);
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[buf]);
+            // O = P V arrives from the tensor core; normalise and store this row's 16 outputs
+            mbar_wait_bounded(&o_full[buf], ph);
+            tc_fence_after();
+            tmem_ld16(t0 + COL_O, sv);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&buf_free[buf]);
+            if (row < N) {
+                const float inv = 1.f / l;
+                float4 *dst = reinterpret_cast<float4 *>(out + (b * N + row) * E + h * D);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    dst[c] = make_float4(__uint_as_float(sv[4 * c]) * inv, __uint_as_float(sv[4 * c + 1]) * inv,
+                                         __uint_as_float(sv[4 * c + 2]) * inv, __uint_as_float(sv[4 * c + 3]) * inv);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace enctc2
+
+int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, int impl, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
         int dev = 0;
@@ -261,14 +573,25 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    cudaError_t e = cudaFuncSetAttribute(enctc::encoder_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         enctc::SMEM_BYTES);
+    const int64_t grid = B < sm_count ? B : sm_count;
+    const bool both = impl == 2 || (impl == 0 && N <= enctc2::NK);     // P V on the tensor cores too
+    if (both && N > enctc2::NK) {
+        set_error("encoder_attention(tc): the two-GEMM kernel needs N <= %d, got %d", enctc2::NK, N);
+        return 1;
+    }
+    const int smem = both ? enctc2::SMEM_BYTES : enctc::SMEM_BYTES;
+    cudaError_t e = both ? cudaFuncSetAttribute(enctc2::encoder_attention_tc2_kernel,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
+                         : cudaFuncSetAttribute(enctc::encoder_attention_tc_kernel,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
-        set_error("encoder_attention(tc): cannot reserve %d B of shared memory: %s", enctc::SMEM_BYTES, cudaGetErrorString(e));
+        set_error("encoder_attention(tc): cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
         return 2;
     }
-    const int64_t grid = B < sm_count ? B : sm_count;
-    enctc::encoder_attention_tc_kernel<<<(unsigned)grid, enctc::kThreads, enctc::SMEM_BYTES, stream>>>(B, N, qkv, out);
+    if (both)
+        enctc2::encoder_attention_tc2_kernel<<<(unsigned)grid, enctc2::kThreads, smem, stream>>>(B, N, qkv, out);
+    else
+        enctc::encoder_attention_tc_kernel<<<(unsigned)grid, enctc::kThreads, smem, stream>>>(B, N, qkv, out);
     RL4CO_CHECK_LAUNCH("encoder_attention(tc)");
     return 0;
 }
@@ -277,11 +600,19 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
 
 using namespace rl4co;
 
+static int g_attention_impl = 0;    // 0 auto (two-GEMM kernel for N <= 112), 1 Q K^T only, 2 two-GEMM kernel
+
+extern "C" int rl4co_set_attention_impl(int32_t impl) {
+    RL4CO_REQUIRE(impl >= 0 && impl <= 2, "set_attention_impl: 0 auto, 1 scores on tensor cores, 2 both GEMMs, got %d", impl);
+    g_attention_impl = impl;
+    return 0;
+}
+
 extern "C" int rl4co_encoder_attention_tc(int64_t B, int32_t N, const float *qkv, float *out, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N >= 1 && N <= 128, "encoder_attention_tc: B=%lld N=%d (N <= 128)", (long long)B, N);
     if (B == 0) return 0;
     RL4CO_REQUIRE(qkv && out, "encoder_attention_tc: null pointer");
     RL4CO_REQUIRE(((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0,
                   "encoder_attention_tc: pointers must be 16-byte aligned");
-    return launch_encoder_attention_tc(B, N, qkv, out, (cudaStream_t)stream);
+    return launch_encoder_attention_tc(B, N, qkv, out, g_attention_impl, (cudaStream_t)stream);
 }

@@ -368,18 +368,29 @@ def test_encoder_fused_skip_batchnorm_epilogue(name, dev):
 
 @pytest.mark.parametrize("B,N,amp", ((3, 100, 1.0), (7, 5, 1.0), (300, 50, 3.0), (150, 128, 1.0), (500, 101, 2.0), (1, 1, 1.0)))
 def test_encoder_attention_kernels_match_fp64(B, N, amp, dev):
-    """rl4co_encoder_attention_tc (Q K^T on tcgen05, 3xTF32) and rl4co_encoder_attention (SIMT) vs an fp64 softmax
+    """rl4co_encoder_attention_tc (both kernels: Q K^T / Q K^T + P V on tcgen05, 3xTF32) and rl4co_encoder_attention (SIMT) vs an fp64 softmax
     attention on the fused Wqkv layout [B, N, 3, 8, 16] (nn/attention.py:81-126, no mask)"""
     from rl4co_slap_b200 import _lib
     torch.manual_seed(B * 131 + N)
     qkv = torch.randn(B, N, 384, device=dev) * amp
     q, k, v = qkv.double().view(B, N, 3, 8, 16).permute(2, 0, 3, 1, 4).unbind(0)
     ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.25, -1) @ v).transpose(1, 2).reshape(B, N, 128)
-    for fn in ("rl4co_encoder_attention_tc", "rl4co_encoder_attention"):
-        out = torch.full((B, N, 128), float("nan"), device=dev)
-        _lib.call(fn, B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev))
-        err = (out.double() - ref).abs().max().item()
-        assert err <= 1e-5 * max(1.0, amp ** 3) * max(1.0, ref.abs().max().item()), (fn, err)
+    variants = [("rl4co_encoder_attention_tc", 1), ("rl4co_encoder_attention", 0)]
+    if N <= 112:
+        variants.append(("rl4co_encoder_attention_tc", 2))     # P V on the tensor cores too (P in TMEM)
+    try:
+        for fn, impl in variants:
+            _lib.call("rl4co_set_attention_impl", impl)
+            out = torch.full((B, N, 128), float("nan"), device=dev)
+            _lib.call(fn, B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev))
+            err = (out.double() - ref).abs().max().item()
+            assert err <= 1e-5 * max(1.0, amp ** 3) * max(1.0, ref.abs().max().item()), (fn, impl, err)
+        if N > 112:
+            _lib.call("rl4co_set_attention_impl", 2)
+            with pytest.raises(RuntimeError, match="N <= 112"):
+                _lib.call("rl4co_encoder_attention_tc", B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev))
+    finally:
+        _lib.call("rl4co_set_attention_impl", 0)
 
 
 @pytest.mark.parametrize("M,n_out,n_in,relu", ((257, 128, 512, False), (1000, 512, 128, True), (130, 256, 256, True)))
