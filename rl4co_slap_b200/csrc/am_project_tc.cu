@@ -216,9 +216,20 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                     const int r = r0 + 32 * i;
                     const float4 a4 = v[kb][i];
                     uint4 hi, lo;
+#ifdef TC_SPLIT_RNA
                     hi.x = to_tf32(a4.x); hi.y = to_tf32(a4.y); hi.z = to_tf32(a4.z); hi.w = to_tf32(a4.w);
                     lo.x = to_tf32(a4.x - __uint_as_float(hi.x)); lo.y = to_tf32(a4.y - __uint_as_float(hi.y));
                     lo.z = to_tf32(a4.z - __uint_as_float(hi.z)); lo.w = to_tf32(a4.w - __uint_as_float(hi.w));
+#else
+                    // split by truncation: hi = top 19 bits, lo = a - hi (exact, <= 13 significant bits, of
+                    // which the MMA reads the leading 11).  Two ALU instructions per element instead of the
+                    // eight that two round-to-nearest conversions (add, overflow test, select, mask) take;
+                    // the representation error goes from 2^-23 to 2^-21 of |a|, far inside the budget.
+                    hi.x = __float_as_uint(a4.x) & 0xffffe000u; hi.y = __float_as_uint(a4.y) & 0xffffe000u;
+                    hi.z = __float_as_uint(a4.z) & 0xffffe000u; hi.w = __float_as_uint(a4.w) & 0xffffe000u;
+                    lo.x = __float_as_uint(a4.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(a4.y - __uint_as_float(hi.y));
+                    lo.z = __float_as_uint(a4.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(a4.w - __uint_as_float(hi.w));
+#endif
                     *reinterpret_cast<uint4 *>(hi_img + swz(r, c)) = hi;
                     *reinterpret_cast<uint4 *>(lo_img + swz(r, c)) = lo;
                 }
