@@ -248,7 +248,7 @@ def run_ours(args):
                 host_reward.copy_(out["reward"], non_blocking=True)
                 torch.cuda.current_stream().synchronize()
 
-            ms_e2e = timed(e2e_step, args.steps, args.warmup)
+            ms_e2e = timed(e2e_step, args.steps, args.warmup, region=args.profile_e2e)
             e2e = {"value": B * world / (ms_e2e * 1e-3), "unit": "rollouts/s",
                    "h2d_bytes_per_step": host_locs.numel() * 4, "d2h_bytes_per_step": host_reward.numel() * 4,
                    "ms_per_step": ms_e2e, "includes": "H2D locs + fp32 encoder (PyTorch modules; linears, skip+BN and attention on library kernels) + K3 + K2 + D2H rewards"}
@@ -314,6 +314,8 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=4, help="timed host-side passes of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile-e2e", action="store_true",
+                    help="cudaProfilerStart/Stop around the timed end-to-end steps instead")
     ap.add_argument("--profile-region", action="store_true",
                     help="cudaProfilerStart/Stop around the timed decode steps (ncu --profile-from-start off)")
     args = ap.parse_args()
