@@ -64,7 +64,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     size_t o = 0;
     L.off_c = o;    o += has_c ? (size_t)2 * N * E * 4 : 0;     // double-buffered context table
     L.off_pl = o;   o += (size_t)kWarps * PLS * 4;              // partial logits [head][node]
-    L.off_xs = o;   o += (size_t)L.xs_rows * 128 * 4;           // processed logits, one row per step (or one in all)
+    L.off_xs = o;   o += (size_t)L.xs_rows * 128 * 4;           // processed logits, one row per step (ring only)
     L.off_o = o;    o += E * 4;                                 // glimpse heads (warp private)
     L.off_ring = o; o += up16((size_t)T * kWarps * 4);          // per step, per warp: sum of exponentials
     L.off_mw = o;   o += up16((size_t)T * 4);                   // per step max logit
@@ -130,6 +130,12 @@ __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
 
 // -DRF_TRACE: thread 0 of CTA 0 writes clock64() at eight points of every step of its first
 // instance into a.logp_all (reused as a [T][8] int64 buffer by tools/trace_rollout.py)
+// -DRF_ABL=<bits>: timing-only ablations for tools/trace_rollout.py (results are wrong): 1 no head max,
+// 2 no glimpse butterfly, 4 no half-head combines, 8 no tanh, 16 no argmax reductions
+#ifndef RF_ABL
+#define RF_ABL 0
+#endif
+#define RF_SHFL_XOR(bit, v, o) ((RF_ABL & (bit)) ? (v) : __shfl_xor_sync(kFull, (v), (o)))
 #ifdef RF_TRACE
 #define RF_TRACE_AT(k) do { if (tid == 0 && blockIdx.x == 0 && it == 0) reinterpret_cast<long long *>(a.logp_all)[t * 8 + (k)] = clock64(); } while (0)
 #else
@@ -245,7 +251,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         }
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
-        for (int q = tid; q < L.xs_rows * 128; q += kThreads) sxs[q] = -INFINITY;
         if (tid < 128)
             s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
         {
@@ -385,7 +390,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
                 for (int j = 0; j < M; ++j) s[j] = hsum2(acc[j]);
 #pragma unroll
-                for (int j = 0; j < M; ++j) s[j] += __shfl_xor_sync(kFull, s[j], 16);
+                for (int j = 0; j < M; ++j) s[j] += RF_SHFL_XOR(4, s[j], 16);
             }
             float mx = -INFINITY;
 #pragma unroll
@@ -393,7 +398,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 s[j] = ((alive >> j) & 1u) ? s[j] : -INFINITY;
                 mx = fmaxf(mx, s[j]);
             }
-            mx = redux_max(mx);
+            if (!(RF_ABL & 1)) mx = redux_max(mx);
             RF_TRACE_AT(1);
             float psum = 0.f;
             u64 oacc[4] = {0ull, 0ull, 0ull, 0ull};
@@ -417,18 +422,18 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float send = b3 ? v[k] : v[k + 4], keep = b3 ? v[k + 4] : v[k];
-                    w4[k] = keep + __shfl_xor_sync(kFull, send, 8);
+                    w4[k] = keep + RF_SHFL_XOR(2, send, 8);
                 }
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     const float send = b2 ? w4[k] : w4[k + 2], keep = b2 ? w4[k + 2] : w4[k];
-                    w2[k] = keep + __shfl_xor_sync(kFull, send, 4);
+                    w2[k] = keep + RF_SHFL_XOR(2, send, 4);
                 }
                 {
                     const float send = b1 ? w2[0] : w2[1], keep = b1 ? w2[1] : w2[0];
-                    w1 = keep + __shfl_xor_sync(kFull, send, 2);
+                    w1 = keep + RF_SHFL_XOR(2, send, 2);
                 }
-                w1 += __shfl_xor_sync(kFull, w1, 1);
+                w1 += RF_SHFL_XOR(2, w1, 1);
                 // this lane now holds head dim (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0) of its half,
                 // un-normalised; 1/psum is applied to the partial logits
                 so[dim0 + (b3 ? 4 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0)] = w1;
@@ -452,7 +457,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
                 for (int j = 0; j < M; ++j) pl[j] = hsum2(acc[j]) * inv;
 #pragma unroll
-                for (int j = 0; j < M; ++j) pl[j] += __shfl_xor_sync(kFull, pl[j], 16);
+                for (int j = 0; j < M; ++j) pl[j] += RF_SHFL_XOR(4, pl[j], 16);
                 float *row = spl + warp * PLS + g;
                 if (hh == 0) {
 #pragma unroll
@@ -464,18 +469,20 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
             RF_TRACE_AT(4);
 
             float *sxrow = sxs + (xring ? t * 128 : 0);
-            // ---- warp w < M finishes nodes 16w .. 16w+15 (lane half hh sums heads hh, hh+2, hh+4, hh+6):
-            //      logit = sum_h pl_h / sqrt(E), then process_logits (utils/decoding.py:141-191)
-            if (warp < M) {
-                const float *col = spl + hh * PLS + 16 * warp + g;
-                float sum = (col[0] + col[2 * PLS]) + (col[4 * PLS] + col[6 * PLS]);
-                sum += __shfl_xor_sync(kFull, sum, 16);
-                const bool exists = (own >> warp) & 1u, feasible = (alive >> warp) & 1u;
+            // ---- warps 0-3, thread = node 32 warp + lane (= g + 16 (2 warp + hh), so its feasibility bit is in the
+            //      owner-layout mask): logit = sum_h pl_h / sqrt(E), then process_logits (utils/decoding.py:141-191)
+            if (warp < 4) {
+                const float *col = spl + tid;
+                const float sum = ((col[0] + col[2 * PLS]) + (col[4 * PLS] + col[6 * PLS])) +
+                                  ((col[PLS] + col[3 * PLS]) + (col[5 * PLS] + col[7 * PLS]));
+                const int jb = 2 * warp + hh;
+                const bool exists = (own >> jb) & 1u, feasible = (alive >> jb) & 1u;
                 float xv;
                 if (std_logits) {
                     // clip * tanh(z) = clip - 2 clip / (2^(2 log2(e) z) + 1), z = sum / sqrt(E)
                     const float e2 = ex2f(sum * (kInvSqrtE * 2.f * kLog2e));
                     xv = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
+                    if (RF_ABL & 8) xv = sum;
                     if (exists && sum != sum) status |= RL4CO_ST_NAN_LOGITS;
                     xv = feasible ? xv : -INFINITY;
                 } else {
@@ -485,7 +492,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                     xv = __fdiv_rn(xv, a.temperature);
                     xv = (exists && (feasible || !a.mask_logits)) ? xv : -INFINITY;
                 }
-                if (hh == 0) sxrow[16 * warp + g] = xv;
+                sxrow[tid] = xv;
             }
             RF_TRACE_AT(5);
             __syncthreads();
@@ -496,13 +503,18 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 const float4 xv = *reinterpret_cast<const float4 *>(sxrow + 4 * lane);
                 x[0] = xv.x; x[1] = xv.y; x[2] = xv.z; x[3] = xv.w;
             }
-            const float gm = redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
+            const float gm = (RF_ABL & 16) ? x[0] : redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
             // ---- selection (utils/decoding.py:371-397,410-499)
             int act;
-            if (a.mode == RL4CO_MODE_GREEDY) {
+            if (RF_ABL & 16) {
+                act = t + (x[0] > 1e30f ? 1 : 0);
+            } else if (a.mode == RL4CO_MODE_GREEDY) {
                 // argmax, lowest index on ties (the log-softmax shift is common to all nodes)
-                const unsigned cand = x[0] == gm ? 4u * lane : x[1] == gm ? 4u * lane + 1u
-                                    : x[2] == gm ? 4u * lane + 2u : x[3] == gm ? 4u * lane + 3u : 0x7fffffffu;
+                unsigned cand = 0x7fffffffu;
+                cand = x[3] == gm ? 4u * lane + 3u : cand;
+                cand = x[2] == gm ? 4u * lane + 2u : cand;
+                cand = x[1] == gm ? 4u * lane + 1u : cand;
+                cand = x[0] == gm ? 4u * lane : cand;
                 const unsigned win = redux_min_u32(cand);
                 act = win < (unsigned)N ? (int)win : 0;
             } else if (a.mode == RL4CO_MODE_EVALUATE) {

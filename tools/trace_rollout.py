@@ -12,9 +12,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 TRACE_LIB = os.path.join(ROOT, "tools", "_trace", "librl4co_trace.so")
 
+ABL = os.environ.get("RF_ABL", "0")          # timing-only ablation bits (csrc/am_rollout_rf.cu)
+if ABL != "0":
+    TRACE_LIB = os.path.join(ROOT, "tools", "_trace", f"abl{ABL}", "librl4co_trace.so")
 if len(sys.argv) > 1 and sys.argv[1] == "build":
     from rl4co_slap_b200 import build
-    print(build.build(extra_flags=["-DRF_TRACE"], lib=TRACE_LIB, obj_dir=os.path.join(ROOT, "tools", "_trace")))
+    print(build.build(extra_flags=["-DRF_TRACE", f"-DRF_ABL={ABL}"], lib=TRACE_LIB, obj_dir=os.path.dirname(TRACE_LIB)))
     sys.exit(0)
 
 import numpy as np, torch
@@ -24,7 +27,8 @@ import rl4co_slap_b200 as R
 
 dev = torch.device("cuda:0")
 torch.manual_seed(1234)
-N, B, T = 100, 148 * 2, 100
+N = int(os.environ.get("RF_N", "100"))
+B, T = 148 * 2, N
 pol = R.AttentionModelPolicy(env_name="tsp").to(dev).eval()
 locs = torch.rand(B, N, 2, device=dev)
 with torch.inference_mode():
@@ -55,8 +59,8 @@ torch.cuda.synchronize()
 tr = trace.cpu().numpy().reshape(T, 8)
 d = np.diff(tr, axis=1)
 names = ["q+scores+max", "softmax+V+butterfly", "L+store", "barrier1", "slice", "barrier2", "select+transition"]
-print("mean reward", rew.mean().item())
-for lo, hi in ((1, 10), (10, 50), (50, 99)):
+print(f"N={N} ablation bits={ABL} mean reward", rew.mean().item())
+for lo, hi in ((1, T // 2), (T // 2, T - 1)):
     m = d[lo:hi].mean(0)
     print(f"steps {lo}-{hi}: " + "  ".join(f"{n} {v:.0f}" for n, v in zip(names, m)), "| step total", (tr[lo + 1:hi + 1, 0] - tr[lo:hi, 0]).mean())
 print("whole trajectory cycles", tr[-1, 7] - tr[0, 0])
