@@ -232,10 +232,12 @@ typedef struct rl4co_am_rollout_args {
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);
 
-/* rl4co_am_rollout picks between two kernels with identical semantics: register-file
- * resident tables (single start, N <= 128) and shared-memory resident tables (multistart,
- * or anything the first cannot hold).  impl = 1 forces the second one (parity tests run
- * both against the oracle); impl = 0 restores the automatic choice. */
+/* rl4co_am_rollout picks between three kernels with identical semantics: register-file
+ * resident tables with node compaction (TSP, greedy, single start, N <= 112), register-file
+ * resident tables (any single start, N <= 128) and shared-memory resident tables (multistart,
+ * or anything the others cannot hold).  impl = 1 forces the last one, impl = 2 skips the
+ * TSP-greedy specialisation (parity tests run all of them against the oracle); impl = 0
+ * restores the automatic choice. */
 int rl4co_set_rollout_impl(int impl);
 
 /* Standalone decode step on given logits: process_logits + greedy / sampling / evaluate +

@@ -497,7 +497,7 @@ static int launch_rollout(const rl4co_am_rollout_args &a, int n_smem_tab, size_t
 
 static int g_rollout_impl = 0;
 extern "C" int rl4co_set_rollout_impl(int impl) {
-    RL4CO_REQUIRE(impl == 0 || impl == 1, "set_rollout_impl: 0 = automatic, 1 = shared-memory kernel only");
+    RL4CO_REQUIRE(impl >= 0 && impl <= 2, "set_rollout_impl: 0 = automatic, 1 = shared-memory kernel only, 2 = no TSP-greedy specialisation");
     g_rollout_impl = impl;
     return 0;
 }
@@ -522,6 +522,8 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         RL4CO_REQUIRE(a.picklist && a.P >= 1 && a.O >= 0 && a.K >= 1 && a.T >= a.P, "am_rollout: slap needs picklist and T>=P");
     if (a.multistart) RL4CO_REQUIRE(a.num_loc >= 1 && a.env != RL4CO_ENV_SLAP, "am_rollout: bad multistart setup");
 
+    // TSP greedy single start: register-file kernel with node compaction (am_rollout_tsp.cu)
+    if (g_rollout_impl == 0 && rollout_tsp_greedy_supports(a)) return launch_rollout_tsp_greedy(a, (cudaStream_t)stream);
     // single-start rollouts: register-file resident kernel (am_rollout_rf.cu)
     if (g_rollout_impl != 1 && rollout_rf_supports(a)) return launch_rollout_rf(a, (cudaStream_t)stream);
 

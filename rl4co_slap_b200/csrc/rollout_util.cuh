@@ -81,5 +81,8 @@ __device__ __forceinline__ float slap_order_len(const float2 *locs, const int *a
 // host-side launchers of the register-file resident single-start kernel (am_rollout_rf.cu)
 int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream);
 bool rollout_rf_supports(const rl4co_am_rollout_args &a);
+// TSP / greedy / standard logit post-processing specialisation with node compaction (am_rollout_tsp.cu)
+int launch_rollout_tsp_greedy(const rl4co_am_rollout_args &a, cudaStream_t stream);
+bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a);
 
 }  // namespace rl4co

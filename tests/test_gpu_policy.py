@@ -14,12 +14,13 @@ pytestmark = pytest.mark.gpu
 RTOL = 1e-5
 
 
-@pytest.fixture(params=("auto", "smem"))
+@pytest.fixture(params=("auto", "rf", "smem"))
 def rollout_impl(request):
-    """Single-start rollouts have two kernels behind rl4co_am_rollout (register-file resident
-    tables / shared-memory resident tables); the parity tests run both."""
+    """Single-start rollouts have three kernels behind rl4co_am_rollout (register-file resident
+    tables with node compaction for TSP greedy / register-file resident tables / shared-memory
+    resident tables); the parity tests run all of them."""
     from rl4co_slap_b200 import _lib
-    _lib.call("rl4co_set_rollout_impl", 1 if request.param == "smem" else 0)
+    _lib.call("rl4co_set_rollout_impl", {"auto": 0, "smem": 1, "rf": 2}[request.param])
     yield request.param
     _lib.call("rl4co_set_rollout_impl", 0)
 
