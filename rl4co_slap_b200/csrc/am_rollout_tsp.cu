@@ -109,8 +109,10 @@ __device__ __forceinline__ void sts_2x128(uint32_t addr, const u64 (&v)[4]) {
 // -DRF_TRACE: thread 0 of CTA 0 stamps clock64() at eight points of every step of its first instance
 #ifdef RF_TRACE
 #define TG_TRACE_AT(k) do { if (threadIdx.x == 0 && blockIdx.x == 0 && c.trace) reinterpret_cast<long long *>(c.trace)[c.t * 8 + (k)] = clock64(); } while (0)
+#define TG_TRACE_ROW(row, k) do { if (threadIdx.x == 0 && blockIdx.x == 0 && c.trace) reinterpret_cast<long long *>(c.trace)[(row) * 8 + (k)] = clock64(); } while (0)
 #else
 #define TG_TRACE_AT(k) do { } while (0)
+#define TG_TRACE_ROW(row, k) do { } while (0)
 #endif
 
 // per-thread state carried through the stages of one trajectory
@@ -123,6 +125,7 @@ struct Ctx {
     int cur, t, status;
     float clip;
     void *trace;
+    int trow;               // RF_TRACE: first spare row of the trace buffer
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -298,6 +301,8 @@ __device__ __forceinline__ void compact(Ctx &c, const u64 (&Ko)[MO][4], const u6
     const int hh = lane >> 4, g = lane & 15;
     int *node_w = reinterpret_cast<int *>(smem + OFF_NODE) + warp * 128;
     const uint32_t scr = smem_u32(smem + OFF_SCR) + (uint32_t)warp * (kScrSlots * 64);
+    const int trow = c.trow + (MN == 4 ? 0 : 1);
+    TG_TRACE_ROW(trow, 0);
     int rank[MO], nid[MO];
     int cnt = 0;
 #pragma unroll
@@ -313,16 +318,25 @@ __device__ __forceinline__ void compact(Ctx &c, const u64 (&Ko)[MO][4], const u6
         for (int j = 0; j < MO; ++j)
             if ((c.alive >> j) & 1u) node_w[rank[j]] = nid[j];
     }
+    // scratch layout [half head][16-byte piece][slot]: consecutive slots are consecutive 16-byte words,
+    // so both the rank-addressed stores and the slot-addressed loads are free of bank conflicts
+    const uint32_t scr_h = scr + (uint32_t)hh * (2u * kScrSlots * 16u);
     auto move = [&](const u64 (&To)[MO][4], u64 (&Tn)[MN][4]) {
 #pragma unroll
         for (int j = 0; j < MO; ++j)
-            if (((c.alive >> j) & 1u) && rank[j] < 16 * MN) sts_2x128(scr + (uint32_t)rank[j] * 64u + (uint32_t)hh * 32u, To[j]);
+            if (((c.alive >> j) & 1u) && rank[j] < 16 * MN) {
+                const uint32_t ad = scr_h + (uint32_t)rank[j] * 16u;
+                asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(ad), "l"(To[j][0]), "l"(To[j][1]) : "memory");
+                asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(ad + kScrSlots * 16u), "l"(To[j][2]), "l"(To[j][3]) : "memory");
+            }
         __syncwarp();
 #pragma unroll
         for (int j = 0; j < MN; ++j) {
             const int slot = g + 16 * j;
             if (slot < cnt) {
-                lds_2x128(scr + (uint32_t)slot * 64u + (uint32_t)hh * 32u, Tn[j]);
+                const uint32_t ad = scr_h + (uint32_t)slot * 16u;
+                asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(Tn[j][0]), "=l"(Tn[j][1]) : "r"(ad));
+                asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(Tn[j][2]), "=l"(Tn[j][3]) : "r"(ad + kScrSlots * 16u));
             } else {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) Tn[j][i] = 0ull;
@@ -330,9 +344,13 @@ __device__ __forceinline__ void compact(Ctx &c, const u64 (&Ko)[MO][4], const u6
         }
         __syncwarp();
     };
+    TG_TRACE_ROW(trow, 1);
     move(Ko, Kn);
+    TG_TRACE_ROW(trow, 2);
     move(Vo, Vn);
+    TG_TRACE_ROW(trow, 3);
     move(Lo, Ln);
+    TG_TRACE_ROW(trow, 4);
     unsigned m = 0;
 #pragma unroll
     for (int j = 0; j < MN; ++j) m |= (g + 16 * j < cnt) ? (1u << j) : 0u;
@@ -463,10 +481,11 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         c.c_addr = smem_u32(cbuf + (size_t)buf * N * E + dim0);
         c.x_addr = smem_u32(sxs);
 #ifdef RF_TRACE
-        c.trace = (blockIdx.x == 0 && it == 0) ? (void *)a.logp_all : nullptr;
+        c.trace = (blockIdx.x == 0 && it == 1) ? (void *)a.logp_all : nullptr;
 #else
         c.trace = nullptr;
 #endif
+        c.trow = T;
         const int t_end = N < T ? N : T;
 
         if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }      // context table landed?

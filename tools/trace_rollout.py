@@ -40,7 +40,7 @@ tables = torch.empty(nt, B * N, 128, device=dev)
 gctx = torch.empty(B, 128, device=dev)
 _lib.call("rl4co_am_project", B * N, nt, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
 _lib.call("rl4co_am_graph_context", B, N, _lib.ptr(h), _lib.ptr(Wfixed), _lib.ptr(gctx), stream)
-trace = torch.zeros(T * 8, dtype=torch.int64, device=dev)
+trace = torch.zeros((T + 2) * 8, dtype=torch.int64, device=dev)
 acts = torch.empty(B, T, dtype=torch.int64, device=dev)
 logp = torch.empty(B, T, device=dev)
 ll, rew = torch.empty(B, device=dev), torch.empty(B, device=dev)
@@ -56,11 +56,16 @@ a.steps, a.status = _lib.ptr(steps), _lib.ptr(status)
 for _ in range(2):
     _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
 torch.cuda.synchronize()
-tr = trace.cpu().numpy().reshape(T, 8)
+full = trace.cpu().numpy().reshape(T + 2, 8)
+tr = full[:T]
 d = np.diff(tr, axis=1)
 names = ["q+scores+max", "softmax+V+butterfly", "L+store", "barrier1", "slice", "barrier2", "select+transition"]
 print(f"N={N} ablation bits={ABL} mean reward", rew.mean().item())
 for lo, hi in ((1, T // 2), (T // 2, T - 1)):
     m = d[lo:hi].mean(0)
     print(f"steps {lo}-{hi}: " + "  ".join(f"{n} {v:.0f}" for n, v in zip(names, m)), "| step total", (tr[lo + 1:hi + 1, 0] - tr[lo:hi, 0]).mean())
+print("cycles from step start to next step start:", " ".join(str(int(v)) for v in (tr[1:, 0] - tr[:-1, 0])))
+for r in (T, T + 1):
+    if full[r, 0]:
+        print(f"compaction {r - T}: ranks+node table {full[r,1]-full[r,0]}  K {full[r,2]-full[r,1]}  V {full[r,3]-full[r,2]}  L {full[r,4]-full[r,3]}")
 print("whole trajectory cycles", tr[-1, 7] - tr[0, 0])
