@@ -97,6 +97,10 @@ __device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi) {
 __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+// 32 contiguous bytes in one request (SASS: LDG.E.256): a thread's 8 dims of one table row are exactly one sector
+__device__ __forceinline__ void ldg_256(const float *p, u64 (&v)[4]) {
+    asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
+}
 __device__ __forceinline__ void lds_2x128(uint32_t addr, u64 (&v)[4]) {
     asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v[0]), "=l"(v[1]) : "r"(addr));
     asm volatile("ld.shared.v2.u64 {%0, %1}, [%2+16];" : "=l"(v[2]), "=l"(v[3]) : "r"(addr));
@@ -400,6 +404,11 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     int it = 0;
     for (int64_t b = blockIdx.x; b < a.B; b += gridDim.x, ++it) {
         const int buf = it & 1;
+#ifdef RF_TRACE
+        Ctx c;
+        c.trace = (blockIdx.x == 0 && it == 1) ? (void *)a.logp_all : nullptr;
+        TG_TRACE_ROW(T + 2, 0);
+#endif
         // ------------------------------------------------ registers <- tables (global / L2)
         u64 K2[M0][4], V2[M0][4], L2[M0][4];
         {
@@ -410,22 +419,18 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             for (int j = 0; j < M0; ++j) {
                 const int n = g + 16 * j;
                 if (n < N) {
-                    const ulonglong2 k0 = __ldg(reinterpret_cast<const ulonglong2 *>(kb + (size_t)n * E));
-                    const ulonglong2 k1 = __ldg(reinterpret_cast<const ulonglong2 *>(kb + (size_t)n * E) + 1);
-                    const ulonglong2 v0 = __ldg(reinterpret_cast<const ulonglong2 *>(vb + (size_t)n * E));
-                    const ulonglong2 v1 = __ldg(reinterpret_cast<const ulonglong2 *>(vb + (size_t)n * E) + 1);
-                    const ulonglong2 l0 = __ldg(reinterpret_cast<const ulonglong2 *>(lb + (size_t)n * E));
-                    const ulonglong2 l1 = __ldg(reinterpret_cast<const ulonglong2 *>(lb + (size_t)n * E) + 1);
-                    K2[j][0] = k0.x; K2[j][1] = k0.y; K2[j][2] = k1.x; K2[j][3] = k1.y;
-                    V2[j][0] = v0.x; V2[j][1] = v0.y; V2[j][2] = v1.x; V2[j][3] = v1.y;
-                    L2[j][0] = l0.x; L2[j][1] = l0.y; L2[j][2] = l1.x; L2[j][3] = l1.y;
+                    ldg_256(kb + (size_t)n * E, K2[j]);
+                    ldg_256(vb + (size_t)n * E, V2[j]);
+                    ldg_256(lb + (size_t)n * E, L2[j]);
                 } else {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) K2[j][i] = V2[j][i] = L2[j][i] = 0ull;
                 }
             }
         }
+#ifndef RF_TRACE
         Ctx c;
+#endif
         // constant part of the query, pre-scaled: scale * (gctx + extra); extra = step-0 placeholder
         // (context.py:111-121), then the first node's half of the context projection
         auto set_qb = [&](const float *extra) {
@@ -446,6 +451,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         set_qb(a.q0 + dim0);
         auto set_first = [&](int node) { set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + node) * E + dim0); };
 
+        TG_TRACE_ROW(T + 2, 1);
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
         {
@@ -467,6 +473,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         }
         __syncthreads();
 
+        TG_TRACE_ROW(T + 2, 2);
         // ------------------------------------------------ env state (tsp/env.py:95-120)
         c.own = 0;
 #pragma unroll
@@ -491,6 +498,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }      // context table landed?
         else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
 
+        TG_TRACE_ROW(T + 2, 3);
         // ================================================== decode, in stages of fewer and fewer rows
         // after t steps N - t nodes are unvisited: 4 rows hold them from t = N - 64 on, 2 rows from t = N - 32
         if (M0 > 4) {
@@ -525,26 +533,46 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             }
         }
 
+        TG_TRACE_ROW(T + 2, 4);
         // ================================================== epilogue =====================
         __syncthreads();
         const int nact = c.t;
         int status = c.status;
-        // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368)
-        for (int q = warp; q < nact; q += kWarps) {      // one warp per step, from the kept logits
-            const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
-            const float m = s_mw[q];
-            float es = 0.f;
-            es += (xv.x == -INFINITY) ? 0.f : expf(xv.x - m);
-            es += (xv.y == -INFINITY) ? 0.f : expf(xv.y - m);
-            es += (xv.z == -INFINITY) ? 0.f : expf(xv.z - m);
-            es += (xv.w == -INFINITY) ? 0.f : expf(xv.w - m);
-            es = warp_sum(es);
-            if (lane == 0) {
-                const float lpa = (sxs[q * 128 + s_slot[q]] - m) - logf(es);
+        // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368); the
+        // exponentials through ex2.approx (relative error 2^-22; masked logits: 2^-inf = 0)
+        {
+            // warp w takes steps w, w + 8, ...: all of its (at most 16) sums are reduced together, then lane u
+            // finishes step w + 8 u, so neither the shuffles nor the logarithm are serialised over the steps
+            constexpr int U = kMaxT / kWarps;
+            float es[U], mm[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int q = warp + u * kWarps;
+                es[u] = 0.f;
+                mm[u] = 0.f;
+                if (q < nact) {
+                    const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
+                    mm[u] = s_mw[q];
+                    es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
+                            (ex2f((xv.z - mm[u]) * kLog2e) + ex2f((xv.w - mm[u]) * kLog2e));
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                for (int u = 0; u < U; ++u) es[u] += __shfl_xor_sync(kFull, es[u], o);
+            float my_es = 1.f, my_m = 0.f;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (lane == u) { my_es = es[u]; my_m = mm[u]; }
+            const int q = warp + lane * kWarps;
+            if (lane < U && q < nact) {
+                const float lpa = (sxs[q * 128 + s_slot[q]] - my_m) - logf(my_es);
                 s_lp[q] = lpa;
                 if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
             }
         }
+        TG_TRACE_ROW(T + 2, 5);
         float part = 0.f;
         for (int q = tid; q < nact; q += kThreads) {     // tsp/env.py:157-163
             float2 p = s_locs[s_act[q]], w = s_locs[s_act[q + 1 == nact ? 0 : q + 1]];
@@ -573,6 +601,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             a.actions[(size_t)b * T + q] = q < nact ? (int64_t)s_act[q] : 0;
             if (a.logp) a.logp[(size_t)b * T + q] = q < nact ? s_lp[q] : 0.f;
         }
+        TG_TRACE_ROW(T + 2, 6);
     }
 }
 

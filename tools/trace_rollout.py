@@ -40,7 +40,7 @@ tables = torch.empty(nt, B * N, 128, device=dev)
 gctx = torch.empty(B, 128, device=dev)
 _lib.call("rl4co_am_project", B * N, nt, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
 _lib.call("rl4co_am_graph_context", B, N, _lib.ptr(h), _lib.ptr(Wfixed), _lib.ptr(gctx), stream)
-trace = torch.zeros((T + 2) * 8, dtype=torch.int64, device=dev)
+trace = torch.zeros((T + 3) * 8, dtype=torch.int64, device=dev)
 acts = torch.empty(B, T, dtype=torch.int64, device=dev)
 logp = torch.empty(B, T, device=dev)
 ll, rew = torch.empty(B, device=dev), torch.empty(B, device=dev)
@@ -56,7 +56,7 @@ a.steps, a.status = _lib.ptr(steps), _lib.ptr(status)
 for _ in range(2):
     _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
 torch.cuda.synchronize()
-full = trace.cpu().numpy().reshape(T + 2, 8)
+full = trace.cpu().numpy().reshape(T + 3, 8)
 tr = full[:T]
 d = np.diff(tr, axis=1)
 names = ["q+scores+max", "softmax+V+butterfly", "L+store", "barrier1", "slice", "barrier2", "select+transition"]
@@ -68,4 +68,7 @@ print("cycles from step start to next step start:", " ".join(str(int(v)) for v i
 for r in (T, T + 1):
     if full[r, 0]:
         print(f"compaction {r - T}: ranks+node table {full[r,1]-full[r,0]}  K {full[r,2]-full[r,1]}  V {full[r,3]-full[r,2]}  L {full[r,4]-full[r,3]}")
+if full[T + 2, 0]:
+    v = full[T + 2]
+    print(f"instance: table loads issued {v[1]-v[0]}  smem init {v[2]-v[1]}  context wait {v[3]-v[2]}  decode {v[4]-v[3]}  log-probs {v[5]-v[4]}  reward+outputs {v[6]-v[5]}  total {v[6]-v[0]}")
 print("whole trajectory cycles", tr[-1, 7] - tr[0, 0])
