@@ -37,11 +37,14 @@ constexpr float kScoreScale = 0.25f * 1.4426950408889634f;   // 1/sqrt(16) * log
 constexpr float kInvSqrtE = 0.08838834764831845f;             // 1/sqrt(128)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int PLS = 144;              // row stride of the partial-logit matrix [head][slot], = 16 (mod 32)
+#ifndef RL4CO_TSPG_FUSED_ROWS
+#define RL4CO_TSPG_FUSED_ROWS 2   // measured: fusing the 4-row stage (2 slots per lane) is 1240 clk/step against 1230
+#endif
 constexpr int kScrSlots = 64;         // compaction target: at most 4 rows of 16 slots
 
 // Shared memory.  The buffers touched on every step sit at compile-time offsets.
-constexpr size_t OFF_PL = 0;                                        // partial logits [head][slot]
-constexpr size_t OFF_O = OFF_PL + (size_t)kWarps * PLS * 4;         // glimpse heads (warp private)
+constexpr size_t OFF_PL = 0;                                        // partial logits [2][head][slot] (2nd copy: fused stage)
+constexpr size_t OFF_O = OFF_PL + (size_t)2 * kWarps * PLS * 4;     // glimpse heads (warp private)
 constexpr size_t OFF_ZERO = OFF_O + E * 4;                          // 512 B of zeros: the "context row" of step 0
 constexpr size_t OFF_MW = OFF_ZERO + E * 4;                         // per step: max logit
 constexpr size_t OFF_ACT = OFF_MW + kMaxT * 4;                      // per step: chosen node
@@ -154,6 +157,15 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
     const float *pl_ld = spl + tid;
     const int jb = 2 * warp + hh;            // slice: thread tid < 128 is slot tid = g + 16 jb
     const float clip = c.clip;
+    // With at most 32 slots a warp holds one slot per lane (slot = lane = g + 16 hh): every warp finishes all
+    // logits itself and goes straight to the argmax - no second barrier, no exchange of the processed logits.
+    // The partial logits then alternate between two buffers (a fast warp may already write step t + 1).
+    constexpr bool FUSED = MM <= RL4CO_TSPG_FUSED_ROWS;
+    constexpr int NS = FUSED ? (MM + 1) / 2 : 1;      // slots per lane in the fused finish: lane + 32 k = g + 16 (hh + 2 k)
+    unsigned fkey[NS];
+#pragma unroll
+    for (int k = 0; k < NS; ++k)
+        fkey[k] = ((unsigned)(lane + 32 * k) << 8) | (unsigned)(reinterpret_cast<const int *>(smem + OFF_NODE)[warp * 128 + lane + 32 * k] & 0xff);
 
     while (c.t < t_stop) {
         TG_TRACE_AT(0);
@@ -244,13 +256,46 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
 #pragma unroll
             for (int j = 0; j < MM; ++j) pl[j] += __shfl_xor_sync(kFull, pl[j], 16);
             if (hh == 0) {
+                float *dst = pl_st + ((FUSED && (c.t & 1)) ? kWarps * PLS : 0);
 #pragma unroll
-                for (int j = 0; j < MM; ++j) pl_st[16 * j] = pl[j];
+                for (int j = 0; j < MM; ++j) dst[16 * j] = pl[j];
             }
         }
         TG_TRACE_AT(3);
         __syncthreads();
         TG_TRACE_AT(4);
+        float gm;
+        unsigned win;
+        if (FUSED) {
+            const float *pl = spl + ((c.t & 1) ? kWarps * PLS : 0) + lane;
+            float xv[NS];
+#pragma unroll
+            for (int k = 0; k < NS; ++k) {
+                const float *pk = pl + 32 * k;
+                const float sum = ((pk[0] + pk[2 * PLS]) + (pk[4 * PLS] + pk[6 * PLS])) +
+                                  ((pk[PLS] + pk[3 * PLS]) + (pk[5 * PLS] + pk[7 * PLS]));
+                const float e2 = ex2f(sum * (kInvSqrtE * 2.f * kLog2e));
+                const float th = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
+                if (((c.own >> (hh + 2 * k)) & 1u) && sum != sum) c.status |= RL4CO_ST_NAN_LOGITS;
+                xv[k] = ((c.alive >> (hh + 2 * k)) & 1u) ? th : -INFINITY;
+            }
+            TG_TRACE_AT(5);
+            TG_TRACE_AT(6);
+            float lm = xv[0];
+#pragma unroll
+            for (int k = 1; k < NS; ++k) lm = fmaxf(lm, xv[k]);
+            gm = redux_max(lm);
+            unsigned cand = 0x7fffffffu;
+#pragma unroll
+            for (int k = NS - 1; k >= 0; --k) cand = xv[k] == gm ? fkey[k] : cand;
+            win = redux_min_u32(cand);
+            // one warp keeps the step's logits for the epilogue (the other slots of the row were set to -inf on entry)
+            if (warp == (c.t & (kWarps - 1))) {
+#pragma unroll
+                for (int k = 0; k < NS; ++k)
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(c.x_addr + 4u * (lane + 32 * k)), "f"(xv[k]) : "memory");
+            }
+        } else {
         // ---- threads 0-127 = slots: logit = sum_h pl_h / sqrt(E); tanh clipping, mask (utils/decoding.py:141-191)
         if (tid < 128) {
             float xv = -INFINITY;
@@ -271,13 +316,14 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
         // ---- every warp: all logits, lane = slots 4 lane .. 4 lane + 3; argmax, lowest slot on ties
         float x0, x1, x2, x3;
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x0), "=f"(x1), "=f"(x2), "=f"(x3) : "r"(c.x_addr + 16u * lane));
-        const float gm = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
+        gm = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
         unsigned cand = 0x7fffffffu;
         cand = x3 == gm ? c.candk[3] : cand;
         cand = x2 == gm ? c.candk[2] : cand;
         cand = x1 == gm ? c.candk[1] : cand;
         cand = x0 == gm ? c.candk[0] : cand;
-        unsigned win = redux_min_u32(cand);
+        win = redux_min_u32(cand);
+        }
         if (win == 0x7fffffffu) win = reinterpret_cast<const int *>(smem + OFF_NODE)[warp * 128];   // NaN logits: slot 0
         const int slot = (int)(win >> 8), node = (int)(win & 0xffu);
         if (tid == 0) { s_act[c.t] = node; s_slot[c.t] = slot; s_mw[c.t] = gm; }
@@ -499,6 +545,10 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
 
         TG_TRACE_ROW(T + 2, 3);
+        // fused stages keep only the live slots of a step's logits: the rest of the rows is -inf from here on
+        auto fill_rows = [&](int t0) {
+            for (int i = tid; i < (t_end - t0) * 128; i += kThreads) sxs[t0 * 128 + i] = -INFINITY;
+        };
         // ================================================== decode, in stages of fewer and fewer rows
         // after t steps N - t nodes are unvisited: 4 rows hold them from t = N - 64 on, 2 rows from t = N - 32
         if (M0 > 4) {
@@ -517,6 +567,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             }
             if (M0 >= 4) {
                 const int stop = N - 32 < t_end ? N - 32 : t_end;
+                if (RL4CO_TSPG_FUSED_ROWS >= 4) fill_rows(c.t);
                 run_stage<4>(c, K4, V4, L4, stop, smem, set_first);
             }
             if (c.t < t_end) {
@@ -529,6 +580,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) { Ka[j][i] = K2[j < M0 ? j : 0][i]; Va[j][i] = V2[j < M0 ? j : 0][i]; La[j][i] = L2[j < M0 ? j : 0][i]; }
                 }
+                if (RL4CO_TSPG_FUSED_ROWS < 4 || M0 < 4) fill_rows(c.t);
                 run_stage<2>(c, Ka, Va, La, t_end, smem, set_first);
             }
         }
