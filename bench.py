@@ -276,7 +276,7 @@ def run_ours(args):
                    "encoder output resident in HBM", "l2": "inputs larger than L2 (encoder output "
                    f"{B * N_NODES * EMBED * 4 / 1e9:.1f} GB per GPU)", "rollout_chunk": pol.rollout_chunk,
                    "mean_reward": mean_reward},
-        "roofline": {"bound": "hbm", "kernel": "am_rollout_rf_kernel<TSP,7> (K2, one launch per chunk)",
+        "roofline": {"bound": "hbm", "kernel": "am_rollout_tsp_greedy_kernel<7> (K2, one launch per chunk)",
                      "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_rollout": ALGO_BYTES_PER_ROLLOUT,

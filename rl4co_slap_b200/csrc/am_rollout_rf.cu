@@ -124,6 +124,10 @@ __device__ __forceinline__ float hsum2(u64 v) {
 __device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi) {
     asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
 }
+// 32 contiguous bytes in one request (SASS: LDG.E.256): a thread's 8 dims of one table row are exactly one sector
+__device__ __forceinline__ void ldg_256(const float *p, u64 (&v)[4]) {
+    asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
+}
 __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
@@ -206,15 +210,9 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
             for (int j = 0; j < M; ++j) {
                 const int n = g + 16 * j;
                 if (n < N) {
-                    const ulonglong2 k0 = __ldg(reinterpret_cast<const ulonglong2 *>(kb + (size_t)n * E));
-                    const ulonglong2 k1 = __ldg(reinterpret_cast<const ulonglong2 *>(kb + (size_t)n * E) + 1);
-                    const ulonglong2 v0 = __ldg(reinterpret_cast<const ulonglong2 *>(vb + (size_t)n * E));
-                    const ulonglong2 v1 = __ldg(reinterpret_cast<const ulonglong2 *>(vb + (size_t)n * E) + 1);
-                    const ulonglong2 l0 = __ldg(reinterpret_cast<const ulonglong2 *>(lb + (size_t)n * E));
-                    const ulonglong2 l1 = __ldg(reinterpret_cast<const ulonglong2 *>(lb + (size_t)n * E) + 1);
-                    K2[j][0] = k0.x; K2[j][1] = k0.y; K2[j][2] = k1.x; K2[j][3] = k1.y;
-                    V2[j][0] = v0.x; V2[j][1] = v0.y; V2[j][2] = v1.x; V2[j][3] = v1.y;
-                    L2[j][0] = l0.x; L2[j][1] = l0.y; L2[j][2] = l1.x; L2[j][3] = l1.y;
+                    ldg_256(kb + (size_t)n * E, K2[j]);
+                    ldg_256(vb + (size_t)n * E, V2[j]);
+                    ldg_256(lb + (size_t)n * E, L2[j]);
                 } else {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) K2[j][i] = V2[j][i] = L2[j][i] = 0ull;
@@ -592,17 +590,34 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         const int nact = t;
         // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368)
         if (xring) {
-            for (int q = warp; q < nact; q += kWarps) {      // one warp per step, from the kept logits
-                const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
-                const float m = s_mw[q];
-                float es = 0.f;
-                es += (xv.x == -INFINITY) ? 0.f : expf(xv.x - m);
-                es += (xv.y == -INFINITY) ? 0.f : expf(xv.y - m);
-                es += (xv.z == -INFINITY) ? 0.f : expf(xv.z - m);
-                es += (xv.w == -INFINITY) ? 0.f : expf(xv.w - m);
-                es = warp_sum(es);
-                if (lane == 0) {
-                    const float lpa = (sxs[q * 128 + s_act[q]] - m) - logf(es);
+            // warp w takes steps w, w + 8, ... in groups of 16: the sums of a group are reduced together and lane u
+            // finishes step w + 8 u, so neither the shuffles nor the logarithm are serialised over the steps;
+            // exponentials through ex2.approx (relative error 2^-22; masked logits: 2^-inf = 0)
+            for (int qb = warp; qb < nact; qb += 16 * kWarps) {
+                float es[16], mm[16];
+#pragma unroll
+                for (int u = 0; u < 16; ++u) {
+                    const int q = qb + u * kWarps;
+                    es[u] = 0.f;
+                    mm[u] = 0.f;
+                    if (q < nact) {
+                        const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
+                        mm[u] = s_mw[q];
+                        es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
+                                (ex2f((xv.z - mm[u]) * kLog2e) + ex2f((xv.w - mm[u]) * kLog2e));
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) es[u] += __shfl_xor_sync(kFull, es[u], o);
+                float my_es = 1.f, my_m = 0.f;
+#pragma unroll
+                for (int u = 0; u < 16; ++u)
+                    if (lane == u) { my_es = es[u]; my_m = mm[u]; }
+                const int q = qb + lane * kWarps;
+                if (lane < 16 && q < nact) {
+                    const float lpa = (sxs[q * 128 + s_act[q]] - my_m) - logf(my_es);
                     s_lp[q] = lpa;
                     if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
                 }
