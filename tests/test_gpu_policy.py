@@ -267,6 +267,41 @@ def test_large_batch_greedy_properties(dev):
     torch.testing.assert_close(out["log_likelihood"][idx].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
 
 
+@pytest.mark.parametrize("N,B", ((2, 5), (3, 33), (16, 150), (17, 40), (32, 149), (33, 300), (64, 200), (65, 160),
+                                 (80, 77), (97, 148), (112, 150)))
+def test_tsp_greedy_compaction_kernel_sizes(N, B, dev):
+    """The TSP greedy kernel (am_rollout_tsp.cu: 7 -> 4 -> 2 rows of node slots, compaction at 64 and 32 nodes left)
+    at every stage boundary and at ragged batch sizes (fewer / more instances than SMs): valid tours, rewards equal to
+    the environment's replay of them, log-likelihoods equal to an evaluate-mode pass and to the oracle on its own
+    tours; tours equal to the generic register-file kernel's except for near-tie flips."""
+    from rl4co_slap_b200 import _lib
+    torch.manual_seed(100 + N)
+    pol, env = load_policy("tsp", dev), R.TSPEnv(generator_params=dict(num_loc=N), device=dev)
+    td = env.reset(batch_size=[B])
+    with torch.inference_mode():
+        out = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True)
+        h = out["hidden"].node_embeddings
+        _lib.call("rl4co_set_rollout_impl", 2)
+        try:
+            gen = pol(td, env, decode_type="greedy", return_actions=True, hidden=h)
+        finally:
+            _lib.call("rl4co_set_rollout_impl", 0)
+        ev = pol(td, env, actions=out["actions"], hidden=h)
+    assert out["actions"].shape == (B, N)
+    assert torch.equal(out["actions"].sort(1).values, torch.arange(N, device=dev).expand(B, N)), "not a permutation"
+    _, r = env.replay(td, out["actions"], check=True)
+    torch.testing.assert_close(r, out["reward"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(ev["log_likelihood"], out["log_likelihood"], rtol=1e-5, atol=2e-5)
+    same = (out["actions"] == gen["actions"]).all(1)
+    assert same.float().mean() >= 0.9, "tours diverge from the generic kernel beyond near-tie flips"
+    torch.testing.assert_close(out["log_likelihood"][same], gen["log_likelihood"][same], rtol=1e-5, atol=2e-5)
+    idx = torch.arange(0, B, max(1, B // 16), device=dev)
+    ref = port.am_rollout("tsp", port.tsp_reset(td["locs"][idx].cpu()), h[idx].cpu(), oracle_weights("tsp"),
+                          actions=out["actions"][idx].cpu())
+    torch.testing.assert_close(out["log_likelihood"][idx].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
+    torch.testing.assert_close(out["reward"][idx].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+
+
 @pytest.mark.parametrize("M,nt", ((1, 1), (100, 3), (128 * 7 + 5, 5), (148 * 128 * 3 + 17, 4)))
 def test_tensor_core_projection_matches_fp64(M, nt, dev):
     """K3 on tcgen05 (3xTF32 split, TMEM accumulation) vs an fp64 matmul and the fp32 SIMT kernel:
