@@ -148,7 +148,7 @@ __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
 
 template <int ENV, int M>
 __global__ void __launch_bounds__(kThreads, 1)
-am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
+am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     constexpr bool HAS_C = ENV != RL4CO_ENV_SLAP;
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T;
@@ -193,11 +193,18 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         for (size_t off = 0; off < c_bytes; off += 16384)
             tma_load_1d(dst + off, src + off, (unsigned)(c_bytes - off < 16384 ? c_bytes - off : 16384), &bar[buf]);
     };
-    if (HAS_C && tid == 0 && (int64_t)blockIdx.x < a.B) stage_context(blockIdx.x, 0);
+    // work item = (instance, range of its starts): with fewer instances than SMs the starts of an instance are
+    // spread over several CTAs (n_parts per instance, each loading the instance's tables for itself)
+    const int S = a.S > 1 ? a.S : 1;
+    const int s_per = (S + n_parts - 1) / n_parts;
+    const int64_t W = a.B * (int64_t)n_parts;
+    const int t_first = a.multistart ? 1 : 0;       // multistart: step 0 is the forced POMO start node
+    if (HAS_C && tid == 0 && (int64_t)blockIdx.x < W) stage_context(blockIdx.x / n_parts, 0);
 
     int it = 0;
-    for (int64_t b = blockIdx.x; b < a.B; b += gridDim.x, ++it) {
-        const int64_t r = b;                        // single start: rollout index = instance
+    for (int64_t w = blockIdx.x; w < W; w += gridDim.x, ++it) {
+        const int64_t b = w / n_parts;
+        const int s_begin = (int)(w % n_parts) * s_per, s_end = s_begin + s_per < S ? s_begin + s_per : S;
         const int buf = it & 1;
         const float *C = cbuf + (size_t)buf * N * E;
         // ------------------------------------------------ registers <- tables (global / L2)
@@ -238,7 +245,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) qbs2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
         };
-        set_qb(ENV == RL4CO_ENV_TSP ? a.q0 + dim0 : nullptr);   // tsp step 0: context.py:111-121
         if (ENV == RL4CO_ENV_CVRP) {                              // remaining-capacity column, context.py:317-331
             const float4 w0 = __ldg(reinterpret_cast<const float4 *>(a.wcap + dim0));
             const float4 w1 = __ldg(reinterpret_cast<const float4 *>(a.wcap + dim0) + 1);
@@ -254,16 +260,11 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         {
             const float2 *lrow = reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2);
             for (int n = tid; n < N; n += kThreads) s_locs[n] = lrow[n];
-            if (a.mode == RL4CO_MODE_EVALUATE)
-                for (int t = tid; t < T; t += kThreads) {
-                    int64_t gv = a.actions_in[(size_t)r * T + t];
-                    s_ain[t] = (gv < 0 || gv >= N) ? -1 : (int)gv;
-                }
         }
         // next instance: context table -> the other buffer (its previous user finished before
         // the barrier above), K/V/L rows -> L2
-        if (tid == 0 && b + gridDim.x < a.B) {
-            const int64_t nb = b + gridDim.x;
+        if (tid == 0 && w + gridDim.x < W) {
+            const int64_t nb = (w + gridDim.x) / n_parts;
             if (HAS_C) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 stage_context(nb, buf ^ 1);
@@ -286,10 +287,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
         unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
-        if (ENV == RL4CO_ENV_SLAP) {                // slap: depot never assignable
-            if (g == 0) alive &= ~1u;
-            if (lane == 0) ralive &= ~1u;
-        }
         float dm[M], rdm[4];
 #pragma unroll
         for (int j = 0; j < M; ++j) dm[j] = (ENV == RL4CO_ENV_CVRP) ? s_dem[g + 16 * j] : 0.f;
@@ -319,7 +316,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
             alive = f;
             ralive = rf;
         };
-        if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
         int cur = 0, t = 0, status = 0;
         bool done = false, use_c = (ENV == RL4CO_ENV_CVRP);
         const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);
@@ -328,6 +324,32 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
             if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }
             else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
         }
+        // transition of the chosen (or forced) action, both mask layouts
+        auto apply = [&](int act) {
+            const unsigned abit = (g == (act & 15)) ? (1u << (act >> 4)) : 0u;
+            const unsigned rbit = (lane == (act >> 2)) ? (1u << (act & 3)) : 0u;
+            if (ENV == RL4CO_ENV_TSP) {                 // tsp/env.py:67-93
+                alive &= ~abit;
+                ralive &= ~rbit;
+                if (t == 0) {
+                    // from step 1 on: ctx = Wc [h_first ; h_cur] (context.py:123-131); the
+                    // first-node half is constant for the rest of the trajectory
+                    set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + act) * E + dim0);
+                    use_c = true;
+                }
+            } else if (ENV == RL4CO_ENV_CVRP) {         // cvrp/env.py:73-105,137-149
+                const float sel = s_dem[act == 0 ? 1 : act];
+                used = __fmul_rn(__fadd_rn(used, sel), act != 0 ? 1.f : 0.f);
+                vis |= abit;
+                rvis |= rbit;
+                cvrp_masks(act);
+                done = __all_sync(kFull, rvis == rown);
+            } else {                                    // slap/env.py:38-93
+                alive &= ~abit;
+                ralive &= ~rbit;
+            }
+            cur = act;
+        };
 
         // log-prob ingredients of step tp (its logits px, their max pgm, its action pact): this warp's
         // share of the sum of exponentials = nodes 16w..16w+15 = lanes 4w..4w+3, chosen logit, action
@@ -351,6 +373,32 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 if (lane == 0) { s_act[tp] = pact; s_xa[tp] = xa; s_mw[tp] = pgm; }
             }
         };
+
+        for (int s = s_begin; s < s_end; ++s) {
+        const int64_t r = (int64_t)s * a.B + b;     // flat rollout index, start-major (utils/ops.py:11-34)
+        // ------------------------------------------------ reset of the per-rollout state
+        if (s != s_begin) __syncthreads();          // the previous rollout's epilogue is done with shared memory
+        if (a.mode == RL4CO_MODE_EVALUATE) {
+            for (int q = tid; q < T; q += kThreads) {
+                int64_t gv = a.actions_in[(size_t)r * T + q];
+                s_ain[q] = (gv < 0 || gv >= N) ? -1 : (int)gv;
+            }
+            __syncthreads();
+        }
+        alive = own; ralive = rown; vis = 0; rvis = 0; used = 0.f;
+        if (ENV == RL4CO_ENV_SLAP) {                // slap: depot never assignable
+            if (g == 0) alive &= ~1u;
+            if (lane == 0) ralive &= ~1u;
+        }
+        if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
+        cur = 0; t = 0; status = 0; done = false; use_c = (ENV == RL4CO_ENV_CVRP);
+        set_qb(ENV == RL4CO_ENV_TSP ? a.q0 + dim0 : nullptr);   // tsp step 0: context.py:111-121
+        if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
+            const int a0 = s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
+            if (tid == 0) { s_act[0] = a0; s_lp[0] = 0.f; }
+            apply(a0);
+            t = 1;
+        }
 
         // ================================================== decode loop ==================
         while (!done && t < t_end) {
@@ -384,7 +432,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int j = 0; j < M; ++j) acc[j] = ffma2(K2[j][i], q2[i], acc[j]);
-                if (!xring && t > 0) book(t - 1);       // overlaps with the FFMA2 latency above
+                if (!xring && t > t_first) book(t - 1); // overlaps with the FFMA2 latency above
 #pragma unroll
                 for (int j = 0; j < M; ++j) s[j] = hsum2(acc[j]);
 #pragma unroll
@@ -556,36 +604,13 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
             pgm = gm;
             pact = act;
             if (xring && tid == 0) { s_act[t] = act; s_mw[t] = gm; }
-            // ---- transition, both mask layouts
-            const unsigned abit = (g == (act & 15)) ? (1u << (act >> 4)) : 0u;
-            const unsigned rbit = (lane == (act >> 2)) ? (1u << (act & 3)) : 0u;
-            if (ENV == RL4CO_ENV_TSP) {                 // tsp/env.py:67-93
-                alive &= ~abit;
-                ralive &= ~rbit;
-                if (t == 0) {
-                    // from step 1 on: ctx = Wc [h_first ; h_cur] (context.py:123-131); the
-                    // first-node half is constant for the rest of the trajectory
-                    set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + act) * E + dim0);
-                    use_c = true;
-                }
-            } else if (ENV == RL4CO_ENV_CVRP) {         // cvrp/env.py:73-105,137-149
-                const float sel = s_dem[act == 0 ? 1 : act];
-                used = __fmul_rn(__fadd_rn(used, sel), act != 0 ? 1.f : 0.f);
-                vis |= abit;
-                rvis |= rbit;
-                cvrp_masks(act);
-                done = __all_sync(kFull, rvis == rown);
-            } else {                                    // slap/env.py:38-93
-                alive &= ~abit;
-                ralive &= ~rbit;
-            }
-            cur = act;
+            apply(act);
             RF_TRACE_AT(7);
             ++t;
         }
 
         // ================================================== epilogue =====================
-        if (!xring && t > 0) book(t - 1);
+        if (!xring && t > t_first) book(t - 1);
         __syncthreads();
         const int nact = t;
         // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368)
@@ -600,7 +625,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                     const int q = qb + u * kWarps;
                     es[u] = 0.f;
                     mm[u] = 0.f;
-                    if (q < nact) {
+                    if (q >= t_first && q < nact) {
                         const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
                         mm[u] = s_mw[q];
                         es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
@@ -616,14 +641,14 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
                 for (int u = 0; u < 16; ++u)
                     if (lane == u) { my_es = es[u]; my_m = mm[u]; }
                 const int q = qb + lane * kWarps;
-                if (lane < 16 && q < nact) {
+                if (lane < 16 && q >= t_first && q < nact) {
                     const float lpa = (sxs[q * 128 + s_act[q]] - my_m) - logf(my_es);
                     s_lp[q] = lpa;
                     if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
                 }
             }
         } else {
-            for (int q = tid; q < nact; q += kThreads) {
+            for (int q = tid + t_first; q < nact; q += kThreads) {
                 const float4 r0 = *reinterpret_cast<const float4 *>(sring + q * kWarps);
                 const float4 r1 = *reinterpret_cast<const float4 *>(sring + q * kWarps + 4);
                 const float tot = ((r0.x + r0.y) + (r0.z + r0.w)) + ((r1.x + r1.y) + (r1.z + r1.w));
@@ -674,6 +699,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a) {
         }
         if (ENV == RL4CO_ENV_SLAP && a.assignment)
             for (int q = tid; q < a.P; q += kThreads) a.assignment[(size_t)r * a.P + q] = q < nact ? s_act[q] : -1;
+        }   // starts of this work item
     }
 }
 
@@ -697,8 +723,18 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         set_error("am_rollout(rf): cannot reserve %zu B of shared memory: %s", L.total, cudaGetErrorString(e));
         return 2;
     }
-    const int64_t grid = a.B < sm_count ? a.B : sm_count;   // persistent: one CTA per SM
-    am_rollout_rf_kernel<ENV, M><<<(unsigned)grid, kThreads, L.total, stream>>>(a);
+    // fewer instances than ~16 per SM: spread the starts of an instance over several work items
+    const int S = a.S > 1 ? a.S : 1;
+    int64_t n_parts = 1;
+    if (S > 1 && a.B < (int64_t)16 * sm_count) {
+        n_parts = ((int64_t)16 * sm_count + a.B - 1) / a.B;
+        if (n_parts > S) n_parts = S;
+        const int64_t per = (S + n_parts - 1) / n_parts;
+        n_parts = (S + per - 1) / per;                       // no empty parts
+    }
+    const int64_t W = a.B * n_parts;
+    const int64_t grid = W < sm_count ? W : sm_count;        // persistent: one CTA per SM
+    am_rollout_rf_kernel<ENV, M><<<(unsigned)grid, kThreads, L.total, stream>>>(a, (int)n_parts);
     RL4CO_CHECK_LAUNCH("am_rollout(rf)");
     return 0;
 }
@@ -721,7 +757,8 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
 #ifndef RF_TRACE
     if (a.logp_all != nullptr) return false;
 #endif
-    if (a.S > 1 || a.multistart || a.N > 128) return false;
+    if (a.N > 128) return false;
+    if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
 }
 
