@@ -51,7 +51,7 @@ constexpr int PLS = 144;              // row stride of the partial-logit matrix 
 struct Layout {
     int xs_rows;        // T: every step keeps its logits (log-probs are formed after the loop); 1: per-step sums
     size_t off_c, off_pl, off_xs, off_o, off_ring, off_mw, off_xa, off_act, off_ain, off_lp, off_locs,
-        off_dem, off_part, off_bar, total;
+        off_dem, off_wc, off_part, off_bar, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
 __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
@@ -59,7 +59,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     // everything except the logits: does a [T][128] ring of them still fit next to it?
     const size_t fixed = (has_c ? (size_t)2 * N * E * 4 : 0) + (size_t)kWarps * PLS * 4 + E * 4 +
                          up16((size_t)T * kWarps * 4) + 5 * up16((size_t)T * 4) + up16((size_t)N * 8) +
-                         128 * 4 + 64 * 4 + 16;
+                         128 * 4 + 128 * 4 + 64 * 4 + 16;
     L.xs_rows = (fixed + (size_t)T * 128 * 4 <= (size_t)227 * 1024) ? T : 1;
     size_t o = 0;
     L.off_c = o;    o += has_c ? (size_t)2 * N * E * 4 : 0;     // double-buffered context table
@@ -74,6 +74,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     L.off_lp = o;   o += up16((size_t)T * 4);
     L.off_locs = o; o += up16((size_t)N * 8);
     L.off_dem = o;  o += 128 * 4;
+    L.off_wc = o;   o += 128 * 4;                               // cvrp: remaining-capacity column, pre-scaled
     L.off_part = o; o += 64 * 4;
     L.off_bar = o;  o += 16;
     L.total = o;
@@ -165,6 +166,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     float *s_lp = reinterpret_cast<float *>(smem + L.off_lp);
     float2 *s_locs = reinterpret_cast<float2 *>(smem + L.off_locs);
     float *s_dem = reinterpret_cast<float *>(smem + L.off_dem);     // demand of node n (0 for depot / pad)
+    float *s_wc = reinterpret_cast<float *>(smem + L.off_wc);
     float *spart = reinterpret_cast<float *>(smem + L.off_part);
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.off_bar); // one per context buffer
 
@@ -184,6 +186,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         mbar_init(&bar[1], 1);
         fence_barrier_init();
     }
+    if (ENV == RL4CO_ENV_CVRP && tid < E) s_wc[tid] = a.wcap[tid] * kScoreScale;   // context.py:317-331
     __syncthreads();
     unsigned par0 = 0u, par1 = 0u;
     auto stage_context = [&](int64_t b, int buf) {  // thread 0: TMA the context table of instance b
@@ -227,7 +230,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             }
         }
         // constant part of the query, pre-scaled: qbs = scale * (gctx [+ step-0 placeholder])
-        u64 qbs2[4], wcs2[4];
+        u64 qbs2[4];
         auto set_qb = [&](const float *extra) {      // extra: 8 floats at this thread's dims, or null
             float v[8];
 #pragma unroll
@@ -245,14 +248,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) qbs2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
         };
-        if (ENV == RL4CO_ENV_CVRP) {                              // remaining-capacity column, context.py:317-331
-            const float4 w0 = __ldg(reinterpret_cast<const float4 *>(a.wcap + dim0));
-            const float4 w1 = __ldg(reinterpret_cast<const float4 *>(a.wcap + dim0) + 1);
-            wcs2[0] = pack2(w0.x * kScoreScale, w0.y * kScoreScale);
-            wcs2[1] = pack2(w0.z * kScoreScale, w0.w * kScoreScale);
-            wcs2[2] = pack2(w1.x * kScoreScale, w1.y * kScoreScale);
-            wcs2[3] = pack2(w1.z * kScoreScale, w1.w * kScoreScale);
-        }
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
         if (tid < 128)
@@ -287,25 +282,20 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
         unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
-        float dm[M], rdm[4];
-#pragma unroll
-        for (int j = 0; j < M; ++j) dm[j] = (ENV == RL4CO_ENV_CVRP) ? s_dem[g + 16 * j] : 0.f;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) rdm[k] = (ENV == RL4CO_ENV_CVRP) ? s_dem[4 * lane + k] : 0.f;
         const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b] : 0.f;
         float used = 0.f;
         auto cvrp_masks = [&](int at) {             // cvrp/env.py:137-149, both layouts
             unsigned f = 0, rf = 0;
 #pragma unroll
-            for (int j = 0; j < M; ++j) {
-                const bool exceeds = __fadd_rn(dm[j], used) > cap;
+            for (int j = 0; j < M; ++j) {           // demands re-read from shared memory: the register file is full
+                const bool exceeds = __fadd_rn(s_dem[g + 16 * j], used) > cap;
                 if (!exceeds && !((vis >> j) & 1u)) f |= 1u << j;
             }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const bool exceeds = __fadd_rn(rdm[k], used) > cap;
-                if (!exceeds && !((rvis >> k) & 1u)) rf |= 1u << k;
-            }
+            const float4 rdm = *reinterpret_cast<const float4 *>(s_dem + 4 * lane);
+            if (!(__fadd_rn(rdm.x, used) > cap) && !(rvis & 1u)) rf |= 1u;
+            if (!(__fadd_rn(rdm.y, used) > cap) && !(rvis & 2u)) rf |= 2u;
+            if (!(__fadd_rn(rdm.z, used) > cap) && !(rvis & 4u)) rf |= 4u;
+            if (!(__fadd_rn(rdm.w, used) > cap) && !(rvis & 8u)) rf |= 8u;
             f &= own;
             rf &= rown;
             if (g == 0) f &= ~1u;
@@ -416,11 +406,15 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) q2[i] = qbs2[i];
             }
-            if (ENV == RL4CO_ENV_CVRP) {
+            if (ENV == RL4CO_ENV_CVRP) {                // + (capacity - used) * remaining-capacity column
                 const float rem = __fsub_rn(cap, used);
                 const u64 rem2 = pack2(rem, rem);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) q2[i] = ffma2(wcs2[i], rem2, q2[i]);
+                const ulonglong2 w0 = *reinterpret_cast<const ulonglong2 *>(s_wc + dim0);
+                const ulonglong2 w1 = *(reinterpret_cast<const ulonglong2 *>(s_wc + dim0) + 1);
+                q2[0] = ffma2(w0.x, rem2, q2[0]);
+                q2[1] = ffma2(w0.y, rem2, q2[1]);
+                q2[2] = ffma2(w1.x, rem2, q2[2]);
+                q2[3] = ffma2(w1.y, rem2, q2[3]);
             }
             // ---- glimpse scores of the own nodes (attention.py:289-306), base-2 scaled
             float s[M];
