@@ -18,6 +18,7 @@ from .ops import (batchify, gather_by_index, get_num_starts, get_tour_length,  #
                   select_start_nodes, unbatchify)
 from .policy import AttentionModelDecoder, AttentionModelPolicy, POMOPolicy  # noqa: F401
 from .tensordict_compat import TensorDict  # noqa: F401
+from .training import reinforce_step, replay_masks, teacher_forced_log_likelihood  # noqa: F401
 from .transforms import StateAugmentation, dihedral_8_augmentation  # noqa: F401
 
 __version__ = "0.1.0"

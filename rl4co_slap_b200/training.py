@@ -1,0 +1,177 @@
+"""Training step for the rollout path: the rollout kernels produce the
+trajectories (inference only), this module re-evaluates their log-likelihood DIFFERENTIABLY so that
+REINFORCE can back-propagate into the decoder weights and, through ``h``, into the encoder.
+
+Because the actions are known, the autoregressive loop of ``ConstructivePolicy.forward``
+(rl4co/models/common/constructive/base.py:196-276, ``decode_type="evaluate"``, :206-207) collapses
+into ONE batched decoder pass over all steps: every step's context query, mask, glimpse, pointer
+logits and log-softmax are computed together with plain PyTorch ops (autograd does the backward),
+in the op order of rl4co/models/zoo/am/decoder.py:134-200, rl4co/models/nn/attention.py:263-309 and
+rl4co/utils/decoding.py:141-191.  The environment quantities that feed the decoder (action masks,
+remaining capacity) are replayed from the actions with the reference's own arithmetic
+(rl4co/envs/routing/tsp/env.py:67-93, cvrp/env.py:73-149, rl4co/envs/warehousing/slap/env.py:38-93).
+
+``reinforce_step`` is ``REINFORCE.shared_step`` + ``calculate_loss``
+(rl4co/models/rl/reinforce/reinforce.py:62-115): sample with the kernel, baseline, loss
+``((reward - bl) * ll).mean()`` with the sign convention of the reference, backward, optimiser step.
+Pure torch: runs on CUDA for training and on CPU for the parity tests against the oracle.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+
+def _exclusive_visited(actions: torch.Tensor, N: int) -> torch.Tensor:
+    """[R,T] int64 -> bool [R,T,N]: node n was chosen at some step < t."""
+    onehot = F.one_hot(actions, N).to(torch.int32)
+    return (onehot.cumsum(1) - onehot) > 0
+
+
+def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
+    """Action masks [R,T,N] (True = feasible), per-step validity [R,T] (False once the episode is done) and, for
+    cvrp, the used capacity [R,T] seen by the context of every step, replayed from ``actions`` [R,T]
+    (R = S * B, start-major as utils/ops.py:11-34)."""
+    R, T = actions.shape
+    N = td["locs"].shape[1]
+    dev = actions.device
+    if env_name == "tsp":       # tsp/env.py:78-81: the mask is "not visited yet"
+        return ~_exclusive_visited(actions, N), torch.ones(R, T, dtype=torch.bool, device=dev), None
+    if env_name == "slap":      # slap/env.py:95-129,86-88: depot never assignable, a location once
+        mask = ~_exclusive_visited(actions, N)
+        mask[:, :, 0] = False
+        return mask, torch.ones(R, T, dtype=torch.bool, device=dev), None
+    # cvrp/env.py:73-149 - sequential in the used capacity (fp32, the reference's order of operations)
+    demand = td["demand"].float()
+    cap = td["vehicle_capacity"].float().reshape(-1, 1)
+    if S > 1:
+        demand, cap = demand.repeat(S, 1), cap.repeat(S, 1)
+    used = torch.zeros(R, 1, device=dev)
+    visited = torch.zeros(R, N, dtype=torch.bool, device=dev)
+    cur = torch.zeros(R, dtype=torch.int64, device=dev)
+    masks, useds, valid = [], [], []
+    done = torch.zeros(R, dtype=torch.bool, device=dev)
+    rows = torch.arange(R, device=dev)
+    for t in range(T):
+        exceeds = demand + used > cap                                   # :139
+        mask_loc = visited[:, 1:] | exceeds                            # :142
+        mask_depot = (cur == 0) & ((~mask_loc).sum(-1) > 0)            # :145
+        masks.append(~torch.cat((mask_depot[:, None], mask_loc), -1))  # :148
+        useds.append(used[:, 0])
+        valid.append(~done)
+        a = actions[:, t]
+        sel = demand.gather(1, (a - 1).clamp(0, N - 2)[:, None])       # :76-79
+        used = (used + sel) * (a != 0).float()[:, None]                # :83-85
+        visited = visited.clone()
+        visited[rows, a] = True                                        # :88
+        done = done | (visited.sum(-1) == N)                           # :91
+        cur = a
+    return torch.stack(masks, 1), torch.stack(valid, 1), torch.stack(useds, 1)
+
+
+def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, actions: torch.Tensor,
+                                  num_starts: int = 0, temperature: Optional[float] = None,
+                                  tanh_clipping: Optional[float] = None, mask_logits: Optional[bool] = None,
+                                  return_sum: bool = True) -> torch.Tensor:
+    """Differentiable log-likelihood of ``actions`` [R,T] under the policy's decoder given the encoder
+    output ``h`` [B,N,E] (R = B, or S*B start-major with ``num_starts`` = S POMO starts whose forced first
+    action carries log-prob 0, utils/decoding.py:287-305).  Returns [R] (or [R,T])."""
+    dec = policy.decoder
+    E, H = dec.embed_dim, dec.num_heads
+    B, N, _ = h.shape
+    S = max(int(num_starts), 1)
+    R, T = actions.shape
+    assert R == B * S, f"actions has {R} rows, expected {B} x {S}"
+    temperature = float(policy.temperature if temperature is None else temperature)
+    tanh_clipping = float(policy.tanh_clipping if tanh_clipping is None else tanh_clipping)
+    mask_logits = bool(policy.mask_logits if mask_logits is None else mask_logits)
+    multistart = num_starts > 0
+    dev = h.device
+
+    mask, valid, used = replay_masks(env_name, td, actions, S)           # [R,T,N], [R,T], [R,T]
+    # ---- cache (am/decoder.py:208-237)
+    gk, gv, lk = dec.project_node_embeddings(h).chunk(3, dim=-1)          # [B,N,E] each
+    gctx = dec.project_fixed_context(h.mean(1)) if dec.use_graph_context else None   # [B,E]
+
+    # rollouts of instance b as extra queries: [R,T] start-major -> [B, L = S*T]
+    def per_instance(x):                                                  # [R,T,...] -> [B,S*T,...]
+        return x.reshape(S, B, T, *x.shape[2:]).transpose(0, 1).reshape(B, S * T, *x.shape[2:])
+    a_bl = per_instance(actions)                                          # [B,L]
+    L = S * T
+    prev = torch.cat((torch.zeros(R, 1, dtype=torch.int64, device=dev), actions[:, :-1]), 1)   # current node of step t
+    prev_bl = per_instance(prev)
+
+    # ---- context embedding (env_embeddings/context.py:47-71,102-137,317-331; examples/slap.py:50-63)
+    Wc = dec.context_embedding.project_context.weight
+    gather = lambda src, idx: src.gather(1, idx[..., None].expand(-1, -1, E))
+    if env_name == "tsp":
+        first_bl = per_instance(actions[:, :1].expand(-1, T))
+        ctx = gather(F.linear(h, Wc[:, :E]), first_bl) + gather(F.linear(h, Wc[:, E:]), prev_bl)
+        if not multistart:      # step 0: no first / current node yet -> W_placeholder (context.py:111-121)
+            ctx0 = F.linear(dec.context_embedding.W_placeholder, Wc)
+            step0 = (torch.arange(L, device=dev) % T == 0)[None, :, None]
+            ctx = torch.where(step0, ctx0.expand(B, L, E), ctx)
+    elif env_name == "cvrp":
+        cap = td["vehicle_capacity"].float().reshape(B, 1)
+        rem = cap.repeat(S, 1) - used                                     # [R,T]  (context.py:326-329)
+        ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
+    else:
+        ctx = torch.zeros(B, L, E, device=dev, dtype=h.dtype)
+    q = ctx if gctx is None else ctx + gctx[:, None, :]                   # decoder.py:141-142
+
+    # ---- pointer attention (nn/attention.py:263-309): masked multi-head glimpse, project_out, logits
+    m_bl = per_instance(mask)                                             # [B,L,N] True = feasible
+    heads = lambda x: x.reshape(B, -1, H, E // H).transpose(1, 2)         # [B,H,*,d]
+    glimpse = F.scaled_dot_product_attention(heads(q), heads(gk), heads(gv), attn_mask=m_bl[:, None])
+    glimpse = dec.pointer.project_out(glimpse.transpose(1, 2).reshape(B, L, E))
+    logits = torch.matmul(glimpse, lk.transpose(1, 2)) / math.sqrt(E)     # [B,L,N]
+    # ---- process_logits (utils/decoding.py:141-191)
+    if tanh_clipping > 0:
+        logits = torch.tanh(logits) * tanh_clipping
+    if mask_logits:
+        logits = logits.masked_fill(~m_bl, float("-inf"))
+    logp = F.log_softmax(logits / temperature, dim=-1).gather(-1, a_bl[..., None])[..., 0]   # [B,L]
+    keep = per_instance(valid)
+    if multistart:              # the forced start node has log-prob 0
+        keep = keep & (torch.arange(L, device=dev) % T != 0)[None]
+    logp = torch.where(keep, logp, torch.zeros_like(logp))
+    logp = logp.reshape(B, S, T).transpose(0, 1).reshape(R, T)            # back to start-major rows
+    return logp.sum(1) if return_sum else logp
+
+
+def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: Optional[str] = None,
+                   num_starts: Optional[int] = None, max_grad_norm: Optional[float] = 1.0) -> dict:
+    """One REINFORCE training step (reinforce.py:62-115, pomo/model.py:87-111): roll out with the fused kernel
+    (no autograd), re-evaluate the sampled trajectories' log-likelihood differentiably, loss
+    ``((reward - baseline) * log_likelihood).mean()`` on the negated... exactly ``-(advantage * ll).mean()`` as in
+    reinforce.py:103-106 with reward = -cost, backward, clip, optimiser step.  ``baseline``: None (no baseline),
+    "shared" (POMO mean over the starts of an instance, baselines.py:57-61) or a tensor [R]."""
+    decode_type = decode_type or policy.train_decode_type
+    multistart = "multistart" in decode_type
+    with torch.no_grad():
+        out = policy(td, env, phase="train", decode_type=decode_type, num_starts=num_starts,
+                     return_actions=True)
+    actions, reward = out["actions"], out["reward"]
+    B = td["locs"].shape[0]
+    S = actions.shape[0] // B if multistart else 0
+    h, _ = policy.encoder(td)
+    ll = teacher_forced_log_likelihood(policy, td, env.name, h.float(), actions, num_starts=S)
+    if baseline is None:
+        bl = torch.zeros_like(reward)
+    elif isinstance(baseline, str) and baseline == "shared":
+        bl = reward.reshape(max(S, 1), B).mean(0, keepdim=True).expand(max(S, 1), B).reshape(-1)
+    else:
+        bl = baseline
+    advantage = reward - bl
+    loss = -(advantage * ll).mean()
+    if optimizer is not None:
+        optimizer.zero_grad(set_to_none=True)
+        loss.backward()
+        if max_grad_norm:
+            torch.nn.utils.clip_grad_norm_(policy.parameters(), max_grad_norm)
+        optimizer.step()
+    return {"loss": loss.detach(), "reward": reward, "log_likelihood": ll.detach(), "actions": actions,
+            "kernel_log_likelihood": out["log_likelihood"]}

@@ -1,0 +1,119 @@
+"""Training step: the differentiable teacher-forced log-likelihood of
+rl4co_slap_b200/training.py against the oracle (CPU, values and autograd gradients) and against the
+rollout kernels' own log-likelihood (GPU), plus one REINFORCE step end to end."""
+import numpy as np
+import pytest
+import torch
+
+import rl4co_slap_b200 as R
+from oracle import port
+from rl4co_slap_b200.training import reinforce_step, replay_masks, teacher_forced_log_likelihood
+from tests.helpers import env_of, fixture, gen_td, load_policy, oracle_reset, oracle_weights, t
+
+RTOL = 1e-5
+
+
+def _cpu_td(name, fx):
+    if name == "cvrp":
+        return {"locs": t(fx["reset.locs"]), "demand": t(fx["gen.demand"]),
+                "vehicle_capacity": t(fx["reset.vehicle_capacity"])}
+    return {"locs": t(fx["gen.locs"])}
+
+
+@pytest.mark.parametrize("case", ("tsp20", "tsp50", "cvrp20", "cvrp50", "slap50"))
+def test_teacher_forced_ll_matches_oracle_cpu(case):
+    """values: the batched all-steps pass equals the oracle's step-by-step evaluate of the reference's tours"""
+    fx, name = fixture(case), env_of(case)
+    pol = load_policy(name, "cpu")
+    h, acts = t(fx["hidden"]), t(fx["greedy.actions"])
+    with torch.no_grad():
+        lp = teacher_forced_log_likelihood(pol, _cpu_td(name, fx), name, h, acts, return_sum=False)
+    np.testing.assert_allclose(lp.numpy(), fx["greedy.logprobs"], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(lp.sum(1).numpy(), fx["greedy.ll"], rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", ("tsp20", "cvrp20"))
+def test_teacher_forced_ll_multistart_cpu(case):
+    fx, name = fixture(case), env_of(case)
+    pol = load_policy(name, "cpu")
+    S = int(fx["ms_greedy.num_starts"])
+    with torch.no_grad():
+        ll = teacher_forced_log_likelihood(pol, _cpu_td(name, fx), name, t(fx["hidden"]), t(fx["ms_greedy.actions"]),
+                                           num_starts=S)
+    np.testing.assert_allclose(ll.numpy(), fx["ms_greedy.ll"], rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", ("tsp20", "cvrp20"))
+def test_replayed_masks_match_reference_trace(case):
+    """the masks fed to the decoder are the reference's per-step action masks bit for bit"""
+    fx, name = fixture(case), env_of(case)
+    acts = t(fx["actions"]) if "actions" in fx.files else t(fx["greedy.actions"])
+    mask, valid, used = replay_masks(name, _cpu_td(name, fx), acts)
+    assert np.array_equal(mask[:, 0].numpy(), fx["reset.action_mask"].astype(bool))
+    for s in range(min(acts.shape[1] - 1, 6)):
+        if f"step{s}.action_mask" in fx.files and "actions" in fx.files:
+            assert np.array_equal(mask[:, s + 1].numpy(), fx[f"step{s}.action_mask"].astype(bool)), s
+
+
+@pytest.mark.parametrize("case", ("tsp20", "cvrp20", "slap50"))
+def test_gradients_match_oracle_autograd_cpu(case):
+    """d ll / d (decoder weights, h) of the batched pass equals autograd through the oracle's reference-order loop"""
+    fx, name = fixture(case), env_of(case)
+    pol = load_policy(name, "cpu").double()
+    h = t(fx["hidden"]).double().requires_grad_(True)
+    acts = t(fx["greedy.actions"])
+    # decoder in float64, environment state (capacities, masks) in float32 like the reference's
+    ll = teacher_forced_log_likelihood(pol, _cpu_td(name, fx), name, h, acts)
+    ll.sum().backward()
+    W = {k: v.double().requires_grad_(True) for k, v in oracle_weights(name).items()}
+    h2 = t(fx["hidden"]).double().requires_grad_(True)
+    ref = port.am_rollout(name, oracle_reset(name, fx), h2, W, actions=acts, check_solution=False)["log_likelihood"]
+    ref.sum().backward()
+    torch.testing.assert_close(ll.detach(), ref.detach(), rtol=1e-9, atol=1e-9)
+    torch.testing.assert_close(h.grad, h2.grad, rtol=1e-7, atol=1e-9)
+    d = pol.decoder
+    torch.testing.assert_close(d.project_node_embeddings.weight.grad, W["Wnode"].grad, rtol=1e-7, atol=1e-9)
+    torch.testing.assert_close(d.pointer.project_out.weight.grad, W["Wout"].grad, rtol=1e-7, atol=1e-9)
+    torch.testing.assert_close(d.project_fixed_context.weight.grad, W["Wfixed"].grad, rtol=1e-7, atol=1e-9)
+    if name != "slap":
+        torch.testing.assert_close(d.context_embedding.project_context.weight.grad, W["Wctx"].grad, rtol=1e-7, atol=1e-9)
+    if name == "tsp":
+        torch.testing.assert_close(d.context_embedding.W_placeholder.grad, W["Wph"].grad, rtol=1e-7, atol=1e-9)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,decode_type,S", (("tsp", "sampling", 0), ("cvrp", "sampling", 0),
+                                                ("cvrp", "multistart_sampling", 7), ("tsp", "multistart_sampling", 5)))
+def test_differentiable_ll_matches_kernel_ll(name, decode_type, S, dev):
+    """on sampled trajectories the differentiable pass reproduces the kernel's log-likelihood"""
+    torch.manual_seed(11)
+    pol, env = load_policy(name, dev), R.get_env(name, device=dev, generator_params=dict(num_loc=20))
+    td = env.reset(batch_size=[48])
+    with torch.no_grad():
+        out = pol(td, env, decode_type=decode_type, num_starts=S or None, return_actions=True, return_hidden=True)
+        ll = teacher_forced_log_likelihood(pol, td, name, out["hidden"].node_embeddings, out["actions"], num_starts=S)
+    torch.testing.assert_close(ll, out["log_likelihood"], rtol=RTOL, atol=2e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,decode_type,baseline", (("tsp", "sampling", None), ("cvrp", "multistart_sampling", "shared")))
+def test_reinforce_step_trains(name, decode_type, baseline, dev):
+    """a few REINFORCE steps on one fixed batch: finite loss, gradients reach encoder and decoder, and the
+    log-likelihood of the first step's own samples goes up when they had a positive advantage on average"""
+    torch.manual_seed(3)
+    pol = R.AttentionModelPolicy(env_name=name, num_encoder_layers=2).to(dev)
+    env = R.get_env(name, device=dev, generator_params=dict(num_loc=20))
+    td = env.reset(batch_size=[64])
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-3)
+    before = [p.detach().clone() for p in pol.parameters()]
+    first = reinforce_step(pol, env, td, opt, baseline=baseline, decode_type=decode_type, num_starts=6 if baseline else None)
+    assert torch.isfinite(first["loss"])
+    torch.testing.assert_close(first["log_likelihood"], first["kernel_log_likelihood"], rtol=1e-4, atol=1e-4)
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in pol.parameters() if p.requires_grad)
+    changed = sum(int(not torch.equal(a, b.detach())) for a, b in zip(before, pol.parameters()))
+    assert changed >= len(before) - 2, "the optimiser step did not reach (almost) every parameter"
+    rewards = [first["reward"].mean().item()]
+    for _ in range(30):
+        rewards.append(reinforce_step(pol, env, td, opt, baseline="shared" if baseline else first["reward"].mean(),
+                                      decode_type=decode_type, num_starts=6 if baseline else None)["reward"].mean().item())
+    assert np.mean(rewards[-5:]) > np.mean(rewards[:5]), f"no improvement on the training batch: {rewards[:5]} -> {rewards[-5:]}"
