@@ -1,12 +1,12 @@
-// K2 (TSP, greedy, single start) - the register-file rollout of am_rollout_rf.cu specialised for
-// the headline configuration and extended with NODE COMPACTION.
+// K2 (TSP, greedy or sampling, single start) - the register-file rollout of am_rollout_rf.cu specialised
+// for the headline configuration and extended with NODE COMPACTION.
 //
 // Same ownership and the same per-step arithmetic as am_rollout_rf.cu (warp = attention head,
 // lane = (half head, node group), K / V / folded-L rows of the thread's nodes in registers,
 // FFMA2 mat-vecs, two block barriers per step).  What is different:
 //   * everything the generic kernel decides at run time (environment, decoding mode, logit
 //     post-processing variant, whether the per-step logits fit in shared memory) is fixed here:
-//     TSP (tsp/env.py:67-120), greedy (utils/decoding.py:371-379,410-419), tanh clipping > 0,
+//     TSP (tsp/env.py:67-120), greedy or sampling as a template parameter (utils/decoding.py:371-397,410-449), tanh clipping > 0,
 //     temperature 1, masked logits, logits of every step kept for the log-probabilities of the
 //     epilogue.  Anything else is routed to am_rollout_rf.cu / am_rollout.cu by the dispatcher.
 //   * a TSP tour never returns to a visited node, so the rows of visited nodes are dead weight in
@@ -131,14 +131,51 @@ struct Ctx {
     unsigned candk[4];      // (slot << 8 | node) of the reader-layout slots 4 lane .. 4 lane + 3
     int cur, t, status;
     float clip;
+    uint64_t seed, offset, r;   // sampling: Philox key, counter base, rollout index (utils/decoding.py:381-397)
     void *trace;
     int trow;               // RF_TRACE: first spare row of the trace buffer
 };
 
+// Inverse-CDF sample of Categorical(softmax(x)) with one Philox uniform; the lane's NV logits are consecutive in
+// slot order (lane-major).  Every warp does the same arithmetic, so all of them agree.  Returns the key
+// (slot << 8 | node) of the picked slot, 0x7fffffff if nothing is feasible.
+template <int NV>
+__device__ __forceinline__ unsigned sample_key(const float (&x)[NV], const unsigned (&key)[NV], float gm, float u01) {
+    const int lane = threadIdx.x & 31;
+    float e[NV], ls = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        e[k] = (x[k] == -INFINITY) ? 0.f : ex2f((x[k] - gm) * kLog2e);
+        ls += e[k];
+    }
+    float incl = ls;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const float up = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += up;
+    }
+    const float total = __shfl_sync(kFull, incl, 31);
+    const float u = u01 * total;
+    float run = incl - ls;
+    unsigned pick = 0x7fffffffu, lastf = 0x7fffffffu;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        if (e[k] > 0.f) {
+            lastf = key[k];
+            run += e[k];
+            if (pick == 0x7fffffffu && run > u) pick = key[k];
+        }
+    }
+    const unsigned has = __ballot_sync(kFull, pick != 0x7fffffffu);
+    const unsigned any = __ballot_sync(kFull, lastf != 0x7fffffffu);
+    return has ? __shfl_sync(kFull, pick, __ffs(has) - 1)
+               : (any ? __shfl_sync(kFull, lastf, 31 - __clz(any)) : 0x7fffffffu);
+}
+
 // ---------------------------------------------------------------------------------------------
 // decode steps t .. t_stop-1 with MM rows of 16 slots
 // ---------------------------------------------------------------------------------------------
-template <int MM, typename SetQ>
+template <int MM, bool SAMPLING, typename SetQ>
 __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const u64 (&V2)[MM][4], const u64 (&L2)[MM][4],
                                           const int t_stop, unsigned char *smem, SetQ &&set_first) {
     float *spl = reinterpret_cast<float *>(smem + OFF_PL);
@@ -169,6 +206,8 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
 
     while (c.t < t_stop) {
         TG_TRACE_AT(0);
+        // the step's uniform depends on (seed, rollout, step) only: drawn here, off the selection's critical path
+        const float u01 = SAMPLING ? philox_uniform(c.seed, c.offset, c.r, (uint32_t)c.t) : 0.f;
         // ---- query of this half head (decoder.py:141-142), pre-scaled; step 0 has no context row
         u64 q2[4];
         {
@@ -285,10 +324,15 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
 #pragma unroll
             for (int k = 1; k < NS; ++k) lm = fmaxf(lm, xv[k]);
             gm = redux_max(lm);
-            unsigned cand = 0x7fffffffu;
+            if (SAMPLING) {
+                static_assert(!SAMPLING || NS == 1, "slot order of the fused layout is lane-major only with one slot per lane");
+                win = sample_key(xv, fkey, gm, u01);
+            } else {
+                unsigned cand = 0x7fffffffu;
 #pragma unroll
-            for (int k = NS - 1; k >= 0; --k) cand = xv[k] == gm ? fkey[k] : cand;
-            win = redux_min_u32(cand);
+                for (int k = NS - 1; k >= 0; --k) cand = xv[k] == gm ? fkey[k] : cand;
+                win = redux_min_u32(cand);
+            }
             // one warp keeps the step's logits for the epilogue (the other slots of the row were set to -inf on entry)
             if (warp == (c.t & (kWarps - 1))) {
 #pragma unroll
@@ -317,12 +361,17 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
         float x0, x1, x2, x3;
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x0), "=f"(x1), "=f"(x2), "=f"(x3) : "r"(c.x_addr + 16u * lane));
         gm = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
-        unsigned cand = 0x7fffffffu;
-        cand = x3 == gm ? c.candk[3] : cand;
-        cand = x2 == gm ? c.candk[2] : cand;
-        cand = x1 == gm ? c.candk[1] : cand;
-        cand = x0 == gm ? c.candk[0] : cand;
-        win = redux_min_u32(cand);
+        if (SAMPLING) {
+            const float xs4[4] = {x0, x1, x2, x3};
+            win = sample_key(xs4, c.candk, gm, u01);
+        } else {
+            unsigned cand = 0x7fffffffu;
+            cand = x3 == gm ? c.candk[3] : cand;
+            cand = x2 == gm ? c.candk[2] : cand;
+            cand = x1 == gm ? c.candk[1] : cand;
+            cand = x0 == gm ? c.candk[0] : cand;
+            win = redux_min_u32(cand);
+        }
         }
         if (win == 0x7fffffffu) win = reinterpret_cast<const int *>(smem + OFF_NODE)[warp * 128];   // NaN logits: slot 0
         const int slot = (int)(win >> 8), node = (int)(win & 0xffu);
@@ -409,7 +458,7 @@ __device__ __forceinline__ void compact(Ctx &c, const u64 (&Ko)[MO][4], const u6
     for (int k = 0; k < 4; ++k) c.candk[k] = ((unsigned)(4 * lane + k) << 8) | (unsigned)(node_w[4 * lane + k] & 0xff);
 }
 
-template <int M0>
+template <int M0, bool SAMPLING>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -531,6 +580,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         c.t = 0;
         c.status = 0;
         c.clip = a.tanh_clipping;
+        c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)b;
         c.c_addr = smem_u32(cbuf + (size_t)buf * N * E + dim0);
         c.x_addr = smem_u32(sxs);
 #ifdef RF_TRACE
@@ -553,7 +603,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         // after t steps N - t nodes are unvisited: 4 rows hold them from t = N - 64 on, 2 rows from t = N - 32
         if (M0 > 4) {
             const int stop = N - 64 < t_end ? N - 64 : t_end;
-            run_stage<M0>(c, K2, V2, L2, stop, smem, set_first);
+            run_stage<M0, SAMPLING>(c, K2, V2, L2, stop, smem, set_first);
         }
         if (M0 > 4 ? c.t < t_end : true) {
             u64 K4[4][4], V4[4][4], L4[4][4];
@@ -568,7 +618,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             if (M0 >= 4) {
                 const int stop = N - 32 < t_end ? N - 32 : t_end;
                 if (RL4CO_TSPG_FUSED_ROWS >= 4) fill_rows(c.t);
-                run_stage<4>(c, K4, V4, L4, stop, smem, set_first);
+                run_stage<4, SAMPLING>(c, K4, V4, L4, stop, smem, set_first);
             }
             if (c.t < t_end) {
                 u64 Ka[2][4], Va[2][4], La[2][4];
@@ -581,7 +631,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                         for (int i = 0; i < 4; ++i) { Ka[j][i] = K2[j < M0 ? j : 0][i]; Va[j][i] = V2[j < M0 ? j : 0][i]; La[j][i] = L2[j < M0 ? j : 0][i]; }
                 }
                 if (RL4CO_TSPG_FUSED_ROWS < 4 || M0 < 4) fill_rows(c.t);
-                run_stage<2>(c, Ka, Va, La, t_end, smem, set_first);
+                run_stage<2, SAMPLING>(c, Ka, Va, La, t_end, smem, set_first);
             }
         }
 
@@ -657,7 +707,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     }
 }
 
-template <int M0>
+template <int M0, bool SAMPLING>
 static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -667,13 +717,13 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         if (sm_count <= 0) sm_count = 148;
     }
     const size_t total = smem_total(a.N, a.T);
-    cudaError_t e = cudaFuncSetAttribute(am_rollout_tsp_greedy_kernel<M0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
+    cudaError_t e = cudaFuncSetAttribute(am_rollout_tsp_greedy_kernel<M0, SAMPLING>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
     if (e != cudaSuccess) {
         set_error("am_rollout(tsp greedy): cannot reserve %zu B of shared memory: %s", total, cudaGetErrorString(e));
         return 2;
     }
     const int64_t grid = a.B < sm_count ? a.B : sm_count;   // persistent: one CTA per SM
-    am_rollout_tsp_greedy_kernel<M0><<<(unsigned)grid, kThreads, total, stream>>>(a);
+    am_rollout_tsp_greedy_kernel<M0, SAMPLING><<<(unsigned)grid, kThreads, total, stream>>>(a);
     RL4CO_CHECK_LAUNCH("am_rollout(tsp greedy)");
     return 0;
 }
@@ -684,16 +734,21 @@ bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a) {
 #ifndef RF_TRACE
     if (a.logp_all != nullptr) return false;
 #endif
-    if (a.env != RL4CO_ENV_TSP || a.mode != RL4CO_MODE_GREEDY || a.S > 1 || a.multistart) return false;
+    if (a.env != RL4CO_ENV_TSP || a.mode == RL4CO_MODE_EVALUATE || a.S > 1 || a.multistart) return false;
     if (!(a.tanh_clipping > 0.f) || a.temperature != 1.f || a.mask_logits == 0) return false;
     if (a.N > 112 || a.T > tspg::kMaxT || a.N < 2) return false;
     return tspg::smem_total(a.N, a.T) <= (size_t)227 * 1024;
 }
 
 int launch_rollout_tsp_greedy(const rl4co_am_rollout_args &a, cudaStream_t stream) {
-    if (a.N <= 32) return tspg::launch<2>(a, stream);
-    if (a.N <= 64) return tspg::launch<4>(a, stream);
-    return tspg::launch<7>(a, stream);
+    if (a.mode == RL4CO_MODE_SAMPLING) {
+        if (a.N <= 32) return tspg::launch<2, true>(a, stream);
+        if (a.N <= 64) return tspg::launch<4, true>(a, stream);
+        return tspg::launch<7, true>(a, stream);
+    }
+    if (a.N <= 32) return tspg::launch<2, false>(a, stream);
+    if (a.N <= 64) return tspg::launch<4, false>(a, stream);
+    return tspg::launch<7, false>(a, stream);
 }
 
 }  // namespace rl4co

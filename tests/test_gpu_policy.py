@@ -300,6 +300,16 @@ def test_tsp_greedy_compaction_kernel_sizes(N, B, dev):
                           actions=out["actions"][idx].cpu())
     torch.testing.assert_close(out["log_likelihood"][idx].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
     torch.testing.assert_close(out["reward"][idx].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+    # the same kernel in sampling mode (Philox inverse-CDF in slot order): feasible tours, ll of the sampled tour
+    with torch.inference_mode():
+        smp = pol(td, env, decode_type="sampling", return_actions=True, hidden=h)
+        ev = pol(td, env, actions=smp["actions"], hidden=h)
+    assert torch.equal(smp["actions"].sort(1).values, torch.arange(N, device=dev).expand(B, N)), "not a permutation"
+    _, r = env.replay(td, smp["actions"], check=True)
+    torch.testing.assert_close(r, smp["reward"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(ev["log_likelihood"], smp["log_likelihood"], rtol=1e-5, atol=2e-5)
+    if N > 3:
+        assert not torch.equal(smp["actions"], out["actions"]), "sampling reproduced the greedy tours"
 
 
 @pytest.mark.parametrize("M,nt", ((1, 1), (100, 3), (128 * 7 + 5, 5), (148 * 128 * 3 + 17, 4)))

@@ -1,6 +1,6 @@
 """K2-only timing (CUDA events) of the single-start rollout kernels on random TSP instances.
 
-    python tools/time_k2.py [N] [instances per SM] [impl]     # impl: 0 auto, 2 no TSP-greedy specialisation
+    python tools/time_k2.py [N] [instances per SM] [impl] [greedy|sampling]     # impl: 0 auto, 2 generic kernel
 """
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -12,6 +12,7 @@ import rl4co_slap_b200 as R
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 per_sm = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 impl = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+mode = {"greedy": _lib.MODE_GREEDY, "sampling": _lib.MODE_SAMPLING}[sys.argv[4] if len(sys.argv) > 4 else "greedy"]
 dev = torch.device("cuda:0")
 torch.manual_seed(1234)
 B, T = 148 * per_sm, N
@@ -32,7 +33,8 @@ ll, rew = torch.empty(B, device=dev), torch.empty(B, device=dev)
 steps = torch.empty(B, dtype=torch.int32, device=dev)
 status = _lib.new_status(dev)
 a = _lib.AmRolloutArgs()
-a.env, a.mode, a.B, a.S, a.multistart, a.num_loc = 0, _lib.MODE_GREEDY, B, 0, 0, N
+a.env, a.mode, a.B, a.S, a.multistart, a.num_loc = 0, mode, B, 0, 0, N
+a.seed, a.offset = 1234, 0
 a.N, a.T, a.P, a.O, a.K, a.n_tables = N, T, 0, 0, 0, nt
 a.temperature, a.tanh_clipping, a.mask_logits = 1.0, 10.0, 1
 a.tables, a.gctx, a.q0, a.locs = _lib.ptr(tables), _lib.ptr(gctx), _lib.ptr(q0), _lib.ptr(locs)
@@ -49,5 +51,5 @@ for i in range(6):
     ts.append(e0.elapsed_time(e1))
 ms = sorted(ts[1:])[len(ts[1:]) // 2]
 clk = ms * 1e-3 * 1.965e9 / per_sm
-print(f"N={N} impl={impl} B={B}: {ms:.3f} ms  {B / ms * 1e3 / 1e6:.3f} M rollouts/s  {clk:.0f} clk/instance  {clk / T:.0f} clk/step"
+print(f"N={N} impl={impl} mode={mode} B={B}: {ms:.3f} ms  {B / ms * 1e3 / 1e6:.3f} M rollouts/s  {clk:.0f} clk/instance  {clk / T:.0f} clk/step"
       f"  mean reward {rew.mean().item():.5f} ll {ll.mean().item():.5f} status {int(status.item())}")
