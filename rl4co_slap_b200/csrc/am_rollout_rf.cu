@@ -393,6 +393,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         // ================================================== decode loop ==================
         while (!done && t < t_end) {
             RF_TRACE_AT(0);
+            float G[4] = {0.f, 0.f, 0.f, 0.f};
+            if (a.mode == RL4CO_MODE_SAMPLING) gumbel4(a.seed, a.offset, (uint64_t)r, (uint32_t)t, lane, G);
             // ---- query of this half head (decoder.py:141-142), pre-scaled
             u64 q2[4];
             if (HAS_C && use_c) {
@@ -561,34 +563,17 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 act = s_ain[t];
                 if (act < 0) { status |= RL4CO_ST_ACTION_RANGE; act = 0; }
             } else {
-                // inverse-CDF sample of Categorical(exp(logp)) with one Philox uniform; every warp
-                // does the same arithmetic, so all of them agree on the action
-                float e[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) e[k] = (x[k] == -INFINITY) ? 0.f : ex2f((x[k] - gm) * kLog2e);
-                const float ls = (e[0] + e[1]) + (e[2] + e[3]);
-                float incl = ls;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const float up = __shfl_up_sync(kFull, incl, o);
-                    if (lane >= o) incl += up;
-                }
-                const float total = __shfl_sync(kFull, incl, 31);
-                const float u = philox_uniform(a.seed, a.offset, (uint64_t)r, (uint32_t)t) * total;
-                float run = incl - ls;
-                int pick = -1, lastf = -1;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    if (e[k] > 0.f) {
-                        lastf = 4 * lane + k;
-                        run += e[k];
-                        if (pick < 0 && run > u) pick = 4 * lane + k;
-                    }
-                }
-                const unsigned has = __ballot_sync(kFull, pick >= 0);
-                const unsigned any = __ballot_sync(kFull, lastf >= 0);
-                act = has ? __shfl_sync(kFull, pick, __ffs(has) - 1)
-                          : (any ? __shfl_sync(kFull, lastf, 31 - __clz(any)) : 0);
+                // Gumbel-max sample of Categorical(exp(logp)) (rollout_util.cuh): arg-max of logits + noise; the
+                // noise was drawn at the top of the step, every warp has the same, so all of them agree
+                const float y0 = x[0] + G[0], y1 = x[1] + G[1], y2 = x[2] + G[2], y3 = x[3] + G[3];
+                const float ym = redux_max(fmaxf(fmaxf(y0, y1), fmaxf(y2, y3)));
+                unsigned cand = 0x7fffffffu;
+                cand = y3 == ym ? 4u * lane + 3u : cand;
+                cand = y2 == ym ? 4u * lane + 2u : cand;
+                cand = y1 == ym ? 4u * lane + 1u : cand;
+                cand = y0 == ym ? 4u * lane : cand;
+                const unsigned win = redux_min_u32(cand);
+                act = win < (unsigned)N ? (int)win : 0;
             }
             // feasibility of the chosen action (utils/decoding.py:377-379,393-395): its owner lane checks
             if (lane == (act >> 2) && !((ralive >> (act & 3)) & 1u)) status |= RL4CO_ST_INFEASIBLE_ACTION;

@@ -136,42 +136,6 @@ struct Ctx {
     int trow;               // RF_TRACE: first spare row of the trace buffer
 };
 
-// Inverse-CDF sample of Categorical(softmax(x)) with one Philox uniform; the lane's NV logits are consecutive in
-// slot order (lane-major).  Every warp does the same arithmetic, so all of them agree.  Returns the key
-// (slot << 8 | node) of the picked slot, 0x7fffffff if nothing is feasible.
-template <int NV>
-__device__ __forceinline__ unsigned sample_key(const float (&x)[NV], const unsigned (&key)[NV], float gm, float u01) {
-    const int lane = threadIdx.x & 31;
-    float e[NV], ls = 0.f;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        e[k] = (x[k] == -INFINITY) ? 0.f : ex2f((x[k] - gm) * kLog2e);
-        ls += e[k];
-    }
-    float incl = ls;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const float up = __shfl_up_sync(kFull, incl, o);
-        if (lane >= o) incl += up;
-    }
-    const float total = __shfl_sync(kFull, incl, 31);
-    const float u = u01 * total;
-    float run = incl - ls;
-    unsigned pick = 0x7fffffffu, lastf = 0x7fffffffu;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        if (e[k] > 0.f) {
-            lastf = key[k];
-            run += e[k];
-            if (pick == 0x7fffffffu && run > u) pick = key[k];
-        }
-    }
-    const unsigned has = __ballot_sync(kFull, pick != 0x7fffffffu);
-    const unsigned any = __ballot_sync(kFull, lastf != 0x7fffffffu);
-    return has ? __shfl_sync(kFull, pick, __ffs(has) - 1)
-               : (any ? __shfl_sync(kFull, lastf, 31 - __clz(any)) : 0x7fffffffu);
-}
-
 // ---------------------------------------------------------------------------------------------
 // decode steps t .. t_stop-1 with MM rows of 16 slots
 // ---------------------------------------------------------------------------------------------
@@ -206,8 +170,10 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
 
     while (c.t < t_stop) {
         TG_TRACE_AT(0);
-        // the step's uniform depends on (seed, rollout, step) only: drawn here, off the selection's critical path
-        const float u01 = SAMPLING ? philox_uniform(c.seed, c.offset, c.r, (uint32_t)c.t) : 0.f;
+        // sampling = arg-max of logits + Gumbel noise (rollout_util.cuh); the noise depends on (seed, rollout, step,
+        // lane) only: drawn here, off the selection's critical path
+        float G[4] = {0.f, 0.f, 0.f, 0.f};
+        if (SAMPLING) gumbel4(c.seed, c.offset, c.r, (uint32_t)c.t, lane, G);
         // ---- query of this half head (decoder.py:141-142), pre-scaled; step 0 has no context row
         u64 q2[4];
         {
@@ -323,16 +289,20 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
             float lm = xv[0];
 #pragma unroll
             for (int k = 1; k < NS; ++k) lm = fmaxf(lm, xv[k]);
-            gm = redux_max(lm);
-            if (SAMPLING) {
-                static_assert(!SAMPLING || NS == 1, "slot order of the fused layout is lane-major only with one slot per lane");
-                win = sample_key(xv, fkey, gm, u01);
-            } else {
-                unsigned cand = 0x7fffffffu;
+            gm = redux_max(lm);                     // max logit: the epilogue's log-sum-exp shift
+            float yv[NS], ym = gm;
 #pragma unroll
-                for (int k = NS - 1; k >= 0; --k) cand = xv[k] == gm ? fkey[k] : cand;
-                win = redux_min_u32(cand);
+            for (int k = 0; k < NS; ++k) yv[k] = xv[k];
+            if (SAMPLING) {
+                ym = -INFINITY;
+#pragma unroll
+                for (int k = 0; k < NS; ++k) { yv[k] = xv[k] + G[k]; ym = fmaxf(ym, yv[k]); }
+                ym = redux_max(ym);
             }
+            unsigned cand = 0x7fffffffu;
+#pragma unroll
+            for (int k = NS - 1; k >= 0; --k) cand = yv[k] == ym ? fkey[k] : cand;
+            win = redux_min_u32(cand);
             // one warp keeps the step's logits for the epilogue (the other slots of the row were set to -inf on entry)
             if (warp == (c.t & (kWarps - 1))) {
 #pragma unroll
@@ -361,17 +331,17 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
         float x0, x1, x2, x3;
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x0), "=f"(x1), "=f"(x2), "=f"(x3) : "r"(c.x_addr + 16u * lane));
         gm = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
+        float ym = gm;
         if (SAMPLING) {
-            const float xs4[4] = {x0, x1, x2, x3};
-            win = sample_key(xs4, c.candk, gm, u01);
-        } else {
-            unsigned cand = 0x7fffffffu;
-            cand = x3 == gm ? c.candk[3] : cand;
-            cand = x2 == gm ? c.candk[2] : cand;
-            cand = x1 == gm ? c.candk[1] : cand;
-            cand = x0 == gm ? c.candk[0] : cand;
-            win = redux_min_u32(cand);
+            x0 += G[0]; x1 += G[1]; x2 += G[2]; x3 += G[3];
+            ym = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
         }
+        unsigned cand = 0x7fffffffu;
+        cand = x3 == ym ? c.candk[3] : cand;
+        cand = x2 == ym ? c.candk[2] : cand;
+        cand = x1 == ym ? c.candk[1] : cand;
+        cand = x0 == ym ? c.candk[0] : cand;
+        win = redux_min_u32(cand);
         }
         if (win == 0x7fffffffu) win = reinterpret_cast<const int *>(smem + OFF_NODE)[warp * 128];   // NaN logits: slot 0
         const int slot = (int)(win >> 8), node = (int)(win & 0xffu);

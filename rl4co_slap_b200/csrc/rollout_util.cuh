@@ -64,6 +64,24 @@ __device__ __forceinline__ float philox_uniform(uint64_t seed, uint64_t offset, 
     return (float)(o.x >> 8) * (1.0f / 16777216.0f);   // [0,1)
 }
 
+// Gumbel-max sampling (register-file kernels): argmax_n (x_n + G_n), G_n = -ln(-ln u_n) i.i.d., picks n with
+// probability softmax(x)_n - the Categorical(exp(logp)) draw of utils/decoding.py:381-397 without the prefix
+// scan over the probabilities.  The noise depends on (seed, rollout, step, lane) only, so it is drawn before
+// the step's logits exist and the selection itself is the greedy arg-max on x + G.  One Philox4x32-10 call
+// gives a lane the four uniforms of its four nodes; every warp draws the same noise, so all warps agree.
+__device__ __forceinline__ void gumbel4(uint64_t seed, uint64_t offset, uint64_t r, uint32_t t, int lane, float (&G)[4]) {
+    const uint4 c = make_uint4((uint32_t)(offset + t), (uint32_t)((offset + t) >> 32), (uint32_t)r,
+                               (uint32_t)(r >> 32) ^ ((uint32_t)(lane + 1) << 24));
+    const uint4 o = philox4x32_10(c, make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const uint32_t w[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float u = ((float)(w[k] >> 8) + 0.5f) * (1.0f / 16777216.0f);     // (0,1)
+        // -ln(-ln u) = -ln2 * log2(-ln2 * log2 u)
+        G[k] = -0.6931471805599453f * __log2f(-0.6931471805599453f * __log2f(u));
+    }
+}
+
 // closed tour through the K storage locations of one order (slap/env.py:136-142)
 __device__ __forceinline__ float slap_order_len(const float2 *locs, const int *assign,
                                                 const int64_t *order, int K) {
