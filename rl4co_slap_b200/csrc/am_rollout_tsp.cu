@@ -55,7 +55,8 @@ constexpr size_t OFF_LOCS = OFF_NODE + (size_t)kWarps * 128 * 4;    // coordinat
 constexpr size_t OFF_PART = OFF_LOCS + 128 * 8;
 constexpr size_t OFF_BAR = OFF_PART + 64 * 4;
 constexpr size_t OFF_SCR = OFF_BAR + 16;                            // per warp compaction scratch [64 slots][16 dims]
-constexpr size_t OFF_XS = OFF_SCR + (size_t)kWarps * kScrSlots * 16 * 4;   // kept logits [T][128]
+constexpr size_t OFF_NOISE = OFF_SCR + (size_t)kWarps * kScrSlots * 16 * 4;  // sampling: Gumbel noise of 16 steps [16][128]
+constexpr size_t OFF_XS = OFF_NOISE + (size_t)16 * 128 * 4;        // kept logits [T][128]
 __host__ __device__ inline size_t off_c(int T) { return OFF_XS + (size_t)T * 128 * 4; }      // context table x2
 __host__ __device__ inline size_t smem_total(int N, int T) { return off_c(T) + (size_t)2 * N * E * 4; }
 
@@ -136,6 +137,15 @@ struct Ctx {
     int trow;               // RF_TRACE: first spare row of the trace buffer
 };
 
+// Sampling noise.  Every warp needs the same 128 Gumbel values per step; instead of eight redundant Philox calls
+// per step, warp w draws the noise of step t0 + 8 + w once every eight steps (t0 = multiple of 8) into a ring of
+// 16 steps in shared memory.  A row is rewritten only after the barrier(s) of the step that read it.
+__device__ __forceinline__ void gen_noise(const Ctx &c, int step, unsigned char *smem) {
+    float Gn[4];
+    gumbel4(c.seed, c.offset, c.r, (uint32_t)step, threadIdx.x & 31, Gn);
+    reinterpret_cast<float4 *>(smem + OFF_NOISE)[(step & 15) * 32 + (threadIdx.x & 31)] = make_float4(Gn[0], Gn[1], Gn[2], Gn[3]);
+}
+
 // ---------------------------------------------------------------------------------------------
 // decode steps t .. t_stop-1 with MM rows of 16 slots
 // ---------------------------------------------------------------------------------------------
@@ -170,10 +180,13 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
 
     while (c.t < t_stop) {
         TG_TRACE_AT(0);
-        // sampling = arg-max of logits + Gumbel noise (rollout_util.cuh); the noise depends on (seed, rollout, step,
-        // lane) only: drawn here, off the selection's critical path
+        // sampling = arg-max of logits + Gumbel noise (rollout_util.cuh), read from the ring
         float G[4] = {0.f, 0.f, 0.f, 0.f};
-        if (SAMPLING) gumbel4(c.seed, c.offset, c.r, (uint32_t)c.t, lane, G);
+        if (SAMPLING) {
+            if ((c.t & 7) == 0 && c.t > 0) gen_noise(c, c.t + 8 + warp, smem);
+            const float4 g4 = reinterpret_cast<const float4 *>(smem + OFF_NOISE)[(c.t & 15) * 32 + lane];
+            G[0] = g4.x; G[1] = g4.y; G[2] = g4.z; G[3] = g4.w;
+        }
         // ---- query of this half head (decoder.py:141-142), pre-scaled; step 0 has no context row
         u64 q2[4];
         {
@@ -289,7 +302,7 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
             float lm = xv[0];
 #pragma unroll
             for (int k = 1; k < NS; ++k) lm = fmaxf(lm, xv[k]);
-            gm = redux_max(lm);                     // max logit: the epilogue's log-sum-exp shift
+            gm = SAMPLING ? 0.f : redux_max(lm);    // max logit (sampling: the epilogue finds the row maxima itself)
             float yv[NS], ym = gm;
 #pragma unroll
             for (int k = 0; k < NS; ++k) yv[k] = xv[k];
@@ -330,7 +343,7 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
         // ---- every warp: all logits, lane = slots 4 lane .. 4 lane + 3; argmax, lowest slot on ties
         float x0, x1, x2, x3;
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x0), "=f"(x1), "=f"(x2), "=f"(x3) : "r"(c.x_addr + 16u * lane));
-        gm = redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
+        gm = SAMPLING ? 0.f : redux_max(fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)));
         float ym = gm;
         if (SAMPLING) {
             x0 += G[0]; x1 += G[1]; x2 += G[2]; x3 += G[3];
@@ -345,7 +358,7 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
         }
         if (win == 0x7fffffffu) win = reinterpret_cast<const int *>(smem + OFF_NODE)[warp * 128];   // NaN logits: slot 0
         const int slot = (int)(win >> 8), node = (int)(win & 0xffu);
-        if (tid == 0) { s_act[c.t] = node; s_slot[c.t] = slot; s_mw[c.t] = gm; }
+        if (tid == 0) { s_act[c.t] = node; s_slot[c.t] = slot; if (!SAMPLING) s_mw[c.t] = gm; }
         // ---- transition (tsp/env.py:67-93); the slot's owner lanes check feasibility (utils/decoding.py:377-379)
         {
             const unsigned bit = (g == (slot & 15)) ? (1u << (slot >> 4)) : 0u;
@@ -526,6 +539,11 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) node_w[4 * lane + k] = 4 * lane + k;
         }
+        if (SAMPLING) {                             // Gumbel noise of steps 0..15 (warp w: steps w and w + 8)
+            c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)b;
+            gen_noise(c, warp, smem);
+            gen_noise(c, warp + 8, smem);
+        }
         if (tid == 0 && b + gridDim.x < a.B) {      // next instance: context table -> other buffer, K/V/L rows -> L2
             const int64_t nb = b + gridDim.x;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -624,7 +642,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 mm[u] = 0.f;
                 if (q < nact) {
                     const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
-                    mm[u] = s_mw[q];
+                    mm[u] = SAMPLING ? redux_max(fmaxf(fmaxf(xv.x, xv.y), fmaxf(xv.z, xv.w))) : s_mw[q];
                     es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
                             (ex2f((xv.z - mm[u]) * kLog2e) + ex2f((xv.w - mm[u]) * kLog2e));
                 }
