@@ -51,7 +51,7 @@ constexpr int PLS = 144;              // row stride of the partial-logit matrix 
 struct Layout {
     int xs_rows;        // T: every step keeps its logits (log-probs are formed after the loop); 1: per-step sums
     size_t off_c, off_pl, off_xs, off_o, off_ring, off_mw, off_xa, off_act, off_ain, off_lp, off_locs,
-        off_dem, off_wc, off_part, off_bar, total;
+        off_dem, off_wc, off_noise, off_part, off_bar, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
 __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
@@ -59,7 +59,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     // everything except the logits: does a [T][128] ring of them still fit next to it?
     const size_t fixed = (has_c ? (size_t)2 * N * E * 4 : 0) + (size_t)kWarps * PLS * 4 + E * 4 +
                          up16((size_t)T * kWarps * 4) + 5 * up16((size_t)T * 4) + up16((size_t)N * 8) +
-                         128 * 4 + 128 * 4 + 64 * 4 + 16;
+                         128 * 4 + 128 * 4 + 16 * 128 * 4 + 64 * 4 + 16;
     L.xs_rows = (fixed + (size_t)T * 128 * 4 <= (size_t)227 * 1024) ? T : 1;
     size_t o = 0;
     L.off_c = o;    o += has_c ? (size_t)2 * N * E * 4 : 0;     // double-buffered context table
@@ -75,6 +75,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     L.off_locs = o; o += up16((size_t)N * 8);
     L.off_dem = o;  o += 128 * 4;
     L.off_wc = o;   o += 128 * 4;                               // cvrp: remaining-capacity column, pre-scaled
+    L.off_noise = o; o += 16 * 128 * 4;                         // sampling: Gumbel noise of 16 steps [16][128]
     L.off_part = o; o += 64 * 4;
     L.off_bar = o;  o += 16;
     L.total = o;
@@ -167,6 +168,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     float2 *s_locs = reinterpret_cast<float2 *>(smem + L.off_locs);
     float *s_dem = reinterpret_cast<float *>(smem + L.off_dem);     // demand of node n (0 for depot / pad)
     float *s_wc = reinterpret_cast<float *>(smem + L.off_wc);
+    float4 *s_noise = reinterpret_cast<float4 *>(smem + L.off_noise);
     float *spart = reinterpret_cast<float *>(smem + L.off_part);
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.off_bar); // one per context buffer
 
@@ -180,6 +182,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     const bool xring = L.xs_rows > 1;
     const bool std_logits = a.tanh_clipping > 0.f && a.temperature == 1.f && a.mask_logits != 0;
     const float clip = a.tanh_clipping;
+    const bool sampling = a.mode == RL4CO_MODE_SAMPLING;
 
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -366,8 +369,18 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 
         for (int s = s_begin; s < s_end; ++s) {
         const int64_t r = (int64_t)s * a.B + b;     // flat rollout index, start-major (utils/ops.py:11-34)
+        auto gen_noise = [&](int step) {
+            float Gn[4];
+            gumbel4(a.seed, a.offset, (uint64_t)r, (uint32_t)step, lane, Gn);
+            s_noise[(step & 15) * 32 + lane] = make_float4(Gn[0], Gn[1], Gn[2], Gn[3]);
+        };
         // ------------------------------------------------ reset of the per-rollout state
         if (s != s_begin) __syncthreads();          // the previous rollout's epilogue is done with shared memory
+        if (sampling) {                             // Gumbel noise of steps 0..15 (warp w: steps w and w + 8)
+            gen_noise(warp);
+            gen_noise(warp + 8);
+            __syncthreads();
+        }
         if (a.mode == RL4CO_MODE_EVALUATE) {
             for (int q = tid; q < T; q += kThreads) {
                 int64_t gv = a.actions_in[(size_t)r * T + q];
@@ -393,8 +406,15 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         // ================================================== decode loop ==================
         while (!done && t < t_end) {
             RF_TRACE_AT(0);
+            // sampling = arg-max of logits + Gumbel noise (rollout_util.cuh).  Every warp needs the same 128 values per
+            // step: warp w draws the noise of step t0 + 8 + w once every eight steps into a ring of 16 steps; a row
+            // is rewritten only after the barriers of the step that read it
             float G[4] = {0.f, 0.f, 0.f, 0.f};
-            if (a.mode == RL4CO_MODE_SAMPLING) gumbel4(a.seed, a.offset, (uint64_t)r, (uint32_t)t, lane, G);
+            if (sampling) {
+                if ((t & 7) == 0 && t > 0) gen_noise(t + 8 + warp);
+                const float4 g4 = s_noise[(t & 15) * 32 + lane];
+                G[0] = g4.x; G[1] = g4.y; G[2] = g4.z; G[3] = g4.w;
+            }
             // ---- query of this half head (decoder.py:141-142), pre-scaled
             u64 q2[4];
             if (HAS_C && use_c) {
@@ -545,7 +565,9 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 const float4 xv = *reinterpret_cast<const float4 *>(sxrow + 4 * lane);
                 x[0] = xv.x; x[1] = xv.y; x[2] = xv.z; x[3] = xv.w;
             }
-            const float gm = (RF_ABL & 16) ? x[0] : redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
+            // the log-sum-exp shift: the max logit; sampling with clipped logits uses their bound instead (no reduction)
+            const float gm = (RF_ABL & 16) ? x[0] : (sampling && std_logits) ? clip
+                                                    : redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
             // ---- selection (utils/decoding.py:371-397,410-499)
             int act;
             if (RF_ABL & 16) {
