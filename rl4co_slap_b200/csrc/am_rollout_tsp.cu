@@ -477,10 +477,18 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         for (size_t off = 0; off < c_bytes; off += 16384)
             tma_load_1d(dst + off, src + off, (unsigned)(c_bytes - off < 16384 ? c_bytes - off : 16384), &bar[buf]);
     };
-    if (tid == 0 && (int64_t)blockIdx.x < a.B) stage_context(blockIdx.x, 0);
+    // work item = one rollout (instance b, start s), flat index r = s * B + b (utils/ops.py:11-34).  Consecutive items go to
+    // different CTAs, so the ~1.5 instances whose starts are in flight at any time keep their tables hot in L2.
+    const int S = a.S > 1 ? a.S : 1;
+    const int64_t W = a.B * (int64_t)S;
+    const int t_first = a.multistart ? 1 : 0;       // multistart: step 0 is the forced POMO start node
+    if (tid == 0 && (int64_t)blockIdx.x < W) stage_context(blockIdx.x / S, 0);
 
     int it = 0;
-    for (int64_t b = blockIdx.x; b < a.B; b += gridDim.x, ++it) {
+    for (int64_t w = blockIdx.x; w < W; w += gridDim.x, ++it) {
+        const int64_t b = w / S;
+        const int s = (int)(w % S);
+        const int64_t r = (int64_t)s * a.B + b;
         const int buf = it & 1;
 #ifdef RF_TRACE
         Ctx c;
@@ -540,12 +548,12 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             for (int k = 0; k < 4; ++k) node_w[4 * lane + k] = 4 * lane + k;
         }
         if (SAMPLING) {                             // Gumbel noise of steps 0..15 (warp w: steps w and w + 8)
-            c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)b;
+            c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)r;
             gen_noise(c, warp, smem);
             gen_noise(c, warp + 8, smem);
         }
-        if (tid == 0 && b + gridDim.x < a.B) {      // next instance: context table -> other buffer, K/V/L rows -> L2
-            const int64_t nb = b + gridDim.x;
+        if (tid == 0 && w + gridDim.x < W) {        // next item: context table -> other buffer, K/V/L rows -> L2
+            const int64_t nb = (w + gridDim.x) / S;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             stage_context(nb, buf ^ 1);
             for (int tb = 0; tb < 3; ++tb) {
@@ -568,7 +576,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         c.t = 0;
         c.status = 0;
         c.clip = a.tanh_clipping;
-        c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)b;
+        c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)r;
         c.c_addr = smem_u32(cbuf + (size_t)buf * N * E + dim0);
         c.x_addr = smem_u32(sxs);
 #ifdef RF_TRACE
@@ -582,6 +590,15 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }      // context table landed?
         else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
 
+        if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
+            const int a0 = s % a.num_loc;           // slot == node before the first compaction
+            c.alive &= ~((g == (a0 & 15)) ? (1u << (a0 >> 4)) : 0u);
+            if (tid == 0) { s_act[0] = a0; s_slot[0] = a0; s_lp[0] = 0.f; }
+            set_first(a0);
+            c.cur = a0;
+            c.t = 1;
+            c.x_addr += 128 * 4;
+        }
         TG_TRACE_ROW(T + 2, 3);
         // fused stages keep only the live slots of a step's logits: the rest of the rows is -inf from here on
         auto fill_rows = [&](int t0) {
@@ -640,7 +657,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 const int q = warp + u * kWarps;
                 es[u] = 0.f;
                 mm[u] = 0.f;
-                if (q < nact) {
+                if (q >= t_first && q < nact) {
                     const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
                     mm[u] = SAMPLING ? redux_max(fmaxf(fmaxf(xv.x, xv.y), fmaxf(xv.z, xv.w))) : s_mw[q];
                     es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
@@ -656,7 +673,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             for (int u = 0; u < U; ++u)
                 if (lane == u) { my_es = es[u]; my_m = mm[u]; }
             const int q = warp + lane * kWarps;
-            if (lane < U && q < nact) {
+            if (lane < U && q >= t_first && q < nact) {
                 const float lpa = (sxs[q * 128 + s_slot[q]] - my_m) - logf(my_es);
                 s_lp[q] = lpa;
                 if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
@@ -681,15 +698,15 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 float len = 0.f;
                 int st = 0;
                 for (int w = 0; w < kWarps; ++w) { len += spart[w]; st |= __float_as_int(spart[40 + w]); }
-                a.reward[b] = -len;
-                a.ll[b] = llp;
-                if (a.steps) a.steps[b] = nact;
+                a.reward[r] = -len;
+                a.ll[r] = llp;
+                if (a.steps) a.steps[r] = nact;
                 if (st) raise_status(a.status, st);
             }
         }
         for (int q = tid; q < T; q += kThreads) {
-            a.actions[(size_t)b * T + q] = q < nact ? (int64_t)s_act[q] : 0;
-            if (a.logp) a.logp[(size_t)b * T + q] = q < nact ? s_lp[q] : 0.f;
+            a.actions[(size_t)r * T + q] = q < nact ? (int64_t)s_act[q] : 0;
+            if (a.logp) a.logp[(size_t)r * T + q] = q < nact ? s_lp[q] : 0.f;
         }
         TG_TRACE_ROW(T + 2, 6);
     }
@@ -710,7 +727,8 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         set_error("am_rollout(tsp greedy): cannot reserve %zu B of shared memory: %s", total, cudaGetErrorString(e));
         return 2;
     }
-    const int64_t grid = a.B < sm_count ? a.B : sm_count;   // persistent: one CTA per SM
+    const int64_t W = a.B * (int64_t)(a.S > 1 ? a.S : 1);
+    const int64_t grid = W < sm_count ? W : sm_count;       // persistent: one CTA per SM
     am_rollout_tsp_greedy_kernel<M0, SAMPLING><<<(unsigned)grid, kThreads, total, stream>>>(a);
     RL4CO_CHECK_LAUNCH("am_rollout(tsp greedy)");
     return 0;
@@ -722,7 +740,7 @@ bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a) {
 #ifndef RF_TRACE
     if (a.logp_all != nullptr) return false;
 #endif
-    if (a.env != RL4CO_ENV_TSP || a.mode == RL4CO_MODE_EVALUATE || a.S > 1 || a.multistart) return false;
+    if (a.env != RL4CO_ENV_TSP || a.mode == RL4CO_MODE_EVALUATE) return false;
     if (!(a.tanh_clipping > 0.f) || a.temperature != 1.f || a.mask_logits == 0) return false;
     if (a.N > 112 || a.T > tspg::kMaxT || a.N < 2) return false;
     return tspg::smem_total(a.N, a.T) <= (size_t)227 * 1024;

@@ -168,6 +168,108 @@ tsp_replay_kernel(int64_t B, int N, int T, const float *__restrict__ locs,
     if (lane == 0) raise_status(status, st);
 }
 
+// ---------------------------------------------------------------- replay, persistent ----------
+// N, T <= 128 (even): warps loop over instances and keep the NEXT instance's rows (locs 8N bytes, actions 8T bytes =
+// at most two 16-byte registers each per lane) in flight while the current one is processed, so the HBM latency is
+// hidden behind the per-instance work instead of behind occupancy alone.  The visited set is four register words
+// built with redux.sync.or (no shared-memory atomics); the final mask goes out as 4-byte stores.
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+tsp_replay_persistent_kernel(int64_t B, int N, int T, const float *__restrict__ locs,
+                             const int64_t *__restrict__ actions, int64_t *first_node,
+                             int64_t *current_node, int64_t *i_out, uint8_t *mask, uint8_t *done,
+                             float *reward, int check, int32_t *status) {
+    __shared__ __align__(16) float2 s_locs[kWarpsPerCta][128];
+    __shared__ int s_act[kWarpsPerCta][132];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float2 *sl = s_locs[warp];
+    int *sa = s_act[warp];
+    const int64_t stride = (int64_t)gridDim.x * kWarpsPerCta;
+    const int nl = N >> 1, na = T >> 1;             // 16-byte pieces per row
+    const bool mask4 = mask != nullptr && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
+
+    float4 l0, l1, nl0, nl1;
+    longlong2 a0, a1, na0, na1;
+    auto load = [&](int64_t b, float4 &x0, float4 &x1, longlong2 &y0, longlong2 &y1) {
+        x0 = x1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        y0 = y1 = make_longlong2(0, 0);
+        if (b >= B) return;
+        const float4 *lv = reinterpret_cast<const float4 *>(locs + b * (int64_t)N * 2);
+        const longlong2 *av = reinterpret_cast<const longlong2 *>(actions + b * (int64_t)T);
+        if (lane < nl) x0 = __ldg(lv + lane);
+        if (lane + 32 < nl) x1 = __ldg(lv + lane + 32);
+        if (lane < na) y0 = __ldg(av + lane);
+        if (lane + 32 < na) y1 = __ldg(av + lane + 32);
+    };
+    int64_t b = blockIdx.x * (int64_t)kWarpsPerCta + warp;
+    load(b, l0, l1, a0, a1);
+    int st = 0;
+    for (; b < B; b += stride) {
+        load(b + stride, nl0, nl1, na0, na1);       // next instance in flight
+        __syncwarp();                               // the previous instance's gathers are done
+        // ---- stage: locs as float2, actions as int (range checked)
+        if (lane < nl) { sl[2 * lane] = make_float2(l0.x, l0.y); sl[2 * lane + 1] = make_float2(l0.z, l0.w); }
+        if (lane + 32 < nl) { sl[2 * lane + 64] = make_float2(l1.x, l1.y); sl[2 * lane + 65] = make_float2(l1.z, l1.w); }
+        unsigned w0 = 0, w1 = 0, w2 = 0, w3 = 0;
+        int dup = 0;
+        auto put = [&](int t, int64_t a) {
+            if (a < 0 || a >= N) { st |= RL4CO_ST_ACTION_RANGE; a = a < 0 ? 0 : N - 1; }
+            sa[t] = (int)a;
+            const unsigned bit = 1u << (a & 31);
+            const int w = (int)(a >> 5);
+            unsigned &word = w == 0 ? w0 : w == 1 ? w1 : w == 2 ? w2 : w3;
+            dup |= (word & bit) != 0 || a >= T;     // (a repeated inside this lane; across lanes: popcount below)
+            word |= bit;
+        };
+        if (lane < na) { put(2 * lane, a0.x); put(2 * lane + 1, a0.y); }
+        if (lane + 32 < na) { put(2 * lane + 64, a1.x); put(2 * lane + 65, a1.y); }
+        w0 = __reduce_or_sync(kFull, w0);
+        w1 = __reduce_or_sync(kFull, w1);
+        w2 = __reduce_or_sync(kFull, w2);
+        w3 = __reduce_or_sync(kFull, w3);
+        const int visited = __popc(w0) + __popc(w1) + __popc(w2) + __popc(w3);
+        // validity: sort(actions) == arange(T) (tsp/env.py:165-173)  <=>  T distinct values, all < T
+        const int bad = __any_sync(kFull, dup) || visited != T;
+        __syncwarp();
+        // ---- tour length (utils/ops.py:93-101): legs a_t -> a_{t+1}, closed
+        float len = 0.f;
+        for (int t = lane; t < T; t += 32) {
+            const float2 p = sl[sa[t]];
+            const float2 q = sl[sa[t + 1 == T ? 0 : t + 1]];
+            len += leg(p.x, p.y, q.x, q.y);
+        }
+        len = warp_sum(len);
+        // ---- final state after T steps (tsp/env.py:83-93)
+        if (mask) {
+            uint8_t *row = mask + b * (int64_t)N;
+            if (mask4) {
+                if (4 * lane < N) {
+                    const unsigned word = lane < 8 ? w0 : lane < 16 ? w1 : lane < 24 ? w2 : w3;
+                    const unsigned nib = (word >> ((4 * lane) & 31)) & 0xfu;     // visited bits of nodes 4 lane .. 4 lane + 3
+                    const unsigned bytes = ((nib & 1u) ? 0u : 1u) | ((nib & 2u) ? 0u : 0x100u) | ((nib & 4u) ? 0u : 0x10000u) |
+                                           ((nib & 8u) ? 0u : 0x1000000u);
+                    reinterpret_cast<unsigned *>(row)[lane] = bytes;
+                }
+            } else {
+                for (int n = lane; n < N; n += 32) {
+                    const unsigned word = n < 32 ? w0 : n < 64 ? w1 : n < 96 ? w2 : w3;
+                    row[n] = ((word >> (n & 31)) & 1u) ? 0 : 1;
+                }
+            }
+        }
+        if (lane == 0) {
+            if (first_node) first_node[b] = T > 0 ? sa[0] : 0;
+            if (current_node) current_node[b] = T > 0 ? sa[T - 1] : 0;
+            if (i_out) i_out[b] = T;
+            if (done) done[b] = (T > 0) && (visited == N);
+            if (reward) reward[b] = -len;
+            if (check && bad) st |= RL4CO_ST_INVALID_TOUR;
+        }
+        l0 = nl0; l1 = nl1; a0 = na0; a1 = na1;
+    }
+    st = __reduce_or_sync(kFull, st);
+    if (lane == 0) raise_status(status, st);
+}
+
 static int grid_for(int64_t n, int per_block) {
     int64_t g = (n + per_block - 1) / per_block;
     int64_t cap = 148 * 32;
@@ -216,6 +318,23 @@ extern "C" int rl4co_tsp_replay(int64_t B, int32_t N, int32_t T, const float *lo
     RL4CO_REQUIRE(B >= 0 && N > 0 && T >= 0, "tsp_replay: bad sizes B=%lld N=%d T=%d", (long long)B, N, T);
     if (B == 0) return 0;
     RL4CO_REQUIRE(locs && actions, "tsp_replay: null input");
+    if (N <= 128 && T <= 128 && T >= 2 && (N & 1) == 0 && (T & 1) == 0 &&
+        (reinterpret_cast<uintptr_t>(locs) & 15) == 0 && (reinterpret_cast<uintptr_t>(actions) & 15) == 0) {
+        static int resident = 0;                            // CTAs the device holds at once (persistent grid)
+        if (resident == 0) {
+            int dev = 0, sm_count = 0, per_sm = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tsp_replay_persistent_kernel, kWarpsPerCta * 32, 0);
+            resident = (sm_count > 0 ? sm_count : 148) * (per_sm > 0 ? per_sm : 4);
+        }
+        int64_t blocks = (B + kWarpsPerCta - 1) / kWarpsPerCta;
+        if (blocks > resident) blocks = resident;
+        tsp_replay_persistent_kernel<<<(unsigned)blocks, kWarpsPerCta * 32, 0, (cudaStream_t)stream>>>(
+            B, N, T, locs, actions, first_node, current_node, i, action_mask, done, reward, check_validity, status);
+        RL4CO_CHECK_LAUNCH("tsp_replay");
+        return 0;
+    }
     int words = (N + 31) / 32;
     int per_warp = N * 8 + ((T + 1) & ~1) * 4 + ((words + 3) & ~3) * 4;
     size_t smem = (size_t)per_warp * kWarpsPerCta;
