@@ -54,14 +54,16 @@ def make_env(env_name, size):
     return SLAPEnv(generator_params={"n_aisles": size // 10, "n_locs": 10})
 
 
-def replay_trace(env, td0):
-    """Random feasible replay through the reference env; every state key after every step."""
+def replay_trace(env, td0, weight=None):
+    """Random feasible replay through the reference env; every state key after every step.
+    ``weight`` optionally reshapes the sampling weights of the feasible actions."""
     td = env.reset(td0.clone())
     skip = set(GEN_KEYS[env.name]) | {"dist_mat", "terminated", "ratio"}
     trace = {f"reset.{k}": np_(v) for k, v in td.items() if k not in skip or k == "locs"}
     acts, t = [], 0
     while not td["done"].all():
-        a = torch.multinomial(td["action_mask"].float(), 1).squeeze(-1)
+        w = td["action_mask"].float()
+        a = torch.multinomial(w if weight is None else weight(w), 1).squeeze(-1)
         td.set("action", a)
         td = env.step(td)["next"]
         for k, v in td.items():

@@ -1,0 +1,62 @@
+"""TEST INFRASTRUCTURE ONLY - tests/golden/op*.npz + policy_op.npz from the UNMODIFIED reference
+(the orienteering problem, the sibling environment of SURVEY.md 8f rank 4).
+
+Runs only in the build container (imports /root/reference through oracle/ref_shim.py):
+    python oracle/gen_golden_op.py
+Same content as oracle/gen_golden.py's cases (generator output, random feasible replay with every
+per-step state tensor, greedy rollout of a small random-init reference policy) plus ``eval.*``: the
+reference policy's per-step log-probs of the replay's random tours (decode_type="evaluate"), which
+exercises long trajectories a random-init greedy policy does not produce.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import gen_golden as G  # noqa: E402  (installs the shim)
+
+from rl4co.envs.routing.op.env import OPEnv  # noqa: E402
+from rl4co.models.zoo.am.policy import AttentionModelPolicy  # noqa: E402
+
+G.GEN_KEYS["op"] = ("locs", "depot", "prize", "max_length")
+
+
+def late_depot(w):
+    """Return to the depot early only rarely, so that the replays are long tours that run into the length
+    budget (a uniform draw over the feasible actions ends most tours within a few steps)."""
+    w = w.clone()
+    w[:, 0] = 1e-3
+    return w
+
+
+def main():
+    torch.manual_seed(4321)
+    np.random.seed(4321)
+    pol = AttentionModelPolicy(env_name="op", num_encoder_layers=1, feedforward_hidden=128).eval()
+    np.savez_compressed(os.path.join(G.OUT, "policy_op.npz"),
+                        **{k: G.np_(v) for k, v in pol.state_dict().items()})
+    for size, B in ((10, 8), (20, 8), (50, 6), (100, 4)):
+        # the default prize_distribution trips torch's Uniform(1, 1) argument validation; "dist" is the
+        # reference's own alternative (op/generator.py)
+        env = OPEnv(generator_params=dict(num_loc=size, prize_distribution="dist"))
+        td0 = env.generator(B)
+        data = {f"gen.{k}": G.np_(td0[k]) for k in G.GEN_KEYS["op"]}
+        data.update(G.replay_trace(env, td0, weight=late_depot))
+        res, h = G.policy_outputs(env, pol, td0, "greedy", decode_type="greedy")
+        data.update(res)
+        data["hidden"] = G.np_(h)
+        res, _ = G.policy_outputs(env, pol, td0, "eval", actions=torch.from_numpy(data["replay.actions"]))
+        data.update(res)
+        path = os.path.join(G.OUT, f"op{size}.npz")
+        np.savez_compressed(path, **data)
+        print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, greedy mean reward "
+              f"{data['greedy.reward'].mean():.4f}, T={data['greedy.actions'].shape[1]}, "
+              f"replay T={data['replay.actions'].shape[1]}")
+
+
+if __name__ == "__main__":
+    main()

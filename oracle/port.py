@@ -67,7 +67,7 @@ def unbatchify(x, repeats: int):
 def num_starts_for(env_name: str, action_mask) -> int:
     """utils/ops.py:126-136."""
     n = action_mask.shape[-1]
-    return n - 1 if env_name == "cvrp" else n
+    return n - 1 if env_name in ("cvrp", "op") else n
 
 
 def select_start_nodes(env_name: str, batch: int, num_starts: int, num_loc: int):
@@ -188,6 +188,73 @@ def cvrp_reward(locs_with_depot, actions):
 
 
 # =====================================================================================
+# OP  (envs/routing/op/env.py) - sibling env of SURVEY.md 8f rank 4
+# =====================================================================================
+def op_action_mask(td: State):
+    """op/env.py:154-170: visited, depot already revisited, or arriving would exceed the per-node
+    length budget; the depot is always feasible."""
+    cur_loc = gather_by_index(td["locs"], td["current_node"])[..., None, :]
+    exceeds = td["tour_length"][..., None] + (td["locs"] - cur_loc).norm(p=2, dim=-1) > td["max_length"]
+    mask = td["visited"] | td["visited"][..., 0:1] | exceeds
+    action_mask = ~mask
+    action_mask[..., 0] = 1
+    return action_mask
+
+
+def op_reset(depot, locs, prize, max_length) -> State:
+    """op/env.py:110-152 (+ merge): per-node budget = max_length - dist(depot, node) - 1e-6."""
+    B, n, _ = locs.shape
+    lw = torch.cat((depot[:, None, :], locs), -2)
+    td = {
+        "locs": lw,
+        "prize": F.pad(prize, (1, 0), mode="constant", value=0),
+        "tour_length": torch.zeros(B),
+        "max_length": max_length[..., None] - (depot[..., None, :] - lw).norm(p=2, dim=-1) - 1e-6,
+        "current_node": torch.zeros(B, 1, dtype=torch.int64),
+        "visited": torch.zeros(B, n + 1, dtype=torch.bool),
+        "current_total_prize": torch.zeros(B),
+        "i": torch.zeros(B, dtype=torch.int64),
+        "done": torch.zeros(B, 1, dtype=torch.bool),
+        "terminated": torch.zeros(B, 1, dtype=torch.bool),
+    }
+    td["action_mask"] = op_action_mask(td)
+    return td
+
+
+def op_step(td: State) -> State:
+    """op/env.py:74-108.  done = back at the depot after the first step, shape [B]."""
+    cur = td["action"][:, None]
+    prev_loc = gather_by_index(td["locs"], td["current_node"])
+    cur_loc = gather_by_index(td["locs"], cur)
+    length = td["tour_length"] + (cur_loc - prev_loc).norm(p=2, dim=-1)
+    total = td["current_total_prize"] + gather_by_index(td["prize"], cur, dim=-1)
+    visited = td["visited"].scatter(-1, cur, 1)
+    done = (cur.squeeze(-1) == 0) & (td["i"] > 0)
+    td.update({"tour_length": length, "current_node": cur, "visited": visited,
+               "current_total_prize": total, "i": td["i"] + 1,
+               "reward": torch.zeros_like(done), "done": done})
+    td["action_mask"] = op_action_mask(td)
+    return td
+
+
+def op_check(locs_with_depot, max_length, actions) -> None:
+    """op/env.py:184-215 (add_distance_to_depot=True)."""
+    sa = actions.sort(1)[0]
+    assert ((sa[:, 1:] == 0) | (sa[:, 1:] > sa[:, :-1])).all(), "Duplicates"
+    length = tour_length(gather_by_index(locs_with_depot, actions))
+    ml = max_length + (locs_with_depot[..., 0:1, :] - locs_with_depot).norm(p=2, dim=-1) + 1e-6
+    assert (length[..., None] <= ml + 1e-5).all(), "Max length exceeded"
+
+
+def op_reward(prize_with_depot, actions):
+    """op/env.py:172-182."""
+    if actions.size(-1) == 1:
+        assert (actions == 0).all(), "If all length 1 tours, they should be zero"
+        return torch.zeros(actions.size(0))
+    return prize_with_depot.gather(1, actions).sum(-1)
+
+
+# =====================================================================================
 # SLAP  (envs/warehousing/slap/env.py)
 # =====================================================================================
 def slap_reset(locs, assignment, n_products: int, extra: Optional[State] = None) -> State:
@@ -281,6 +348,10 @@ def context_embedding(env_name: str, cache, td: State, W):
         cur = gather_by_index(h, td["current_node"])
         state = (td["vehicle_capacity"] - td["used_capacity"]).to(cur.dtype)   # (no-op in fp32; fp64 decoder checks)
         return F.linear(torch.cat([cur, state], -1), W["Wctx"])
+    if env_name == "op":        # OPContext, nn/env_embeddings/context.py:385-397
+        cur = gather_by_index(h, td["current_node"])
+        state = (td["max_length"][..., 0] - td["tour_length"])[..., None].to(cur.dtype)
+        return F.linear(torch.cat([cur, state], -1), W["Wctx"])
     if env_name == "slap":
         return h.new_zeros(B, h.size(-1))
     raise ValueError(env_name)
@@ -345,7 +416,7 @@ def select_action(logprobs, mask, decode_type: str, given=None):
     return sel
 
 
-_STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step}
+_STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step, "op": op_step}
 
 
 def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
@@ -394,6 +465,10 @@ def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
         if check_solution:
             cvrp_check(td["demand"], td["vehicle_capacity"], out_actions)
         reward = cvrp_reward(td["locs"], out_actions)
+    elif env_name == "op":
+        if check_solution:
+            op_check(td["locs"], td["max_length"], out_actions)
+        reward = op_reward(td["prize"], out_actions)
     else:
         reward = slap_reward(td["locs"], td["assignment"], td["picklist"])
     lp_sel = logprobs.gather(-1, out_actions.unsqueeze(-1)).squeeze(-1) if logprobs.dim() == 3 else logprobs

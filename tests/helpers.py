@@ -8,6 +8,7 @@ import torch
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TSP_CASES, CVRP_CASES, SLAP_CASES = ("tsp5", "tsp20", "tsp50", "tsp100"), ("cvrp10", "cvrp20", "cvrp50", "cvrp100"), ("slap50", "slap100")
+OP_CASES = ("op10", "op20", "op50", "op100")
 
 
 def fixture(name):
@@ -58,7 +59,8 @@ def gen_td(env_name: str, fx, dev=None):
     """The generator output stored in a fixture as a product TensorDict."""
     from rl4co_slap_b200 import TensorDict
     keys = {"tsp": ("locs",), "cvrp": ("locs", "depot", "demand", "capacity"),
-            "slap": ("locs", "freq", "assignment", "picklist", "depot_loc_dist")}[env_name]
+            "slap": ("locs", "freq", "assignment", "picklist", "depot_loc_dist"),
+            "op": ("locs", "depot", "prize", "max_length")}[env_name]
     d = {k: t(fx[f"gen.{k}"], dev) for k in keys}
     return TensorDict(d, batch_size=[d["locs"].shape[0]])
 
@@ -74,5 +76,7 @@ def oracle_reset(env_name: str, fx):
     if env_name == "cvrp":
         return port.cvrp_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.demand"]),
                                float(fx["gen.vehicle_capacity"]))
+    if env_name == "op":
+        return port.op_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.prize"]), t(fx["gen.max_length"]))
     extra = {k: t(fx[f"gen.{k}"]) for k in ("freq", "picklist", "depot_loc_dist")}
     return port.slap_reset(t(fx["gen.locs"]), t(fx["gen.assignment"]), fx["gen.freq"].shape[-2], extra)
