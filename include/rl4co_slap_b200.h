@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RL4CO_ABI_VERSION 1
+#define RL4CO_ABI_VERSION 2
 
 /* status bits (device int32 word) */
 #define RL4CO_ST_INVALID_TOUR      1   /* tsp/env.py:173, cvrp/env.py:175 */
@@ -38,6 +38,8 @@ extern "C" {
 #define RL4CO_ST_NAN_LOGITS        8   /* models/nn/attention.py:285 */
 #define RL4CO_ST_NEG_INF_LOGP      16  /* utils/decoding.py:59 */
 #define RL4CO_ST_ACTION_RANGE      32  /* action outside [0,N): torch gather/scatter would raise */
+#define RL4CO_ST_DUPLICATES        64  /* op/env.py:196-199 */
+#define RL4CO_ST_OVER_LENGTH       128 /* op/env.py:211-215 */
 
 typedef void *rl4co_stream_t;
 
@@ -91,6 +93,32 @@ int rl4co_cvrp_replay(int64_t B, int32_t N, int32_t T, const float *locs,
                       uint8_t *visited, uint8_t *action_mask, uint8_t *done, float *reward,
                       int32_t check_validity, int32_t *status, rl4co_stream_t stream);
 
+/* ------------------------------------------------------------------ OP (K1) -------- */
+/* Orienteering problem, the sibling environment of the routing family.  N counts the depot (node 0);
+ * locs [B,N,2], prize [B,N] (0 for the depot) and max_length [B,N] are the tensors of the reset state
+ * (op/env.py:110-152): max_length[b,n] is the budget when ARRIVING at n (return leg and 1e-6 already
+ * subtracted).  visited is the reference's bool tensor (1 byte per node), tour_length /
+ * current_total_prize / i are [B], current_node [B,1]. */
+
+/* OPEnv.get_action_mask, envs/routing/op/env.py:154-170. */
+int rl4co_op_action_mask(int64_t B, int32_t N, const float *locs, const float *max_length,
+                         const float *tour_length, const uint8_t *visited, const int64_t *current_node,
+                         uint8_t *action_mask, rl4co_stream_t stream);
+
+/* OPEnv._step, envs/routing/op/env.py:74-108 (transition + mask in one launch).  done is [B]. */
+int rl4co_op_step(int64_t B, int32_t N, const int64_t *action, const float *locs, const float *prize,
+                  const float *max_length, float *tour_length, float *current_total_prize,
+                  int64_t *current_node, uint8_t *visited, int64_t *i, uint8_t *action_mask,
+                  uint8_t *done, int32_t *status, rl4co_stream_t stream);
+
+/* Fused reset-state + T x _step + _get_reward + check_solution_validity (op/env.py:74-215).  Outputs may be
+ * NULL.  check_validity != 0 ORs RL4CO_ST_DUPLICATES / RL4CO_ST_OVER_LENGTH. */
+int rl4co_op_replay(int64_t B, int32_t N, int32_t T, const float *locs, const float *prize,
+                    const float *max_length, const int64_t *actions, int64_t *current_node,
+                    float *tour_length, float *current_total_prize, uint8_t *visited,
+                    uint8_t *action_mask, int64_t *i, uint8_t *done, float *reward,
+                    int32_t check_validity, int32_t *status, rl4co_stream_t stream);
+
 /* ------------------------------------------------------------------ SLAP (K1) ------ */
 /* N storage locations (node 0 = depot, never assignable), P products. */
 
@@ -120,6 +148,7 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
 #define RL4CO_ENV_TSP  0
 #define RL4CO_ENV_CVRP 1
 #define RL4CO_ENV_SLAP 2
+#define RL4CO_ENV_OP   3   /* envs/routing/op/env.py; single start, register-file kernel only (N <= 128) */
 
 #define RL4CO_MODE_GREEDY   0  /* utils/decoding.py:371-381,410-418 */
 #define RL4CO_MODE_SAMPLING 1  /* utils/decoding.py:383-397,475-483 (Philox instead of torch.multinomial) */
@@ -228,6 +257,11 @@ typedef struct rl4co_am_rollout_args {
     int32_t *steps;         /* [R] steps until done, may be NULL */
     int32_t *assignment;    /* slap [R,P] out, may be NULL */
     int32_t *status;
+    /* op (appended, ABI 2): prize [B,N] with 0 for the depot (op/env.py:124-126) and the per-node length
+     * budget max_length [B,N] of the reset state (op/env.py:129-133); wcap = the remaining-length column of
+     * project_context (context.py:385-397); reward = collected prize */
+    const float *prize;
+    const float *max_length;
 } rl4co_am_rollout_args;
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);

@@ -46,6 +46,8 @@ def main():
         td0 = env.generator(B)
         data = {f"gen.{k}": G.np_(td0[k]) for k in G.GEN_KEYS["op"]}
         data.update(G.replay_trace(env, td0, weight=late_depot))
+        td_r = env.reset(td0.clone())       # reset-state tensors that share a name with a generator key
+        data["reset.prize"], data["reset.max_length"] = G.np_(td_r["prize"]), G.np_(td_r["max_length"])
         res, h = G.policy_outputs(env, pol, td0, "greedy", decode_type="greedy")
         data.update(res)
         data["hidden"] = G.np_(h)

@@ -31,7 +31,7 @@
 // Reference op order being reproduced (all fp32): SURVEY.md appendix A;
 // rl4co/models/zoo/am/decoder.py:134-200, rl4co/models/nn/attention.py:263-309,
 // rl4co/utils/decoding.py:141-191,327-397, rl4co/envs/routing/{tsp,cvrp}/env.py,
-// rl4co/envs/warehousing/slap/env.py:38-143.
+// rl4co/envs/warehousing/slap/env.py:38-143, rl4co/envs/routing/op/env.py:74-182 (sibling env, this kernel only).
 #include "rollout_util.cuh"
 
 namespace rl4co {
@@ -152,6 +152,7 @@ template <int ENV, int M>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     constexpr bool HAS_C = ENV != RL4CO_ENV_SLAP;
+    constexpr bool CAPCOL = ENV == RL4CO_ENV_CVRP || ENV == RL4CO_ENV_OP;   // context = [h_cur ; scalar state]
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T;
     const Layout L = make_layout(N, T, HAS_C);
@@ -189,7 +190,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         mbar_init(&bar[1], 1);
         fence_barrier_init();
     }
-    if (ENV == RL4CO_ENV_CVRP && tid < E) s_wc[tid] = a.wcap[tid] * kScoreScale;   // context.py:317-331
+    if (CAPCOL && tid < E) s_wc[tid] = a.wcap[tid] * kScoreScale;   // context.py:317-331 (cvrp), :385-397 (op)
     __syncthreads();
     unsigned par0 = 0u, par1 = 0u;
     auto stage_context = [&](int64_t b, int buf) {  // thread 0: TMA the context table of instance b
@@ -253,8 +254,12 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         };
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
-        if (tid < 128)
-            s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
+        if (tid < 128) {
+            if (ENV == RL4CO_ENV_OP)    // op: length budget when ARRIVING at node n (op/env.py:129-133), pads never reachable
+                s_dem[tid] = tid < N ? a.max_length[b * (int64_t)N + tid] : -INFINITY;
+            else
+                s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
+        }
         {
             const float2 *lrow = reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2);
             for (int n = tid; n < N; n += kThreads) s_locs[n] = lrow[n];
@@ -285,7 +290,9 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
         unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
-        const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b] : 0.f;
+        // cvrp: vehicle capacity / used capacity; op: the depot's length budget / tour length so far
+        const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b]
+                        : (ENV == RL4CO_ENV_OP) ? a.max_length[b * (int64_t)N] : 0.f;
         float used = 0.f;
         auto cvrp_masks = [&](int at) {             // cvrp/env.py:137-149, both layouts
             unsigned f = 0, rf = 0;
@@ -309,9 +316,35 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             alive = f;
             ralive = rf;
         };
+        auto op_masks = [&](int at) {               // op/env.py:154-170, both layouts
+            const float2 pc = s_locs[at];
+            const bool closed = (__shfl_sync(kFull, rvis, 0) & 1u) != 0u;   // depot visited: nothing else is feasible
+            unsigned f = 0, rf = 0;
+#pragma unroll
+            for (int j = 0; j < M; ++j) {
+                const int n = g + 16 * j;
+                const float2 p = s_locs[n < N ? n : 0];
+                const bool exceeds = __fadd_rn(used, leg_fma(pc.x, pc.y, p.x, p.y)) > s_dem[n];
+                if (!exceeds && !((vis >> j) & 1u)) f |= 1u << j;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int n = 4 * lane + k;
+                const float2 p = s_locs[n < N ? n : 0];
+                const bool exceeds = __fadd_rn(used, leg_fma(pc.x, pc.y, p.x, p.y)) > s_dem[n];
+                if (!exceeds && !((rvis >> k) & 1u)) rf |= 1u << k;
+            }
+            f &= own;
+            rf &= rown;
+            if (closed) { f = 0u; rf = 0u; }
+            if (g == 0) f |= 1u;                    // the depot can always be visited (:168-169)
+            if (lane == 0) rf |= 1u;
+            alive = f;
+            ralive = rf;
+        };
         int cur = 0, t = 0, status = 0;
-        bool done = false, use_c = (ENV == RL4CO_ENV_CVRP);
-        const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);
+        bool done = false, use_c = CAPCOL;
+        const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);   // cvrp, op: until done
 
         if (HAS_C) {                                // context table landed?
             if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }
@@ -337,6 +370,13 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 rvis |= rbit;
                 cvrp_masks(act);
                 done = __all_sync(kFull, rvis == rown);
+            } else if (ENV == RL4CO_ENV_OP) {           // op/env.py:74-108
+                const float2 pp = s_locs[cur], pn = s_locs[act];
+                used = __fadd_rn(used, leg_fma(pp.x, pp.y, pn.x, pn.y));
+                vis |= abit;
+                rvis |= rbit;
+                done = act == 0 && t > 0;               // back at the depot, except on the very first step
+                if (!done) op_masks(act);
             } else {                                    // slap/env.py:38-93
                 alive &= ~abit;
                 ralive &= ~rbit;
@@ -394,7 +434,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             if (lane == 0) ralive &= ~1u;
         }
         if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
-        cur = 0; t = 0; status = 0; done = false; use_c = (ENV == RL4CO_ENV_CVRP);
+        if (ENV == RL4CO_ENV_OP) op_masks(0);
+        cur = 0; t = 0; status = 0; done = false; use_c = CAPCOL;
         set_qb(ENV == RL4CO_ENV_TSP ? a.q0 + dim0 : nullptr);   // tsp step 0: context.py:111-121
         if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
             const int a0 = s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
@@ -428,7 +469,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) q2[i] = qbs2[i];
             }
-            if (ENV == RL4CO_ENV_CVRP) {                // + (capacity - used) * remaining-capacity column
+            if (CAPCOL) {                               // + (capacity - used) * remaining-capacity column (op: length)
                 const float rem = __fsub_rn(cap, used);
                 const u64 rem2 = pack2(rem, rem);
                 const ulonglong2 w0 = *reinterpret_cast<const ulonglong2 *>(s_wc + dim0);
@@ -670,6 +711,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 float2 w = q == nact ? s_locs[0] : s_locs[s_act[q]];
                 part += leg(p.x, p.y, w.x, w.y);
             }
+        } else if (ENV == RL4CO_ENV_OP) {        // op/env.py:172-182: minus the collected prize (negated below)
+            for (int q = tid; q < nact; q += kThreads) part -= a.prize[b * (int64_t)N + s_act[q]];
         } else {                                 // slap/env.py:131-143 (assignment[t] = s_act[t])
             const int64_t *pl = a.picklist + b * (int64_t)a.O * a.K;
             for (int o = tid; o < a.O; o += kThreads)
@@ -759,7 +802,7 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
-    if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
+    if (a.multistart && (a.env == RL4CO_ENV_SLAP || a.env == RL4CO_ENV_OP)) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
 }
 
@@ -767,6 +810,7 @@ int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream) {
     switch (a.env) {
         case RL4CO_ENV_TSP: return rf::launch_env<RL4CO_ENV_TSP>(a, stream);
         case RL4CO_ENV_CVRP: return rf::launch_env<RL4CO_ENV_CVRP>(a, stream);
+        case RL4CO_ENV_OP: return rf::launch_env<RL4CO_ENV_OP>(a, stream);
         default: return rf::launch_env<RL4CO_ENV_SLAP>(a, stream);
     }
 }

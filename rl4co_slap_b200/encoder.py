@@ -38,6 +38,21 @@ class VRPInitEmbedding(nn.Module):
         return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
 
 
+class OPInitEmbedding(nn.Module):
+    """x, y, prize for the customers, x, y for the depot (nn/env_embeddings/init.py:207-233)."""
+
+    def __init__(self, embed_dim: int, linear_bias: bool = True):
+        super().__init__()
+        self.init_embed = nn.Linear(3, embed_dim, linear_bias)
+        self.init_embed_depot = nn.Linear(2, embed_dim, linear_bias)
+
+    def forward(self, td):
+        locs = td["locs"]
+        depot, cities = locs[:, :1, :], locs[:, 1:, :]
+        feats = torch.cat((cities, td["prize"][..., 1:, None]), -1)
+        return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
+
+
 class SLAPInitEmbedding(nn.Module):
     """x, y and Manhattan distance to node 0 (examples/slap.py:11-47)."""
 
@@ -51,7 +66,8 @@ class SLAPInitEmbedding(nn.Module):
         return self.init_embed(torch.cat((locs, d0[..., None]), -1))
 
 
-INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding}
+INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding,
+                   "op": OPInitEmbedding}
 
 
 # ---- linears (widths multiples of 128) on the tensor cores ----------------------------------------------

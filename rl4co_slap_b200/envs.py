@@ -15,13 +15,22 @@ from __future__ import annotations
 from typing import Optional
 
 import torch
+import torch.nn.functional as F
 
 from . import _lib
-from .generators import CVRPGenerator, SLAPGenerator, TSPGenerator
+from .generators import CVRPGenerator, OPGenerator, SLAPGenerator, TSPGenerator
 from .ops import get_num_starts, select_start_nodes
 from .tensordict_compat import TensorDict
 
 _u8 = torch.uint8
+
+
+def _norm2(d: torch.Tensor) -> torch.Tensor:
+    """L2 norm of [..., 2] differences with the rounding sequence of torch's CPU vector norm,
+    sqrt(fma(dy, dy, dx * dx)) (addcmul is a fused multiply-add on CUDA): the reset-time budgets the masks
+    are compared against are then the same fp32 numbers as the CPU reference's."""
+    dx, dy = d[..., 0], d[..., 1]
+    return torch.sqrt(torch.addcmul(dx * dx, dy, dy))
 
 
 def _as_u8(t: torch.Tensor) -> torch.Tensor:
@@ -355,6 +364,126 @@ class CVRPEnv(RL4COEnvBase):
 
 
 # =====================================================================================
+class OPEnv(RL4COEnvBase):
+    """rl4co/envs/routing/op/env.py:25-238 (orienteering problem): collect prizes and be back at the depot
+    within ``max_length``; the sibling routing environment on the same kernels' skeleton."""
+
+    name = "op"
+
+    def __init__(self, generator: OPGenerator = None, generator_params: dict = {}, prize_type: str = "dist",
+                 **kwargs):
+        super().__init__(**kwargs)
+        if generator is None:
+            generator = OPGenerator(**{"device": self.device, **generator_params})
+        self.generator = generator
+        assert prize_type in ("dist", "unif", "const"), f"Invalid prize_type: {prize_type}"
+        self.prize_type = prize_type
+
+    def _reset(self, td, batch_size=None):
+        """op/env.py:110-152.  The per-node budget is plain tensor arithmetic done once per episode."""
+        _need_cuda(td["locs"], "OPEnv.reset")
+        dev, B = td["locs"].device, int(batch_size[0])
+        locs = torch.cat((td["depot"][:, None, :], td["locs"]), -2)
+        N = locs.shape[-2]
+        out = TensorDict({
+            "locs": locs,
+            "prize": F.pad(td["prize"], (1, 0), mode="constant", value=0),
+            "tour_length": torch.zeros(B, device=dev),
+            "max_length": td["max_length"][..., None] - _norm2(td["depot"][..., None, :] - locs) - 1e-6,
+            "current_node": torch.zeros(B, 1, dtype=torch.long, device=dev),
+            "visited": torch.zeros(B, N, dtype=torch.bool, device=dev),
+            "current_total_prize": torch.zeros(B, dtype=torch.float, device=dev),
+            "i": torch.zeros(B, dtype=torch.int64, device=dev),
+        }, batch_size=batch_size)
+        out.set("action_mask", self.get_action_mask(out))
+        return out
+
+    @staticmethod
+    def get_action_mask(td):
+        """op/env.py:154-170 -> rl4co_op_action_mask."""
+        locs = td["locs"]
+        _need_cuda(locs, "OPEnv.get_action_mask")
+        dev, (B, N, _) = locs.device, locs.shape
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        _lib.call("rl4co_op_action_mask", B, N, _lib.ptr(locs.contiguous(), torch.float32),
+                  _lib.ptr(td["max_length"].contiguous(), torch.float32),
+                  _lib.ptr(td["tour_length"].contiguous(), torch.float32),
+                  _lib.ptr(_as_u8(td["visited"].contiguous())),
+                  _lib.ptr(td["current_node"].contiguous(), torch.int64),
+                  _lib.ptr(_as_u8(mask)), _lib.stream_ptr(dev))
+        return mask
+
+    def _step(self, td):
+        """op/env.py:74-108 -> rl4co_op_step (transition + mask in one launch)."""
+        action = td["action"]
+        _need_cuda(action, "OPEnv._step")
+        dev, (B, N, _) = action.device, td["locs"].shape
+        length, total = td["tour_length"].clone(), td["current_total_prize"].clone()
+        visited, i = td["visited"].clone(), td["i"].clone()
+        cur = td["current_node"].clone()
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        done = torch.empty(B, dtype=torch.bool, device=dev)
+        status = _lib.deferred_status(dev)
+        _lib.call("rl4co_op_step", B, N, _lib.ptr(action.contiguous(), torch.int64),
+                  _lib.ptr(td["locs"].contiguous(), torch.float32), _lib.ptr(td["prize"].contiguous(), torch.float32),
+                  _lib.ptr(td["max_length"].contiguous(), torch.float32), _lib.ptr(length), _lib.ptr(total),
+                  _lib.ptr(cur, torch.int64), _lib.ptr(_as_u8(visited)), _lib.ptr(i, torch.int64),
+                  _lib.ptr(_as_u8(mask)), _lib.ptr(_as_u8(done)), _lib.ptr(status), _lib.stream_ptr(dev))
+        td.update({"tour_length": length, "current_node": cur, "visited": visited,
+                   "current_total_prize": total, "i": i, "reward": torch.zeros_like(done), "done": done})
+        td.set("action_mask", mask)
+        return td
+
+    def _replay_call(self, td, actions, check, want_state):
+        locs = td["locs"]
+        _need_cuda(locs, "OPEnv.replay")
+        dev, (B, N, _) = locs.device, locs.shape
+        T = actions.shape[1]
+        reward = torch.empty(B, dtype=torch.float32, device=dev)
+        status = _lib.new_status(dev)
+        st = {}
+        if want_state:
+            st = {"current_node": torch.empty(B, 1, dtype=torch.int64, device=dev),
+                  "tour_length": torch.empty(B, dtype=torch.float32, device=dev),
+                  "current_total_prize": torch.empty(B, dtype=torch.float32, device=dev),
+                  "visited": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "action_mask": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "i": torch.empty(B, dtype=torch.int64, device=dev),
+                  "done": torch.empty(B, dtype=torch.bool, device=dev)}
+        p = lambda k: _lib.ptr(_as_u8(st[k])) if k in st else None  # noqa: E731
+        _lib.call("rl4co_op_replay", B, N, T, _lib.ptr(locs.contiguous(), torch.float32),
+                  _lib.ptr(td["prize"].contiguous(), torch.float32),
+                  _lib.ptr(td["max_length"].contiguous(), torch.float32),
+                  _lib.ptr(actions.contiguous(), torch.int64), p("current_node"), p("tour_length"),
+                  p("current_total_prize"), p("visited"), p("action_mask"), p("i"), p("done"),
+                  _lib.ptr(reward), int(bool(check)), _lib.ptr(status), _lib.stream_ptr(dev))
+        _lib.raise_for_status(status)
+        return st, reward
+
+    def replay(self, td, actions, check: Optional[bool] = None):
+        """Fused reset-state + T x _step + get_reward.  ``td`` is a reset td."""
+        check = self.check_solution if check is None else check
+        st, reward = self._replay_call(td, actions, check, True)
+        out = TensorDict({"locs": td["locs"], "prize": td["prize"], "max_length": td["max_length"], **st,
+                          "reward": torch.zeros_like(st["done"])}, batch_size=[actions.shape[0]])
+        return out, reward
+
+    def _get_reward(self, td, actions):
+        """op/env.py:172-182."""
+        if actions.size(-1) == 1:
+            assert (actions == 0).all(), "If all length 1 tours, they should be zero"
+            return torch.zeros(actions.size(0), dtype=torch.float, device=actions.device)
+        return self._replay_call(td, actions, False, False)[1]
+
+    def check_solution_validity(self, td, actions, add_distance_to_depot: bool = True) -> None:
+        """op/env.py:184-215: "Duplicates" / "Max length exceeded" (``td`` carries the reset state's budgets, so
+        the depot leg is added back as with the reference's default add_distance_to_depot=True)."""
+        if not add_distance_to_depot:
+            raise NotImplementedError("check_solution_validity(add_distance_to_depot=False)")
+        self._replay_call(td, actions, True, False)
+
+
+# =====================================================================================
 class SLAPEnv(RL4COEnvBase):
     """rl4co/envs/warehousing/slap/env.py:17-182."""
 
@@ -448,7 +577,7 @@ class SLAPEnv(RL4COEnvBase):
         return out, reward
 
 
-ENV_REGISTRY = {"tsp": TSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv}
+ENV_REGISTRY = {"tsp": TSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv}
 
 
 def get_env(env_name: str, *args, **kwargs) -> RL4COEnvBase:

@@ -2,7 +2,7 @@
 
 Follows rl4co/envs/common/utils.py:11-92 (Generator, get_sampler),
 rl4co/envs/routing/tsp/generator.py:14-60, rl4co/envs/routing/cvrp/generator.py:15-143,
-rl4co/envs/warehousing/slap/generator.py:21-155.
+rl4co/envs/warehousing/slap/generator.py:21-155, rl4co/envs/routing/op/generator.py:15-169.
 
 Generators are data preparation, not the hot path: they are vectorised torch code that
 runs on whatever ``device`` is asked for (the reference always samples on the CPU; its
@@ -138,6 +138,64 @@ class CVRPGenerator(Generator):
         capacity = torch.full((*batch_size, 1), self.capacity, device=demand.device)
         return TensorDict({"locs": locs, "depot": depot, "demand": demand / self.capacity,
                            "capacity": capacity}, batch_size=batch_size)
+
+
+# Kool et al. 2019 length budgets (op/generator.py:15-16)
+MAX_LENGTHS = {20: 2.0, 50: 3.0, 100: 4.0}
+
+
+class OPGenerator(Generator):
+    """op/generator.py:19-169 -> td{"locs" [B,n,2], "depot" [B,2], "prize" [B,n], "max_length" [B]}.
+    ``prize_type``: "dist" (1..100 / 100 by the distance to the depot, the default), "unif", "const"
+    (Fischetti et al. 1998, Kool et al. 2019; :133-152)."""
+
+    def __init__(self, num_loc: int = 20, min_loc: float = 0.0, max_loc: float = 1.0,
+                 loc_distribution=Uniform, depot_distribution=None, min_prize: float = 1.0,
+                 max_prize: float = 1.0, prize_distribution=Uniform, prize_type: str = "dist",
+                 max_length=None, device=None, **kwargs):
+        self.num_loc, self.min_loc, self.max_loc = num_loc, min_loc, max_loc
+        self.min_prize, self.max_prize, self.prize_type = min_prize, max_prize, prize_type
+        self.device = device
+        self.loc_sampler = kwargs.get("loc_sampler") or get_sampler(
+            "loc", loc_distribution, min_loc, max_loc, device=device, **kwargs)
+        if kwargs.get("depot_sampler") is not None:
+            self.depot_sampler = kwargs["depot_sampler"]
+        else:
+            self.depot_sampler = (get_sampler("depot", depot_distribution, min_loc, max_loc, device=device, **kwargs)
+                                  if depot_distribution is not None else None)
+        # the reference also builds a prize sampler (:79-88) that _generate never uses; kept only when given
+        self.prize_sampler = kwargs.get("prize_sampler")
+        if max_length is None:
+            max_length = MAX_LENGTHS.get(num_loc)
+        if max_length is None:  # closest table entry (:96-103)
+            closest = min(MAX_LENGTHS.keys(), key=lambda x: abs(x - num_loc))
+            max_length = MAX_LENGTHS[closest]
+        self.max_length = max_length
+
+    def _generate(self, batch_size) -> TensorDict:
+        if self.depot_sampler is not None:
+            depot = self.depot_sampler.sample((*batch_size, 2))
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc, 2))
+        else:  # depot = first sampled location (:112-116)
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc + 1, 2))
+            depot = locs[..., 0, :]
+            locs = locs[..., 1:, :]
+        dev = locs.device
+        if self.prize_type == "const":
+            prize = torch.ones(*batch_size, self.num_loc, device=dev)
+        elif self.prize_type == "unif":
+            prize = (1 + torch.randint(0, 100, (*batch_size, self.num_loc), device=dev).float()) / 100
+        elif self.prize_type == "dist":
+            prize = (depot[..., None, :] - locs).norm(p=2, dim=-1)
+            prize = (1 + (prize / prize.max(dim=-1, keepdim=True)[0] * 99).int()).float() / 100
+        else:
+            raise ValueError(f"Invalid prize_type: {self.prize_type}")
+        if not isinstance(self.max_length, torch.Tensor):
+            max_length = torch.full((*batch_size,), float(self.max_length), device=dev)
+        else:
+            max_length = self.max_length.to(dev)
+        return TensorDict({"locs": locs, "depot": depot, "prize": prize, "max_length": max_length},
+                          batch_size=batch_size)
 
 
 class SLAPGenerator(Generator):

@@ -33,7 +33,7 @@ def _exclusive_visited(actions: torch.Tensor, N: int) -> torch.Tensor:
 
 def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
     """Action masks [R,T,N] (True = feasible), per-step validity [R,T] (False once the episode is done) and, for
-    cvrp, the used capacity [R,T] seen by the context of every step, replayed from ``actions`` [R,T]
+    cvrp / op, the used capacity / tour length [R,T] seen by the context of every step, replayed from ``actions`` [R,T]
     (R = S * B, start-major as utils/ops.py:11-34)."""
     R, T = actions.shape
     N = td["locs"].shape[1]
@@ -44,6 +44,8 @@ def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
         mask = ~_exclusive_visited(actions, N)
         mask[:, :, 0] = False
         return mask, torch.ones(R, T, dtype=torch.bool, device=dev), None
+    if env_name == "op":
+        return _replay_masks_op(td, actions, S)
     # cvrp/env.py:73-149 - sequential in the used capacity (fp32, the reference's order of operations)
     demand = td["demand"].float()
     cap = td["vehicle_capacity"].float().reshape(-1, 1)
@@ -70,6 +72,43 @@ def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
         done = done | (visited.sum(-1) == N)                           # :91
         cur = a
     return torch.stack(masks, 1), torch.stack(valid, 1), torch.stack(useds, 1)
+
+
+def _leg(d: torch.Tensor) -> torch.Tensor:
+    """[..., 2] -> [...] Euclidean length with the rounding of torch's CPU vector norm on either device
+    (sqrt(fma(dy, dy, dx dx)); on CUDA addcmul is the fused multiply-add)."""
+    if not d.is_cuda:
+        return d.norm(p=2, dim=-1)
+    return torch.sqrt(torch.addcmul(d[..., 0] * d[..., 0], d[..., 1], d[..., 1]))
+
+
+def _replay_masks_op(td, actions: torch.Tensor, S: int):
+    """op/env.py:74-170 replayed from the actions: masks, validity and the tour length seen by every step."""
+    R, T = actions.shape
+    locs, budget = td["locs"].float(), td["max_length"].float()
+    if S > 1:
+        locs, budget = locs.repeat(S, 1, 1), budget.repeat(S, 1)
+    N, dev = locs.shape[1], actions.device
+    rows = torch.arange(R, device=dev)
+    length = torch.zeros(R, device=dev)
+    visited = torch.zeros(R, N, dtype=torch.bool, device=dev)
+    cur = torch.zeros(R, dtype=torch.int64, device=dev)
+    done = torch.zeros(R, dtype=torch.bool, device=dev)
+    masks, lengths, valid = [], [], []
+    for t in range(T):
+        exceeds = length[:, None] + _leg(locs - locs[rows, cur][:, None, :]) > budget     # :159-162
+        m = ~(visited | visited[:, 0:1] | exceeds)                                        # :163-165
+        m[:, 0] = True                                                                    # :168
+        masks.append(m)
+        lengths.append(length)
+        valid.append(~done)
+        a = actions[:, t]
+        length = length + _leg(locs[rows, a] - locs[rows, cur])                           # :78-81
+        visited = visited.clone()
+        visited[rows, a] = True
+        done = done | ((a == 0) & (t > 0))                                                # :92
+        cur = a
+    return torch.stack(masks, 1), torch.stack(valid, 1), torch.stack(lengths, 1)
 
 
 def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, actions: torch.Tensor,
@@ -117,6 +156,9 @@ def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, ac
     elif env_name == "cvrp":
         cap = td["vehicle_capacity"].float().reshape(B, 1)
         rem = cap.repeat(S, 1) - used                                     # [R,T]  (context.py:326-329)
+        ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
+    elif env_name == "op":            # [h_cur ; max_length[..., 0] - tour_length] (context.py:385-397)
+        rem = td["max_length"].float()[:, :1].repeat(S, 1) - used
         ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
     else:
         ctx = torch.zeros(B, L, E, device=dev, dtype=h.dtype)

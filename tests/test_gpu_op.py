@@ -1,0 +1,141 @@
+"""GPU parity of the orienteering problem (OP), the sibling routing environment:
+env kernels and the register-file rollout kernel vs the fixtures of the unmodified reference and the oracle
+port.  (tests/test_gpu_envs.py runs the step-by-step and fused replays of the op fixtures bit-exact.)
+Tours / masks bit-exact; rewards and log-likelihoods within 1e-5 relative."""
+import numpy as np
+import pytest
+import torch
+
+import rl4co_slap_b200 as R
+from oracle import port
+from tests.helpers import OP_CASES, fixture, gen_td, load_policy, oracle_reset, oracle_weights, t
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def _setup(case, dev):
+    fx = fixture(case)
+    pol, env = load_policy("op", dev), R.OPEnv(device=dev)
+    return fx, pol, env, env.reset(gen_td("op", fx, dev))
+
+
+@pytest.mark.parametrize("case", OP_CASES)
+def test_greedy_matches_reference_fixture(case, dev):
+    fx, pol, env, td = _setup(case, dev)
+    out = pol(td, env, decode_type="greedy", return_actions=True, hidden=t(fx["hidden"], dev),
+              return_sum_log_likelihood=False)
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["greedy.actions"]), "tours differ from the reference"
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["greedy.reward"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["greedy.logprobs"], rtol=1e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("case", OP_CASES)
+def test_evaluate_random_tours_matches_reference_fixture(case, dev):
+    """the reference policy's per-step log-probs of the replay's random tours (they run into the length budget,
+    so the masks that feed the glimpse and the log-softmax are exercised)"""
+    fx, pol, env, td = _setup(case, dev)
+    acts = t(fx["replay.actions"], dev)
+    out = pol(td, env, actions=acts, hidden=t(fx["hidden"], dev), return_actions=True,
+              return_sum_log_likelihood=False)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["eval.logprobs"], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(out["log_likelihood"].sum(1).cpu().numpy(), fx["eval.ll"], rtol=RTOL, atol=2e-5)
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["eval.reward"], rtol=RTOL, atol=1e-6)
+
+
+def _nearest_neighbour_tours(o0):
+    """long feasible tours from the oracle env: always the nearest feasible customer, depot when none is left"""
+    td = dict(o0)
+    acts = []
+    while not td["done"].all():
+        cur = port.gather_by_index(td["locs"], td["current_node"])[:, None, :]
+        d = (td["locs"] - cur).norm(p=2, dim=-1).masked_fill(~td["action_mask"], float("inf"))
+        d[:, 0] = 1e9                                    # depot only when nothing else is feasible
+        a = d.argmin(-1)
+        td["action"] = a
+        td = port.op_step(td)
+        acts.append(a)
+    return torch.stack(acts, 1)
+
+
+@pytest.mark.parametrize("size,B", [(100, 48), (127, 9), (33, 40), (5, 16)])
+def test_full_policy_vs_oracle(size, B, dev):
+    """random instances, fresh random weights, the PyTorch encoder on the GPU: greedy tours and nearest-neighbour
+    tours (the longest the budget allows) against the oracle fed with the same embeddings"""
+    torch.manual_seed(100 + size)
+    env = R.OPEnv(generator_params=dict(num_loc=size), device=dev)
+    pol = R.AttentionModelPolicy(env_name="op", num_encoder_layers=2).to(dev).eval()
+    td0 = env.generator(B)
+    td = env.reset(td0)
+    out = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True, return_sum_log_likelihood=False)
+    h = out["hidden"].node_embeddings.cpu()
+    sd = {k: v.detach().cpu() for k, v in pol.state_dict().items()}
+    W = {"Wnode": sd["decoder.project_node_embeddings.weight"], "Wfixed": sd["decoder.project_fixed_context.weight"],
+         "Wout": sd["decoder.pointer.project_out.weight"], "Wctx": sd["decoder.context_embedding.project_context.weight"]}
+    c = td0.cpu()
+    o0 = port.op_reset(c["depot"], c["locs"], c["prize"], c["max_length"])
+    assert torch.equal(td["max_length"].cpu(), o0["max_length"]), "reset budgets differ from the CPU reference arithmetic"
+    assert torch.equal(td["action_mask"].cpu(), o0["action_mask"])
+    ref = port.am_rollout("op", o0, h, W, "greedy")
+    assert torch.equal(out["actions"].cpu(), ref["actions"])
+    torch.testing.assert_close(out["log_likelihood"].cpu(), ref["logprobs"], rtol=1e-4, atol=2e-5)
+    torch.testing.assert_close(out["reward"].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+    nn_acts = _nearest_neighbour_tours(o0)
+    assert nn_acts.shape[1] > min(size, 8)              # these are long tours
+    ref = port.am_rollout("op", o0, h, W, actions=nn_acts)
+    got = pol(td, env, actions=nn_acts.to(dev), hidden=h.to(dev), return_sum_log_likelihood=False)
+    torch.testing.assert_close(got["log_likelihood"].cpu(), ref["logprobs"], rtol=1e-4, atol=3e-5)
+    torch.testing.assert_close(got["reward"].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+    final, reward = env.replay(td, nn_acts.to(dev))
+    torch.testing.assert_close(reward.cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+    for k in ("action_mask", "visited", "tour_length", "current_total_prize", "current_node", "i", "done"):
+        assert torch.equal(final[k].cpu().view(ref["td"][k].shape), ref["td"][k]), k
+
+
+def test_sampling_is_feasible_and_consistent(dev):
+    """sampled tours are valid (the reference's own validity check), their log-likelihood equals the evaluate
+    path's on the same actions, and repeated sampling visits different tours"""
+    torch.manual_seed(7)
+    env = R.OPEnv(generator_params=dict(num_loc=50), device=dev)
+    pol = R.AttentionModelPolicy(env_name="op", num_encoder_layers=1).to(dev).eval()
+    td = env.reset(env.generator(512))
+    out = pol(td, env, decode_type="sampling", return_actions=True, return_hidden=True)
+    env.check_solution_validity(td, out["actions"])
+    c = {k: v.cpu() for k, v in td.items()}
+    port.op_check(c["locs"], c["max_length"], out["actions"].cpu())
+    ev = pol(td, env, actions=out["actions"], hidden=out["hidden"].node_embeddings)
+    torch.testing.assert_close(ev["log_likelihood"], out["log_likelihood"], rtol=RTOL, atol=2e-5)
+    torch.testing.assert_close(ev["reward"], out["reward"], rtol=RTOL, atol=1e-6)
+    torch.testing.assert_close(out["reward"].cpu(), port.op_reward(c["prize"], out["actions"].cpu()), rtol=RTOL, atol=1e-6)
+    out2 = pol(td, env, decode_type="sampling", return_actions=True)
+    T = min(out["actions"].shape[1], out2["actions"].shape[1])
+    assert (out["actions"][:, :T] != out2["actions"][:, :T]).any()
+
+
+def test_invalid_tours_raise_reference_messages(dev):
+    fx, pol, env, td = _setup("op20", dev)
+    acts = t(fx["replay.actions"], dev).clone()
+    bad = acts.clone()
+    row = int((bad[:, 1] != 0).nonzero()[0])
+    bad[row, 0] = bad[row, 1]
+    with pytest.raises(AssertionError, match="Duplicates"):
+        env.check_solution_validity(td, bad)
+    # every customer in index order is far beyond the length budget
+    N = td["locs"].shape[1]
+    long = torch.cat((torch.arange(1, N, device=dev), torch.zeros(1, dtype=torch.int64, device=dev)))[None].repeat(acts.shape[0], 1)
+    with pytest.raises(AssertionError, match="Max length exceeded"):
+        env.check_solution_validity(td, long)
+    with pytest.raises(AssertionError, match="Max length exceeded"):     # get_reward's validity check, as the reference
+        pol(td, env, actions=long, hidden=t(fx["hidden"], dev))
+    with pytest.raises(NotImplementedError, match="multistart"):
+        pol(td, env, decode_type="multistart_greedy", hidden=t(fx["hidden"], dev))
+
+
+def test_training_step_log_likelihood(dev):
+    """the differentiable teacher-forced pass (training.py) reproduces the kernel's log-likelihood for op"""
+    torch.manual_seed(3)
+    env = R.OPEnv(generator_params=dict(num_loc=20), device=dev)
+    pol = R.AttentionModelPolicy(env_name="op", num_encoder_layers=1).to(dev).eval()
+    td = env.reset(env.generator(64))
+    res = R.reinforce_step(pol, env, td, optimizer=None, decode_type="sampling")
+    torch.testing.assert_close(res["log_likelihood"], res["kernel_log_likelihood"], rtol=1e-4, atol=5e-5)

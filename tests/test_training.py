@@ -17,7 +17,25 @@ def _cpu_td(name, fx):
     if name == "cvrp":
         return {"locs": t(fx["reset.locs"]), "demand": t(fx["gen.demand"]),
                 "vehicle_capacity": t(fx["reset.vehicle_capacity"])}
+    if name == "op":
+        return {"locs": t(fx["reset.locs"]), "prize": t(fx["reset.prize"]), "max_length": t(fx["reset.max_length"])}
     return {"locs": t(fx["gen.locs"])}
+
+
+@pytest.mark.parametrize("case", ("op20", "op50", "op100"))
+def test_teacher_forced_ll_op_cpu(case):
+    """op: per-step log-probs of the replay's random tours (and the masks behind them) equal the reference's"""
+    fx = fixture(case)
+    pol = load_policy("op", "cpu")
+    acts = t(fx["replay.actions"])
+    mask, valid, length = replay_masks("op", _cpu_td("op", fx), acts)
+    assert np.array_equal(mask[:, 0].numpy(), fx["reset.action_mask"])
+    for s in range(acts.shape[1] - 1):
+        assert np.array_equal(mask[:, s + 1].numpy(), fx[f"step{s}.action_mask"]), s
+        assert np.array_equal(length[:, s + 1].numpy(), fx[f"step{s}.tour_length"]), s
+    with torch.no_grad():
+        lp = teacher_forced_log_likelihood(pol, _cpu_td("op", fx), "op", t(fx["hidden"]), acts, return_sum=False)
+    np.testing.assert_allclose(lp.numpy(), fx["eval.logprobs"], rtol=1e-4, atol=2e-5)
 
 
 @pytest.mark.parametrize("case", ("tsp20", "tsp50", "cvrp20", "cvrp50", "slap50"))
