@@ -292,7 +292,7 @@ def run_ours(args):
     }
     if e2e is not None:
         line["e2e"] = e2e
-    if not args.no_cpu_baseline and world >= 1:
+    if not args.no_cpu_baseline and world == 1:     # host-core baseline: rank 0 of the single-GPU run only
         threads = os.cpu_count() or 1
         v, sec = cpu_reference(build_policy("cpu"), args.ref_batch, args.ref_steps, 1, threads)
         line["cpu_baseline"] = {"value": v, "unit": "rollouts/s", "cores": threads, "kind": "port",
