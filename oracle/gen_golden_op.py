@@ -20,9 +20,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import gen_golden as G  # noqa: E402  (installs the shim)
 
 from rl4co.envs.routing.op.env import OPEnv  # noqa: E402
+from rl4co.envs.routing.pctsp.env import PCTSPEnv  # noqa: E402
+from rl4co.envs.routing.spctsp.env import SPCTSPEnv  # noqa: E402
 from rl4co.models.zoo.am.policy import AttentionModelPolicy  # noqa: E402
 
 G.GEN_KEYS["op"] = ("locs", "depot", "prize", "max_length")
+G.GEN_KEYS["pctsp"] = G.GEN_KEYS["spctsp"] = ("locs", "depot", "penalty", "deterministic_prize", "stochastic_prize")
 
 
 def late_depot(w):
@@ -60,5 +63,35 @@ def main():
               f"replay T={data['replay.actions'].shape[1]}")
 
 
+def main_pctsp():
+    """pctsp / spctsp (same policy class; spctsp collects the stochastic prize)."""
+    torch.manual_seed(8765)
+    np.random.seed(8765)
+    for name, cls in (("pctsp", PCTSPEnv), ("spctsp", SPCTSPEnv)):
+        pol = AttentionModelPolicy(env_name=name, num_encoder_layers=1, feedforward_hidden=128).eval()
+        np.savez_compressed(os.path.join(G.OUT, f"policy_{name}.npz"),
+                            **{k: G.np_(v) for k, v in pol.state_dict().items()})
+        for size, B in (((10, 8), (20, 8), (50, 6), (100, 4)) if name == "pctsp" else ((20, 8), (50, 6))):
+            env = cls(generator_params=dict(num_loc=size))
+            td0 = env.generator(B)
+            data = {f"gen.{k}": G.np_(td0[k]) for k in G.GEN_KEYS[name]}
+            data["gen.prize_required"] = np.float32(env.generator.prize_required)
+            data.update(G.replay_trace(env, td0))
+            td_r = env.reset(td0.clone())
+            data["reset.penalty"] = G.np_(td_r["penalty"])
+            res, h = G.policy_outputs(env, pol, td0, "greedy", decode_type="greedy")
+            data.update(res)
+            data["hidden"] = G.np_(h)
+            res, _ = G.policy_outputs(env, pol, td0, "eval", actions=torch.from_numpy(data["replay.actions"]))
+            data.update(res)
+            path = os.path.join(G.OUT, f"{name}{size}.npz")
+            np.savez_compressed(path, **data)
+            print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, greedy mean reward "
+                  f"{data['greedy.reward'].mean():.4f}, T={data['greedy.actions'].shape[1]}, "
+                  f"replay T={data['replay.actions'].shape[1]}")
+
+
 if __name__ == "__main__":
-    main()
+    if "--pctsp-only" not in sys.argv:
+        main()
+    main_pctsp()

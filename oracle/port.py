@@ -67,7 +67,7 @@ def unbatchify(x, repeats: int):
 def num_starts_for(env_name: str, action_mask) -> int:
     """utils/ops.py:126-136."""
     n = action_mask.shape[-1]
-    return n - 1 if env_name in ("cvrp", "op") else n
+    return n - 1 if env_name in ("cvrp", "op", "pctsp", "spctsp") else n
 
 
 def select_start_nodes(env_name: str, batch: int, num_starts: int, num_loc: int):
@@ -255,6 +255,74 @@ def op_reward(prize_with_depot, actions):
 
 
 # =====================================================================================
+# PCTSP / SPCTSP  (envs/routing/pctsp/env.py, envs/routing/spctsp/env.py)
+# =====================================================================================
+def pctsp_action_mask(td: State):
+    """pctsp/env.py:141-148: no node twice, nothing after the return to the depot; the depot is closed while
+    the collected prize is below 1 and customers remain."""
+    mask = td["visited"] | td["visited"][..., 0:1]
+    mask[..., 0] = (td["cur_total_prize"] < 1.0) & (
+        td["visited"][..., 1:].int().sum(-1) < td["visited"][..., 1:].size(-1))
+    return ~(mask > 0)
+
+
+def pctsp_reset(depot, locs, penalty, deterministic_prize, stochastic_prize, prize_required: float = 1.0,
+                stochastic: bool = False) -> State:
+    """pctsp/env.py:103-139 (+ merge).  spctsp: the collected (real) prize is the stochastic one, the encoder
+    still sees the expected prize (spctsp/env.py:8-17)."""
+    B, n, _ = locs.shape
+    real = stochastic_prize if stochastic else deterministic_prize
+    td = {
+        "locs": torch.cat([depot[..., None, :], locs], dim=-2),
+        "current_node": torch.zeros(B, dtype=torch.int64),
+        "expected_prize": deterministic_prize,
+        "real_prize": torch.cat([torch.zeros_like(real[..., :1]), real], dim=-1),
+        "penalty": F.pad(penalty, (1, 0), mode="constant", value=0),
+        "cur_total_prize": torch.zeros(B),
+        "cur_total_penalty": penalty.sum(-1),
+        "visited": torch.zeros(B, n + 1, dtype=torch.bool),
+        "prize_required": torch.full((B,), prize_required),
+        "i": torch.zeros(B, dtype=torch.int64),
+        "done": torch.zeros(B, 1, dtype=torch.bool),
+        "terminated": torch.zeros(B, 1, dtype=torch.bool),
+    }
+    td["action_mask"] = pctsp_action_mask(td)
+    return td
+
+
+def pctsp_step(td: State) -> State:
+    """pctsp/env.py:69-101."""
+    cur = td["action"]
+    prize = td["cur_total_prize"] + gather_by_index(td["real_prize"], cur)
+    pen = td["cur_total_penalty"] + gather_by_index(td["penalty"], cur)
+    visited = td["visited"].scatter(-1, cur[..., None], 1)
+    done = (td["i"] > 0) & (cur == 0)
+    td.update({"current_node": cur, "cur_total_prize": prize, "cur_total_penalty": pen, "visited": visited,
+               "i": td["i"] + 1, "reward": torch.zeros_like(done), "done": done})
+    td["action_mask"] = pctsp_action_mask(td)
+    return td
+
+
+def pctsp_check(td: State, actions) -> None:
+    """pctsp/env.py:176-200."""
+    sa = actions.sort(1)[0]
+    assert ((sa[..., 1:] == 0) | (sa[..., 1:] > sa[..., :-1])).all(), "Duplicates"
+    p = td["real_prize"].gather(1, actions)
+    assert ((p.sum(-1) >= 1 - 1e-5) | (sa.size(-1) - (sa == 0).int().sum(-1) == (td["locs"].size(-2) - 1))
+            ).all(), "Total prize does not satisfy min total prize"
+
+
+def pctsp_reward(td: State, actions):
+    """pctsp/env.py:150-174: saved penalties - (tour length from and to the depot + all penalties)."""
+    if actions.size(-1) == 1:
+        assert (actions == 0).all(), "If all length 1 tours, they should be zero"
+        return torch.zeros(actions.size(0))
+    ordered = torch.cat([td["locs"][..., 0:1, :], gather_by_index(td["locs"], actions)], dim=1)
+    saved = td["penalty"].gather(1, actions)
+    return saved.sum(-1) - (tour_length(ordered) + td["penalty"][..., 1:].sum(-1))
+
+
+# =====================================================================================
 # SLAP  (envs/warehousing/slap/env.py)
 # =====================================================================================
 def slap_reset(locs, assignment, n_products: int, extra: Optional[State] = None) -> State:
@@ -352,6 +420,10 @@ def context_embedding(env_name: str, cache, td: State, W):
         cur = gather_by_index(h, td["current_node"])
         state = (td["max_length"][..., 0] - td["tour_length"])[..., None].to(cur.dtype)
         return F.linear(torch.cat([cur, state], -1), W["Wctx"])
+    if env_name in ("pctsp", "spctsp"):     # PCTSPContext, context.py:368-382
+        cur = gather_by_index(h, td["current_node"])
+        state = torch.clamp(td["prize_required"] - td["cur_total_prize"], min=0)[..., None].to(cur.dtype)
+        return F.linear(torch.cat([cur, state], -1), W["Wctx"])
     if env_name == "slap":
         return h.new_zeros(B, h.size(-1))
     raise ValueError(env_name)
@@ -416,7 +488,8 @@ def select_action(logprobs, mask, decode_type: str, given=None):
     return sel
 
 
-_STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step, "op": op_step}
+_STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step, "op": op_step, "pctsp": pctsp_step,
+         "spctsp": pctsp_step}
 
 
 def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
@@ -469,6 +542,10 @@ def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
         if check_solution:
             op_check(td["locs"], td["max_length"], out_actions)
         reward = op_reward(td["prize"], out_actions)
+    elif env_name in ("pctsp", "spctsp"):
+        if check_solution:
+            pctsp_check(td, out_actions)
+        reward = pctsp_reward(td, out_actions)
     else:
         reward = slap_reward(td["locs"], td["assignment"], td["picklist"])
     lp_sel = logprobs.gather(-1, out_actions.unsqueeze(-1)).squeeze(-1) if logprobs.dim() == 3 else logprobs

@@ -9,6 +9,8 @@ import torch
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TSP_CASES, CVRP_CASES, SLAP_CASES = ("tsp5", "tsp20", "tsp50", "tsp100"), ("cvrp10", "cvrp20", "cvrp50", "cvrp100"), ("slap50", "slap100")
 OP_CASES = ("op10", "op20", "op50", "op100")
+PCTSP_CASES = ("pctsp10", "pctsp20", "pctsp50", "pctsp100", "spctsp20", "spctsp50")
+_PCTSP_KEYS = ("locs", "depot", "penalty", "deterministic_prize", "stochastic_prize")
 
 
 def fixture(name):
@@ -60,7 +62,7 @@ def gen_td(env_name: str, fx, dev=None):
     from rl4co_slap_b200 import TensorDict
     keys = {"tsp": ("locs",), "cvrp": ("locs", "depot", "demand", "capacity"),
             "slap": ("locs", "freq", "assignment", "picklist", "depot_loc_dist"),
-            "op": ("locs", "depot", "prize", "max_length")}[env_name]
+            "op": ("locs", "depot", "prize", "max_length"), "pctsp": _PCTSP_KEYS, "spctsp": _PCTSP_KEYS}[env_name]
     d = {k: t(fx[f"gen.{k}"], dev) for k in keys}
     return TensorDict(d, batch_size=[d["locs"].shape[0]])
 
@@ -78,5 +80,9 @@ def oracle_reset(env_name: str, fx):
                                float(fx["gen.vehicle_capacity"]))
     if env_name == "op":
         return port.op_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.prize"]), t(fx["gen.max_length"]))
+    if env_name in ("pctsp", "spctsp"):
+        return port.pctsp_reset(*(t(fx[f"gen.{k}"]) for k in ("depot", "locs", "penalty", "deterministic_prize",
+                                                               "stochastic_prize")),
+                                prize_required=float(fx["gen.prize_required"]), stochastic=env_name == "spctsp")
     extra = {k: t(fx[f"gen.{k}"]) for k in ("freq", "picklist", "depot_loc_dist")}
     return port.slap_reset(t(fx["gen.locs"]), t(fx["gen.assignment"]), fx["gen.freq"].shape[-2], extra)

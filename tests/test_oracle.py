@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import port
-from tests.helpers import (CVRP_CASES, OP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
+from tests.helpers import (CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
                            oracle_weights, t)
 
 
@@ -14,7 +14,7 @@ def _state_keys(fx, prefix):
     return [k[len(prefix) + 1:] for k in fx.files if k.startswith(prefix + ".")]
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
 def test_replay_bit_exact(case):
     """every per-step state tensor (mask, visited, capacity, i, done ...) equals the reference's"""
     fx, name = fixture(case), env_of(case)
@@ -39,12 +39,15 @@ def test_replay_bit_exact(case):
     elif name == "op":
         port.op_check(td["locs"], td["max_length"], acts)
         r = port.op_reward(td["prize"], acts)
+    elif name in ("pctsp", "spctsp"):
+        port.pctsp_check(td, acts)
+        r = port.pctsp_reward(td, acts)
     else:
         r = port.slap_reward(td["locs"], td["assignment"], td["picklist"])
     assert np.array_equal(r.numpy(), fx["replay.reward"])
 
 
-@pytest.mark.parametrize("case", ("tsp20", "tsp50", "tsp100", "cvrp20", "cvrp50", "slap50", "slap100") + OP_CASES)
+@pytest.mark.parametrize("case", ("tsp20", "tsp50", "tsp100", "cvrp20", "cvrp50", "slap50", "slap100") + OP_CASES + PCTSP_CASES)
 def test_greedy_rollout_matches_reference(case):
     fx, name = fixture(case), env_of(case)
     out = port.am_rollout(name, oracle_reset(name, fx), t(fx["hidden"]), oracle_weights(name), "greedy")
@@ -80,11 +83,11 @@ def test_evaluate_reproduces_ll():
     np.testing.assert_allclose(out["log_likelihood"].numpy(), fx["greedy.ll"], rtol=1e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("case", OP_CASES)
+@pytest.mark.parametrize("case", OP_CASES + PCTSP_CASES)
 def test_op_evaluate_long_tours(case):
     """per-step log-probs of the replay's random tours (they run into the length budget) = the reference's"""
-    fx = fixture(case)
-    out = port.am_rollout("op", oracle_reset("op", fx), t(fx["hidden"]), oracle_weights("op"),
+    fx, name = fixture(case), env_of(case)
+    out = port.am_rollout(name, oracle_reset(name, fx), t(fx["hidden"]), oracle_weights(name),
                           actions=t(fx["replay.actions"]))
     np.testing.assert_allclose(out["logprobs"].numpy(), fx["eval.logprobs"], rtol=1e-5, atol=2e-6)
     np.testing.assert_allclose(out["reward"].numpy(), fx["eval.reward"], rtol=1e-6, atol=1e-6)
