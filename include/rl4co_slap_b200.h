@@ -40,6 +40,7 @@ extern "C" {
 #define RL4CO_ST_ACTION_RANGE      32  /* action outside [0,N): torch gather/scatter would raise */
 #define RL4CO_ST_DUPLICATES        64  /* op/env.py:196-199 */
 #define RL4CO_ST_OVER_LENGTH       128 /* op/env.py:211-215 */
+#define RL4CO_ST_PRIZE_SHORT       256 /* pctsp/env.py:193-200 */
 
 typedef void *rl4co_stream_t;
 
@@ -119,6 +120,29 @@ int rl4co_op_replay(int64_t B, int32_t N, int32_t T, const float *locs, const fl
                     uint8_t *action_mask, int64_t *i, uint8_t *done, float *reward,
                     int32_t check_validity, int32_t *status, rl4co_stream_t stream);
 
+/* ------------------------------------------------------------------ PCTSP (K1) ----- */
+/* Prize-collecting TSP and its stochastic variant (spctsp: real_prize is the stochastic prize).  N counts the
+ * depot; real_prize / penalty [B,N] carry 0 for the depot (pctsp/env.py:114-118); current_node, cur_total_prize,
+ * cur_total_penalty, i are [B]; visited is the reference's bool tensor. */
+
+/* PCTSPEnv.get_action_mask, envs/routing/pctsp/env.py:141-148. */
+int rl4co_pctsp_action_mask(int64_t B, int32_t N, const float *cur_total_prize, const uint8_t *visited,
+                            uint8_t *action_mask, rl4co_stream_t stream);
+
+/* PCTSPEnv._step, envs/routing/pctsp/env.py:69-101 (transition + mask in one launch).  done is [B]. */
+int rl4co_pctsp_step(int64_t B, int32_t N, const int64_t *action, const float *real_prize, const float *penalty,
+                     float *cur_total_prize, float *cur_total_penalty, int64_t *current_node, uint8_t *visited,
+                     int64_t *i, uint8_t *action_mask, uint8_t *done, int32_t *status, rl4co_stream_t stream);
+
+/* Fused reset-state + T x _step + _get_reward + check_solution_validity (pctsp/env.py:69-200).  Outputs may be
+ * NULL; cur_total_penalty is in/out and enters holding the reset state's value (penalty.sum(-1), :123).
+ * check_validity != 0 ORs RL4CO_ST_DUPLICATES / RL4CO_ST_PRIZE_SHORT. */
+int rl4co_pctsp_replay(int64_t B, int32_t N, int32_t T, const float *locs, const float *real_prize,
+                       const float *penalty, const int64_t *actions, int64_t *current_node,
+                       float *cur_total_prize, float *cur_total_penalty, uint8_t *visited, uint8_t *action_mask,
+                       int64_t *i, uint8_t *done, float *reward, int32_t check_validity, int32_t *status,
+                       rl4co_stream_t stream);
+
 /* ------------------------------------------------------------------ SLAP (K1) ------ */
 /* N storage locations (node 0 = depot, never assignable), P products. */
 
@@ -149,6 +173,7 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
 #define RL4CO_ENV_CVRP 1
 #define RL4CO_ENV_SLAP 2
 #define RL4CO_ENV_OP   3   /* envs/routing/op/env.py; single start, register-file kernel only (N <= 128) */
+#define RL4CO_ENV_PCTSP 4  /* envs/routing/pctsp/env.py and spctsp/env.py (prize = the real prize); same limits as OP */
 
 #define RL4CO_MODE_GREEDY   0  /* utils/decoding.py:371-381,410-418 */
 #define RL4CO_MODE_SAMPLING 1  /* utils/decoding.py:383-397,475-483 (Philox instead of torch.multinomial) */
@@ -262,6 +287,11 @@ typedef struct rl4co_am_rollout_args {
      * project_context (context.py:385-397); reward = collected prize */
     const float *prize;
     const float *max_length;
+    /* pctsp / spctsp (appended, ABI 2): prize = real_prize [B,N] (0 for the depot; the stochastic prize for spctsp),
+     * penalty [B,N] (0 for the depot), prize_required [B]; wcap = the remaining-prize column of project_context
+     * (context.py:368-382); reward = saved penalties - (tour length + all penalties) (pctsp/env.py:150-174) */
+    const float *penalty;
+    const float *prize_required;
 } rl4co_am_rollout_args;
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);

@@ -506,14 +506,14 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     RL4CO_REQUIRE(args != nullptr, "am_rollout: null args");
     const rl4co_am_rollout_args &a = *args;
     if (a.B == 0) return 0;
-    RL4CO_REQUIRE(a.env >= RL4CO_ENV_TSP && a.env <= RL4CO_ENV_OP, "am_rollout: unknown env %d", a.env);
+    RL4CO_REQUIRE(a.env >= RL4CO_ENV_TSP && a.env <= RL4CO_ENV_PCTSP, "am_rollout: unknown env %d", a.env);
     RL4CO_REQUIRE(a.mode >= RL4CO_MODE_GREEDY && a.mode <= RL4CO_MODE_EVALUATE, "am_rollout: unknown mode %d", a.mode);
     RL4CO_REQUIRE(a.B >= 0 && a.N >= 2 && a.T >= 1, "am_rollout: bad sizes B=%lld N=%d T=%d", (long long)a.B, a.N, a.T);
     RL4CO_REQUIRE(a.N <= kMaxNodes, "am_rollout: N=%d exceeds the %d node slots of this kernel", a.N, kMaxNodes);
     RL4CO_REQUIRE(a.tables && a.locs && a.actions && a.ll && a.reward, "am_rollout: null tensor");
     RL4CO_REQUIRE(a.temperature > 0.f, "am_rollout: temperature must be > 0");
     RL4CO_REQUIRE(a.mode != RL4CO_MODE_EVALUATE || a.actions_in, "am_rollout: evaluate needs actions_in");
-    const int need_tab = a.env == RL4CO_ENV_TSP ? 5 : (a.env == RL4CO_ENV_CVRP || a.env == RL4CO_ENV_OP ? 4 : 3);
+    const int need_tab = a.env == RL4CO_ENV_TSP ? 5 : (a.env == RL4CO_ENV_SLAP ? 3 : 4);
     RL4CO_REQUIRE(a.n_tables >= need_tab, "am_rollout: env needs %d tables, got %d", need_tab, a.n_tables);
     if (a.env == RL4CO_ENV_TSP) RL4CO_REQUIRE(a.q0, "am_rollout: tsp needs q0");
     if (a.env == RL4CO_ENV_CVRP)
@@ -525,6 +525,12 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         RL4CO_REQUIRE(!a.multistart, "am_rollout: op multistart resamples infeasible start nodes with torch.multinomial "
                                      "(utils/ops.py:166-176), not implemented");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: op runs on the register-file kernel only (N <= 128, no logp_all)");
+        return launch_rollout_rf(a, (cudaStream_t)stream);
+    }
+    if (a.env == RL4CO_ENV_PCTSP) {
+        RL4CO_REQUIRE(a.wcap && a.prize && a.penalty && a.prize_required, "am_rollout: pctsp needs wcap/prize/penalty/prize_required");
+        RL4CO_REQUIRE(!a.multistart, "am_rollout: pctsp multistart is not implemented");
+        RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: pctsp runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
     if (a.multistart) RL4CO_REQUIRE(a.num_loc >= 1 && a.env != RL4CO_ENV_SLAP, "am_rollout: bad multistart setup");

@@ -152,7 +152,7 @@ template <int ENV, int M>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     constexpr bool HAS_C = ENV != RL4CO_ENV_SLAP;
-    constexpr bool CAPCOL = ENV == RL4CO_ENV_CVRP || ENV == RL4CO_ENV_OP;   // context = [h_cur ; scalar state]
+    constexpr bool CAPCOL = ENV == RL4CO_ENV_CVRP || ENV == RL4CO_ENV_OP || ENV == RL4CO_ENV_PCTSP;   // context = [h_cur ; scalar state]
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T;
     const Layout L = make_layout(N, T, HAS_C);
@@ -257,6 +257,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         if (tid < 128) {
             if (ENV == RL4CO_ENV_OP)    // op: length budget when ARRIVING at node n (op/env.py:129-133), pads never reachable
                 s_dem[tid] = tid < N ? a.max_length[b * (int64_t)N + tid] : -INFINITY;
+            else if (ENV == RL4CO_ENV_PCTSP)    // pctsp: prize collected at node n (0 for the depot, pctsp/env.py:114-117)
+                s_dem[tid] = tid < N ? a.prize[b * (int64_t)N + tid] : 0.f;
             else
                 s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
         }
@@ -290,9 +292,11 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
         unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
-        // cvrp: vehicle capacity / used capacity; op: the depot's length budget / tour length so far
+        // cvrp: vehicle capacity / used capacity; op: the depot's length budget / tour length so far;
+        // pctsp: required prize / collected prize
         const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b]
-                        : (ENV == RL4CO_ENV_OP) ? a.max_length[b * (int64_t)N] : 0.f;
+                        : (ENV == RL4CO_ENV_OP) ? a.max_length[b * (int64_t)N]
+                        : (ENV == RL4CO_ENV_PCTSP) ? a.prize_required[b] : 0.f;
         float used = 0.f;
         auto cvrp_masks = [&](int at) {             // cvrp/env.py:137-149, both layouts
             unsigned f = 0, rf = 0;
@@ -342,6 +346,16 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             alive = f;
             ralive = rf;
         };
+        auto pctsp_masks = [&]() {                  // pctsp/env.py:141-148, both layouts
+            const bool closed = (__shfl_sync(kFull, rvis, 0) & 1u) != 0u;   // back at the depot: nothing else is feasible
+            const bool all_seen = __all_sync(kFull, (rvis | (lane == 0 ? 1u : 0u)) == rown);
+            const bool depot = !(used < 1.0f && !all_seen);      // closed while the prize is short and customers remain
+            unsigned f = closed ? 0u : (own & ~vis), rf = closed ? 0u : (rown & ~rvis);
+            if (g == 0) f = depot ? (f | 1u) : (f & ~1u);
+            if (lane == 0) rf = depot ? (rf | 1u) : (rf & ~1u);
+            alive = f;
+            ralive = rf;
+        };
         int cur = 0, t = 0, status = 0;
         bool done = false, use_c = CAPCOL;
         const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);   // cvrp, op: until done
@@ -377,6 +391,12 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 rvis |= rbit;
                 done = act == 0 && t > 0;               // back at the depot, except on the very first step
                 if (!done) op_masks(act);
+            } else if (ENV == RL4CO_ENV_PCTSP) {        // pctsp/env.py:69-101
+                used = __fadd_rn(used, s_dem[act]);
+                vis |= abit;
+                rvis |= rbit;
+                done = act == 0 && t > 0;
+                if (!done) pctsp_masks();
             } else {                                    // slap/env.py:38-93
                 alive &= ~abit;
                 ralive &= ~rbit;
@@ -435,6 +455,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         }
         if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
         if (ENV == RL4CO_ENV_OP) op_masks(0);
+        if (ENV == RL4CO_ENV_PCTSP) pctsp_masks();
         cur = 0; t = 0; status = 0; done = false; use_c = CAPCOL;
         set_qb(ENV == RL4CO_ENV_TSP ? a.q0 + dim0 : nullptr);   // tsp step 0: context.py:111-121
         if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
@@ -470,7 +491,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 for (int i = 0; i < 4; ++i) q2[i] = qbs2[i];
             }
             if (CAPCOL) {                               // + (capacity - used) * remaining-capacity column (op: length)
-                const float rem = __fsub_rn(cap, used);
+                // cvrp: capacity - used; op: length budget - tour length; pctsp: max(required - collected prize, 0)
+                const float rem = (ENV == RL4CO_ENV_PCTSP) ? fmaxf(__fsub_rn(cap, used), 0.f) : __fsub_rn(cap, used);
                 const u64 rem2 = pack2(rem, rem);
                 const ulonglong2 w0 = *reinterpret_cast<const ulonglong2 *>(s_wc + dim0);
                 const ulonglong2 w1 = *(reinterpret_cast<const ulonglong2 *>(s_wc + dim0) + 1);
@@ -711,6 +733,15 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 float2 w = q == nact ? s_locs[0] : s_locs[s_act[q]];
                 part += leg(p.x, p.y, w.x, w.y);
             }
+        } else if (ENV == RL4CO_ENV_PCTSP) {     // pctsp/env.py:150-174: length + all penalties - saved penalties
+            const float *pen = a.penalty + b * (int64_t)N;
+            for (int q = tid; q <= nact; q += kThreads) {
+                float2 p = q == 0 ? s_locs[0] : s_locs[s_act[q - 1]];
+                float2 w = q == nact ? s_locs[0] : s_locs[s_act[q]];
+                part += leg(p.x, p.y, w.x, w.y);
+                if (q < nact) part -= pen[s_act[q]];
+            }
+            for (int n = tid + 1; n < N; n += kThreads) part += pen[n];
         } else if (ENV == RL4CO_ENV_OP) {        // op/env.py:172-182: minus the collected prize (negated below)
             for (int q = tid; q < nact; q += kThreads) part -= a.prize[b * (int64_t)N + s_act[q]];
         } else {                                 // slap/env.py:131-143 (assignment[t] = s_act[t])
@@ -803,6 +834,7 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
 #endif
     if (a.N > 128) return false;
     if (a.multistart && (a.env == RL4CO_ENV_SLAP || a.env == RL4CO_ENV_OP)) return false;
+    if (a.multistart && a.env == RL4CO_ENV_PCTSP) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
 }
 
@@ -811,6 +843,7 @@ int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         case RL4CO_ENV_TSP: return rf::launch_env<RL4CO_ENV_TSP>(a, stream);
         case RL4CO_ENV_CVRP: return rf::launch_env<RL4CO_ENV_CVRP>(a, stream);
         case RL4CO_ENV_OP: return rf::launch_env<RL4CO_ENV_OP>(a, stream);
+        case RL4CO_ENV_PCTSP: return rf::launch_env<RL4CO_ENV_PCTSP>(a, stream);
         default: return rf::launch_env<RL4CO_ENV_SLAP>(a, stream);
     }
 }

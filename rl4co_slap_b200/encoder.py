@@ -53,6 +53,21 @@ class OPInitEmbedding(nn.Module):
         return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
 
 
+class PCTSPInitEmbedding(nn.Module):
+    """x, y, expected prize, penalty for the customers, x, y for the depot (nn/env_embeddings/init.py:174-204)."""
+
+    def __init__(self, embed_dim: int, linear_bias: bool = True):
+        super().__init__()
+        self.init_embed = nn.Linear(4, embed_dim, linear_bias)
+        self.init_embed_depot = nn.Linear(2, embed_dim, linear_bias)
+
+    def forward(self, td):
+        locs = td["locs"]
+        depot, cities = locs[:, :1, :], locs[:, 1:, :]
+        feats = torch.cat((cities, td["expected_prize"][..., None], td["penalty"][..., 1:, None]), -1)
+        return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
+
+
 class SLAPInitEmbedding(nn.Module):
     """x, y and Manhattan distance to node 0 (examples/slap.py:11-47)."""
 
@@ -67,7 +82,7 @@ class SLAPInitEmbedding(nn.Module):
 
 
 INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding,
-                   "op": OPInitEmbedding}
+                   "op": OPInitEmbedding, "pctsp": PCTSPInitEmbedding, "spctsp": PCTSPInitEmbedding}
 
 
 # ---- linears (widths multiples of 128) on the tensor cores ----------------------------------------------

@@ -18,7 +18,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
-from .generators import CVRPGenerator, OPGenerator, SLAPGenerator, TSPGenerator
+from .generators import CVRPGenerator, OPGenerator, PCTSPGenerator, SLAPGenerator, TSPGenerator
 from .ops import get_num_starts, select_start_nodes
 from .tensordict_compat import TensorDict
 
@@ -484,6 +484,131 @@ class OPEnv(RL4COEnvBase):
 
 
 # =====================================================================================
+class PCTSPEnv(RL4COEnvBase):
+    """rl4co/envs/routing/pctsp/env.py:26-238 (prize-collecting TSP): collect a total prize of at least 1 (or visit
+    everything), pay the penalties of the customers left out."""
+
+    name = "pctsp"
+    _stochastic = False
+
+    def __init__(self, generator: PCTSPGenerator = None, generator_params: dict = {}, **kwargs):
+        super().__init__(**kwargs)
+        if generator is None:
+            generator = PCTSPGenerator(**{"device": self.device, **generator_params})
+        self.generator = generator
+
+    @property
+    def stochastic(self):
+        return self._stochastic
+
+    def _reset(self, td, batch_size=None):
+        """pctsp/env.py:103-139."""
+        _need_cuda(td["locs"], "PCTSPEnv.reset")
+        dev, B = td["locs"].device, int(batch_size[0])
+        locs = torch.cat([td["depot"][..., None, :], td["locs"]], dim=-2)
+        real = td["stochastic_prize"] if self.stochastic else td["deterministic_prize"]
+        penalty = td["penalty"]
+        out = TensorDict({
+            "locs": locs,
+            "current_node": torch.zeros(B, dtype=torch.int64, device=dev),
+            "expected_prize": td["deterministic_prize"],
+            "real_prize": torch.cat([torch.zeros_like(real[..., :1]), real], dim=-1),
+            "penalty": F.pad(penalty, (1, 0), mode="constant", value=0),
+            "cur_total_prize": torch.zeros(B, device=dev),
+            "cur_total_penalty": penalty.sum(-1),
+            "visited": torch.zeros(B, locs.shape[-2], dtype=torch.bool, device=dev),
+            "prize_required": torch.full((B,), float(self.generator.prize_required), device=dev),
+            "i": torch.zeros(B, dtype=torch.int64, device=dev),
+        }, batch_size=batch_size)
+        out.set("action_mask", self.get_action_mask(out))
+        return out
+
+    @staticmethod
+    def get_action_mask(td):
+        """pctsp/env.py:141-148 -> rl4co_pctsp_action_mask."""
+        visited = td["visited"]
+        _need_cuda(visited, "PCTSPEnv.get_action_mask")
+        dev, (B, N) = visited.device, visited.shape
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        _lib.call("rl4co_pctsp_action_mask", B, N, _lib.ptr(td["cur_total_prize"].contiguous(), torch.float32),
+                  _lib.ptr(_as_u8(visited.contiguous())), _lib.ptr(_as_u8(mask)), _lib.stream_ptr(dev))
+        return mask
+
+    def _step(self, td):
+        """pctsp/env.py:69-101 -> rl4co_pctsp_step (transition + mask in one launch)."""
+        action = td["action"]
+        _need_cuda(action, "PCTSPEnv._step")
+        dev, (B, N) = action.device, td["visited"].shape
+        prize, pen = td["cur_total_prize"].clone(), td["cur_total_penalty"].clone()
+        visited, i = td["visited"].clone(), td["i"].clone()
+        cur = torch.empty(B, dtype=torch.int64, device=dev)
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        done = torch.empty(B, dtype=torch.bool, device=dev)
+        status = _lib.deferred_status(dev)
+        _lib.call("rl4co_pctsp_step", B, N, _lib.ptr(action.contiguous(), torch.int64),
+                  _lib.ptr(td["real_prize"].contiguous(), torch.float32),
+                  _lib.ptr(td["penalty"].contiguous(), torch.float32), _lib.ptr(prize), _lib.ptr(pen),
+                  _lib.ptr(cur), _lib.ptr(_as_u8(visited)), _lib.ptr(i, torch.int64), _lib.ptr(_as_u8(mask)),
+                  _lib.ptr(_as_u8(done)), _lib.ptr(status), _lib.stream_ptr(dev))
+        td.update({"current_node": cur, "cur_total_prize": prize, "cur_total_penalty": pen, "visited": visited,
+                   "i": i, "reward": torch.zeros_like(done), "done": done})
+        td.set("action_mask", mask)
+        return td
+
+    def _replay_call(self, td, actions, check, want_state):
+        locs = td["locs"]
+        _need_cuda(locs, "PCTSPEnv.replay")
+        dev, (B, N, _) = locs.device, locs.shape
+        T = actions.shape[1]
+        reward = torch.empty(B, dtype=torch.float32, device=dev)
+        status = _lib.new_status(dev)
+        st = {}
+        if want_state:
+            st = {"current_node": torch.empty(B, dtype=torch.int64, device=dev),
+                  "cur_total_prize": torch.empty(B, dtype=torch.float32, device=dev),
+                  "cur_total_penalty": td["penalty"][..., 1:].sum(-1),      # in/out: the reset state's value
+                  "visited": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "action_mask": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "i": torch.empty(B, dtype=torch.int64, device=dev),
+                  "done": torch.empty(B, dtype=torch.bool, device=dev)}
+        p = lambda k: _lib.ptr(_as_u8(st[k])) if k in st else None  # noqa: E731
+        _lib.call("rl4co_pctsp_replay", B, N, T, _lib.ptr(locs.contiguous(), torch.float32),
+                  _lib.ptr(td["real_prize"].contiguous(), torch.float32),
+                  _lib.ptr(td["penalty"].contiguous(), torch.float32),
+                  _lib.ptr(actions.contiguous(), torch.int64), p("current_node"), p("cur_total_prize"),
+                  p("cur_total_penalty"), p("visited"), p("action_mask"), p("i"), p("done"),
+                  _lib.ptr(reward), int(bool(check)), _lib.ptr(status), _lib.stream_ptr(dev))
+        _lib.raise_for_status(status)
+        return st, reward
+
+    def replay(self, td, actions, check: Optional[bool] = None):
+        """Fused reset-state + T x _step + get_reward.  ``td`` is a reset td."""
+        check = self.check_solution if check is None else check
+        st, reward = self._replay_call(td, actions, check, True)
+        keep = {k: td[k] for k in ("locs", "expected_prize", "real_prize", "penalty", "prize_required")}
+        out = TensorDict({**keep, **st, "reward": torch.zeros_like(st["done"])}, batch_size=[actions.shape[0]])
+        return out, reward
+
+    def _get_reward(self, td, actions):
+        """pctsp/env.py:150-174."""
+        if actions.size(-1) == 1:
+            assert (actions == 0).all(), "If all length 1 tours, they should be zero"
+            return torch.zeros(actions.size(0), dtype=torch.float, device=actions.device)
+        return self._replay_call(td, actions, False, False)[1]
+
+    def check_solution_validity(self, td, actions) -> None:
+        """pctsp/env.py:176-200: "Duplicates" / "Total prize does not satisfy min total prize"."""
+        self._replay_call(td, actions, True, False)
+
+
+class SPCTSPEnv(PCTSPEnv):
+    """rl4co/envs/routing/spctsp/env.py:8-31: the collected prize is the stochastic one, revealed on the visit."""
+
+    name = "spctsp"
+    _stochastic = True
+
+
+# =====================================================================================
 class SLAPEnv(RL4COEnvBase):
     """rl4co/envs/warehousing/slap/env.py:17-182."""
 
@@ -577,7 +702,8 @@ class SLAPEnv(RL4COEnvBase):
         return out, reward
 
 
-ENV_REGISTRY = {"tsp": TSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv}
+ENV_REGISTRY = {"tsp": TSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv, "pctsp": PCTSPEnv,
+                "spctsp": SPCTSPEnv}
 
 
 def get_env(env_name: str, *args, **kwargs) -> RL4COEnvBase:

@@ -198,6 +198,51 @@ class OPGenerator(Generator):
                           batch_size=batch_size)
 
 
+class PCTSPGenerator(Generator):
+    """pctsp/generator.py:19-160 -> td{"locs" [B,n,2], "depot" [B,2], "penalty", "deterministic_prize",
+    "stochastic_prize" [B,n]}.  Prizes ~ U(0, 4/n) so that about half of the customers satisfy the constraint
+    ``total prize >= 1``; penalties ~ U(0, max_penalty * penalty_factor / n) (Kool et al. 2019)."""
+
+    def __init__(self, num_loc: int = 20, min_loc: float = 0.0, max_loc: float = 1.0, loc_distribution=Uniform,
+                 depot_distribution=None, penalty_factor: float = 3.0, prize_required: float = 1.0, device=None,
+                 **kwargs):
+        self.num_loc, self.min_loc, self.max_loc = num_loc, min_loc, max_loc
+        self.penalty_factor, self.prize_required = penalty_factor, prize_required
+        self.device = device
+        self.loc_sampler = kwargs.get("loc_sampler") or get_sampler(
+            "loc", loc_distribution, min_loc, max_loc, device=device, **kwargs)
+        if kwargs.get("depot_sampler") is not None:
+            self.depot_sampler = kwargs["depot_sampler"]
+        else:
+            self.depot_sampler = (get_sampler("depot", depot_distribution, min_loc, max_loc, device=device, **kwargs)
+                                  if depot_distribution is not None else None)
+        self.deterministic_prize_sampler = _DeviceUniform(0.0, 4.0 / num_loc, device)
+        self.stochastic_prize_sampler = _DeviceUniform(0.0, 8.0 / num_loc, device)
+        max_penalty = kwargs.get("max_penalty")
+        if max_penalty is None:
+            max_penalty = MAX_LENGTHS.get(num_loc)
+        if max_penalty is None:  # closest table entry (:88-97)
+            closest = min(MAX_LENGTHS.keys(), key=lambda x: abs(x - num_loc))
+            max_penalty = MAX_LENGTHS[closest]
+        self.max_penalty = max_penalty * penalty_factor / num_loc
+        self.penalty_sampler = _DeviceUniform(0.0, self.max_penalty, device)
+
+    def _generate(self, batch_size) -> TensorDict:
+        if self.depot_sampler is not None:
+            depot = self.depot_sampler.sample((*batch_size, 2))
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc, 2))
+        else:
+            locs = self.loc_sampler.sample((*batch_size, self.num_loc + 1, 2))
+            depot = locs[..., 0, :]
+            locs = locs[..., 1:, :]
+        penalty = self.penalty_sampler.sample((*batch_size, self.num_loc))
+        deterministic_prize = self.deterministic_prize_sampler.sample((*batch_size, self.num_loc))
+        stochastic_prize = self.stochastic_prize_sampler.sample((*batch_size, self.num_loc)) * deterministic_prize
+        return TensorDict({"locs": locs, "depot": depot, "penalty": penalty,
+                           "deterministic_prize": deterministic_prize, "stochastic_prize": stochastic_prize},
+                          batch_size=batch_size)
+
+
 class SLAPGenerator(Generator):
     """slap/generator.py:21-155.  Grid warehouse: location i sits in aisle i // n_locs at
     x = aisle * inter_aisle_dist, y = (i % n_locs) * inter_loc_dist (:67-80); Manhattan

@@ -35,7 +35,7 @@ class _ContextEmbedding(nn.Module):
 
     def __init__(self, env_name: str, embed_dim: int):
         super().__init__()
-        in_dim = {"tsp": 2 * embed_dim, "cvrp": embed_dim + 1, "op": embed_dim + 1, "slap": embed_dim}[env_name]
+        in_dim = {"tsp": 2 * embed_dim, "slap": embed_dim}.get(env_name, embed_dim + 1)    # cvrp, op, (s)pctsp: + 1 scalar
         self.project_context = nn.Linear(in_dim, embed_dim, bias=False)
         if env_name == "tsp":
             self.W_placeholder = nn.Parameter(torch.Tensor(2 * embed_dim).uniform_(-1, 1))
@@ -116,7 +116,7 @@ class AttentionModelDecoder(nn.Module):
             if self.env_name == "tsp":
                 parts += [Wc[:, E:], Wc[:, :E]]
                 q0 = (Wc @ self.context_embedding.W_placeholder.float()).contiguous()
-            elif self.env_name in ("cvrp", "op"):    # [h_cur ; remaining capacity / length]
+            elif self.env_name in ("cvrp", "op", "pctsp", "spctsp"):    # [h_cur ; remaining capacity / length / prize]
                 parts += [Wc[:, :E]]
                 wcap = Wc[:, E].contiguous()
         finally:
@@ -223,13 +223,14 @@ class AttentionModelPolicy(nn.Module):
         elif name == "slap":
             P, O, K = td["freq"].shape[-2], td["picklist"].shape[1], td["picklist"].shape[2]
             T = P
-        elif name == "op":  # at worst: depot first (not done at step 0), ..., every customer, depot
-            T = N + 1
+        elif name in ("op", "pctsp", "spctsp"):
+            # op at worst: depot first (not done at step 0), ..., every customer, depot; pctsp: every customer, depot
+            T = N + 1 if name == "op" else N
             if multistart:
-                raise NotImplementedError("op multistart: the reference resamples infeasible start nodes with "
-                                          "torch.multinomial (utils/ops.py:166-176); not implemented")
+                raise NotImplementedError(f"{name} multistart is not implemented (op: the reference resamples "
+                                          "infeasible start nodes with torch.multinomial, utils/ops.py:166-176)")
             if store_all_logp:
-                raise NotImplementedError("op: per-node log-probs (return_entropy / store_all_logp) are not "
+                raise NotImplementedError(f"{name}: per-node log-probs (return_entropy / store_all_logp) are not "
                                           "produced by the register-file rollout kernel")
         else:  # every customer may be followed by a depot return
             T = 2 * (N - 1) + 1
@@ -294,6 +295,10 @@ class AttentionModelPolicy(nn.Module):
             if name == "op":
                 a.prize = _lib.ptr(td["prize"][c0:c1].contiguous(), torch.float32)
                 a.max_length = _lib.ptr(td["max_length"][c0:c1].contiguous(), torch.float32)
+            if name in ("pctsp", "spctsp"):
+                a.prize = _lib.ptr(td["real_prize"][c0:c1].contiguous(), torch.float32)
+                a.penalty = _lib.ptr(td["penalty"][c0:c1].contiguous(), torch.float32)
+                a.prize_required = _lib.ptr(td["prize_required"][c0:c1].contiguous(), torch.float32)
             if name == "slap":
                 a.picklist = _lib.ptr(td["picklist"][c0:c1].contiguous(), torch.int64)
             # single start: rollouts of the chunk are rows c0..c1; multistart runs unchunked
@@ -317,7 +322,7 @@ class AttentionModelPolicy(nn.Module):
         self.last_launches = launches
 
         # ---- the reference's output construction (base.py:253-276) --------------------
-        if name in ("cvrp", "op") and actions is None:
+        if name in ("cvrp", "op", "pctsp", "spctsp") and actions is None:
             # the reference loops until the slowest episode is done (base.py:230): T = max steps
             Tmax = int(out_steps.max().item())
             out_actions, out_logp = out_actions[:, :Tmax], out_logp[:, :Tmax]
