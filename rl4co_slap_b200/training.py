@@ -46,6 +46,8 @@ def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
         return mask, torch.ones(R, T, dtype=torch.bool, device=dev), None
     if env_name == "op":
         return _replay_masks_op(td, actions, S)
+    if env_name in ("pctsp", "spctsp"):
+        return _replay_masks_pctsp(td, actions, S)
     # cvrp/env.py:73-149 - sequential in the used capacity (fp32, the reference's order of operations)
     demand = td["demand"].float()
     cap = td["vehicle_capacity"].float().reshape(-1, 1)
@@ -111,6 +113,32 @@ def _replay_masks_op(td, actions: torch.Tensor, S: int):
     return torch.stack(masks, 1), torch.stack(valid, 1), torch.stack(lengths, 1)
 
 
+def _replay_masks_pctsp(td, actions: torch.Tensor, S: int):
+    """pctsp/env.py:69-148 replayed from the actions: masks, validity and the collected prize seen by every step."""
+    R, T = actions.shape
+    prize = td["real_prize"].float()
+    if S > 1:
+        prize = prize.repeat(S, 1)
+    N, dev = prize.shape[1], actions.device
+    rows = torch.arange(R, device=dev)
+    total = torch.zeros(R, device=dev)
+    visited = torch.zeros(R, N, dtype=torch.bool, device=dev)
+    done = torch.zeros(R, dtype=torch.bool, device=dev)
+    masks, totals, valid = [], [], []
+    for t in range(T):
+        m = visited | visited[:, 0:1]                                                     # :143
+        m[:, 0] = (total < 1.0) & (visited[:, 1:].int().sum(-1) < N - 1)                  # :144-146
+        masks.append(~m)
+        totals.append(total)
+        valid.append(~done)
+        a = actions[:, t]
+        total = total + prize[rows, a]                                                    # :73-75
+        visited = visited.clone()
+        visited[rows, a] = True
+        done = done | ((a == 0) & (t > 0))                                                # :84
+    return torch.stack(masks, 1), torch.stack(valid, 1), torch.stack(totals, 1)
+
+
 def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, actions: torch.Tensor,
                                   num_starts: int = 0, temperature: Optional[float] = None,
                                   tanh_clipping: Optional[float] = None, mask_logits: Optional[bool] = None,
@@ -159,6 +187,9 @@ def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, ac
         ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
     elif env_name == "op":            # [h_cur ; max_length[..., 0] - tour_length] (context.py:385-397)
         rem = td["max_length"].float()[:, :1].repeat(S, 1) - used
+        ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
+    elif env_name in ("pctsp", "spctsp"):    # [h_cur ; max(prize_required - cur_total_prize, 0)] (context.py:368-382)
+        rem = torch.clamp(td["prize_required"].float().reshape(B, 1).repeat(S, 1) - used, min=0)
         ctx = gather(F.linear(h, Wc[:, :E]), prev_bl) + per_instance(rem)[..., None] * Wc[:, E]
     else:
         ctx = torch.zeros(B, L, E, device=dev, dtype=h.dtype)

@@ -6,7 +6,7 @@ import torch
 
 import rl4co_slap_b200 as R
 from oracle import port
-from tests.helpers import (CVRP_CASES, OP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
+from tests.helpers import (CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
 
 pytestmark = pytest.mark.gpu
 
@@ -29,7 +29,7 @@ def _same(got, want, what):
     assert np.array_equal(got, want), what
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
 def test_step_by_step_replay_bit_exact(case, dev):
     """reset + every _step through the env API: each state tensor equals the reference's
     (dtype, shape and value) after every step; then get_reward."""
@@ -49,7 +49,7 @@ def test_step_by_step_replay_bit_exact(case, dev):
     _close(reward, fx["replay.reward"], (case, "reward"))
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
 def test_fused_replay_matches_fixture(case, dev):
     fx, name = fixture(case), env_of(case)
     env = R.get_env(name, device=dev)

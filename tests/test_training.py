@@ -19,7 +19,29 @@ def _cpu_td(name, fx):
                 "vehicle_capacity": t(fx["reset.vehicle_capacity"])}
     if name == "op":
         return {"locs": t(fx["reset.locs"]), "prize": t(fx["reset.prize"]), "max_length": t(fx["reset.max_length"])}
+    if name in ("pctsp", "spctsp"):
+        return {"locs": t(fx["reset.locs"]), "real_prize": t(fx["reset.real_prize"]),
+                "prize_required": t(fx["reset.prize_required"])}
     return {"locs": t(fx["gen.locs"])}
+
+
+@pytest.mark.parametrize("case", ("pctsp20", "pctsp100", "spctsp50"))
+def test_teacher_forced_ll_pctsp_cpu(case):
+    """(s)pctsp: masks, collected prize and per-step log-probs of the reference's greedy tours and of random tours"""
+    fx, name = fixture(case), env_of(case)
+    pol = load_policy(name, "cpu")
+    acts = t(fx["replay.actions"])
+    mask, valid, total = replay_masks(name, _cpu_td(name, fx), acts)
+    assert np.array_equal(mask[:, 0].numpy(), fx["reset.action_mask"])
+    for s in range(acts.shape[1] - 1):
+        assert np.array_equal(mask[:, s + 1].numpy(), fx[f"step{s}.action_mask"]), s
+        assert np.array_equal(total[:, s + 1].numpy(), fx[f"step{s}.cur_total_prize"]), s
+    with torch.no_grad():
+        lp = teacher_forced_log_likelihood(pol, _cpu_td(name, fx), name, t(fx["hidden"]), acts, return_sum=False)
+        lg = teacher_forced_log_likelihood(pol, _cpu_td(name, fx), name, t(fx["hidden"]), t(fx["greedy.actions"]),
+                                           return_sum=False)
+    np.testing.assert_allclose(lp.numpy(), fx["eval.logprobs"], rtol=1e-4, atol=2e-5)
+    np.testing.assert_allclose(lg.numpy(), fx["greedy.logprobs"], rtol=1e-4, atol=2e-5)
 
 
 @pytest.mark.parametrize("case", ("op20", "op50", "op100"))
