@@ -22,7 +22,14 @@ def _close(got, want, what):
     assert got.cpu().numpy().dtype == want.dtype and got.shape == want.shape, what
 
 
+# the one state tensor whose value depends on torch's own reduction order: pctsp's cur_total_penalty starts from
+# penalty.sum(-1) (pctsp/env.py:123), which the reference itself computes differently on CPU and on CUDA
+_SUM_ORDER_KEYS = ("cur_total_penalty",)
+
+
 def _same(got, want, what):
+    if what[-1] in _SUM_ORDER_KEYS:
+        return _close(got, want, what)
     got = got.cpu().numpy()
     assert got.dtype == want.dtype, (what, got.dtype, want.dtype)
     assert got.shape == want.shape, (what, got.shape, want.shape)
