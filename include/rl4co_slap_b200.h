@@ -172,7 +172,9 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
 #define RL4CO_ENV_TSP  0
 #define RL4CO_ENV_CVRP 1
 #define RL4CO_ENV_SLAP 2
-#define RL4CO_ENV_OP   3   /* envs/routing/op/env.py; single start, register-file kernel only (N <= 128) */
+#define RL4CO_ENV_OP   3   /* envs/routing/op/env.py; register-file kernel only (N <= 128, no logp_all); multistart forces
+                            * start node s % num_loc + 1 - the reference's multinomial resampling of infeasible starts
+                            * (utils/ops.py:166-176) is the caller's business */
 #define RL4CO_ENV_PCTSP 4  /* envs/routing/pctsp/env.py and spctsp/env.py (prize = the real prize); same limits as OP */
 
 #define RL4CO_MODE_GREEDY   0  /* utils/decoding.py:371-381,410-418 */

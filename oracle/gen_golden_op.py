@@ -56,6 +56,14 @@ def main():
         data["hidden"] = G.np_(h)
         res, _ = G.policy_outputs(env, pol, td0, "eval", actions=torch.from_numpy(data["replay.actions"]))
         data.update(res)
+        S = min(size, 8)    # POMO starts; only where the reference does not resample them (utils/ops.py:166-176)
+        if not bool((td_r["action_mask"][..., 1:].float().sum(-1) < S).any()):
+            try:    # a forced start node beyond the budget fails the reference's own validity check: no fixture then
+                res, _ = G.policy_outputs(env, pol, td0, "ms_greedy", decode_type="multistart_greedy", num_starts=S)
+                data.update(res)
+                data["ms_greedy.num_starts"] = np.int64(S)
+            except AssertionError as e:
+                print(f"op{size}: reference multistart rejected its own tour ({e})")
         path = os.path.join(G.OUT, f"op{size}.npz")
         np.savez_compressed(path, **data)
         print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, greedy mean reward "
@@ -84,6 +92,10 @@ def main_pctsp():
             data["hidden"] = G.np_(h)
             res, _ = G.policy_outputs(env, pol, td0, "eval", actions=torch.from_numpy(data["replay.actions"]))
             data.update(res)
+            S = min(size, 8)
+            res, _ = G.policy_outputs(env, pol, td0, "ms_greedy", decode_type="multistart_greedy", num_starts=S)
+            data.update(res)
+            data["ms_greedy.num_starts"] = np.int64(S)
             path = os.path.join(G.OUT, f"{name}{size}.npz")
             np.savez_compressed(path, **data)
             print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, greedy mean reward "

@@ -522,14 +522,14 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         RL4CO_REQUIRE(a.picklist && a.P >= 1 && a.O >= 0 && a.K >= 1 && a.T >= a.P, "am_rollout: slap needs picklist and T>=P");
     if (a.env == RL4CO_ENV_OP) {
         RL4CO_REQUIRE(a.wcap && a.prize && a.max_length, "am_rollout: op needs wcap/prize/max_length");
-        RL4CO_REQUIRE(!a.multistart, "am_rollout: op multistart resamples infeasible start nodes with torch.multinomial "
-                                     "(utils/ops.py:166-176), not implemented");
+        // multistart: the caller guarantees that the reference would not resample the start nodes (utils/ops.py:166-176)
+        RL4CO_REQUIRE(!a.multistart || a.num_loc >= 1, "am_rollout: bad multistart setup");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: op runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
     if (a.env == RL4CO_ENV_PCTSP) {
         RL4CO_REQUIRE(a.wcap && a.prize && a.penalty && a.prize_required, "am_rollout: pctsp needs wcap/prize/penalty/prize_required");
-        RL4CO_REQUIRE(!a.multistart, "am_rollout: pctsp multistart is not implemented");
+        RL4CO_REQUIRE(!a.multistart || a.num_loc >= 1, "am_rollout: bad multistart setup");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: pctsp runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }

@@ -833,8 +833,7 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
-    if (a.multistart && (a.env == RL4CO_ENV_SLAP || a.env == RL4CO_ENV_OP)) return false;
-    if (a.multistart && a.env == RL4CO_ENV_PCTSP) return false;
+    if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
 }
 

@@ -226,9 +226,9 @@ class AttentionModelPolicy(nn.Module):
         elif name in ("op", "pctsp", "spctsp"):
             # op at worst: depot first (not done at step 0), ..., every customer, depot; pctsp: every customer, depot
             T = N + 1 if name == "op" else N
-            if multistart:
-                raise NotImplementedError(f"{name} multistart is not implemented (op: the reference resamples "
-                                          "infeasible start nodes with torch.multinomial, utils/ops.py:166-176)")
+            if multistart and name == "op" and bool((td["action_mask"][..., 1:].sum(-1) < S).any()):
+                raise NotImplementedError("op multistart with fewer feasible start nodes than starts: the reference "
+                                          "resamples them with torch.multinomial (utils/ops.py:166-176); not implemented")
             if store_all_logp:
                 raise NotImplementedError(f"{name}: per-node log-probs (return_entropy / store_all_logp) are not "
                                           "produced by the register-file rollout kernel")

@@ -127,8 +127,21 @@ def test_invalid_tours_raise_reference_messages(dev):
         env.check_solution_validity(td, long)
     with pytest.raises(AssertionError, match="Max length exceeded"):     # get_reward's validity check, as the reference
         pol(td, env, actions=long, hidden=t(fx["hidden"], dev))
+    # op10 has instances with fewer than 8 feasible start nodes: the reference would resample them
+    fx, pol, env, td = _setup("op10", dev)
     with pytest.raises(NotImplementedError, match="multistart"):
-        pol(td, env, decode_type="multistart_greedy", hidden=t(fx["hidden"], dev))
+        pol(td, env, decode_type="multistart_greedy", num_starts=10, hidden=t(fx["hidden"], dev))
+
+
+@pytest.mark.parametrize("case", ("op20", "op50", "op100"))
+def test_multistart_greedy_matches_reference_fixture(case, dev):
+    """POMO starts (forced first customer s % num_loc + 1, log-prob 0) where the reference does not resample them"""
+    fx, pol, env, td = _setup(case, dev)
+    S = int(fx["ms_greedy.num_starts"])
+    out = pol(td, env, decode_type="multistart_greedy", num_starts=S, return_actions=True, hidden=t(fx["hidden"], dev))
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["ms_greedy.actions"])
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["ms_greedy.reward"], rtol=RTOL, atol=1e-6)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["ms_greedy.ll"], rtol=RTOL, atol=2e-5)
 
 
 def test_training_step_log_likelihood(dev):

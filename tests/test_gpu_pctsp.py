@@ -101,8 +101,32 @@ def test_invalid_tours_raise_reference_messages(dev):
     short[:, 0] = 1                                      # one customer, then the depot: far too little prize
     with pytest.raises(AssertionError, match="Total prize does not satisfy min total prize"):
         env.check_solution_validity(td, short)
-    with pytest.raises(NotImplementedError, match="multistart"):
-        pol(td, env, decode_type="multistart_greedy", hidden=t(fx["hidden"], dev))
+
+
+@pytest.mark.parametrize("case", PCTSP_CASES)
+def test_multistart_greedy_matches_reference_fixture(case, dev):
+    fx, pol, env, td = _setup(case, dev)
+    S = int(fx["ms_greedy.num_starts"])
+    out = pol(td, env, decode_type="multistart_greedy", num_starts=S, return_actions=True, hidden=t(fx["hidden"], dev))
+    assert np.array_equal(out["actions"].cpu().numpy(), fx["ms_greedy.actions"])
+    np.testing.assert_allclose(out["reward"].cpu().numpy(), fx["ms_greedy.reward"], rtol=RTOL, atol=2e-6)
+    np.testing.assert_allclose(out["log_likelihood"].cpu().numpy(), fx["ms_greedy.ll"], rtol=RTOL, atol=3e-5)
+
+
+def test_pomo_sampling_default_starts(dev):
+    """multistart sampling with the default number of starts (one per customer): valid tours, ll = evaluate ll, and
+    the shared-baseline REINFORCE step's differentiable ll = the kernel's"""
+    torch.manual_seed(21)
+    env = R.PCTSPEnv(generator_params=dict(num_loc=20), device=dev)
+    pol = R.AttentionModelPolicy(env_name="pctsp", num_encoder_layers=1).to(dev).eval()
+    td = env.reset(env.generator(32))
+    res = R.reinforce_step(pol, env, td, optimizer=None, decode_type="multistart_sampling", baseline="shared")
+    assert res["actions"].shape[0] == 32 * 20
+    first = res["actions"][:, 0].reshape(20, 32)
+    assert torch.equal(first, (torch.arange(20, device=dev) + 1)[:, None].expand(20, 32))
+    torch.testing.assert_close(res["log_likelihood"], res["kernel_log_likelihood"], rtol=1e-4, atol=5e-5)
+    from rl4co_slap_b200.ops import batchify
+    env.check_solution_validity(batchify(td, 20), res["actions"])
 
 
 def test_training_step_log_likelihood(dev):

@@ -56,7 +56,7 @@ def test_greedy_rollout_matches_reference(case):
     np.testing.assert_allclose(out["logprobs"].numpy(), fx["greedy.logprobs"], rtol=1e-5, atol=2e-6)
 
 
-@pytest.mark.parametrize("case", ("tsp20", "cvrp20"))
+@pytest.mark.parametrize("case", ("tsp20", "cvrp20", "op20", "op50", "op100", "pctsp20", "pctsp100", "spctsp50"))
 def test_multistart_greedy_matches_reference(case):
     fx, name = fixture(case), env_of(case)
     S = int(fx["ms_greedy.num_starts"])

@@ -58,4 +58,18 @@ with torch.inference_mode():
         h = torch.cat([pol.encoder(td[i:i + 8192])[0] for i in range(0, Bs, 8192)])
         s = timed(lambda: pol(td, env, decode_type="greedy", hidden=h), warm=2, reps=3)
         out[f"C5_slap_B{Bs}"] = {"batch": Bs, "seconds": s, "rollouts_per_s": Bs / s, "env_steps_per_s": Bs * 20 / s}
+    # ---- sibling routing envs on the register-file kernel: 100 customers, greedy and sampling
+    for name in ("op", "pctsp"):
+        torch.manual_seed(1234)
+        Bs = 16384
+        env = R.get_env(name, generator_params=dict(num_loc=100), device=dev, check_solution=False)
+        pol = R.AttentionModelPolicy(env_name=name).to(dev).eval()
+        td = env.reset(env.generator(Bs).to(dev))
+        h = torch.cat([pol.encoder(td[i:i + 8192])[0] for i in range(0, Bs, 8192)])
+        for mode in ("greedy", "sampling"):
+            s = timed(lambda: pol(td, env, decode_type=mode, hidden=h), warm=2, reps=3)
+            o = pol(td, env, decode_type=mode, hidden=h, return_actions=True)
+            steps = float((o["actions"] != 0).sum(1).float().mean().item()) + 1
+            out[f"{name}100_{mode}_B{Bs}"] = {"batch": Bs, "seconds": s, "rollouts_per_s": Bs / s, "mean_steps": steps,
+                                              "env_steps_per_s": Bs * steps / s, "mean_reward": float(o["reward"].mean().item())}
 print(json.dumps(out, indent=1))
