@@ -441,7 +441,10 @@ __device__ __forceinline__ void compact(Ctx &c, const u64 (&Ko)[MO][4], const u6
     for (int k = 0; k < 4; ++k) c.candk[k] = ((unsigned)(4 * lane + k) << 8) | (unsigned)(node_w[4 * lane + k] & 0xff);
 }
 
-template <int M0, bool SAMPLING>
+// MS: POMO multistart (work item = rollout, forced first action).  A compile-time switch because the extra live values
+// of the multistart bookkeeping cost the single-start step loop 4 % (8.22 vs 7.90 ms per 16 280 TSP100 rollouts) when they
+// are run-time state of the same kernel.
+template <int M0, bool SAMPLING, bool MS>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -479,16 +482,16 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     };
     // work item = one rollout (instance b, start s), flat index r = s * B + b (utils/ops.py:11-34).  Consecutive items go to
     // different CTAs, so the ~1.5 instances whose starts are in flight at any time keep their tables hot in L2.
-    const int S = a.S > 1 ? a.S : 1;
-    const int64_t W = a.B * (int64_t)S;
-    const int t_first = a.multistart ? 1 : 0;       // multistart: step 0 is the forced POMO start node
-    if (tid == 0 && (int64_t)blockIdx.x < W) stage_context(blockIdx.x / S, 0);
+    const int S = MS ? (a.S > 1 ? a.S : 1) : 1;
+    const int64_t W = MS ? a.B * (int64_t)S : a.B;
+    constexpr int t_first = MS ? 1 : 0;             // multistart: step 0 is the forced POMO start node
+    if (tid == 0 && (int64_t)blockIdx.x < W) stage_context(MS ? blockIdx.x / S : blockIdx.x, 0);
 
     int it = 0;
     for (int64_t w = blockIdx.x; w < W; w += gridDim.x, ++it) {
-        const int64_t b = w / S;
-        const int s = (int)(w % S);
-        const int64_t r = (int64_t)s * a.B + b;
+        const int64_t b = MS ? w / S : w;
+        const int s = MS ? (int)(w % S) : 0;
+        const int64_t r = MS ? (int64_t)s * a.B + b : w;
         const int buf = it & 1;
 #ifdef RF_TRACE
         Ctx c;
@@ -553,7 +556,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             gen_noise(c, warp + 8, smem);
         }
         if (tid == 0 && w + gridDim.x < W) {        // next item: context table -> other buffer, K/V/L rows -> L2
-            const int64_t nb = (w + gridDim.x) / S;
+            const int64_t nb = MS ? (w + gridDim.x) / S : w + gridDim.x;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             stage_context(nb, buf ^ 1);
             for (int tb = 0; tb < 3; ++tb) {
@@ -590,7 +593,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         if (buf == 0) { mbar_wait(&bar[0], par0); par0 ^= 1u; }      // context table landed?
         else          { mbar_wait(&bar[1], par1); par1 ^= 1u; }
 
-        if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
+        if (MS) {                                   // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
             const int a0 = s % a.num_loc;           // slot == node before the first compaction
             c.alive &= ~((g == (a0 & 15)) ? (1u << (a0 >> 4)) : 0u);
             if (tid == 0) { s_act[0] = a0; s_slot[0] = a0; s_lp[0] = 0.f; }
@@ -712,7 +715,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     }
 }
 
-template <int M0, bool SAMPLING>
+template <int M0, bool SAMPLING, bool MS>
 static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -722,14 +725,14 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         if (sm_count <= 0) sm_count = 148;
     }
     const size_t total = smem_total(a.N, a.T);
-    cudaError_t e = cudaFuncSetAttribute(am_rollout_tsp_greedy_kernel<M0, SAMPLING>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
+    cudaError_t e = cudaFuncSetAttribute(am_rollout_tsp_greedy_kernel<M0, SAMPLING, MS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)total);
     if (e != cudaSuccess) {
         set_error("am_rollout(tsp greedy): cannot reserve %zu B of shared memory: %s", total, cudaGetErrorString(e));
         return 2;
     }
-    const int64_t W = a.B * (int64_t)(a.S > 1 ? a.S : 1);
+    const int64_t W = MS ? a.B * (int64_t)(a.S > 1 ? a.S : 1) : a.B;
     const int64_t grid = W < sm_count ? W : sm_count;       // persistent: one CTA per SM
-    am_rollout_tsp_greedy_kernel<M0, SAMPLING><<<(unsigned)grid, kThreads, total, stream>>>(a);
+    am_rollout_tsp_greedy_kernel<M0, SAMPLING, MS><<<(unsigned)grid, kThreads, total, stream>>>(a);
     RL4CO_CHECK_LAUNCH("am_rollout(tsp greedy)");
     return 0;
 }
@@ -741,20 +744,23 @@ bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.env != RL4CO_ENV_TSP || a.mode == RL4CO_MODE_EVALUATE) return false;
+    if (a.S > 1 && !a.multistart) return false;      // several free starts per instance: the generic kernel
     if (!(a.tanh_clipping > 0.f) || a.temperature != 1.f || a.mask_logits == 0) return false;
     if (a.N > 112 || a.T > tspg::kMaxT || a.N < 2) return false;
     return tspg::smem_total(a.N, a.T) <= (size_t)227 * 1024;
 }
 
+template <bool SAMPLING, bool MS>
+static int launch_rows(const rl4co_am_rollout_args &a, cudaStream_t stream) {
+    if (a.N <= 32) return tspg::launch<2, SAMPLING, MS>(a, stream);
+    if (a.N <= 64) return tspg::launch<4, SAMPLING, MS>(a, stream);
+    return tspg::launch<7, SAMPLING, MS>(a, stream);
+}
+
 int launch_rollout_tsp_greedy(const rl4co_am_rollout_args &a, cudaStream_t stream) {
-    if (a.mode == RL4CO_MODE_SAMPLING) {
-        if (a.N <= 32) return tspg::launch<2, true>(a, stream);
-        if (a.N <= 64) return tspg::launch<4, true>(a, stream);
-        return tspg::launch<7, true>(a, stream);
-    }
-    if (a.N <= 32) return tspg::launch<2, false>(a, stream);
-    if (a.N <= 64) return tspg::launch<4, false>(a, stream);
-    return tspg::launch<7, false>(a, stream);
+    const bool ms = a.multistart != 0;
+    if (a.mode == RL4CO_MODE_SAMPLING) return ms ? launch_rows<true, true>(a, stream) : launch_rows<true, false>(a, stream);
+    return ms ? launch_rows<false, true>(a, stream) : launch_rows<false, false>(a, stream);
 }
 
 }  // namespace rl4co

@@ -8,6 +8,8 @@ sys.path.insert(0, ROOT)
 import torch
 from rl4co_slap_b200 import _lib
 import rl4co_slap_b200 as R
+if os.environ.get("RL4CO_LIB"):          # A/B timing of a side build (tools/_exp/)
+    _lib.LIB_PATH = os.environ["RL4CO_LIB"]
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 per_sm = int(sys.argv[2]) if len(sys.argv) > 2 else 64
