@@ -86,13 +86,36 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
     }
     __syncthreads();
     const int e = tid & (PE - 1), half = tid >> 7;
+    // column sums with 16-byte loads: lane = 4 consecutive dims, warp w takes rows w, w + 8, ... (four rows in flight
+    // per thread - the kernel is a pure stream over h and needs the bytes in flight, not the arithmetic)
+    const int c4 = tid & 31, rg = tid >> 5;
+    float4 *colsum = reinterpret_cast<float4 *>(part + 2 * PE);     // [8][32] float4
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
-        const float *hb = h + b * (int64_t)N * PE;
-        float s = 0.f;
-        for (int n = half; n < N; n += 2) s += hb[(size_t)n * PE + e];
-        mean[half * PE + e] = s;
+        const float4 *hb = reinterpret_cast<const float4 *>(h + b * (int64_t)N * PE) + c4;
+        float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0, s2 = s0, s3 = s0;
+        int n = rg;
+        for (; n + 24 < N; n += 32) {
+            const float4 v0 = __ldg(hb + (size_t)n * 32), v1 = __ldg(hb + (size_t)(n + 8) * 32);
+            const float4 v2 = __ldg(hb + (size_t)(n + 16) * 32), v3 = __ldg(hb + (size_t)(n + 24) * 32);
+            s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+            s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
+            s2.x += v2.x; s2.y += v2.y; s2.z += v2.z; s2.w += v2.w;
+            s3.x += v3.x; s3.y += v3.y; s3.z += v3.z; s3.w += v3.w;
+        }
+        for (; n < N; n += 8) {
+            const float4 v0 = __ldg(hb + (size_t)n * 32);
+            s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+        }
+        colsum[rg * 32 + c4] = make_float4((s0.x + s1.x) + (s2.x + s3.x), (s0.y + s1.y) + (s2.y + s3.y),
+                                           (s0.z + s1.z) + (s2.z + s3.z), (s0.w + s1.w) + (s2.w + s3.w));
         __syncthreads();
-        if (half == 0) mean[e] = (mean[e] + mean[PE + e]) / (float)N;
+        if (half == 0) {
+            const float *cs = reinterpret_cast<const float *>(colsum);
+            float m = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) m += cs[w * PE + e];
+            mean[e] = m / (float)N;
+        }
         __syncthreads();
         float d = 0.f;
         for (int k = half * 64; k < half * 64 + 64; ++k) d = fmaf(mean[k], Wt[k * (PE + 1) + e], d);
@@ -193,7 +216,7 @@ extern "C" int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, cons
     RL4CO_REQUIRE(B >= 0 && N >= 1, "am_graph_context: bad sizes");
     if (B == 0) return 0;
     RL4CO_REQUIRE(h && Wfixed && gctx, "am_graph_context: null pointer");
-    size_t smem = (size_t)(PE * (PE + 1) + 4 * PE) * sizeof(float);
+    size_t smem = (size_t)(PE * (PE + 1) + 4 * PE + 8 * PE) * sizeof(float);
     cudaFuncSetAttribute(am_graph_context_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int64_t grid = B < 148 * 3 ? B : 148 * 3;
     am_graph_context_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(B, N, h, Wfixed, gctx);
