@@ -71,6 +71,15 @@ int rl4co_tsp_replay(int64_t B, int32_t N, int32_t T, const float *locs,
                      int64_t *i, uint8_t *action_mask, uint8_t *done, float *reward,
                      int32_t check_validity, int32_t *status, rl4co_stream_t stream);
 
+/* ------------------------------------------------------------------ ATSP (K1) ------ */
+/* Asymmetric TSP, envs/routing/atsp/env.py: the state machine is the TSP one (rl4co_tsp_reset / rl4co_tsp_step);
+ * the fused replay takes the cost matrix [B,N,N] instead of coordinates and gathers the T tour edges
+ * (reward = -sum cost[a_t, a_{t+1}], closed; atsp/env.py:152-162).  Outputs as rl4co_tsp_replay. */
+int rl4co_atsp_replay(int64_t B, int32_t N, int32_t T, const float *cost_matrix, const int64_t *actions,
+                      int64_t *first_node, int64_t *current_node, int64_t *i, uint8_t *action_mask,
+                      uint8_t *done, float *reward, int32_t check_validity, int32_t *status,
+                      rl4co_stream_t stream);
+
 /* ------------------------------------------------------------------ CVRP (K1) ------ */
 /* N counts the depot (node 0).  demand [B,N-1] is already divided by capacity. */
 

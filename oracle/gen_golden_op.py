@@ -19,6 +19,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import gen_golden as G  # noqa: E402  (installs the shim)
 
+from rl4co.envs.routing.atsp.env import ATSPEnv  # noqa: E402
 from rl4co.envs.routing.op.env import OPEnv  # noqa: E402
 from rl4co.envs.routing.pctsp.env import PCTSPEnv  # noqa: E402
 from rl4co.envs.routing.spctsp.env import SPCTSPEnv  # noqa: E402
@@ -103,7 +104,26 @@ def main_pctsp():
                   f"replay T={data['replay.actions'].shape[1]}")
 
 
+def main_atsp():
+    """atsp: environment only (generator incl. the triangle-inequality closure, replay states, reward)."""
+    torch.manual_seed(2468)
+    G.GEN_KEYS["atsp"] = ()
+    for size, B in ((5, 8), (20, 8), (50, 6), (100, 4)):
+        env = ATSPEnv(generator_params=dict(num_loc=size))
+        td0 = env.generator(B)
+        data = {"gen.cost_matrix": G.np_(td0["cost_matrix"])}
+        tr = G.replay_trace(env, td0)
+        data.update({k: v for k, v in tr.items() if not k.endswith(".cost_matrix")})
+        path = os.path.join(G.OUT, f"atsp{size}.npz")
+        np.savez_compressed(path, **data)
+        print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, replay mean reward {data['replay.reward'].mean():.4f}")
+
+
 if __name__ == "__main__":
+    if "--atsp-only" in sys.argv:
+        main_atsp()
+        sys.exit(0)
     if "--pctsp-only" not in sys.argv:
         main()
     main_pctsp()
+    main_atsp()

@@ -323,6 +323,48 @@ def pctsp_reward(td: State, actions):
 
 
 # =====================================================================================
+# ATSP  (envs/routing/atsp/env.py) - env only: the AM init embedding registered for "atsp" needs td["locs"]
+# =====================================================================================
+def atsp_reset(cost_matrix) -> State:
+    """atsp/env.py:92-112 (+ merge)."""
+    B, N, _ = cost_matrix.shape
+    cur = torch.zeros(B, 1, dtype=torch.int64)
+    return {
+        "cost_matrix": cost_matrix,
+        "first_node": cur,
+        "current_node": cur,
+        "i": torch.zeros(B, 1, dtype=torch.int64),
+        "action_mask": torch.ones(B, N, dtype=torch.bool),
+        "done": torch.zeros(B, 1, dtype=torch.bool),
+        "terminated": torch.zeros(B, 1, dtype=torch.bool),
+    }
+
+
+def atsp_step(td: State) -> State:
+    """atsp/env.py:64-90: first-step test on element 0 of i (utils/ops.py batch_to_scalar), done [B]."""
+    cur = td["action"]
+    first = cur if td["i"].reshape(-1)[0].item() == 0 else td["first_node"]
+    avail = td["action_mask"].scatter(-1, cur.unsqueeze(-1).expand_as(td["action_mask"]), 0)
+    done = torch.count_nonzero(avail, dim=-1) <= 0
+    td.update({"first_node": first, "current_node": cur, "i": td["i"] + 1, "action_mask": avail,
+               "reward": torch.zeros_like(done), "done": done})
+    return td
+
+
+def atsp_check(actions) -> None:
+    """atsp/env.py:164-171."""
+    ok = (torch.arange(actions.size(1)).view(1, -1).expand_as(actions) == actions.sort(1)[0]).all()
+    assert ok, "Invalid tour"
+
+
+def atsp_reward(cost_matrix, actions):
+    """atsp/env.py:152-162: minus the sum of the cost-matrix entries along the closed tour."""
+    tgt = torch.roll(actions, -1, dims=1)
+    bidx = torch.arange(cost_matrix.shape[0]).unsqueeze(1)
+    return -cost_matrix[bidx, actions, tgt].sum(-1)
+
+
+# =====================================================================================
 # SLAP  (envs/warehousing/slap/env.py)
 # =====================================================================================
 def slap_reset(locs, assignment, n_products: int, extra: Optional[State] = None) -> State:
@@ -489,7 +531,7 @@ def select_action(logprobs, mask, decode_type: str, given=None):
 
 
 _STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step, "op": op_step, "pctsp": pctsp_step,
-         "spctsp": pctsp_step}
+         "spctsp": pctsp_step, "atsp": atsp_step}
 
 
 def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",

@@ -10,11 +10,11 @@ from .baselines import (RolloutBaseline, SharedBaseline, global_reward_mean, rei
 from .data import (TensorDictDataset, generate_dataset, load_npz_to_tensordict,  # noqa: F401
                    save_tensordict_to_npz)
 from .decoding import decode_step, get_log_likelihood, random_policy, rollout  # noqa: F401
-from .envs import (ENV_REGISTRY, CVRPEnv, OPEnv, PCTSPEnv, RL4COEnvBase, SLAPEnv, SPCTSPEnv, TSPEnv,  # noqa: F401
+from .envs import (ENV_REGISTRY, ATSPEnv, CVRPEnv, OPEnv, PCTSPEnv, RL4COEnvBase, SLAPEnv, SPCTSPEnv, TSPEnv,  # noqa: F401
                    get_env)
 from .evaluation import (AugmentationEval, GreedyEval, GreedyMultiStartAugmentEval,  # noqa: F401
                          GreedyMultiStartEval, SamplingEval, evaluate_policy)
-from .generators import CVRPGenerator, OPGenerator, PCTSPGenerator, SLAPGenerator, TSPGenerator  # noqa: F401
+from .generators import ATSPGenerator, CVRPGenerator, OPGenerator, PCTSPGenerator, SLAPGenerator, TSPGenerator  # noqa: F401
 from .ops import (batchify, gather_by_index, get_num_starts, get_tour_length,  # noqa: F401
                   select_start_nodes, unbatchify)
 from .policy import AttentionModelDecoder, AttentionModelPolicy, POMOPolicy  # noqa: F401

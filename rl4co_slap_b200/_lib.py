@@ -58,6 +58,7 @@ _SIGNATURES = {
     "rl4co_tsp_reset": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_tsp_step": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_tsp_replay": ([_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p], C.c_int),
+    "rl4co_atsp_replay": ([_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p], C.c_int),
     "rl4co_cvrp_action_mask": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_cvrp_step": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_cvrp_replay": ([_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p], C.c_int),

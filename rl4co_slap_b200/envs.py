@@ -18,7 +18,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
-from .generators import CVRPGenerator, OPGenerator, PCTSPGenerator, SLAPGenerator, TSPGenerator
+from .generators import ATSPGenerator, CVRPGenerator, OPGenerator, PCTSPGenerator, SLAPGenerator, TSPGenerator
 from .ops import get_num_starts, select_start_nodes
 from .tensordict_compat import TensorDict
 
@@ -253,6 +253,72 @@ class TSPEnv(RL4COEnvBase):
     def check_solution_validity(self, td, actions) -> None:
         """tsp/env.py:165-173: AssertionError("Invalid tour")."""
         self._reward_and_check(td, actions, True)
+
+
+# =====================================================================================
+class ATSPEnv(TSPEnv):
+    """rl4co/envs/routing/atsp/env.py:22-175: the TSP state machine on a cost matrix.  Environment only - the
+    reference registers TSPInitEmbedding for "atsp", which needs coordinates the instances do not have."""
+
+    name = "atsp"
+
+    def __init__(self, generator: ATSPGenerator = None, generator_params: dict = {}, **kwargs):
+        RL4COEnvBase.__init__(self, **kwargs)
+        if generator is None:
+            generator = ATSPGenerator(**{"device": self.device, **generator_params})
+        self.generator = generator
+
+    def _reset(self, td, batch_size=None):
+        """atsp/env.py:92-112 (current_node / first_node are ONE [B,1] tensor there)."""
+        cm = td["cost_matrix"]
+        _need_cuda(cm, "ATSPEnv.reset")
+        dev, B, N = cm.device, int(batch_size[0]), cm.shape[-1]
+        cur = torch.zeros(B, 1, dtype=torch.int64, device=dev)
+        return TensorDict({"cost_matrix": cm, "first_node": cur, "current_node": cur,
+                           "i": torch.zeros(B, 1, dtype=torch.int64, device=dev),
+                           "action_mask": torch.ones(B, N, dtype=torch.bool, device=dev)}, batch_size=batch_size)
+
+    @staticmethod
+    def _step(td):
+        """atsp/env.py:64-90 -> rl4co_tsp_step (same transition; first_node becomes [B] like the action)."""
+        td.set("first_node", td["first_node"].reshape(-1))
+        return TSPEnv._step(td)
+
+    def _replay_call(self, td, actions, check, want_state):
+        cm = td["cost_matrix"]
+        _need_cuda(cm, "ATSPEnv.replay")
+        dev, (B, N, _) = cm.device, cm.shape
+        reward = torch.empty(B, dtype=torch.float32, device=dev)
+        status = _lib.new_status(dev)
+        st = {}
+        if want_state:
+            st = {"first_node": torch.empty(B, dtype=torch.int64, device=dev),
+                  "current_node": torch.empty(B, dtype=torch.int64, device=dev),
+                  "i": torch.empty(B, 1, dtype=torch.int64, device=dev),
+                  "action_mask": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "done": torch.empty(B, dtype=torch.bool, device=dev)}
+        p = lambda k: _lib.ptr(_as_u8(st[k])) if k in st else None  # noqa: E731
+        _lib.call("rl4co_atsp_replay", B, N, actions.shape[1], _lib.ptr(cm.contiguous(), torch.float32),
+                  _lib.ptr(actions.contiguous(), torch.int64), p("first_node"), p("current_node"), p("i"),
+                  p("action_mask"), p("done"), _lib.ptr(reward), int(bool(check)), _lib.ptr(status),
+                  _lib.stream_ptr(dev))
+        _lib.raise_for_status(status)
+        return st, reward
+
+    def replay(self, td, actions, check: Optional[bool] = None):
+        check = self.check_solution if check is None else check
+        st, reward = self._replay_call(td, actions, check, True)
+        out = TensorDict({"cost_matrix": td["cost_matrix"], **st, "reward": torch.zeros_like(st["done"])},
+                         batch_size=[actions.shape[0]])
+        return out, reward
+
+    def _get_reward(self, td, actions):
+        """atsp/env.py:152-162."""
+        return self._replay_call(td, actions, False, False)[1]
+
+    def check_solution_validity(self, td, actions) -> None:
+        """atsp/env.py:164-171: AssertionError("Invalid tour")."""
+        self._replay_call(td, actions, True, False)
 
 
 # =====================================================================================
@@ -702,7 +768,7 @@ class SLAPEnv(RL4COEnvBase):
         return out, reward
 
 
-ENV_REGISTRY = {"tsp": TSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv, "pctsp": PCTSPEnv,
+ENV_REGISTRY = {"tsp": TSPEnv, "atsp": ATSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv, "pctsp": PCTSPEnv,
                 "spctsp": SPCTSPEnv}
 
 

@@ -97,6 +97,38 @@ class TSPGenerator(Generator):
         return TensorDict({"locs": locs}, batch_size=batch_size)
 
 
+class ATSPGenerator(Generator):
+    """atsp/generator.py:14-85 -> td{"cost_matrix" [B,n,n]}: uniform entries, zero diagonal and, with
+    ``tmat_class``, the min-plus closure iterated to its fixed point so that the triangle inequality holds
+    (MatNet, Kwon et al. 2021).  The closure materialises [b,n,n,n] sums, so it runs over slices of the batch."""
+
+    def __init__(self, num_loc: int = 10, min_dist: float = 0.0, max_dist: float = 1.0, dist_distribution=Uniform,
+                 tmat_class: bool = True, device=None, **kwargs):
+        self.num_loc, self.min_dist, self.max_dist, self.tmat_class = num_loc, min_dist, max_dist, tmat_class
+        self.device = device
+        self.dist_sampler = kwargs.get("dist_sampler") or get_sampler("dist", dist_distribution, 0.0, 1.0,
+                                                                      device=device, **kwargs)
+
+    def _generate(self, batch_size) -> TensorDict:
+        n = self.num_loc
+        dms = self.dist_sampler.sample((*batch_size, n, n)) * (self.max_dist - self.min_dist) + self.min_dist
+        dms[..., torch.arange(n), torch.arange(n)] = 0
+        if self.tmat_class:
+            flat = dms.reshape(-1, n, n)
+            step = max(1, (1 << 26) // (n * n * n))            # <= 256 MB of fp32 sums at a time
+            for c0 in range(0, flat.shape[0], step):
+                blk = flat[c0:c0 + step]
+                while True:
+                    new = (blk[:, :, None, :] + blk[:, None, :, :].transpose(-2, -1)).min(dim=-1)[0]
+                    same = bool((new == blk).all())
+                    blk = new
+                    if same:
+                        break
+                flat[c0:c0 + step] = blk
+            dms = flat.reshape(*batch_size, n, n)
+        return TensorDict({"cost_matrix": dms}, batch_size=batch_size)
+
+
 class CVRPGenerator(Generator):
     """cvrp/generator.py:33-143 -> td{"locs" [B,n,2], "depot" [B,2], "demand" [B,n]
     (already / capacity), "capacity" [B,1]}."""

@@ -9,6 +9,7 @@ import torch
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TSP_CASES, CVRP_CASES, SLAP_CASES = ("tsp5", "tsp20", "tsp50", "tsp100"), ("cvrp10", "cvrp20", "cvrp50", "cvrp100"), ("slap50", "slap100")
 OP_CASES = ("op10", "op20", "op50", "op100")
+ATSP_CASES = ("atsp5", "atsp20", "atsp50", "atsp100")
 PCTSP_CASES = ("pctsp10", "pctsp20", "pctsp50", "pctsp100", "spctsp20", "spctsp50")
 _PCTSP_KEYS = ("locs", "depot", "penalty", "deterministic_prize", "stochastic_prize")
 
@@ -62,7 +63,11 @@ def gen_td(env_name: str, fx, dev=None):
     from rl4co_slap_b200 import TensorDict
     keys = {"tsp": ("locs",), "cvrp": ("locs", "depot", "demand", "capacity"),
             "slap": ("locs", "freq", "assignment", "picklist", "depot_loc_dist"),
-            "op": ("locs", "depot", "prize", "max_length"), "pctsp": _PCTSP_KEYS, "spctsp": _PCTSP_KEYS}[env_name]
+            "op": ("locs", "depot", "prize", "max_length"), "pctsp": _PCTSP_KEYS, "spctsp": _PCTSP_KEYS,
+            "atsp": ("cost_matrix",)}[env_name]
+    if env_name == "atsp":
+        d = {"cost_matrix": t(fx["gen.cost_matrix"], dev)}
+        return TensorDict(d, batch_size=[d["cost_matrix"].shape[0]])
     d = {k: t(fx[f"gen.{k}"], dev) for k in keys}
     return TensorDict(d, batch_size=[d["locs"].shape[0]])
 
@@ -78,6 +83,8 @@ def oracle_reset(env_name: str, fx):
     if env_name == "cvrp":
         return port.cvrp_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.demand"]),
                                float(fx["gen.vehicle_capacity"]))
+    if env_name == "atsp":
+        return port.atsp_reset(t(fx["gen.cost_matrix"]))
     if env_name == "op":
         return port.op_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.prize"]), t(fx["gen.max_length"]))
     if env_name in ("pctsp", "spctsp"):

@@ -6,7 +6,7 @@ import torch
 
 import rl4co_slap_b200 as R
 from oracle import port
-from tests.helpers import (CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
+from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
 
 pytestmark = pytest.mark.gpu
 
@@ -36,7 +36,7 @@ def _same(got, want, what):
     assert np.array_equal(got, want), what
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
 def test_step_by_step_replay_bit_exact(case, dev):
     """reset + every _step through the env API: each state tensor equals the reference's
     (dtype, shape and value) after every step; then get_reward."""
@@ -56,7 +56,7 @@ def test_step_by_step_replay_bit_exact(case, dev):
     _close(reward, fx["replay.reward"], (case, "reward"))
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
 def test_fused_replay_matches_fixture(case, dev):
     fx, name = fixture(case), env_of(case)
     env = R.get_env(name, device=dev)
@@ -209,3 +209,29 @@ def test_full_size_replay_properties(dev):
     want = port.tsp_reward(locs[idx].cpu(), acts[idx].cpu())
     torch.testing.assert_close(r[idx].cpu(), want, rtol=1e-5, atol=1e-6)
     assert abs(r.double().mean().item() + 52.14) < 0.05   # theory: N * 0.5214
+
+
+@pytest.mark.parametrize("size,B", [(100, 300), (37, 64), (128, 33)])
+def test_atsp_generator_and_replay_vs_oracle(size, B, dev):
+    """cost matrices from the on-device generator satisfy the triangle inequality (the generator's fixed point);
+    random permutations replayed through the fused kernel against the oracle's gather"""
+    torch.manual_seed(31 + size)
+    env = R.ATSPEnv(generator_params=dict(num_loc=size), device=dev)
+    td0 = env.generator(B)
+    cm = td0["cost_matrix"]
+    assert cm.shape == (B, size, size) and bool((cm.diagonal(dim1=-2, dim2=-1) == 0).all())
+    sub = cm[:8]
+    closure = (sub[:, :, None, :] + sub[:, None, :, :].transpose(-2, -1)).min(-1)[0]
+    assert torch.equal(closure, sub), "triangle inequality (min-plus fixed point) violated"
+    td = env.reset(td0)
+    acts = torch.rand(B, size, device=dev).argsort(1)
+    final, reward = env.replay(td, acts)
+    want = port.atsp_reward(cm.cpu(), acts.cpu())
+    torch.testing.assert_close(reward.cpu(), want, rtol=1e-5, atol=1e-6)
+    assert bool(final["done"].all()) and not bool(final["action_mask"].any())
+    assert torch.equal(final["first_node"], acts[:, 0]) and torch.equal(final["current_node"], acts[:, -1])
+    torch.testing.assert_close(env.get_reward(td, acts).cpu(), want, rtol=1e-5, atol=1e-6)
+    bad = acts.clone()
+    bad[1, 3] = bad[1, 2]
+    with pytest.raises(AssertionError, match="Invalid tour"):
+        env.check_solution_validity(td, bad)

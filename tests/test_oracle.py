@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import port
-from tests.helpers import (CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
+from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
                            oracle_weights, t)
 
 
@@ -14,7 +14,7 @@ def _state_keys(fx, prefix):
     return [k[len(prefix) + 1:] for k in fx.files if k.startswith(prefix + ".")]
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
 def test_replay_bit_exact(case):
     """every per-step state tensor (mask, visited, capacity, i, done ...) equals the reference's"""
     fx, name = fixture(case), env_of(case)
@@ -42,6 +42,9 @@ def test_replay_bit_exact(case):
     elif name in ("pctsp", "spctsp"):
         port.pctsp_check(td, acts)
         r = port.pctsp_reward(td, acts)
+    elif name == "atsp":
+        port.atsp_check(acts)
+        r = port.atsp_reward(td["cost_matrix"], acts)
     else:
         r = port.slap_reward(td["locs"], td["assignment"], td["picklist"])
     assert np.array_equal(r.numpy(), fx["replay.reward"])
