@@ -5,7 +5,8 @@ AttentionModelPolicy.forward(decode_type=greedy|sampling|multistart_*|evaluate),
 hand-written CUDA kernels behind a C ABI (include/rl4co_slap_b200.h).  No CPU fallback.
 """
 from . import _lib  # noqa: F401
-from .baselines import (RolloutBaseline, SharedBaseline, global_reward_mean, reinforce_loss,  # noqa: F401
+from .baselines import (REINFORCE_BASELINES_REGISTRY, ExponentialBaseline, MeanBaseline, NoBaseline, RolloutBaseline,  # noqa: F401
+                        SharedBaseline, WarmupBaseline, get_reinforce_baseline, global_reward_mean, reinforce_loss,  # noqa: F401
                         reward_stats, shard_bounds)
 from .data import (TensorDictDataset, generate_dataset, load_npz_to_tensordict,  # noqa: F401
                    save_tensordict_to_npz)

@@ -116,6 +116,77 @@ class SharedBaseline:
         return out["baseline"].unsqueeze(1), out["loss_partial"]
 
 
+class NoBaseline:
+    """baselines.py:49-53."""
+
+    def wrap_dataset(self, dataset, *args, **kw):
+        return dataset
+
+    def setup(self, *args, **kw):
+        pass
+
+    def epoch_callback(self, *args, **kw):
+        pass
+
+    def eval(self, td, reward, env=None):
+        return 0, 0
+
+
+class ExponentialBaseline(NoBaseline):
+    """baselines.py:64-83: exponential moving average of the batch-mean reward.  The mean is taken over the GLOBAL
+    batch (fp64 partial sums from rl4co_reward_stats, one all-reduce across ranks) - the reference
+    averages per rank."""
+
+    def __init__(self, beta: float = 0.8, group=None, **kw):
+        self.beta, self.v, self.group = beta, None, group
+
+    def eval(self, td, reward, env=None):
+        mean = global_reward_mean(reward, self.group).to(torch.float32)
+        v = mean if self.v is None else self.beta * self.v + (1.0 - self.beta) * mean
+        self.v = v.detach()
+        return self.v, 0
+
+
+class MeanBaseline:
+    """baselines.py:86-90: the batch mean = an exponential baseline with beta 0."""
+
+    def __new__(cls, **kw):
+        return ExponentialBaseline(beta=0.0, **kw)
+
+
+class WarmupBaseline(NoBaseline):
+    """baselines.py:93-135: convex combination of ``baseline`` and an exponential baseline, alpha = (epoch + 1) /
+    n_epochs during the warm-up epochs."""
+
+    def __init__(self, baseline, n_epochs: int = 1, warmup_exp_beta: float = 0.8, **kw):
+        assert n_epochs > 0, "n_epochs to warmup must be positive"
+        self.baseline = baseline
+        self.warmup_baseline = ExponentialBaseline(warmup_exp_beta)
+        self.alpha, self.n_epochs = 0, n_epochs
+
+    def wrap_dataset(self, dataset, *args, **kw):
+        if self.alpha > 0:
+            return self.baseline.wrap_dataset(dataset, *args, **kw)
+        return self.warmup_baseline.wrap_dataset(dataset, *args, **kw)
+
+    def setup(self, *args, **kw):
+        self.baseline.setup(*args, **kw)
+
+    def eval(self, td, reward, env=None):
+        if self.alpha == 1:
+            return self.baseline.eval(td, reward, env)
+        if self.alpha == 0:
+            return self.warmup_baseline.eval(td, reward, env)
+        v_b, l_b = self.baseline.eval(td, reward, env)
+        v_wb, l_wb = self.warmup_baseline.eval(td, reward, env)
+        return self.alpha * v_b + (1 - self.alpha) * v_wb, self.alpha * l_b + (1 - self.alpha) * l_wb
+
+    def epoch_callback(self, *args, **kw):
+        self.baseline.epoch_callback(*args, **kw)
+        if kw["epoch"] < self.n_epochs:
+            self.alpha = (kw["epoch"] + 1) / float(self.n_epochs)
+
+
 def reinforce_loss(loss_partial: torch.Tensor, group=None) -> torch.Tensor:
     """reinforce.py:103-106 over the GLOBAL batch: -(sum adv*ll)/count after one all-reduce."""
     p = all_reduce_sum_(loss_partial.clone(), group)
@@ -196,3 +267,26 @@ class RolloutBaseline:
             dataset = TensorDictDataset(dataset)
         rewards = self.rollout(self.policy, env, batch_size, device, dataset=dataset).detach()
         return dataset.add_key("extra", rewards)
+
+
+# baselines.py:275-299 (the critic baseline needs a critic network: out of scope)
+REINFORCE_BASELINES_REGISTRY = {"no": NoBaseline, "shared": SharedBaseline, "exponential": ExponentialBaseline,
+                                "mean": MeanBaseline, "rollout_only": RolloutBaseline, "warmup": WarmupBaseline}
+
+
+def get_reinforce_baseline(name, **kw):
+    """baselines.py:286-299: "rollout" = a warm-up baseline around the greedy-rollout baseline."""
+    if name == "warmup":
+        inner = kw.get("baseline", "rollout")
+        if not isinstance(inner, NoBaseline) and isinstance(inner, str):
+            inner = get_reinforce_baseline(inner, **kw)
+        return WarmupBaseline(inner, **{k: v for k, v in kw.items() if k != "baseline"})
+    if name == "rollout":
+        return WarmupBaseline(RolloutBaseline(bl_alpha=kw.get("bl_alpha", 0.05), group=kw.get("group")),
+                              kw.get("n_epochs", 1), kw.get("exp_beta", 0.8))
+    if name is None:
+        name = "no"
+    cls = REINFORCE_BASELINES_REGISTRY.get(name)
+    if cls is None:
+        raise ValueError(f"Unknown baseline {name}. Available baselines: {REINFORCE_BASELINES_REGISTRY.keys()}")
+    return cls(**kw)

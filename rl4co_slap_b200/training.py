@@ -221,7 +221,8 @@ def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: 
     (no autograd), re-evaluate the sampled trajectories' log-likelihood differentiably, loss
     ``((reward - baseline) * log_likelihood).mean()`` on the negated... exactly ``-(advantage * ll).mean()`` as in
     reinforce.py:103-106 with reward = -cost, backward, clip, optimiser step.  ``baseline``: None (no baseline),
-    "shared" (POMO mean over the starts of an instance, baselines.py:57-61) or a tensor [R]."""
+    "shared" (POMO mean over the starts of an instance, baselines.py:57-61), a tensor [R], or a baseline object with the
+    reference's ``eval(td, reward, env) -> (value, loss)`` (rl4co_slap_b200.baselines)."""
     decode_type = decode_type or policy.train_decode_type
     multistart = "multistart" in decode_type
     with torch.no_grad():
@@ -236,6 +237,8 @@ def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: 
         bl = torch.zeros_like(reward)
     elif isinstance(baseline, str) and baseline == "shared":
         bl = reward.reshape(max(S, 1), B).mean(0, keepdim=True).expand(max(S, 1), B).reshape(-1)
+    elif hasattr(baseline, "eval"):     # a baselines.py object (No / Exponential / Mean / Warmup / Rollout)
+        bl, _ = baseline.eval(td, reward, env)
     else:
         bl = baseline
     advantage = reward - bl

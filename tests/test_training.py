@@ -164,3 +164,41 @@ def test_reinforce_step_trains(name, decode_type, baseline, dev):
         ll_after = teacher_forced_log_likelihood(pol, td, name, h.float(), first["actions"], num_starts=S)
     j0, j1 = (adv * first["log_likelihood"]).mean().item(), (adv * ll_after).mean().item()
     assert j1 > j0, f"surrogate objective did not increase: {j0} -> {j1}"
+
+
+@pytest.mark.gpu
+def test_small_baselines_follow_reference_formulas(dev):
+    """No / Exponential / Mean / Warmup baselines (baselines.py:49-135) and the registry; the exponential baseline's
+    batch mean comes from the fp64 partial-sum kernel"""
+    torch.manual_seed(0)
+    r1, r2 = torch.randn(4096, device=dev) - 7, torch.randn(4096, device=dev) - 6
+    assert R.get_reinforce_baseline("no").eval(None, r1) == (0, 0)
+    eb = R.get_reinforce_baseline("exponential", beta=0.8)
+    v1, l1 = eb.eval(None, r1)
+    v2, _ = eb.eval(None, r2)
+    torch.testing.assert_close(v1, r1.double().mean().float(), rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(v2, (0.8 * r1.double().mean() + 0.2 * r2.double().mean()).float(), rtol=1e-6, atol=1e-6)
+    assert l1 == 0 and v2.dtype == torch.float32 and not v2.requires_grad
+    mb = R.get_reinforce_baseline("mean")
+    mb.eval(None, r1)
+    torch.testing.assert_close(mb.eval(None, r2)[0], r2.double().mean().float(), rtol=1e-6, atol=1e-6)
+    wb = R.WarmupBaseline(R.get_reinforce_baseline("mean"), n_epochs=2, warmup_exp_beta=0.5)
+    a0 = wb.eval(None, r1)[0]                                   # alpha 0: the warm-up exponential baseline alone
+    torch.testing.assert_close(a0, r1.double().mean().float(), rtol=1e-6, atol=1e-6)
+    wb.epoch_callback(epoch=0)
+    assert wb.alpha == 0.5
+    mix = wb.eval(None, r2)[0]
+    want = 0.5 * r2.double().mean() + 0.5 * (0.5 * r1.double().mean() + 0.5 * r2.double().mean())
+    torch.testing.assert_close(mix, want.float(), rtol=1e-6, atol=1e-6)
+    wb.epoch_callback(epoch=1)
+    assert wb.alpha == 1.0
+    assert isinstance(R.get_reinforce_baseline("rollout"), R.WarmupBaseline)
+    with pytest.raises(ValueError, match="Unknown baseline"):
+        R.get_reinforce_baseline("critic_nope")
+    # a baseline object drives reinforce_step exactly like the reference's calculate_loss (reinforce.py:95-106)
+    pol = R.AttentionModelPolicy(env_name="tsp", num_encoder_layers=1).to(dev)
+    env = R.TSPEnv(generator_params=dict(num_loc=10), device=dev)
+    td = env.reset(batch_size=[32])
+    res = reinforce_step(pol, env, td, optimizer=None, baseline=R.get_reinforce_baseline("exponential"))
+    adv = res["reward"] - res["reward"].double().mean().float()
+    torch.testing.assert_close(res["loss"], -(adv * res["log_likelihood"]).mean(), rtol=1e-5, atol=1e-6)
