@@ -22,6 +22,7 @@ from oracle import gen_golden as G  # noqa: E402  (installs the shim)
 from rl4co.envs.routing.atsp.env import ATSPEnv  # noqa: E402
 from rl4co.envs.routing.op.env import OPEnv  # noqa: E402
 from rl4co.envs.routing.pctsp.env import PCTSPEnv  # noqa: E402
+from rl4co.envs.routing.sdvrp.env import SDVRPEnv  # noqa: E402
 from rl4co.envs.routing.spctsp.env import SPCTSPEnv  # noqa: E402
 from rl4co.models.zoo.am.policy import AttentionModelPolicy  # noqa: E402
 
@@ -119,7 +120,33 @@ def main_atsp():
         print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, replay mean reward {data['replay.reward'].mean():.4f}")
 
 
+def main_sdvrp():
+    """sdvrp: split deliveries (nodes revisited) and the per-step dynamic embedding of the remaining demands."""
+    torch.manual_seed(1357)
+    G.GEN_KEYS["sdvrp"] = G.GEN_KEYS["cvrp"]
+    pol = AttentionModelPolicy(env_name="sdvrp", num_encoder_layers=1, feedforward_hidden=128).eval()
+    np.savez_compressed(os.path.join(G.OUT, "policy_sdvrp.npz"), **{k: G.np_(v) for k, v in pol.state_dict().items()})
+    for size, B in ((10, 8), (20, 8), (50, 6), (100, 4)):
+        env = SDVRPEnv(generator_params=dict(num_loc=size))
+        td0 = env.generator(B)
+        data = {f"gen.{k}": G.np_(td0[k]) for k in G.GEN_KEYS["sdvrp"]}
+        data["gen.vehicle_capacity"] = np.float32(env.generator.vehicle_capacity)
+        data.update(G.replay_trace(env, td0))
+        res, h = G.policy_outputs(env, pol, td0, "greedy", decode_type="greedy")
+        data.update(res)
+        data["hidden"] = G.np_(h)
+        res, _ = G.policy_outputs(env, pol, td0, "eval", actions=torch.from_numpy(data["replay.actions"]))
+        data.update(res)
+        path = os.path.join(G.OUT, f"sdvrp{size}.npz")
+        np.savez_compressed(path, **data)
+        print(f"{path}: {os.path.getsize(path) / 1024:.0f} KiB, greedy mean reward {data['greedy.reward'].mean():.4f}, "
+              f"T={data['greedy.actions'].shape[1]}, replay T={data['replay.actions'].shape[1]}")
+
+
 if __name__ == "__main__":
+    if "--sdvrp-only" in sys.argv:
+        main_sdvrp()
+        sys.exit(0)
     if "--atsp-only" in sys.argv:
         main_atsp()
         sys.exit(0)
@@ -127,3 +154,4 @@ if __name__ == "__main__":
         main()
     main_pctsp()
     main_atsp()
+    main_sdvrp()

@@ -67,7 +67,7 @@ def unbatchify(x, repeats: int):
 def num_starts_for(env_name: str, action_mask) -> int:
     """utils/ops.py:126-136."""
     n = action_mask.shape[-1]
-    return n - 1 if env_name in ("cvrp", "op", "pctsp", "spctsp") else n
+    return n - 1 if env_name in ("cvrp", "sdvrp", "op", "pctsp", "spctsp") else n
 
 
 def select_start_nodes(env_name: str, batch: int, num_starts: int, num_loc: int):
@@ -365,6 +365,65 @@ def atsp_reward(cost_matrix, actions):
 
 
 # =====================================================================================
+# SDVRP  (envs/routing/sdvrp/env.py; dynamic embedding nn/env_embeddings/dynamic.py:61-79)
+# =====================================================================================
+def sdvrp_action_mask(td: State):
+    """sdvrp/env.py:132-140."""
+    mask_loc = (td["demand_with_depot"][..., 1:] == 0) | (td["used_capacity"] >= td["vehicle_capacity"])
+    mask_depot = (td["current_node"] == 0).squeeze(-1) & ((mask_loc == 0).int().sum(-1) > 0)
+    return ~torch.cat((mask_depot[..., None], mask_loc), -1)
+
+
+def sdvrp_reset(depot, locs, demand, vehicle_capacity: float = 1.0) -> State:
+    """sdvrp/env.py:103-130 (+ merge)."""
+    B = locs.shape[0]
+    td = {
+        "locs": torch.cat((depot[..., None, :], locs), -2),
+        "demand": demand,
+        "demand_with_depot": torch.cat((torch.zeros_like(demand[..., 0:1]), demand), -1),
+        "current_node": torch.zeros(B, 1, dtype=torch.int64),
+        "used_capacity": torch.zeros(B, 1),
+        "vehicle_capacity": torch.full((B, 1), vehicle_capacity),
+        "done": torch.zeros(B, 1, dtype=torch.bool),
+        "terminated": torch.zeros(B, 1, dtype=torch.bool),
+    }
+    td["action_mask"] = sdvrp_action_mask(td)
+    return td
+
+
+def sdvrp_step(td: State) -> State:
+    """sdvrp/env.py:63-101: deliver min(remaining demand, remaining capacity), nodes may be revisited."""
+    cur = td["action"][:, None]
+    sel = gather_by_index(td["demand_with_depot"], cur, dim=-1, squeeze=False)[..., :1]
+    delivered = torch.min(sel, td["vehicle_capacity"] - td["used_capacity"])
+    used = (td["used_capacity"] + delivered) * (cur != 0).float()
+    dwd = td["demand_with_depot"].scatter_add(-1, cur, -delivered)
+    done = ~(dwd > 0).any(-1)
+    td.update({"demand_with_depot": dwd, "current_node": cur, "used_capacity": used,
+               "reward": torch.zeros_like(done), "done": done})
+    td["action_mask"] = sdvrp_action_mask(td)
+    return td
+
+
+def sdvrp_check(demand, vehicle_capacity, actions) -> None:
+    """sdvrp/env.py:142-164."""
+    B = demand.size(0)
+    demands = torch.cat((-vehicle_capacity, demand), 1)
+    rng = torch.arange(B)
+    used = torch.zeros_like(demand[..., 0])
+    a_prev = None
+    for a in actions.transpose(0, 1):
+        assert a_prev is None or (demands[((a_prev == 0) & (a == 0)), :] == 0).all(), \
+            "Cannot visit depot twice if any nonzero demand"
+        d = torch.min(demands[rng, a], vehicle_capacity.squeeze(-1) - used)
+        demands[rng, a] -= d
+        used += d
+        used[a == 0] = 0
+        a_prev = a
+    assert (demands == 0).all(), "All demand must be satisfied"
+
+
+# =====================================================================================
 # SLAP  (envs/warehousing/slap/env.py)
 # =====================================================================================
 def slap_reset(locs, assignment, n_products: int, extra: Optional[State] = None) -> State:
@@ -454,7 +513,7 @@ def context_embedding(env_name: str, cache, td: State, W):
                 h, torch.stack([td["first_node"], td["current_node"]], -1).view(B, -1)
             ).view(B, *node_dim)
         return F.linear(x, W["Wctx"])
-    if env_name == "cvrp":
+    if env_name in ("cvrp", "sdvrp"):
         cur = gather_by_index(h, td["current_node"])
         state = (td["vehicle_capacity"] - td["used_capacity"]).to(cur.dtype)   # (no-op in fp32; fp64 decoder checks)
         return F.linear(torch.cat([cur, state], -1), W["Wctx"])
@@ -498,6 +557,12 @@ def decoder_forward(env_name, td_flat: State, cache, W, num_starts: int):
     if q.ndim == 2:
         q = q.unsqueeze(1)
     mask = td["action_mask"]
+    if env_name == "sdvrp":     # SDVRPDynamicEmbedding, dynamic.py:61-79 + _compute_kvl, am/decoder.py:148-160
+        assert num_starts <= 1, "sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not restated"
+        d = td["demand_with_depot"][..., None].clone().to(cache["gk"].dtype)
+        d[..., 0, :] = 0
+        k_dyn, v_dyn, l_dyn = F.linear(d, W["Wdyn"]).chunk(3, dim=-1)
+        cache = dict(cache, gk=cache["gk"] + k_dyn, gv=cache["gv"] + v_dyn, lk=cache["lk"] + l_dyn)
     logits = pointer_logits(q, cache, mask, W)
     if num_starts > 1:
         S = num_starts
@@ -531,7 +596,7 @@ def select_action(logprobs, mask, decode_type: str, given=None):
 
 
 _STEP = {"tsp": tsp_step, "cvrp": cvrp_step, "slap": slap_step, "op": op_step, "pctsp": pctsp_step,
-         "spctsp": pctsp_step, "atsp": atsp_step}
+         "spctsp": pctsp_step, "atsp": atsp_step, "sdvrp": sdvrp_step}
 
 
 def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
@@ -579,6 +644,10 @@ def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
     elif env_name == "cvrp":
         if check_solution:
             cvrp_check(td["demand"], td["vehicle_capacity"], out_actions)
+        reward = cvrp_reward(td["locs"], out_actions)
+    elif env_name == "sdvrp":
+        if check_solution:
+            sdvrp_check(td["demand"], td["vehicle_capacity"], out_actions)
         reward = cvrp_reward(td["locs"], out_actions)
     elif env_name == "op":
         if check_solution:

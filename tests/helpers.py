@@ -9,6 +9,7 @@ import torch
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TSP_CASES, CVRP_CASES, SLAP_CASES = ("tsp5", "tsp20", "tsp50", "tsp100"), ("cvrp10", "cvrp20", "cvrp50", "cvrp100"), ("slap50", "slap100")
 OP_CASES = ("op10", "op20", "op50", "op100")
+SDVRP_CASES = ("sdvrp10", "sdvrp20", "sdvrp50", "sdvrp100")
 ATSP_CASES = ("atsp5", "atsp20", "atsp50", "atsp100")
 PCTSP_CASES = ("pctsp10", "pctsp20", "pctsp50", "pctsp100", "spctsp20", "spctsp50")
 _PCTSP_KEYS = ("locs", "depot", "penalty", "deterministic_prize", "stochastic_prize")
@@ -55,6 +56,8 @@ def oracle_weights(env_name: str, variant: str = None):
         W["Wctx"] = sd["decoder.context_embedding.project_context.weight"]
     if env_name == "tsp":
         W["Wph"] = sd["decoder.context_embedding.W_placeholder"]
+    if env_name == "sdvrp":
+        W["Wdyn"] = sd["decoder.dynamic_embedding.projection.weight"]
     return W
 
 
@@ -64,7 +67,7 @@ def gen_td(env_name: str, fx, dev=None):
     keys = {"tsp": ("locs",), "cvrp": ("locs", "depot", "demand", "capacity"),
             "slap": ("locs", "freq", "assignment", "picklist", "depot_loc_dist"),
             "op": ("locs", "depot", "prize", "max_length"), "pctsp": _PCTSP_KEYS, "spctsp": _PCTSP_KEYS,
-            "atsp": ("cost_matrix",)}[env_name]
+            "atsp": ("cost_matrix",), "sdvrp": ("locs", "depot", "demand", "capacity")}[env_name]
     if env_name == "atsp":
         d = {"cost_matrix": t(fx["gen.cost_matrix"], dev)}
         return TensorDict(d, batch_size=[d["cost_matrix"].shape[0]])
@@ -85,6 +88,9 @@ def oracle_reset(env_name: str, fx):
                                float(fx["gen.vehicle_capacity"]))
     if env_name == "atsp":
         return port.atsp_reset(t(fx["gen.cost_matrix"]))
+    if env_name == "sdvrp":
+        return port.sdvrp_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.demand"]),
+                                float(fx["gen.vehicle_capacity"]))
     if env_name == "op":
         return port.op_reset(t(fx["gen.depot"]), t(fx["gen.locs"]), t(fx["gen.prize"]), t(fx["gen.max_length"]))
     if env_name in ("pctsp", "spctsp"):

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from oracle import port
-from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
+from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, SDVRP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, oracle_reset,
                            oracle_weights, t)
 
 
@@ -14,7 +14,7 @@ def _state_keys(fx, prefix):
     return [k[len(prefix) + 1:] for k in fx.files if k.startswith(prefix + ".")]
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES + SDVRP_CASES)
 def test_replay_bit_exact(case):
     """every per-step state tensor (mask, visited, capacity, i, done ...) equals the reference's"""
     fx, name = fixture(case), env_of(case)
@@ -45,12 +45,15 @@ def test_replay_bit_exact(case):
     elif name == "atsp":
         port.atsp_check(acts)
         r = port.atsp_reward(td["cost_matrix"], acts)
+    elif name == "sdvrp":
+        port.sdvrp_check(td["demand"], td["vehicle_capacity"], acts)
+        r = port.cvrp_reward(td["locs"], acts)
     else:
         r = port.slap_reward(td["locs"], td["assignment"], td["picklist"])
     assert np.array_equal(r.numpy(), fx["replay.reward"])
 
 
-@pytest.mark.parametrize("case", ("tsp20", "tsp50", "tsp100", "cvrp20", "cvrp50", "slap50", "slap100") + OP_CASES + PCTSP_CASES)
+@pytest.mark.parametrize("case", ("tsp20", "tsp50", "tsp100", "cvrp20", "cvrp50", "slap50", "slap100") + OP_CASES + PCTSP_CASES + SDVRP_CASES)
 def test_greedy_rollout_matches_reference(case):
     fx, name = fixture(case), env_of(case)
     out = port.am_rollout(name, oracle_reset(name, fx), t(fx["hidden"]), oracle_weights(name), "greedy")
@@ -86,7 +89,7 @@ def test_evaluate_reproduces_ll():
     np.testing.assert_allclose(out["log_likelihood"].numpy(), fx["greedy.ll"], rtol=1e-5, atol=1e-5)
 
 
-@pytest.mark.parametrize("case", OP_CASES + PCTSP_CASES)
+@pytest.mark.parametrize("case", OP_CASES + PCTSP_CASES + SDVRP_CASES)
 def test_op_evaluate_long_tours(case):
     """per-step log-probs of the replay's random tours (they run into the length budget) = the reference's"""
     fx, name = fixture(case), env_of(case)
