@@ -41,6 +41,8 @@ extern "C" {
 #define RL4CO_ST_DUPLICATES        64  /* op/env.py:196-199 */
 #define RL4CO_ST_OVER_LENGTH       128 /* op/env.py:211-215 */
 #define RL4CO_ST_PRIZE_SHORT       256 /* pctsp/env.py:193-200 */
+#define RL4CO_ST_DEPOT_TWICE       512 /* sdvrp/env.py:155-157 */
+#define RL4CO_ST_DEMAND_LEFT       1024 /* sdvrp/env.py:164 */
 
 typedef void *rl4co_stream_t;
 
@@ -151,6 +153,27 @@ int rl4co_pctsp_replay(int64_t B, int32_t N, int32_t T, const float *locs, const
                        float *cur_total_prize, float *cur_total_penalty, uint8_t *visited, uint8_t *action_mask,
                        int64_t *i, uint8_t *done, float *reward, int32_t check_validity, int32_t *status,
                        rl4co_stream_t stream);
+
+/* ------------------------------------------------------------------ SDVRP (K1) ----- */
+/* Split-delivery VRP, envs/routing/sdvrp/env.py.  N counts the depot; demand_with_depot [B,N] (slot 0 = depot = 0)
+ * is the remaining demand, updated in place by the step; demand [B,N-1] is the original one (already / capacity). */
+
+/* SDVRPEnv.get_action_mask, sdvrp/env.py:132-140. */
+int rl4co_sdvrp_action_mask(int64_t B, int32_t N, const float *demand_with_depot, const float *used_capacity,
+                            const float *vehicle_capacity, const int64_t *current_node, uint8_t *action_mask,
+                            rl4co_stream_t stream);
+
+/* SDVRPEnv._step, sdvrp/env.py:63-101 (transition + mask in one launch).  done is [B]. */
+int rl4co_sdvrp_step(int64_t B, int32_t N, const int64_t *action, const float *vehicle_capacity,
+                     float *demand_with_depot, float *used_capacity, int64_t *current_node,
+                     uint8_t *action_mask, uint8_t *done, int32_t *status, rl4co_stream_t stream);
+
+/* Fused reset + T x _step + get_reward (cvrp/env.py:151-160, inherited) + check_solution_validity
+ * (sdvrp/env.py:142-164).  check_validity != 0 ORs RL4CO_ST_DEPOT_TWICE / RL4CO_ST_DEMAND_LEFT. */
+int rl4co_sdvrp_replay(int64_t B, int32_t N, int32_t T, const float *locs, const float *demand,
+                       const float *vehicle_capacity, const int64_t *actions, int64_t *current_node,
+                       float *used_capacity, float *demand_with_depot, uint8_t *action_mask, uint8_t *done,
+                       float *reward, int32_t check_validity, int32_t *status, rl4co_stream_t stream);
 
 /* ------------------------------------------------------------------ SLAP (K1) ------ */
 /* N storage locations (node 0 = depot, never assignable), P products. */

@@ -11,7 +11,7 @@ from .baselines import (REINFORCE_BASELINES_REGISTRY, ExponentialBaseline, MeanB
 from .data import (TensorDictDataset, generate_dataset, load_npz_to_tensordict,  # noqa: F401
                    save_tensordict_to_npz)
 from .decoding import decode_step, get_log_likelihood, random_policy, rollout  # noqa: F401
-from .envs import (ENV_REGISTRY, ATSPEnv, CVRPEnv, OPEnv, PCTSPEnv, RL4COEnvBase, SLAPEnv, SPCTSPEnv, TSPEnv,  # noqa: F401
+from .envs import (ENV_REGISTRY, ATSPEnv, CVRPEnv, OPEnv, PCTSPEnv, RL4COEnvBase, SDVRPEnv, SLAPEnv, SPCTSPEnv, TSPEnv,  # noqa: F401
                    get_env)
 from .evaluation import (AugmentationEval, GreedyEval, GreedyMultiStartAugmentEval,  # noqa: F401
                          GreedyMultiStartEval, SamplingEval, evaluate_policy)

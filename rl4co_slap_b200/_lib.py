@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "librl4co_slap_b200.so")
 ST_INVALID_TOUR, ST_OVER_CAPACITY, ST_INFEASIBLE_ACTION = 1, 2, 4
 ST_NAN_LOGITS, ST_NEG_INF_LOGP, ST_ACTION_RANGE = 8, 16, 32
 ST_DUPLICATES, ST_OVER_LENGTH, ST_PRIZE_SHORT = 64, 128, 256
+ST_DEPOT_TWICE, ST_DEMAND_LEFT = 512, 1024
 # messages are the reference's assertion texts (tsp/env.py:173, cvrp/env.py:175,190,
 # utils/decoding.py:59,379, models/nn/attention.py:285)
 STATUS_MESSAGES = [
@@ -30,6 +31,8 @@ STATUS_MESSAGES = [
     (ST_DUPLICATES, "Duplicates"),                       # op/env.py:199
     (ST_OVER_LENGTH, "Max length exceeded"),             # op/env.py:213
     (ST_PRIZE_SHORT, "Total prize does not satisfy min total prize"),   # pctsp/env.py:200
+    (ST_DEPOT_TWICE, "Cannot visit depot twice if any nonzero demand"),   # sdvrp/env.py:157
+    (ST_DEMAND_LEFT, "All demand must be satisfied"),                     # sdvrp/env.py:164
 ]
 ENV_IDS = {"tsp": 0, "cvrp": 1, "slap": 2, "op": 3, "pctsp": 4, "spctsp": 4}
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -68,6 +71,9 @@ _SIGNATURES = {
     "rl4co_pctsp_action_mask": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_pctsp_step": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_pctsp_replay": ([_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p], C.c_int),
+    "rl4co_sdvrp_action_mask": ([_i64, _i32, _p, _p, _p, _p, _p, _p], C.c_int),
+    "rl4co_sdvrp_step": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
+    "rl4co_sdvrp_replay": ([_i64, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p], C.c_int),
     "rl4co_slap_step": ([_i64, _i32, _i32, _p, _p, _i64, _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_slap_reward": ([_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_slap_replay": ([_i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),

@@ -430,6 +430,94 @@ class CVRPEnv(RL4COEnvBase):
 
 
 # =====================================================================================
+class SDVRPEnv(CVRPEnv):
+    """rl4co/envs/routing/sdvrp/env.py:22-214 (split-delivery VRP): customers may be visited several times, each
+    visit delivers min(remaining demand, remaining capacity).  Generator and reward are the CVRP ones."""
+
+    name = "sdvrp"
+
+    def _reset(self, td, batch_size=None):
+        """sdvrp/env.py:103-130."""
+        _need_cuda(td["locs"], "SDVRPEnv.reset")
+        dev, B = td["locs"].device, int(batch_size[0])
+        out = TensorDict({
+            "locs": torch.cat((td["depot"][..., None, :], td["locs"]), -2),
+            "demand": td["demand"],
+            "demand_with_depot": torch.cat((torch.zeros_like(td["demand"][..., 0:1]), td["demand"]), -1),
+            "current_node": torch.zeros(B, 1, dtype=torch.long, device=dev),
+            "used_capacity": torch.zeros(B, 1, device=dev),
+            "vehicle_capacity": torch.full((B, 1), self.generator.vehicle_capacity, device=dev),
+        }, batch_size=batch_size)
+        out.set("action_mask", self.get_action_mask(out))
+        return out
+
+    @staticmethod
+    def get_action_mask(td):
+        """sdvrp/env.py:132-140 -> rl4co_sdvrp_action_mask."""
+        dwd = td["demand_with_depot"]
+        _need_cuda(dwd, "SDVRPEnv.get_action_mask")
+        dev, (B, N) = dwd.device, dwd.shape
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        _lib.call("rl4co_sdvrp_action_mask", B, N, _lib.ptr(dwd.contiguous(), torch.float32),
+                  _lib.ptr(td["used_capacity"].contiguous(), torch.float32),
+                  _lib.ptr(td["vehicle_capacity"].contiguous(), torch.float32),
+                  _lib.ptr(td["current_node"].contiguous(), torch.int64), _lib.ptr(_as_u8(mask)), _lib.stream_ptr(dev))
+        return mask
+
+    def _step(self, td):
+        """sdvrp/env.py:63-101 -> rl4co_sdvrp_step (transition + mask in one launch)."""
+        action = td["action"]
+        _need_cuda(action, "SDVRPEnv._step")
+        dev, (B, N) = action.device, td["demand_with_depot"].shape
+        dwd, used = td["demand_with_depot"].clone(), td["used_capacity"].clone()
+        cur = torch.empty(B, 1, dtype=torch.int64, device=dev)
+        mask = torch.empty(B, N, dtype=torch.bool, device=dev)
+        done = torch.empty(B, dtype=torch.bool, device=dev)
+        status = _lib.deferred_status(dev)
+        _lib.call("rl4co_sdvrp_step", B, N, _lib.ptr(action.contiguous(), torch.int64),
+                  _lib.ptr(td["vehicle_capacity"].contiguous(), torch.float32), _lib.ptr(dwd), _lib.ptr(used),
+                  _lib.ptr(cur), _lib.ptr(_as_u8(mask)), _lib.ptr(_as_u8(done)), _lib.ptr(status), _lib.stream_ptr(dev))
+        td.update({"demand_with_depot": dwd, "current_node": cur, "used_capacity": used,
+                   "reward": torch.zeros_like(done), "done": done})
+        td.set("action_mask", mask)
+        return td
+
+    def _replay_call(self, td, actions, check, want_state):
+        locs, demand = td["locs"], td["demand"]
+        _need_cuda(locs, "SDVRPEnv.replay")
+        dev, (B, N, _) = locs.device, locs.shape
+        reward = torch.empty(B, dtype=torch.float32, device=dev)
+        status = _lib.new_status(dev)
+        st = {}
+        if want_state:
+            st = {"current_node": torch.empty(B, 1, dtype=torch.int64, device=dev),
+                  "used_capacity": torch.empty(B, 1, dtype=torch.float32, device=dev),
+                  "demand_with_depot": torch.empty(B, N, dtype=torch.float32, device=dev),
+                  "action_mask": torch.empty(B, N, dtype=torch.bool, device=dev),
+                  "done": torch.empty(B, dtype=torch.bool, device=dev)}
+        p = lambda k: _lib.ptr(_as_u8(st[k])) if k in st else None  # noqa: E731
+        _lib.call("rl4co_sdvrp_replay", B, N, actions.shape[1], _lib.ptr(locs.contiguous(), torch.float32),
+                  _lib.ptr(demand.contiguous(), torch.float32),
+                  _lib.ptr(td["vehicle_capacity"].contiguous(), torch.float32),
+                  _lib.ptr(actions.contiguous(), torch.int64), p("current_node"), p("used_capacity"),
+                  p("demand_with_depot"), p("action_mask"), p("done"), _lib.ptr(reward), int(bool(check)),
+                  _lib.ptr(status), _lib.stream_ptr(dev))
+        _lib.raise_for_status(status)
+        return st, reward
+
+    def replay(self, td, actions, check: Optional[bool] = None):
+        check = self.check_solution if check is None else check
+        st, reward = self._replay_call(td, actions, check, True)
+        out = TensorDict({"locs": td["locs"], "demand": td["demand"], "vehicle_capacity": td["vehicle_capacity"], **st,
+                          "reward": torch.zeros_like(st["done"])}, batch_size=[actions.shape[0]])
+        return out, reward
+
+    def check_solution_validity(self, td, actions) -> None:
+        """sdvrp/env.py:142-164: "Cannot visit depot twice if any nonzero demand" / "All demand must be satisfied"."""
+        self._replay_call(td, actions, True, False)
+
+
+# =====================================================================================
 class OPEnv(RL4COEnvBase):
     """rl4co/envs/routing/op/env.py:25-238 (orienteering problem): collect prizes and be back at the depot
     within ``max_length``; the sibling routing environment on the same kernels' skeleton."""
@@ -768,7 +856,7 @@ class SLAPEnv(RL4COEnvBase):
         return out, reward
 
 
-ENV_REGISTRY = {"tsp": TSPEnv, "atsp": ATSPEnv, "cvrp": CVRPEnv, "slap": SLAPEnv, "op": OPEnv, "pctsp": PCTSPEnv,
+ENV_REGISTRY = {"tsp": TSPEnv, "atsp": ATSPEnv, "cvrp": CVRPEnv, "sdvrp": SDVRPEnv, "slap": SLAPEnv, "op": OPEnv, "pctsp": PCTSPEnv,
                 "spctsp": SPCTSPEnv}
 
 

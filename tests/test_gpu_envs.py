@@ -6,7 +6,7 @@ import torch
 
 import rl4co_slap_b200 as R
 from oracle import port
-from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
+from tests.helpers import (ATSP_CASES, CVRP_CASES, OP_CASES, SDVRP_CASES, PCTSP_CASES, SLAP_CASES, TSP_CASES, env_of, fixture, gen_td, oracle_reset, t)
 
 pytestmark = pytest.mark.gpu
 
@@ -36,7 +36,7 @@ def _same(got, want, what):
     assert np.array_equal(got, want), what
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES + SDVRP_CASES)
 def test_step_by_step_replay_bit_exact(case, dev):
     """reset + every _step through the env API: each state tensor equals the reference's
     (dtype, shape and value) after every step; then get_reward."""
@@ -56,7 +56,7 @@ def test_step_by_step_replay_bit_exact(case, dev):
     _close(reward, fx["replay.reward"], (case, "reward"))
 
 
-@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES)
+@pytest.mark.parametrize("case", TSP_CASES + CVRP_CASES + SLAP_CASES + OP_CASES + PCTSP_CASES + ATSP_CASES + SDVRP_CASES)
 def test_fused_replay_matches_fixture(case, dev):
     fx, name = fixture(case), env_of(case)
     env = R.get_env(name, device=dev)
@@ -234,4 +234,17 @@ def test_atsp_generator_and_replay_vs_oracle(size, B, dev):
     bad = acts.clone()
     bad[1, 3] = bad[1, 2]
     with pytest.raises(AssertionError, match="Invalid tour"):
+        env.check_solution_validity(td, bad)
+
+
+def test_sdvrp_invalid_tours_raise_reference_messages(dev):
+    fx = fixture("sdvrp20")
+    env = R.SDVRPEnv(device=dev)
+    td = env.reset(gen_td("sdvrp", fx, dev))
+    acts = t(fx["replay.actions"], dev)
+    env.check_solution_validity(td, acts)
+    with pytest.raises(AssertionError, match="All demand must be satisfied"):
+        env.check_solution_validity(td, acts[:, :5])
+    bad = torch.cat((torch.zeros_like(acts[:, :2]), acts), 1)
+    with pytest.raises(AssertionError, match="Cannot visit depot twice"):
         env.check_solution_validity(td, bad)
