@@ -208,6 +208,7 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
                             * start node s % num_loc + 1 - the reference's multinomial resampling of infeasible starts
                             * (utils/ops.py:166-176) is the caller's business */
 #define RL4CO_ENV_PCTSP 4  /* envs/routing/pctsp/env.py and spctsp/env.py (prize = the real prize); same limits as OP */
+#define RL4CO_ENV_SDVRP 5  /* envs/routing/sdvrp/env.py with SDVRPDynamicEmbedding; single start, register-file kernel only */
 
 #define RL4CO_MODE_GREEDY   0  /* utils/decoding.py:371-381,410-418 */
 #define RL4CO_MODE_SAMPLING 1  /* utils/decoding.py:383-397,475-483 (Philox instead of torch.multinomial) */
@@ -326,6 +327,10 @@ typedef struct rl4co_am_rollout_args {
      * (context.py:368-382); reward = saved penalties - (tour length + all penalties) (pctsp/env.py:150-174) */
     const float *penalty;
     const float *prize_required;
+    /* sdvrp (appended, ABI 2): demand / vehicle_capacity / wcap as for cvrp, plus the dynamic embedding
+     * (nn/env_embeddings/dynamic.py:61-79) as wdyn [3][E] = its Linear(1, 3E) weight split into the glimpse-key and
+     * glimpse-value columns and Wout^T times the logit-key column (project_out folded as for table 2) */
+    const float *wdyn;
 } rl4co_am_rollout_args;
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);

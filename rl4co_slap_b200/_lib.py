@@ -34,7 +34,7 @@ STATUS_MESSAGES = [
     (ST_DEPOT_TWICE, "Cannot visit depot twice if any nonzero demand"),   # sdvrp/env.py:157
     (ST_DEMAND_LEFT, "All demand must be satisfied"),                     # sdvrp/env.py:164
 ]
-ENV_IDS = {"tsp": 0, "cvrp": 1, "slap": 2, "op": 3, "pctsp": 4, "spctsp": 4}
+ENV_IDS = {"tsp": 0, "cvrp": 1, "slap": 2, "op": 3, "pctsp": 4, "spctsp": 4, "sdvrp": 5}
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
 
 _p = C.c_void_p
@@ -51,7 +51,7 @@ class AmRolloutArgs(C.Structure):
         ("seed", _u64), ("offset", _u64),
         ("actions", _p), ("logp", _p), ("logp_all", _p), ("ll", _p), ("reward", _p),
         ("steps", _p), ("assignment", _p), ("status", _p),
-        ("prize", _p), ("max_length", _p), ("penalty", _p), ("prize_required", _p),
+        ("prize", _p), ("max_length", _p), ("penalty", _p), ("prize_required", _p), ("wdyn", _p),
     ]
 
 

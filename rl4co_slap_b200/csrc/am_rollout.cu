@@ -506,7 +506,7 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     RL4CO_REQUIRE(args != nullptr, "am_rollout: null args");
     const rl4co_am_rollout_args &a = *args;
     if (a.B == 0) return 0;
-    RL4CO_REQUIRE(a.env >= RL4CO_ENV_TSP && a.env <= RL4CO_ENV_PCTSP, "am_rollout: unknown env %d", a.env);
+    RL4CO_REQUIRE(a.env >= RL4CO_ENV_TSP && a.env <= RL4CO_ENV_SDVRP, "am_rollout: unknown env %d", a.env);
     RL4CO_REQUIRE(a.mode >= RL4CO_MODE_GREEDY && a.mode <= RL4CO_MODE_EVALUATE, "am_rollout: unknown mode %d", a.mode);
     RL4CO_REQUIRE(a.B >= 0 && a.N >= 2 && a.T >= 1, "am_rollout: bad sizes B=%lld N=%d T=%d", (long long)a.B, a.N, a.T);
     RL4CO_REQUIRE(a.N <= kMaxNodes, "am_rollout: N=%d exceeds the %d node slots of this kernel", a.N, kMaxNodes);
@@ -525,6 +525,12 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         // multistart: the caller guarantees that the reference would not resample the start nodes (utils/ops.py:166-176)
         RL4CO_REQUIRE(!a.multistart || a.num_loc >= 1, "am_rollout: bad multistart setup");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: op runs on the register-file kernel only (N <= 128, no logp_all)");
+        return launch_rollout_rf(a, (cudaStream_t)stream);
+    }
+    if (a.env == RL4CO_ENV_SDVRP) {
+        RL4CO_REQUIRE(a.wcap && a.demand && a.vehicle_capacity && a.wdyn, "am_rollout: sdvrp needs wcap/demand/capacity/wdyn");
+        RL4CO_REQUIRE(!a.multistart, "am_rollout: sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not implemented");
+        RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: sdvrp runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
     if (a.env == RL4CO_ENV_PCTSP) {

@@ -51,15 +51,16 @@ constexpr int PLS = 144;              // row stride of the partial-logit matrix 
 struct Layout {
     int xs_rows;        // T: every step keeps its logits (log-probs are formed after the loop); 1: per-step sums
     size_t off_c, off_pl, off_xs, off_o, off_ring, off_mw, off_xa, off_act, off_ain, off_lp, off_locs,
-        off_dem, off_wc, off_noise, off_part, off_bar, total;
+        off_dem, off_wc, off_noise, off_part, off_bar, off_dyn, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
+constexpr size_t kDynBytes = 3 * 128 * 4 + 8 * 128 * 4;     // sdvrp: dynamic-embedding columns + one demand copy per warp
+__host__ __device__ inline Layout make_layout(int N, int T, bool has_c, bool has_dyn = false) {
     Layout L;
     // everything except the logits: does a [T][128] ring of them still fit next to it?
     const size_t fixed = (has_c ? (size_t)2 * N * E * 4 : 0) + (size_t)kWarps * PLS * 4 + E * 4 +
                          up16((size_t)T * kWarps * 4) + 5 * up16((size_t)T * 4) + up16((size_t)N * 8) +
-                         128 * 4 + 128 * 4 + 16 * 128 * 4 + 64 * 4 + 16;
+                         128 * 4 + 128 * 4 + 16 * 128 * 4 + 64 * 4 + 16 + (has_dyn ? kDynBytes : 0);
     L.xs_rows = (fixed + (size_t)T * 128 * 4 <= (size_t)227 * 1024) ? T : 1;
     size_t o = 0;
     L.off_c = o;    o += has_c ? (size_t)2 * N * E * 4 : 0;     // double-buffered context table
@@ -78,6 +79,7 @@ __host__ __device__ inline Layout make_layout(int N, int T, bool has_c) {
     L.off_noise = o; o += 16 * 128 * 4;                         // sampling: Gumbel noise of 16 steps [16][128]
     L.off_part = o; o += 64 * 4;
     L.off_bar = o;  o += 16;
+    L.off_dyn = o;  o += has_dyn ? kDynBytes : 0;               // sdvrp: [3][128] dynamic columns, [8][128] remaining demands
     L.total = o;
     return L;
 }
@@ -111,6 +113,16 @@ __device__ __forceinline__ unsigned redux_min_u32(unsigned v) {
 __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {  // SASS: FFMA2
     u64 d;
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+    u64 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b) {
+    u64 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
     return d;
 }
 __device__ __forceinline__ u64 pack2(float lo, float hi) {
@@ -152,10 +164,12 @@ template <int ENV, int M>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     constexpr bool HAS_C = ENV != RL4CO_ENV_SLAP;
-    constexpr bool CAPCOL = ENV == RL4CO_ENV_CVRP || ENV == RL4CO_ENV_OP || ENV == RL4CO_ENV_PCTSP;   // context = [h_cur ; scalar state]
+    constexpr bool VRP = ENV == RL4CO_ENV_CVRP || ENV == RL4CO_ENV_SDVRP;                // capacity state, depot at both ends
+    constexpr bool CAPCOL = VRP || ENV == RL4CO_ENV_OP || ENV == RL4CO_ENV_PCTSP;        // context = [h_cur ; scalar state]
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T;
-    const Layout L = make_layout(N, T, HAS_C);
+    constexpr bool DYN = ENV == RL4CO_ENV_SDVRP;    // per-step dynamic embedding of the remaining demands
+    const Layout L = make_layout(N, T, HAS_C, DYN);
     float *cbuf = reinterpret_cast<float *>(smem + L.off_c);
     float *spl = reinterpret_cast<float *>(smem + L.off_pl);
     float *sxs = reinterpret_cast<float *>(smem + L.off_xs);
@@ -172,6 +186,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
     float4 *s_noise = reinterpret_cast<float4 *>(smem + L.off_noise);
     float *spart = reinterpret_cast<float *>(smem + L.off_part);
     uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.off_bar); // one per context buffer
+    float *s_wdyn = reinterpret_cast<float *>(smem + L.off_dyn);    // sdvrp: w_k, w_v, Wout^T w_l of the dynamic embedding
+    float *s_rem = s_wdyn + 3 * 128;                                // sdvrp: remaining demand per node, one copy per warp
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int hh = lane >> 4, g = lane & 15;
@@ -191,6 +207,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         fence_barrier_init();
     }
     if (CAPCOL && tid < E) s_wc[tid] = a.wcap[tid] * kScoreScale;   // context.py:317-331 (cvrp), :385-397 (op)
+    if (DYN) for (int q = tid; q < 3 * E; q += kThreads) s_wdyn[q] = a.wdyn[q];
     __syncthreads();
     unsigned par0 = 0u, par1 = 0u;
     auto stage_context = [&](int64_t b, int buf) {  // thread 0: TMA the context table of instance b
@@ -260,7 +277,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             else if (ENV == RL4CO_ENV_PCTSP)    // pctsp: prize collected at node n (0 for the depot, pctsp/env.py:114-117)
                 s_dem[tid] = tid < N ? a.prize[b * (int64_t)N + tid] : 0.f;
             else
-                s_dem[tid] = (ENV == RL4CO_ENV_CVRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
+                s_dem[tid] = (VRP && tid >= 1 && tid < N) ? a.demand[b * (int64_t)(N - 1) + tid - 1] : 0.f;
         }
         {
             const float2 *lrow = reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2);
@@ -294,7 +311,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         unsigned alive = own, ralive = rown, vis = 0, rvis = 0;
         // cvrp: vehicle capacity / used capacity; op: the depot's length budget / tour length so far;
         // pctsp: required prize / collected prize
-        const float cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b]
+        const float cap = VRP ? a.vehicle_capacity[b]
                         : (ENV == RL4CO_ENV_OP) ? a.max_length[b * (int64_t)N]
                         : (ENV == RL4CO_ENV_PCTSP) ? a.prize_required[b] : 0.f;
         float used = 0.f;
@@ -356,6 +373,40 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             alive = f;
             ralive = rf;
         };
+        float *rem_w = s_rem + warp * 128;           // sdvrp: this warp's copy of demand_with_depot
+        auto sdvrp_masks = [&](int at) {            // sdvrp/env.py:132-140, both layouts; done = no demand left (:89)
+            const bool full = used >= cap;
+            unsigned f = 0, rf = 0;
+#pragma unroll
+            for (int j = 0; j < M; ++j)
+                if (!(rem_w[g + 16 * j] == 0.f) && !full) f |= 1u << j;
+            const float4 r4 = *reinterpret_cast<const float4 *>(rem_w + 4 * lane);
+            if (!(r4.x == 0.f) && !full) rf |= 1u;
+            if (!(r4.y == 0.f) && !full) rf |= 2u;
+            if (!(r4.z == 0.f) && !full) rf |= 4u;
+            if (!(r4.w == 0.f) && !full) rf |= 8u;
+            f &= own;
+            rf &= rown;
+            if (g == 0) f &= ~1u;
+            if (lane == 0) rf &= ~1u;
+            const bool depot = !(at == 0 && __any_sync(kFull, rf != 0));
+            if (g == 0 && depot) f |= 1u;
+            if (lane == 0 && depot) rf |= 1u;
+            alive = f;
+            ralive = rf;
+            return !__any_sync(kFull, r4.x > 0.f || r4.y > 0.f || r4.z > 0.f || r4.w > 0.f);
+        };
+        // rows of node n with the dynamic embedding of demand d added: X_n = X_stat_n + d w_x (dynamic.py:61-79,
+        // am/decoder.py:148-160); product and sum rounded separately like the reference's Linear(1, 3E) + add
+        auto dyn_row = [&](u64 (&dst)[4], const u64 (&stat)[4], int tab, float d) {
+            const ulonglong2 w0 = *reinterpret_cast<const ulonglong2 *>(s_wdyn + tab * 128 + dim0);
+            const ulonglong2 w1 = *(reinterpret_cast<const ulonglong2 *>(s_wdyn + tab * 128 + dim0) + 1);
+            const u64 d2 = pack2(d, d);
+            dst[0] = fadd2(stat[0], fmul2(d2, w0.x));
+            dst[1] = fadd2(stat[1], fmul2(d2, w0.y));
+            dst[2] = fadd2(stat[2], fmul2(d2, w1.x));
+            dst[3] = fadd2(stat[3], fmul2(d2, w1.y));
+        };
         int cur = 0, t = 0, status = 0;
         bool done = false, use_c = CAPCOL;
         const int t_end = (ENV == RL4CO_ENV_TSP) ? (N < T ? N : T) : (ENV == RL4CO_ENV_SLAP ? (a.P < T ? a.P : T) : T);   // cvrp, op: until done
@@ -384,6 +435,38 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 rvis |= rbit;
                 cvrp_masks(act);
                 done = __all_sync(kFull, rvis == rown);
+            } else if (ENV == RL4CO_ENV_SDVRP) {        // sdvrp/env.py:63-101
+                const float sel = rem_w[act];               // the depot slot is 0
+                const float delivered = fminf(sel, __fsub_rn(cap, used));
+                used = __fmul_rn(__fadd_rn(used, delivered), act != 0 ? 1.f : 0.f);
+                const float left = __fadd_rn(sel, -delivered);
+                __syncwarp();
+                if (lane == 0) rem_w[act] = left;
+                __syncwarp();
+                done = sdvrp_masks(act);
+                // the visited node's keys / values / logit keys follow its remaining demand: its owner threads rebuild
+                // their 8 dims from the static rows (tables 0-2, L2 resident) - one row per step, nothing else changes
+                if (!done && act != 0 && g == (act & 15)) {
+                    const float *srow = a.tables + (b * (int64_t)N + act) * E + dim0;
+                    u64 sk[4], sv[4], sl[4];
+                    ldg_256(srow, sk);
+                    ldg_256(srow + (size_t)Mrows * E, sv);
+                    ldg_256(srow + (size_t)2 * Mrows * E, sl);
+                    dyn_row(sk, sk, 0, left);
+                    dyn_row(sv, sv, 1, left);
+                    dyn_row(sl, sl, 2, left);
+                    const int row = act >> 4;
+#pragma unroll
+                    for (int j = 0; j < M; ++j) {       // selects, not indexing: the tables must stay in registers
+                        const bool hit = j == row;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            K2[j][i] = hit ? sk[i] : K2[j][i];
+                            V2[j][i] = hit ? sv[i] : V2[j][i];
+                            L2[j][i] = hit ? sl[i] : L2[j][i];
+                        }
+                    }
+                }
             } else if (ENV == RL4CO_ENV_OP) {           // op/env.py:74-108
                 const float2 pp = s_locs[cur], pn = s_locs[act];
                 used = __fadd_rn(used, leg_fma(pp.x, pp.y, pn.x, pn.y));
@@ -454,6 +537,18 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
             if (lane == 0) ralive &= ~1u;
         }
         if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
+        if (ENV == RL4CO_ENV_SDVRP) {               // remaining demands = demands, every row gets its dynamic term
+            *reinterpret_cast<float4 *>(rem_w + 4 * lane) = *reinterpret_cast<const float4 *>(s_dem + 4 * lane);
+            __syncwarp();
+            sdvrp_masks(0);
+#pragma unroll
+            for (int j = 0; j < M; ++j) {
+                const float d = rem_w[g + 16 * j];
+                dyn_row(K2[j], K2[j], 0, d);
+                dyn_row(V2[j], V2[j], 1, d);
+                dyn_row(L2[j], L2[j], 2, d);
+            }
+        }
         if (ENV == RL4CO_ENV_OP) op_masks(0);
         if (ENV == RL4CO_ENV_PCTSP) pctsp_masks();
         cur = 0; t = 0; status = 0; done = false; use_c = CAPCOL;
@@ -727,7 +822,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 float2 p = s_locs[s_act[q]], w = s_locs[s_act[q + 1 == nact ? 0 : q + 1]];
                 part += leg(p.x, p.y, w.x, w.y);
             }
-        } else if (ENV == RL4CO_ENV_CVRP) {      // cvrp/env.py:151-160 (depot at both ends)
+        } else if (VRP) {                        // cvrp/env.py:151-160 (depot at both ends; sdvrp inherits it)
             for (int q = tid; q <= nact; q += kThreads) {
                 float2 p = q == 0 ? s_locs[0] : s_locs[s_act[q - 1]];
                 float2 w = q == nact ? s_locs[0] : s_locs[s_act[q]];
@@ -787,7 +882,7 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    const Layout L = make_layout(a.N, a.T, ENV != RL4CO_ENV_SLAP);
+    const Layout L = make_layout(a.N, a.T, ENV != RL4CO_ENV_SLAP, ENV == RL4CO_ENV_SDVRP);
     if (L.total > (size_t)227 * 1024) {
         set_error("am_rollout(rf): N=%d T=%d needs %zu B shared memory", a.N, a.T, L.total);
         return 1;
@@ -833,8 +928,8 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
-    if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
-    return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP).total <= (size_t)227 * 1024;
+    if (a.multistart && (a.env == RL4CO_ENV_SLAP || a.env == RL4CO_ENV_SDVRP)) return false;
+    return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP, a.env == RL4CO_ENV_SDVRP).total <= (size_t)227 * 1024;
 }
 
 int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream) {
@@ -843,6 +938,7 @@ int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         case RL4CO_ENV_CVRP: return rf::launch_env<RL4CO_ENV_CVRP>(a, stream);
         case RL4CO_ENV_OP: return rf::launch_env<RL4CO_ENV_OP>(a, stream);
         case RL4CO_ENV_PCTSP: return rf::launch_env<RL4CO_ENV_PCTSP>(a, stream);
+        case RL4CO_ENV_SDVRP: return rf::launch_env<RL4CO_ENV_SDVRP>(a, stream);
         default: return rf::launch_env<RL4CO_ENV_SLAP>(a, stream);
     }
 }

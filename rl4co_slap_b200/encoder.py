@@ -81,7 +81,7 @@ class SLAPInitEmbedding(nn.Module):
         return self.init_embed(torch.cat((locs, d0[..., None]), -1))
 
 
-INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding,
+INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "sdvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding,
                    "op": OPInitEmbedding, "pctsp": PCTSPInitEmbedding, "spctsp": PCTSPInitEmbedding}
 
 

@@ -41,6 +41,14 @@ class _ContextEmbedding(nn.Module):
             self.W_placeholder = nn.Parameter(torch.Tensor(2 * embed_dim).uniform_(-1, 1))
 
 
+class _DynamicEmbedding(nn.Module):
+    """Parameter holder of SDVRPDynamicEmbedding (dynamic.py:61-79)."""
+
+    def __init__(self, embed_dim: int):
+        super().__init__()
+        self.projection = nn.Linear(1, 3 * embed_dim, bias=False)
+
+
 class _Pointer(nn.Module):
     def __init__(self, embed_dim: int):
         super().__init__()
@@ -66,6 +74,8 @@ class AttentionModelDecoder(nn.Module):
         self.project_node_embeddings = nn.Linear(embed_dim, 3 * embed_dim, bias=False)
         self.project_fixed_context = nn.Linear(embed_dim, embed_dim, bias=False)
         self.use_graph_context = use_graph_context
+        if env_name == "sdvrp":     # SDVRPDynamicEmbedding (nn/env_embeddings/dynamic.py:61-79): Linear(1 -> 3E), no bias
+            self.dynamic_embedding = _DynamicEmbedding(embed_dim)
 
     def folded_weights(self):
         """Cached on the parameters' version counters (an optimiser step invalidates it)."""
@@ -73,6 +83,8 @@ class AttentionModelDecoder(nn.Module):
               self.context_embedding.project_context.weight, self.project_fixed_context.weight]
         if hasattr(self.context_embedding, "W_placeholder"):
             ps.append(self.context_embedding.W_placeholder)
+        if hasattr(self, "dynamic_embedding"):
+            ps.append(self.dynamic_embedding.projection.weight)
         def version(p):     # inference tensors (module built under torch.inference_mode) carry no counter
             try:
                 return p._version
@@ -82,6 +94,19 @@ class AttentionModelDecoder(nn.Module):
         if getattr(self, "_fold_key", None) != key:
             self._fold = self._fold_weights() + (self.project_fixed_context.weight.detach().float().contiguous(),)
             self._fold_key = key
+            self._wdyn = None
+            if hasattr(self, "dynamic_embedding"):
+                # [3][E]: glimpse-key column, glimpse-value column, Wout^T x logit-key column (project_out folded as in
+                # table 2); fp32 matmul without TF32
+                E = self.embed_dim
+                w = self.dynamic_embedding.projection.weight.detach().float()[:, 0]
+                prev = torch.backends.cuda.matmul.allow_tf32
+                torch.backends.cuda.matmul.allow_tf32 = False
+                try:
+                    wl = self.pointer.project_out.weight.detach().float().t() @ w[2 * E:]
+                finally:
+                    torch.backends.cuda.matmul.allow_tf32 = prev
+                self._wdyn = torch.stack((w[:E], w[E:2 * E], wl)).contiguous()
             self._image = None
         return self._fold
 
@@ -116,7 +141,7 @@ class AttentionModelDecoder(nn.Module):
             if self.env_name == "tsp":
                 parts += [Wc[:, E:], Wc[:, :E]]
                 q0 = (Wc @ self.context_embedding.W_placeholder.float()).contiguous()
-            elif self.env_name in ("cvrp", "op", "pctsp", "spctsp"):    # [h_cur ; remaining capacity / length / prize]
+            elif self.env_name in ("cvrp", "sdvrp", "op", "pctsp", "spctsp"):    # [h_cur ; remaining capacity / length / prize]
                 parts += [Wc[:, :E]]
                 wcap = Wc[:, E].contiguous()
         finally:
@@ -223,6 +248,14 @@ class AttentionModelPolicy(nn.Module):
         elif name == "slap":
             P, O, K = td["freq"].shape[-2], td["picklist"].shape[1], td["picklist"].shape[2]
             T = P
+        elif name == "sdvrp":
+            # a customer visit either completes the customer or fills the vehicle, every fill costs one depot visit
+            T = 3 * N
+            if multistart:
+                raise NotImplementedError("sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not implemented")
+            if store_all_logp:
+                raise NotImplementedError("sdvrp: per-node log-probs (return_entropy / store_all_logp) are not "
+                                          "produced by the register-file rollout kernel")
         elif name in ("op", "pctsp", "spctsp"):
             # op at worst: depot first (not done at step 0), ..., every customer, depot; pctsp: every customer, depot
             T = N + 1 if name == "op" else N
@@ -289,9 +322,11 @@ class AttentionModelPolicy(nn.Module):
             a.tables, a.gctx = _lib.ptr(tables), _lib.ptr(gctx)
             a.q0, a.wcap = _lib.ptr(q0), _lib.ptr(wcap)
             a.locs = _lib.ptr(locs[c0:c1].contiguous(), torch.float32)
-            if name == "cvrp":
+            if name in ("cvrp", "sdvrp"):
                 a.demand = _lib.ptr(td["demand"][c0:c1].contiguous(), torch.float32)
                 a.vehicle_capacity = _lib.ptr(td["vehicle_capacity"][c0:c1].contiguous(), torch.float32)
+            if name == "sdvrp":
+                a.wdyn = _lib.ptr(self.decoder._wdyn)
             if name == "op":
                 a.prize = _lib.ptr(td["prize"][c0:c1].contiguous(), torch.float32)
                 a.max_length = _lib.ptr(td["max_length"][c0:c1].contiguous(), torch.float32)
@@ -322,7 +357,7 @@ class AttentionModelPolicy(nn.Module):
         self.last_launches = launches
 
         # ---- the reference's output construction (base.py:253-276) --------------------
-        if name in ("cvrp", "op", "pctsp", "spctsp") and actions is None:
+        if name in ("cvrp", "sdvrp", "op", "pctsp", "spctsp") and actions is None:
             # the reference loops until the slowest episode is done (base.py:230): T = max steps
             Tmax = int(out_steps.max().item())
             out_actions, out_logp = out_actions[:, :Tmax], out_logp[:, :Tmax]
