@@ -59,7 +59,7 @@ with torch.inference_mode():
         s = timed(lambda: pol(td, env, decode_type="greedy", hidden=h), warm=2, reps=3)
         out[f"C5_slap_B{Bs}"] = {"batch": Bs, "seconds": s, "rollouts_per_s": Bs / s, "env_steps_per_s": Bs * 20 / s}
     # ---- sibling routing envs on the register-file kernel: 100 customers, greedy and sampling
-    for name in ("op", "pctsp"):
+    for name in ("op", "pctsp", "sdvrp"):
         torch.manual_seed(1234)
         Bs = 16384
         env = R.get_env(name, generator_params=dict(num_loc=100), device=dev, check_solution=False)
