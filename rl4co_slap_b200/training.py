@@ -44,6 +44,9 @@ def replay_masks(env_name: str, td, actions: torch.Tensor, S: int = 1):
         mask = ~_exclusive_visited(actions, N)
         mask[:, :, 0] = False
         return mask, torch.ones(R, T, dtype=torch.bool, device=dev), None
+    if env_name not in ("cvrp", "op", "pctsp", "spctsp"):
+        raise NotImplementedError(f"{env_name}: the differentiable teacher-forced pass covers tsp / cvrp / slap / op / pctsp / "
+                                  "spctsp (sdvrp's keys and values change every step with the dynamic embedding)")
     if env_name == "op":
         return _replay_masks_op(td, actions, S)
     if env_name in ("pctsp", "spctsp"):
