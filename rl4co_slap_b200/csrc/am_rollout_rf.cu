@@ -142,6 +142,9 @@ __device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi) {
 __device__ __forceinline__ void ldg_256(const float *p, u64 (&v)[4]) {
     asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
 }
+__device__ __forceinline__ void prefetch_l1(const void *p) {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p) : "memory");
+}
 __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
@@ -436,6 +439,12 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 cvrp_masks(act);
                 done = __all_sync(kFull, rvis == rown);
             } else if (ENV == RL4CO_ENV_SDVRP) {        // sdvrp/env.py:63-101
+                const float *srow = a.tables + (b * (int64_t)N + act) * E + dim0;
+                if (act != 0 && g == (act & 15)) {          // the rows rebuilt below: start them towards L1 now (no registers)
+                    prefetch_l1(srow);
+                    prefetch_l1(srow + (size_t)Mrows * E);
+                    prefetch_l1(srow + (size_t)2 * Mrows * E);
+                }
                 const float sel = rem_w[act];               // the depot slot is 0
                 const float delivered = fminf(sel, __fsub_rn(cap, used));
                 used = __fmul_rn(__fadd_rn(used, delivered), act != 0 ? 1.f : 0.f);
@@ -447,7 +456,6 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 // the visited node's keys / values / logit keys follow its remaining demand: its owner threads rebuild
                 // their 8 dims from the static rows (tables 0-2, L2 resident) - one row per step, nothing else changes
                 if (!done && act != 0 && g == (act & 15)) {
-                    const float *srow = a.tables + (b * (int64_t)N + act) * E + dim0;
                     u64 sk[4], sv[4], sl[4];
                     ldg_256(srow, sk);
                     ldg_256(srow + (size_t)Mrows * E, sv);
