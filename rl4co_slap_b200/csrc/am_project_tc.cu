@@ -65,8 +65,12 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const f
     }
 }
 
+// RES: the epilogue adds skip rows (`residual`).  A compile-time switch: the 32 registers of the prefetched skip rows
+// push the drain over the 128-register cap, and its spilled loop state reloads behind the row stores.
+template <bool RES>
 __global__ void __launch_bounds__(kThreads, 1)
-am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb, const float *__restrict__ h,
+am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_groups, int n_chunks, int tb,
+                     const float *__restrict__ h,
                      const float *__restrict__ image, float *__restrict__ tables, int64_t table_stride, int64_t ldo,
                      const float *__restrict__ bias, int relu, int64_t ldx, int accumulate,
                      const float *__restrict__ residual, const float *__restrict__ scale,
@@ -81,16 +85,17 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
     uint64_t *acc_full = a_empty + A_STAGES, *acc_empty = acc_full + TB;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + TB);
     float *s_bias = reinterpret_cast<float *>(sO + 2 * OUT_BYTES + 256);   // this table's 128 bias values (zeros if none)
-    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 <= 256, "barrier block");
+    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 + 4 * 4 <= 256, "barrier block (+ tmem slot + 4 tile-count slots)");
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int table = blockIdx.x % n_tables, group = blockIdx.x / n_tables;
-    const int64_t n_tiles = (M + BM - 1) / BM;
+    // n_tiles = ceil(M / BM) and n_blocks = ceil(n_tiles / tb) come in as kernel parameters: computed here they are
+    // loop-invariant registers the 128-register cap spills, and a local-memory reload returns BEHIND the producer's
+    // prefetch loads of the next tile (10.7 % of the kernel's stall samples sat on that one reload, ncu source page)
     // Every role walks the same order: block of `tb` consecutive tiles -> K chunk -> tile -> k-block.
     // A block's accumulators stay in TMEM across the K chunks; with one chunk (K = 128) the weight
     // image is loaded once and the accumulators are simply a tb-deep ring.
-    const int64_t n_blocks = (n_tiles + tb - 1) / tb;
-    auto tiles_in = [&](int64_t blk) { const int64_t left = n_tiles - blk * tb; return (int)(left < tb ? left : tb); };
+    auto tiles_in = [&](int blk) { const int left = n_tiles - blk * tb; return left < tb ? left : tb; };
 
     if (tid == 0) {
         mbar_init(w_full, 1);
@@ -125,7 +130,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
         static_assert(A_STAGES == 2 && NKB % A_STAGES == 0, "stage of k-block kb is kb & 1");
         unsigned a_phase = 0, w_phase = 0, we_phase = 0;
         int bi = 0;
-        for (int64_t blk = group; blk < n_blocks; blk += n_groups, ++bi) {
+        for (int blk = group; blk < n_blocks; blk += n_groups, ++bi) {
             const int nt = tiles_in(blk);
             for (int kc = 0; kc < n_chunks; ++kc) {
                 if (n_chunks > 1 || bi == 0) {                  // (re)load the weight image of this K chunk
@@ -185,23 +190,23 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
         int stage = 0;
         unsigned phase = 0;
         float4 v[NKB][RPT];                                     // one tile of h: 16 LDG.128 per thread in flight
-        auto load_kb = [&](int64_t blk, int kc, int t, int kb) {
+        auto load_kb = [&](int blk, int kc, int t, int kb) {
 #pragma unroll
             for (int i = 0; i < RPT; ++i) {
-                const int64_t m = (blk * tb + t) * BM + r0 + 32 * i;
+                const int64_t m = (int64_t)(blk * tb + t) * BM + r0 + 32 * i;
                 v[kb][i] = (blk < n_blocks && m < M)
                                ? __ldg(reinterpret_cast<const float4 *>(h + m * ldx + kc * E + kb * KB) + c)
                                : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
-        auto advance = [&](int64_t &blk, int &kc, int &t) {     // next (block, chunk, tile) of the walk
+        auto advance = [&](int &blk, int &kc, int &t) {         // next (block, chunk, tile) of the walk
             if (blk >= n_blocks) return;
             if (++t >= tiles_in(blk)) {
                 t = 0;
                 if (++kc >= n_chunks) { kc = 0; blk += n_groups; }
             }
         };
-        int64_t blk = group, nblk = group;
+        int blk = group, nblk = group;
         int kc = 0, t = 0, nkc = 0, ntl = 0;
         advance(nblk, nkc, ntl);
 #pragma unroll
@@ -270,25 +275,37 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
 #pragma unroll
             for (int l = 0; l < 4; ++l) asm volatile("prefetch.global.L2 [%0];" ::"l"(row_ptr + 128 * l));
         };
+        // the tile count of the block lives in shared memory (one slot per epilogue warp), not in a register the
+        // drain's 64 live values would push to local memory: its reload queued behind the row stores (4.8 % of samples)
+        const uint32_t s_nt = smem_u32(tmem_slot + 1 + q);
+        auto lds_nt = [&]() {
+            int v;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(s_nt) : "memory");
+            return v;
+        };
         int bi = 0;
-        for (int64_t blk = group; blk < n_blocks; blk += n_groups, ++bi)
-        for (int t = 0, nt = tiles_in(blk); t < nt; ++t) {
-            const int64_t tile = blk * tb + t;
-            if (residual) {                                     // next tile's skip rows -> L2, a tile time ahead of their loads
-                const int64_t nxt = (t + 1 < nt) ? tile + 1 : (blk + n_groups) * tb;
+        for (int blk = group; blk < n_blocks; blk += n_groups, ++bi) {
+        __syncwarp();
+        if (lane == 0) asm volatile("st.shared.b32 [%0], %1;" ::"r"(s_nt), "r"(tiles_in(blk)) : "memory");
+        __syncwarp();
+        for (int t = 0; t < lds_nt(); ++t) {
+            const int nt = lds_nt();
+            const int64_t tile = (int64_t)blk * tb + t;
+            if (RES && residual) {                              // next tile's skip rows -> L2, a tile time ahead of their loads
+                const int64_t nxt = (t + 1 < nt) ? tile + 1 : (int64_t)(blk + n_groups) * tb;
                 prefetch_rows(bi == 0 && t == 0 ? tile : -1);   // (and the first tile's own)
                 prefetch_rows(nxt);
             }
             const int64_t m0 = tile * BM + rr0;                 // this thread's rows: m0 + 16 j
             const int rows_ok = (int)((M - m0 + 15) / 16 < 8 ? (M - m0 + 15) / 16 : 8);    // 8 on all but a ragged tile
             float *o_ptr = out + m0 * ldo + ch * 4;
-            const float *r_ptr = residual ? residual + m0 * ldo + table * BN + ch * 4 : nullptr;
+            const float *r_ptr = (RES && residual) ? residual + m0 * ldo + table * BN + ch * 4 : nullptr;
             mbar_wait_bounded(&acc_full[t], (unsigned)(bi & 1));
             tc_fence_after();
 #pragma unroll
             for (int cb = 0; cb < BN / 32; ++cb) {
                 float4 rs[8];
-                if (r_ptr) {                                    // skip rows of this column block: in flight under the drain
+                if (RES && r_ptr) {                             // skip rows of this column block: in flight under the drain
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         rs[j] = j < rows_ok ? __ldg(reinterpret_cast<const float4 *>(r_ptr + j * row_step + cb * 32))
@@ -348,7 +365,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                     const float4 sh = *reinterpret_cast<const float4 *>(s_bias + 2 * BN + cb * 32 + ch * 4);   // batch norm
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        if (r_ptr) { y[j].x += rs[j].x; y[j].y += rs[j].y; y[j].z += rs[j].z; y[j].w += rs[j].w; }
+                        if (RES && r_ptr) { y[j].x += rs[j].x; y[j].y += rs[j].y; y[j].z += rs[j].z; y[j].w += rs[j].w; }
                         y[j].x = fmaf(y[j].x, sc.x, sh.x); y[j].y = fmaf(y[j].y, sc.y, sh.y);
                         y[j].z = fmaf(y[j].z, sc.z, sh.z); y[j].w = fmaf(y[j].w, sc.w, sh.w);
                     }
@@ -366,6 +383,7 @@ am_project_tc_kernel(int64_t M, int n_tables, int n_groups, int n_chunks, int tb
                 }
             }
         }
+        }   // blocks of this CTA
     }
 
     tc_fence_before();
@@ -395,13 +413,19 @@ int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, con
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    cudaError_t e = cudaFuncSetAttribute(tc::am_project_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(tc::am_project_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          tc::SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(tc::am_project_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
     if (e != cudaSuccess) {
         set_error("am_project(tc): cannot reserve %d B of shared memory: %s", tc::SMEM_BYTES, cudaGetErrorString(e));
         return 2;
     }
     const int64_t n_tiles = (M + tc::BM - 1) / tc::BM;
+    if (n_tiles >= (1ll << 30)) {
+        set_error("am_project(tc): M=%lld rows exceed the 32-bit tile index", (long long)M);
+        return 1;
+    }
     int64_t groups = sm_count / n_tables;                       // persistent: one CTA per SM
     if (groups < 1) groups = 1;
     if (groups > n_tiles) groups = n_tiles;
@@ -409,9 +433,10 @@ int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, con
     int64_t tb = n_tiles / groups;
     if (tb > tc::TB) tb = tc::TB;
     if (tb < 1) tb = 1;
-    tc::am_project_tc_kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
-        M, n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride, ldo, bias, relu, ldx, accumulate,
-        residual, scale, shift);
+    auto kernel = residual ? tc::am_project_tc_kernel<true> : tc::am_project_tc_kernel<false>;
+    kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
+        M, (int)n_tiles, (int)((n_tiles + tb - 1) / tb), n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride,
+        ldo, bias, relu, ldx, accumulate, residual, scale, shift);
     RL4CO_CHECK_LAUNCH("am_project(tc)");
     return 0;
 }
