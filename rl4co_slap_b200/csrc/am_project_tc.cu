@@ -156,6 +156,14 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                     for (int kb = 0; kb < NKB; ++kb) {
                         const int stage = kb & 1;
                         mbar_wait_bounded(&a_full[stage], a_phase);
+#ifndef TC_PRODUCER_FENCE
+                        // generic-proxy writes of the producers (observed through the mbarrier's release / acquire) ->
+                        // async proxy of the MMAs issued below.  The proxy fence sits HERE, on the consumer side of the
+                        // causality chain, because in a producer warp ptxas makes FENCE.VIEW.ASYNC wait for every
+                        // outstanding scoreboard - i.e. for the prefetch loads of the next tile, a full HBM latency per
+                        // k-block (20 % of the kernel's stall samples on the four fences, ncu source page)
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
                         tc_fence_after();
                         const uint32_t a_hi = dA + (uint32_t)((stage * A_STAGE_BYTES) >> 4), a_lo = a_hi + (KB_BYTES >> 4);
                         const uint32_t b_hi = dW + (uint32_t)((kb * KB_BYTES) >> 4), b_lo = b_hi + ((NKB * KB_BYTES) >> 4);
@@ -238,7 +246,9 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                     *reinterpret_cast<uint4 *>(hi_img + swz(r, c)) = hi;
                     *reinterpret_cast<uint4 *>(lo_img + swz(r, c)) = lo;
                 }
+#ifdef TC_PRODUCER_FENCE
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
+#endif
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&a_full[stage]);
                 // refill the same registers for the next tile AFTER the fence: the fence's MEMBAR waits for every
