@@ -83,18 +83,42 @@ def paired_ttest_finalize(partials: torch.Tensor, group=None):
 
 
 class SharedBaseline:
-    """baselines.py:57-61: mean over the starts of each instance + REINFORCE loss partials.
-    ``eval(td, reward, ll)`` takes reward / ll in the policy's flat start-major layout
-    [S*B] (or [B,S] like the reference after unbatchify) and returns
-    (baseline [B,1], loss_partial float64[2] = [sum adv*ll, count])."""
+    """baselines.py:57-61: the mean over the starts of each instance.
 
-    def __init__(self, num_starts: Optional[int] = None):
+    ``eval(td, reward, env=None, on_dim=1) -> (baseline, 0)`` is the reference's surface: ``reward`` is [B,S]
+    (after unbatchify, as POMO passes it) and the result is ``reward.mean(on_dim, keepdims=True)``; a flat start-major
+    [S*B] reward (what this repo's policy returns) is accepted when ``num_starts`` was given to the constructor and
+    yields a flat [S*B] baseline.  ``eval_fused`` is the one-launch variant that also produces the advantage,
+    the REINFORCE loss partials and the max over starts (rl4co_shared_baseline)."""
+
+    def __init__(self, num_starts: Optional[int] = None, **kw):
         self.num_starts = num_starts
+        self.last = None
 
-    def eval(self, td, reward: torch.Tensor, ll: Optional[torch.Tensor] = None, env=None,
-             num_starts: Optional[int] = None):
+    def wrap_dataset(self, dataset, *args, **kw):
+        return dataset
+
+    def setup(self, *args, **kw):
+        pass
+
+    def epoch_callback(self, *args, **kw):
+        pass
+
+    def eval(self, td, reward: torch.Tensor, env=None, on_dim: int = 1):
+        if reward.dim() >= 2:
+            return reward.mean(dim=on_dim, keepdims=True), 0
+        if not self.num_starts:
+            raise ValueError("SharedBaseline.eval: a flat [S*B] reward needs SharedBaseline(num_starts=S); "
+                             "pass reward as [B,S] otherwise (baselines.py:60-61)")
+        baseline, _ = self.eval_fused(reward, None, int(self.num_starts))
+        S = int(self.num_starts)
+        return baseline.view(1, -1).expand(S, -1).reshape(-1), 0
+
+    def eval_fused(self, reward: torch.Tensor, ll: Optional[torch.Tensor] = None, num_starts: Optional[int] = None):
+        """reward / ll flat start-major [S*B] or [B,S] -> (baseline [B,1], loss_partial float64[2] = [sum adv*ll, count]);
+        advantage / max_reward / best_start stay in ``self.last``."""
         if not reward.is_cuda:
-            raise RuntimeError("SharedBaseline.eval needs CUDA tensors (no CPU fallback)")
+            raise RuntimeError("SharedBaseline.eval_fused needs CUDA tensors (no CPU fallback)")
         dev = reward.device
         if reward.dim() == 2:  # [B,S] -> start-major flat
             B, S = reward.shape
@@ -118,6 +142,9 @@ class SharedBaseline:
 
 class NoBaseline:
     """baselines.py:49-53."""
+
+    def __init__(self, *args, **kw):
+        pass
 
     def wrap_dataset(self, dataset, *args, **kw):
         return dataset
@@ -245,12 +272,22 @@ class RolloutBaseline:
                 updated = True
         return candidate_mean, t, p_val, updated
 
-    def rollout(self, policy, env, batch_size: int = 65536, device="cuda", dataset=None) -> torch.Tensor:
-        """baselines.py:226-243: rewards [D_local] of greedy rollouts, in dataset order, on the device."""
+    def _world(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    def _rank(self) -> int:
+        return dist.get_rank(self.group) if dist.is_available() and dist.is_initialized() else 0
+
+    def rollout(self, policy, env, batch_size: int = 65536, device="cuda", dataset=None, shard: bool = True) -> torch.Tensor:
+        """baselines.py:226-243: rewards of greedy rollouts, in dataset order, on the device.  With a process group
+        every rank holds the SAME dataset (same seed) and rolls out only its contiguous shard -> [D_local]."""
         from .data import TensorDictDataset
         dataset = self.dataset if dataset is None else dataset
         if not isinstance(dataset, TensorDictDataset):
             dataset = TensorDictDataset(dataset)
+        if shard and self._world() > 1:      # this rank's contiguous slice; the statistics are all-reduced
+            lo, hi = shard_bounds(len(dataset), self._rank(), self._world())
+            dataset = TensorDictDataset(dataset.data[lo:hi])
         policy.eval()
         policy = policy.to(device)
         out = []
@@ -265,7 +302,8 @@ class RolloutBaseline:
         from .data import TensorDictDataset
         if not isinstance(dataset, TensorDictDataset):
             dataset = TensorDictDataset(dataset)
-        rewards = self.rollout(self.policy, env, batch_size, device, dataset=dataset).detach()
+        # the wrapped (training) dataset is this rank's own data: every row needs its baseline value here
+        rewards = self.rollout(self.policy, env, batch_size, device, dataset=dataset, shard=False).detach()
         return dataset.add_key("extra", rewards)
 
 

@@ -76,7 +76,9 @@ __device__ __forceinline__ void gumbel4(uint64_t seed, uint64_t offset, uint64_t
     const uint32_t w[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float u = ((float)(w[k] >> 8) + 0.5f) * (1.0f / 16777216.0f);     // (0,1)
+        // 23 random bits: (k + 0.5) * 2^-23 is exact in fp32 for every k < 2^23 and strictly inside (0,1)
+        // (with 24 bits the +0.5 is lost above 2^23 and k = 2^24 - 1 rounds to u = 1 -> G = +inf)
+        const float u = ((float)(w[k] >> 9) + 0.5f) * (1.0f / 8388608.0f);
         // -ln(-ln u) = -ln2 * log2(-ln2 * log2 u)
         G[k] = -0.6931471805599453f * __log2f(-0.6931471805599453f * __log2f(u));
     }

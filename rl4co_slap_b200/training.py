@@ -228,20 +228,28 @@ def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: 
     reference's ``eval(td, reward, env) -> (value, loss)`` (rl4co_slap_b200.baselines)."""
     decode_type = decode_type or policy.train_decode_type
     multistart = "multistart" in decode_type
+    # ONE encoder pass over the whole batch with autograd (train-mode batch norm sees the full batch once and updates
+    # its running statistics once); the rollout kernels sample from exactly this h, so the teacher-forced ll below is
+    # the log-likelihood of the policy that drew the actions
+    h, _ = policy.encoder(td)
     with torch.no_grad():
         out = policy(td, env, phase="train", decode_type=decode_type, num_starts=num_starts,
-                     return_actions=True)
+                     return_actions=True, hidden=h.detach())
     actions, reward = out["actions"], out["reward"]
     B = td["locs"].shape[0]
     S = actions.shape[0] // B if multistart else 0
-    h, _ = policy.encoder(td)
     ll = teacher_forced_log_likelihood(policy, td, env.name, h.float(), actions, num_starts=S)
     if baseline is None:
         bl = torch.zeros_like(reward)
     elif isinstance(baseline, str) and baseline == "shared":
         bl = reward.reshape(max(S, 1), B).mean(0, keepdim=True).expand(max(S, 1), B).reshape(-1)
-    elif hasattr(baseline, "eval"):     # a baselines.py object (No / Exponential / Mean / Warmup / Rollout)
-        bl, _ = baseline.eval(td, reward, env)
+    elif hasattr(baseline, "eval"):     # a baselines.py object (No / Shared / Exponential / Mean / Warmup / Rollout)
+        if S > 1:   # POMO hands the baseline reward as [B,S] (pomo/model.py:99-107); back to the flat start-major order
+            r2 = reward.view(S, B).t()
+            bl, _ = baseline.eval(td, r2, env)
+            bl = (torch.zeros_like(r2) + bl).t().reshape(-1)
+        else:
+            bl, _ = baseline.eval(td, reward, env)
     else:
         bl = baseline
     advantage = reward - bl

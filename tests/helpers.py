@@ -99,3 +99,53 @@ def oracle_reset(env_name: str, fx):
                                 prize_required=float(fx["gen.prize_required"]), stochastic=env_name == "spctsp")
     extra = {k: t(fx[f"gen.{k}"]) for k in ("freq", "picklist", "depot_loc_dist")}
     return port.slap_reset(t(fx["gen.locs"]), t(fx["gen.assignment"]), fx["gen.freq"].shape[-2], extra)
+
+
+# ---- tolerances of the parity tests ------------------------------------------------------------------------------
+# Summed log-likelihoods and rewards: 1e-5 relative (BASELINE.json north_star).  A PER-STEP log-prob is
+# logit_a - logsumexp(logits) with |logit| <= tanh_clipping = 10: the fp32 resolution of the logits themselves
+# (ulp(10) = 9.5e-7, a sum over <= 128 exponentials, the 3xTF32 table projection's ~2e-5 absolute error on entries of
+# size ~18 feeding a 128-term dot product) is an ABSOLUTE floor of ~1e-5 whatever the log-prob's size (a log-prob of
+# -1e-3 cannot be held to 1e-8), so per-step values are held to 1e-5 relative + 2e-5 absolute.
+LOGP_RTOL, LOGP_ATOL = 1e-5, 2e-5
+NEAR_TIE_EPS = 1e-4     # two candidates whose fp32 log-probs differ by less than 10 ulp of the clip bound are a tie
+
+
+def assert_logp_close(got, want):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    err, bound = np.abs(got - want), LOGP_RTOL * np.abs(want) + LOGP_ATOL
+    assert (err <= bound).all(), f"per-step log-prob off by {err.max():.3e} (worst excess {(err - bound).max():.3e})"
+
+
+def assert_divergences_are_near_ties(env_name, state, h, W, a, b, eps=NEAR_TIE_EPS, **rollout_kw):
+    """``a`` and ``b`` [B,T] are two greedy tour sets for the same instances.  For every instance where they differ,
+    take the FIRST differing step t (the prefixes agree, so both kernels saw the same state there), evaluate the
+    oracle's log-probs at that step on the common prefix and require that the two chosen nodes are tied to within
+    ``eps`` AND are the oracle's two best candidates (i.e. the flip is an fp32 rounding artefact, not a bug).
+    Returns (number of diverging instances, largest gap seen)."""
+    from oracle import port
+    a, b = torch.as_tensor(a).cpu(), torch.as_tensor(b).cpu()
+    T = max(a.shape[1], b.shape[1])
+    a = torch.nn.functional.pad(a, (0, T - a.shape[1]))
+    b = torch.nn.functional.pad(b, (0, T - b.shape[1]))
+    rows = (a != b).any(1).nonzero().flatten()
+    if rows.numel() == 0:
+        return 0, 0.0
+    first = (a[rows] != b[rows]).float().argmax(1)
+    sub = {k: (v[rows] if isinstance(v, torch.Tensor) and v.dim() > 0 and v.shape[0] == a.shape[0] else v)
+           for k, v in state.items()}
+    ref = port.am_rollout(env_name, sub, h[rows].cpu(), W, actions=a[rows], return_all_logp=True,
+                          check_solution=False, **rollout_kw)
+    lp = ref["logprobs"]                                    # [rows, T, N]
+    worst = 0.0
+    for j in range(rows.numel()):
+        t0 = int(first[j])
+        row = lp[j, t0]
+        ca, cb = int(a[rows[j], t0]), int(b[rows[j], t0])
+        gap = abs(float(row[ca]) - float(row[cb]))
+        top = float(row.max())
+        assert gap < eps, f"instance {int(rows[j])} step {t0}: chosen nodes {ca}/{cb} differ by {gap:.3e} in log-prob"
+        assert top - min(float(row[ca]), float(row[cb])) < eps, \
+            f"instance {int(rows[j])} step {t0}: a chosen node is {top - min(float(row[ca]), float(row[cb])):.3e} below the best"
+        worst = max(worst, gap)
+    return int(rows.numel()), worst

@@ -176,6 +176,38 @@ assert abs(loss - want) < 1e-12, (loss, want)
 d = torch.randn(1001, dtype=torch.float64)[lo:hi] + 0.1
 tstat, n = B.paired_ttest_finalize(torch.stack((d.sum(), (d * d).sum(), torch.tensor(float(hi - lo), dtype=torch.float64))))
 assert n == 1001 and tstat == tstat
+
+# RolloutBaseline over a sharded dataset: every rank rolls out its own slice, the all-reduced t-test equals
+# scipy.stats.ttest_rel on the FULL data (baselines.py:202-224)
+import scipy.stats
+def cpu_stats(reward, stats=None):           # host stand-in of rl4co_reward_stats (the kernel needs a GPU)
+    r = reward.double().reshape(-1)
+    s = torch.stack((r.sum(), (r * r).sum(), torch.tensor(float(r.numel()), dtype=torch.float64)))
+    return s if stats is None else stats.add_(s)
+B.reward_stats = cpu_stats
+from rl4co_slap_b200 import TensorDict
+data = TensorDict({"locs": torch.rand(1001, 5, 2)}, batch_size=[1001])      # same seed on both ranks
+class FakeEnv:
+    def reset(self, td): return td
+    def dataset(self, batch_size): return data
+class FakePolicy(torch.nn.Module):
+    def __init__(self, shift):
+        super().__init__(); self.shift = shift
+    def forward(self, td, env, decode_type="greedy"):
+        return {"reward": -td["locs"].sum((1, 2)) + self.shift * td["locs"][:, 0, 0]}
+rb = B.RolloutBaseline(bl_alpha=0.05)
+rb._update_policy(FakePolicy(0.0), FakeEnv(), batch_size=100, device="cpu", dataset=data)
+assert rb.bl_vals.numel() == hi - lo, rb.bl_vals.shape
+full_bl, full_c = FakePolicy(0.0)(data, None)["reward"], FakePolicy(0.5)(data, None)["reward"]
+assert abs(rb.mean - full_bl.double().mean().item()) < 1e-9
+cand_mean, tstat, p_val, updated = rb.epoch_callback(FakePolicy(0.5), FakeEnv(), batch_size=100, device="cpu", epoch=0)
+want = scipy.stats.ttest_rel(-full_c.double().numpy(), -full_bl.double().numpy())
+assert abs(cand_mean - full_c.double().mean().item()) < 1e-9
+assert abs(tstat - want.statistic) < 1e-6 * abs(want.statistic), (tstat, want.statistic)
+assert abs(p_val - want.pvalue / 2) <= 1e-6 * max(want.pvalue, 1e-300) + 1e-300, (p_val, want.pvalue)
+assert updated and abs(rb.mean - full_c.double().mean().item()) < 1e-9
+wrapped = rb.wrap_dataset(data, FakeEnv(), batch_size=100, device="cpu")
+assert wrapped.data["extra"].numel() == 1001          # wrap_dataset covers every local row, not a shard
 dist.barrier(); dist.destroy_process_group()
 print("ok", rank)
 """
@@ -190,3 +222,17 @@ def test_sharded_reductions_world2_gloo(tmp_path):
     outs = [p.communicate(timeout=240)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_gumbel_uniform_is_strictly_inside_unit_interval():
+    """csrc/rollout_util.cuh gumbel4: u = ((w >> 9) + 0.5) * 2^-23 in fp32 is exact and in (0,1) for every 32-bit
+    Philox word, so the Gumbel noise -ln(-ln u) is finite (the 24-bit form rounded w = 2^32 - 1 to u = 1 -> +inf)"""
+    w = np.array([0, 1, 511, 512, 2 ** 31, 2 ** 32 - 512, 2 ** 32 - 1], dtype=np.uint64)
+    k = (w >> np.uint64(9)).astype(np.float32)
+    u = (k + np.float32(0.5)) * np.float32(1.0 / 8388608.0)
+    assert u.dtype == np.float32 and (u > 0).all() and (u < 1).all()
+    assert np.array_equal(u.astype(np.float64), ((w >> np.uint64(9)).astype(np.float64) + 0.5) / 8388608.0)   # exact
+    g = -np.log(-np.log(u.astype(np.float64)))
+    assert np.isfinite(g).all()
+    old = (np.float32(2 ** 24 - 1) + np.float32(0.5)) * np.float32(1.0 / 16777216.0)
+    assert old == np.float32(1.0)       # what the fix removes

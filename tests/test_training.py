@@ -202,3 +202,13 @@ def test_small_baselines_follow_reference_formulas(dev):
     res = reinforce_step(pol, env, td, optimizer=None, baseline=R.get_reinforce_baseline("exponential"))
     adv = res["reward"] - res["reward"].double().mean().float()
     torch.testing.assert_close(res["loss"], -(adv * res["log_likelihood"]).mean(), rtol=1e-5, atol=1e-6)
+    # SharedBaseline objects (from the class, the registry, and inside a warm-up baseline) through reinforce_step
+    S = 5
+    for bl in (R.SharedBaseline(), R.get_reinforce_baseline("shared"),
+               R.get_reinforce_baseline("warmup", baseline="shared", n_epochs=1)):
+        if isinstance(bl, R.WarmupBaseline):
+            bl.epoch_callback(epoch=0)      # alpha = 1: the shared baseline alone
+        res = reinforce_step(pol, env, td, optimizer=None, baseline=bl, decode_type="multistart_sampling", num_starts=S)
+        r2 = R.unbatchify(res["reward"], S)
+        adv = (r2 - r2.mean(1, keepdim=True)).t().reshape(-1)
+        torch.testing.assert_close(res["loss"], -(adv * res["log_likelihood"]).mean(), rtol=1e-5, atol=1e-6)
