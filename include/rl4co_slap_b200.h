@@ -335,6 +335,24 @@ typedef struct rl4co_am_rollout_args {
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);
 
+/* rl4co_am_rollout with its scratch memory held by the library.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory around the call (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch of the rollout path is the table block
+ * [n_tables][B*N][128] fp32 that rl4co_am_project_tc writes and only the rollout kernel reads; here it is a static
+ * __device__ array of RL4CO_STATIC_TABLE_BYTES inside the library (held by every GPU that loads the library until the
+ * process exits).  The call runs rl4co_am_project_tc(h, weight_image) into that array and rl4co_am_rollout out of it on
+ * `stream`; it calls no cudaMalloc / cudaFree / allocating routine.
+ *   args          as for rl4co_am_rollout, except args->tables, which must be NULL
+ *   h             [B*N,128] fp32 encoder output, weight_image = rl4co_am_pack_weights(n_tables, W)
+ * Limit: n_tables * B * N * 512 bytes <= RL4CO_STATIC_TABLE_BYTES (131 TSP100 instances with 5 tables, 162 CVRP100
+ * instances - 16 200 POMO rollouts - with 4); larger requests return non-zero with a message naming the limit.
+ * All calls on a device share the array; nothing in it needs clearing (the projection overwrites every row the rollout
+ * reads).  Calls that OVERLAP on the GPU (different streams or host threads, same device) race on it - serialise them
+ * on one stream or use rl4co_am_rollout with caller-owned tables. */
+#define RL4CO_STATIC_TABLE_BYTES (32u << 20)
+int rl4co_am_rollout_static(const rl4co_am_rollout_args *args, const float *h, const float *weight_image,
+                            rl4co_stream_t stream);
+
 /* rl4co_am_rollout picks between three kernels with identical semantics: register-file
  * resident tables with node compaction (TSP, greedy, single start, N <= 112), register-file
  * resident tables (any single start, N <= 128) and shared-memory resident tables (multistart,

@@ -36,6 +36,7 @@ STATUS_MESSAGES = [
 ]
 ENV_IDS = {"tsp": 0, "cvrp": 1, "slap": 2, "op": 3, "pctsp": 4, "spctsp": 4, "sdvrp": 5}
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
+STATIC_TABLE_BYTES = 32 << 20       # RL4CO_STATIC_TABLE_BYTES: scratch of rl4co_am_rollout_static
 
 _p = C.c_void_p
 _i64, _i32, _f32, _u64 = C.c_int64, C.c_int32, C.c_float, C.c_uint64
@@ -89,6 +90,7 @@ _SIGNATURES = {
     "rl4co_set_attention_impl": ([_i32], C.c_int),
     "rl4co_am_graph_context": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_am_rollout": ([C.POINTER(AmRolloutArgs), _p], C.c_int),
+    "rl4co_am_rollout_static": ([C.POINTER(AmRolloutArgs), _p, _p, _p], C.c_int),
     "rl4co_set_rollout_impl": ([C.c_int], C.c_int),
     "rl4co_decode_step": ([_i64, _i32, _p, _p, _i32, _f32, _f32, _i32, _p, _u64, _u64, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_reward_stats": ([_i64, _p, _p, _p], C.c_int),
