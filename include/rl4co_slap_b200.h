@@ -386,6 +386,29 @@ int rl4co_shared_baseline(int64_t B, int32_t S, const float *reward, const float
                           float *baseline, float *advantage, float *max_reward,
                           int64_t *best_start, double *loss_partial, rl4co_stream_t stream);
 
+/* ------------------------------------------- POMO val / test epilogue ---- */
+
+/* dihedral_8_augmentation, rl4co/data/transforms.py:15-37: locs [B,N,2] -> out [8*B,N,2], copy a of instance b at
+ * row a*B + b, copies in the reference's order (x,y) (1-x,y) (x,1-y) (1-x,1-y) (y,x) (1-y,x) (y,1-x) (1-y,1-x).
+ * Bit exact (one fp32 subtraction per coordinate). */
+int rl4co_dihedral8_augment(int64_t B, int32_t N, const float *locs, float *out, rl4co_stream_t stream);
+
+/* symmetric_transform, rl4co/data/transforms.py:50-71: xy [rows,N,2], phi [rows] -> out [rows,N,2]: rotation by phi about
+ * (0.5, 0.5); phi > 2*pi additionally swaps the two coordinates.  (The caller draws phi, transforms.py:83-87.) */
+int rl4co_symmetric_augment(int64_t rows, int32_t N, const float *xy, const float *phi, float *out,
+                            rl4co_stream_t stream);
+
+/* Best of starts and of augmentations with the tours that achieved them: POMO.shared_step's val / test branch
+ * (rl4co/models/zoo/pomo/model.py:113-141), DecodingStrategy._select_best (rl4co/utils/decoding.py:399-407) and the
+ * max / gather of the eval drivers (rl4co/tasks/eval.py:137-147,293-304).
+ * reward [S*A*B] and actions [S*A*B,T] in the reference's batchify order for (n_aug, n_start): rollout
+ * r = (s*A + a)*B + b.  A = 1 or S = 1 when that dimension is absent.  Outputs (each may be NULL):
+ *   max_reward [B,A], best_start [B,A] (lowest index on ties, like torch.max), best_multistart_actions [B,A,T],
+ *   max_aug_reward [B], best_aug [B], best_aug_actions [B,T] (tour of the best (copy, start) pair). */
+int rl4co_pomo_best(int64_t B, int32_t A, int32_t S, int32_t T, const float *reward, const int64_t *actions,
+                    float *max_reward, int64_t *best_start, int64_t *best_multistart_actions,
+                    float *max_aug_reward, int64_t *best_aug, int64_t *best_aug_actions, rl4co_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,6 +19,7 @@ from .generators import ATSPGenerator, CVRPGenerator, OPGenerator, PCTSPGenerato
 from .ops import (batchify, gather_by_index, get_num_starts, get_tour_length,  # noqa: F401
                   select_start_nodes, unbatchify)
 from .policy import AttentionModelDecoder, AttentionModelPolicy, POMOPolicy  # noqa: F401
+from .pomo import POMO, best_of_rollouts  # noqa: F401
 from .tensordict_compat import TensorDict  # noqa: F401
 from .training import reinforce_step, replay_masks, teacher_forced_log_likelihood  # noqa: F401
 from .transforms import StateAugmentation, dihedral_8_augmentation  # noqa: F401

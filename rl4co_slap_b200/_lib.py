@@ -95,6 +95,9 @@ _SIGNATURES = {
     "rl4co_decode_step": ([_i64, _i32, _p, _p, _i32, _f32, _f32, _i32, _p, _u64, _u64, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_reward_stats": ([_i64, _p, _p, _p], C.c_int),
     "rl4co_shared_baseline": ([_i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
+    "rl4co_dihedral8_augment": ([_i64, _i32, _p, _p, _p], C.c_int),
+    "rl4co_symmetric_augment": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
+    "rl4co_pomo_best": ([_i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p], C.c_int),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 

@@ -1,101 +1,111 @@
-"""Tensor helpers with the reference's names and semantics (rl4co/utils/ops.py:11-183).
+"""Rollout-order bookkeeping: how S starts and A augmented copies of B instances are laid out in one flat batch.
 
-These are layout / indexing glue around the kernels (views, expands, gathers); the heavy
-lifting of the rollout path lives in csrc/.
+The kernels and the reference agree on ONE convention (rl4co/utils/ops.py:11-62): the repeat index is the slow
+one.  Repeating a batch ``(A, S)`` times puts start ``s`` of copy ``a`` of instance ``b`` at row
+``(s*A + a)*B + b``; ``unbatchify`` turns such a flat axis back into ``[B, A, S]``.  The public names are the
+reference's (callers and tests use them); the implementations are written around that index formula: one tiling
+and one view + axis reversal regardless of how many repeat levels there are.
+
+Also here: the small tensor utilities of the same reference file that the host layer needs (index gather, closed
+tour length, policy entropy) and the multistart conventions (number of starts, forced start nodes).
 """
 from __future__ import annotations
 
-from typing import Union
+import math
+from typing import Sequence, Union
 
 import torch
 from torch import Tensor
 
 from .tensordict_compat import is_tensordict
 
-
-def _batchify_single(x, repeats: int):
-    """ops.py:11-16 - start-major repeat: out[s*B + b] = x[b]."""
-    s = x.shape
-    return x.expand(repeats, *s).contiguous().view(s[0] * repeats, *s[1:])
+# environments whose node 0 is a depot that is never a POMO start (utils/ops.py:126-136, 158-163)
+_DEPOT_ENVS = frozenset(("cvrp", "cvrptw", "sdvrp", "mtsp", "op", "pctsp", "spctsp"))
+_NO_DEPOT_START_ENVS = frozenset(("tsp", "atsp", "flp", "mcp"))
 
 
-def batchify(x, shape: Union[tuple, int]):
-    """ops.py:19-34."""
-    shape = [shape] if isinstance(shape, int) else shape
-    for s in reversed(shape):
-        x = _batchify_single(x, s) if s > 0 else x
-    return x
+def _levels(shape: Union[int, Sequence[int]]) -> list:
+    """Repeat counts that actually repeat (the reference skips levels <= 0, utils/ops.py:31-33)."""
+    levels = [shape] if isinstance(shape, int) else list(shape)
+    return [int(n) for n in levels if n > 0]
 
 
-def _unbatchify_single(x, repeats: int):
-    """ops.py:37-42 - [(S B), ...] -> [B, S, ...]."""
-    s = x.shape
-    return x.view(repeats, s[0] // repeats, *s[1:]).permute(1, 0, *range(2, len(s) + 1))
+def batchify(x, shape: Union[int, Sequence[int]]):
+    """Tile ``x`` along its batch axis ``prod(shape)`` times, instance index fastest (utils/ops.py:11-34).
+    Nested repeats compose into a single tiling, so ``(A, S)`` costs one copy, not two."""
+    total = math.prod(_levels(shape))
+    if total <= 1:
+        return x
+    lead = x.shape[0]
+    tiled = x.expand(total, *x.shape).contiguous()          # [total, B, ...] (batch dims only for a TensorDict)
+    return tiled.view(total * lead, *x.shape[1:])
 
 
-def unbatchify(x, shape: Union[tuple, int]):
-    """ops.py:45-62."""
-    shape = [shape] if isinstance(shape, int) else shape
-    for s in reversed(shape):
-        x = _unbatchify_single(x, s) if s > 0 else x
-    return x
+def unbatchify(x, shape: Union[int, Sequence[int]]):
+    """Inverse view of :func:`batchify`: ``[(S A B), ...] -> [B, A, S, ...]`` for ``shape = (A, S)``
+    (utils/ops.py:37-62).  No copy: a view with the repeat axes reversed behind the instance axis."""
+    levels = _levels(shape)
+    if not levels:
+        return x
+    k = len(levels)
+    lead = x.shape[0] // math.prod(levels)
+    split = x.view(*levels[::-1], lead, *x.shape[1:])       # slowest repeat level first
+    order = list(range(k, -1, -1)) + list(range(k + 1, k + 1 + len(x.shape) - 1))
+    return split.permute(*order)
 
 
 def gather_by_index(src: Tensor, idx: Tensor, dim: int = 1, squeeze: bool = True) -> Tensor:
-    """ops.py:65-77."""
-    expanded_shape = list(src.shape)
-    expanded_shape[dim] = -1
-    idx = idx.view(idx.shape + (1,) * (src.dim() - idx.dim())).expand(expanded_shape)
-    squeeze = idx.size(dim) == 1 and squeeze
-    return src.gather(dim, idx).squeeze(dim) if squeeze else src.gather(dim, idx)
+    """``src`` indexed along ``dim`` by one index (or a list of them) per leading position
+    (utils/ops.py:65-77): idx is broadcast over the trailing axes of ``src``."""
+    index = idx.reshape(*idx.shape, *([1] * (src.dim() - idx.dim())))
+    out = torch.take_along_dim(src, index, dim=dim)
+    return out.squeeze(dim) if (squeeze and out.shape[dim] == 1) else out
 
 
 def unbatchify_and_gather(x, idx: Tensor, n: int):
-    """ops.py:80-85."""
-    x = unbatchify(x, n)
-    if is_tensordict(x):
-        return x.gather(idx.dim(), idx) if hasattr(x, "gather") else x
-    return gather_by_index(x, idx, dim=idx.dim())
+    """Pick entry ``idx[b]`` out of the ``n`` repeats of instance ``b`` (utils/ops.py:80-85)."""
+    per_instance = unbatchify(x, n)
+    if is_tensordict(per_instance):
+        return per_instance.gather(idx.dim(), idx)
+    return gather_by_index(per_instance, idx, dim=idx.dim())
 
 
 def get_distance(x: Tensor, y: Tensor) -> Tensor:
-    """ops.py:88-90."""
-    return (x - y).norm(p=2, dim=-1)
+    """Euclidean distance along the last axis (utils/ops.py:88-90)."""
+    return torch.linalg.vector_norm(x - y, ord=2, dim=-1)
 
 
 def get_tour_length(ordered_locs: Tensor) -> Tensor:
-    """ops.py:93-101."""
-    return get_distance(torch.roll(ordered_locs, -1, dims=-2), ordered_locs).sum(-1)
+    """Length of the closed tour through ``ordered_locs [..., T, 2]`` (utils/ops.py:93-101)."""
+    successor = ordered_locs.roll(shifts=-1, dims=-2)
+    return get_distance(successor, ordered_locs).sum(dim=-1)
 
 
 def calculate_entropy(logprobs: Tensor) -> Tensor:
-    """ops.py:114-122.  logprobs [batch, steps, actions]."""
-    logprobs = torch.nan_to_num(logprobs, nan=0.0)
-    entropy = -(logprobs.exp() * logprobs).sum(dim=-1).sum(dim=1)
-    assert entropy.isfinite().all(), "Entropy is not finite"
+    """Summed per-step entropy of the policy, ``logprobs [B, T, N]`` (utils/ops.py:114-122).  Masked actions carry
+    -inf (and rows after ``done`` may carry NaN): both contribute zero, as in the reference, whose nan_to_num maps
+    NaN to 0 and -inf to the lowest finite float, i.e. p * log p = 0 * finite."""
+    p = logprobs.exp()
+    terms = torch.where(torch.isfinite(logprobs) & (p > 0), p * logprobs, torch.zeros_like(p))
+    entropy = -terms.sum(dim=(1, 2))
+    assert torch.isfinite(entropy).all(), "Entropy is not finite"
     return entropy
 
 
 def get_num_starts(td, env_name=None) -> int:
-    """ops.py:126-136."""
-    num_starts = td["action_mask"].shape[-1]
+    """Default number of POMO starts = number of candidate start nodes (utils/ops.py:126-136)."""
+    n_nodes = td["action_mask"].shape[-1]
     if env_name == "pdp":
-        num_starts = (num_starts - 1) // 2
-    elif env_name in ["cvrp", "cvrptw", "sdvrp", "mtsp", "op", "pctsp", "spctsp"]:
-        num_starts = num_starts - 1
-    return num_starts
+        return (n_nodes - 1) // 2
+    return n_nodes - 1 if env_name in _DEPOT_ENVS else n_nodes
 
 
 def select_start_nodes(td, env, num_starts: int) -> Tensor:
-    """ops.py:139-163 (tsp / depot branches; the op / mtsp resampling branches are out of scope)."""
-    num_loc = env.generator.num_loc if hasattr(env.generator, "num_loc") else 0xFFFFFFFF
-    selected = torch.arange(num_starts, device=td.device).repeat_interleave(td.shape[0]) % num_loc
-    if env.name in ["tsp", "atsp", "flp", "mcp"]:
-        return selected
-    return selected + 1
-
-
-def get_best_actions(actions: Tensor, max_idxs: Tensor) -> Tensor:
-    """ops.py:186-188."""
-    actions = unbatchify(actions, max_idxs.shape[0])
-    return actions.gather(0, max_idxs[..., None, None])
+    """Forced first action of rollout ``r = s*B + b``: node ``s mod num_loc``, shifted past the depot where there is
+    one (utils/ops.py:139-163; the op / mtsp resampling branches are out of scope).  This is the formula the rollout
+    kernel applies on the device (csrc/am_rollout*.cu)."""
+    num_loc = getattr(env.generator, "num_loc", 0xFFFFFFFF)
+    batch = td.shape[0]
+    start_of_row = torch.arange(num_starts * batch, device=td.device) // batch
+    first = start_of_row % num_loc
+    return first if env.name in _NO_DEPOT_START_ENVS else first + 1

@@ -218,9 +218,14 @@ class AttentionModelPolicy(nn.Module):
         for k in ("top_k", "top_p"):
             if decoding_kwargs.pop(k, 0):
                 raise NotImplementedError(f"{k} > 0 is not implemented by the fused rollout kernel")
-        for k in ("multisample", "select_start_nodes_fn", "improvement_method_mode"):
-            if decoding_kwargs.pop(k, None):
-                raise NotImplementedError(f"{k} is not implemented by the fused rollout kernel")
+        # multisample (utils/decoding.py:271-308): the batch is tiled num_starts times and every copy is an independent
+        # rollout of the decode type - no forced first action.  select_start_nodes_fn is only consulted by MULTISTART
+        # decoding in the reference (:286-291); with multisample it is accepted and unused, exactly as there.
+        multisample = bool(decoding_kwargs.pop("multisample", False))
+        start_fn = decoding_kwargs.pop("select_start_nodes_fn", None)
+        if decoding_kwargs.pop("improvement_method_mode", None):
+            raise NotImplementedError("improvement_method_mode is not implemented by the fused rollout kernel")
+        decoding_kwargs.pop("softmax_temp", None)       # tasks/eval.py:191 passes it; the reference's strategy ignores it
         decoding_kwargs.pop("key", None)
         if decoding_kwargs:
             raise TypeError(f"unknown decoding kwargs: {sorted(decoding_kwargs)}")
@@ -233,11 +238,16 @@ class AttentionModelPolicy(nn.Module):
         if name != self.decoder.env_name:
             raise ValueError(f"policy was built for {self.decoder.env_name!r}, env is {name!r}")
         multistart = "multistart" in decode_type
+        if multistart and start_fn is not None:
+            raise NotImplementedError("select_start_nodes_fn with multistart decoding: the kernel forces start node "
+                                      "s % num_loc (+1 past a depot), utils/ops.py:139-163")
+        if multisample and multistart:
+            multisample = False                         # decoding.py:286: the multistart branch wins
         S = 0
-        if multistart:  # utils/decoding.py:265-284
+        if multistart or multisample:  # utils/decoding.py:265-284
             S = int(num_starts) if num_starts is not None else env.get_num_starts(td)
             if S < 1:
-                multistart, S = False, 0
+                multistart, multisample, S = False, False, 0
         mode = {"greedy": _lib.MODE_GREEDY, "sampling": _lib.MODE_SAMPLING,
                 "evaluate": _lib.MODE_EVALUATE}[decode_type.replace("multistart_", "")]
         Sx = max(S, 1)
@@ -251,7 +261,7 @@ class AttentionModelPolicy(nn.Module):
         elif name == "sdvrp":
             # a customer visit either completes the customer or fills the vehicle, every fill costs one depot visit
             T = 3 * N
-            if multistart:
+            if multistart or multisample:
                 raise NotImplementedError("sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not implemented")
             if store_all_logp:
                 raise NotImplementedError("sdvrp: per-node log-probs (return_entropy / store_all_logp) are not "
@@ -289,7 +299,7 @@ class AttentionModelPolicy(nn.Module):
         hiddens, inits, gctxs, tabs = [], [], [], []
         launches = 0
 
-        chunk = B if multistart else min(B, max(1, int(self.rollout_chunk)))
+        chunk = B if S > 0 else min(B, max(1, int(self.rollout_chunk)))
         for c0 in range(0, B, chunk):
             c1 = min(B, c0 + chunk)
             Bc = c1 - c0
@@ -336,8 +346,8 @@ class AttentionModelPolicy(nn.Module):
                 a.prize_required = _lib.ptr(td["prize_required"][c0:c1].contiguous(), torch.float32)
             if name == "slap":
                 a.picklist = _lib.ptr(td["picklist"][c0:c1].contiguous(), torch.int64)
-            # single start: rollouts of the chunk are rows c0..c1; multistart runs unchunked
-            sl = slice(c0, c1) if not multistart else slice(0, R)
+            # single start: rollouts of the chunk are rows c0..c1; multistart / multisample run unchunked
+            sl = slice(c0, c1) if S == 0 else slice(0, R)
             a.actions_in = _lib.ptr(actions[sl]) if actions is not None else None
             a.seed, a.offset = seed, c0 * T
             a.actions, a.logp = _lib.ptr(out_actions[sl]), _lib.ptr(out_logp[sl])
