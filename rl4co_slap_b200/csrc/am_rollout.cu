@@ -541,6 +541,8 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     }
     if (a.multistart) RL4CO_REQUIRE(a.num_loc >= 1 && a.env != RL4CO_ENV_SLAP, "am_rollout: bad multistart setup");
 
+    // multistart (POMO) tsp / cvrp: tensor-core kernel, starts = TMEM lanes (am_rollout_ms_tc.cu)
+    if (g_rollout_impl == 0 && rollout_ms_tc_supports(a)) return launch_rollout_ms_tc(a, (cudaStream_t)stream);
     // TSP greedy single start: register-file kernel with node compaction (am_rollout_tsp.cu)
     if (g_rollout_impl == 0 && rollout_tsp_greedy_supports(a)) return launch_rollout_tsp_greedy(a, (cudaStream_t)stream);
     // single-start rollouts: register-file resident kernel (am_rollout_rf.cu)

@@ -105,4 +105,8 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a);
 int launch_rollout_tsp_greedy(const rl4co_am_rollout_args &a, cudaStream_t stream);
 bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a);
 
+// multistart (POMO) rollouts of tsp / cvrp on the tensor cores, starts = TMEM lanes (am_rollout_ms_tc.cu)
+int launch_rollout_ms_tc(const rl4co_am_rollout_args &a, cudaStream_t stream);
+bool rollout_ms_tc_supports(const rl4co_am_rollout_args &a);
+
 }  // namespace rl4co
