@@ -18,7 +18,7 @@
 // of the projection kernel would need 344 KB of shared memory for the tables; FP16 halves that (176 KB) and runs at
 // twice the TF32 rate.  Values below 2^-14 lose low-order bits of `lo` (absolute error <= 3e-8 per element).
 //
-// Pipeline of one step (MMA warp | 4 consumer warps):
+// Pipeline of one step (MMA warp | 2 consumer groups of 4 warps; group g owns heads 4g..4g+3 and score buffer g):
 //   consumers  q = scale (gctx + ctx rows + capacity column)  -> TMEM [QH|QL]                      -> q_ready
 //   MMA        scores(0), scores(1)                           -> S0, S1                           -> s_full[b]
 //   consumers  head j: max, P = 2^(s - max) (masked: 0), l_j  -> P_hi over S, P_lo beside it       -> p_full[b]
@@ -43,8 +43,11 @@ using namespace tcu;
 
 constexpr int E = RL4CO_EMBED_DIM, H = RL4CO_NUM_HEADS, D = 16;
 constexpr int NK = 112;                                 // node columns of the score / logit tiles (multiple of 16)
-constexpr int kConsumerWarps = 4;
-constexpr int kThreads = (1 + kConsumerWarps) * 32;     // warp 0: MMA issue, warps 1-4: thread = start
+constexpr int kGroupWarps = 4, kGroups = 2;             // a consumer group covers the 128 TMEM lanes once
+constexpr int kConsumerWarps = kGroups * kGroupWarps;
+constexpr int kThreads = (1 + kConsumerWarps) * 32;     // warp 0: MMA issue; warps 1-4 / 5-8: thread = (start, group)
+constexpr int HG = H / kGroups;                         // heads per group
+constexpr int NH = NK / kGroups;                        // logit columns per group (56)
 constexpr float kScoreScale = 0.25f * 1.4426950408889634f;   // 1/sqrt(16) * log2(e)
 constexpr float kInvSqrtE = 0.08838834764831845f;
 constexpr float kLog2e = 1.4426950408889634f;
@@ -59,6 +62,7 @@ struct Misc {
     float2 locs[128];
     float wc[128];          // cvrp: remaining-capacity column of project_context, pre-scaled
     float gq[128];          // graph context, pre-scaled (0 without one)
+    float4 xch[kGroups][128];   // logit phase: each group's partial (sum of e, best logit, its node, its e) per start
     uint64_t bars[12];
     uint32_t tmem_slot;
     int stop;               // written by one consumer before q_ready: every rollout of the instance is done
@@ -134,14 +138,14 @@ __device__ __forceinline__ void split2(float x0, float x1, uint32_t &hi, uint32_
     hi = *reinterpret_cast<const uint32_t *>(&h);
     lo = *reinterpret_cast<const uint32_t *>(&l);
 }
-// barrier among the 128 consumer threads with an AND reduction of a predicate
+// barrier among the 256 consumer threads with an AND reduction of a predicate
 __device__ __forceinline__ bool consumers_all(bool pred) {
     uint32_t r;
     asm volatile(
         "{\n\t"
         ".reg .pred p, q;\n\t"
         "setp.ne.b32 q, %1, 0;\n\t"
-        "bar.red.and.pred p, 1, 128, q;\n\t"
+        "bar.red.and.pred p, 1, 256, q;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t"
         "}\n"
         : "=r"(r)
@@ -206,7 +210,20 @@ __device__ __forceinline__ void tmem_ld16_nw(uint32_t taddr, uint32_t *v) {
           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld8_nw(uint32_t taddr, uint32_t *v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// the NH = 56 logit columns of one consumer group
+__device__ __forceinline__ void tmem_ld_half(uint32_t taddr, uint32_t (&v)[NH]) {
+    tmem_ld32_nw(taddr, v);
+    tmem_ld16_nw(taddr + 32, v + 32);
+    tmem_ld8_nw(taddr + 48, v + 48);
+    tmem_ld_wait();
+}
+__device__ __forceinline__ void consumers_sync() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 // all NK columns of a score / logit tile of this thread's lane
 __device__ __forceinline__ void tmem_ld_row(uint32_t taddr, uint32_t (&v)[NK]) {
     tmem_ld32_nw(taddr, v);
@@ -238,6 +255,8 @@ __device__ __forceinline__ Bits make_bits(u64 lo, u64 hi) {
     return m;
 }
 
+// registers are allocated to warps in groups of four: 9 warps are budgeted as 12, i.e. 168 registers per thread - the
+// softmax and the sampling scan therefore work on 64 + 48 columns at a time instead of holding a whole row
 template <int ENV, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
@@ -254,9 +273,9 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
     // pad rows (nodes >= N) of every operand image must read as zero for the whole launch
     for (int off = tid * 16; off < OFF_MISC; off += kThreads * 16) *reinterpret_cast<uint4 *>(smem + off) = make_uint4(0u, 0u, 0u, 0u);
     if (tid == 0) {
-        mbar_init(&bars[B_QREADY], kConsumerWarps);
+        mbar_init(&bars[B_QREADY], kConsumerWarps);         // every consumer warp stores its part of the query
         mbar_init(&bars[B_SFULL], 1);      mbar_init(&bars[B_SFULL + 1], 1);
-        mbar_init(&bars[B_PFULL], kConsumerWarps);  mbar_init(&bars[B_PFULL + 1], kConsumerWarps);
+        mbar_init(&bars[B_PFULL], kGroupWarps);     mbar_init(&bars[B_PFULL + 1], kGroupWarps);   // per group
         mbar_init(&bars[B_OFULL], 1);      mbar_init(&bars[B_OFULL + 1], 1);
         mbar_init(&bars[B_OREADY], kConsumerWarps);
         mbar_init(&bars[B_LGFULL], 1);
@@ -274,7 +293,7 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
     const uint32_t tmem_base = ms.tmem_slot;
 
     // running phase parities of the mbarriers (bit b = buffer b)
-    unsigned ph_q = 0, ph_s = 0, ph_p = 0, ph_o = 0, ph_or = 0, ph_lg = 0;
+    unsigned ph_q = 0, ph_p = 0, ph_or = 0, ph_lg = 0;
 
     for (int64_t b = blockIdx.x; b < a.B; b += gridDim.x) {
         __syncthreads();                                        // the previous instance is done with shared memory
@@ -296,14 +315,15 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
             const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
             const uint32_t kh = d0 + (OFF_KH >> 4), kl = d0 + (OFF_KL >> 4), lh = d0 + (OFF_LH >> 4), ll = d0 + (OFF_LL >> 4);
             const uint32_t vh = d0 + (OFF_VH >> 4), vl = d0 + (OFF_VL >> 4);
-            auto scores = [&](int j) {                          // head j: S[j & 1] = q_j K_j^T, three split terms
+            auto scores = [&](int j) {                          // head j of group j / HG: S[group] = q_j K_j^T, three split terms
+                const int g = j / HG;
                 const uint32_t boff = (uint32_t)(((j >> 2) * KT_TILE + (j & 3) * 32) >> 4);
-                const uint32_t dcol = tmem_u + ((j & 1) ? C_S1 : C_S0);
+                const uint32_t dcol = tmem_u + (g ? C_S1 : C_S0);
                 const uint32_t qh = tmem_u + C_QH + 8u * j, ql = tmem_u + C_QL + 8u * j;
                 umma_f16_ts(dcol, ql, kh + boff, kIdescS, 0u);
                 umma_f16_ts(dcol, qh, kl + boff, kIdescS, 1u);
                 umma_f16_ts(dcol, qh, kh + boff, kIdescS, 1u);
-                umma_commit(&bars[B_SFULL + (j & 1)]);
+                umma_commit(&bars[B_SFULL + g]);
             };
             for (;;) {
                 mbar_wait_bounded(&bars[B_QREADY], ph_q);
@@ -312,18 +332,18 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                 if (*reinterpret_cast<volatile int *>(&ms.stop)) break;
                 if (elect_one()) {
                     scores(0);
-                    scores(1);
+                    scores(HG);
                 }
                 __syncwarp();
 #pragma unroll 1
-                for (int j = 0; j < H; ++j) {
-                    const int bb = j & 1;
-                    mbar_wait_bounded(&bars[B_PFULL + bb], (ph_p >> bb) & 1u);
-                    ph_p ^= 1u << bb;
+                for (int it = 0; it < H; ++it) {                // the two groups alternate: head jj of group 0, head jj of group 1
+                    const int g = it & 1, j = g * HG + (it >> 1);
+                    mbar_wait_bounded(&bars[B_PFULL + g], (ph_p >> g) & 1u);
+                    ph_p ^= 1u << g;
                     tc_fence_after();
                     if (elect_one()) {
-                        const uint32_t o = tmem_u + (bb ? C_O1 : C_O0);
-                        const uint32_t p_hi = tmem_u + (bb ? C_S1 : C_S0), p_lo = tmem_u + (bb ? C_PL1 : C_PL0);
+                        const uint32_t o = tmem_u + (g ? C_O1 : C_O0);
+                        const uint32_t p_hi = tmem_u + (g ? C_S1 : C_S0), p_lo = tmem_u + (g ? C_PL1 : C_PL0);
 #pragma unroll
                         for (int ks = 0; ks < NK / 16; ++ks) {  // 7 k-steps of 16 nodes
                             const uint32_t voff = (uint32_t)(((ks >> 2) * VT_TILE + j * 16 * 128 + (ks & 3) * 32) >> 4);
@@ -331,8 +351,8 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                             umma_f16_ts(o, p_hi + 8u * ks, vl + voff, kIdescO, 1u);
                             umma_f16_ts(o, p_hi + 8u * ks, vh + voff, kIdescO, 1u);
                         }
-                        umma_commit(&bars[B_OFULL + bb]);
-                        if (j + 2 < H) scores(j + 2);           // executes after the P V above: S[bb] is free again
+                        umma_commit(&bars[B_OFULL + g]);
+                        if ((it >> 1) + 1 < HG) scores(j + 1);  // executes after the P V above: the group's S is free again
                     }
                     __syncwarp();
                 }
@@ -353,11 +373,16 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                 __syncwarp();
             }
         } else {
-            // ============================================================ consumers: thread = start = TMEM lane
+            // ============================================================ consumers: thread = (start = TMEM lane, group)
+            // Both groups cover all 128 lanes; group g owns heads HG g .. HG g + 3 (query dims 64 g .. 64 g + 63, score
+            // buffer g) and the logit columns NH g .. NH g + 55.  The environment state of a start is replicated in its
+            // two threads (both apply every transition); group 0 writes the outputs.
+            const int grp = (warp - 1) / kGroupWarps;
             const int quarter = warp & 3;                       // the TMEM lanes a warp may touch: 32 (warp % 4) ...
             const int sidx = 32 * quarter + lane;
             const uint32_t tl = tmem_base + ((uint32_t)(32 * quarter) << 16);
             const bool active = sidx < S;
+            const bool writer = active && grp == 0;
             const int64_t r = (int64_t)sidx * a.B + b;          // rollout index, start-major (utils/ops.py:11-34)
             const u64 own_lo = N >= 64 ? ~0ull : ((1ull << N) - 1ull);
             const u64 own_hi = N <= 64 ? 0ull : ((1ull << (N - 64)) - 1ull);
@@ -367,9 +392,11 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
             float2 prev = ms.locs[0];
             int cur = 0, first = 0, t = 0, status = 0;
             bool done = !active;
+            unsigned ph_sg = 0, ph_og = 0;                      // parities of this group's s_full / o_full
+            const uint32_t sb = tl + (grp ? C_S1 : C_S0), plb = tl + (grp ? C_PL1 : C_PL0), ob = tl + (grp ? C_O1 : C_O0);
 #ifdef MS_TRACE
             long long *trace = reinterpret_cast<long long *>(a.logp_all);
-            const bool trace_on = trace != nullptr && blockIdx.x == 0 && sidx == 0 && b == (int64_t)blockIdx.x;
+            const bool trace_on = trace != nullptr && blockIdx.x == 0 && sidx == 0 && grp == 0 && b == (int64_t)blockIdx.x;
 #endif
 
             auto cvrp_mask = [&]() {                            // cvrp/env.py:137-149
@@ -415,8 +442,10 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
             };
             if (active) {                                       // forced POMO start node, log-prob 0 (decoding.py:287-305)
                 const int a0 = sidx % a.num_loc + (CVRP ? 1 : 0);
-                a.actions[(size_t)r * T] = a0;
-                if (a.logp) a.logp[(size_t)r * T] = 0.f;
+                if (writer) {
+                    a.actions[(size_t)r * T] = a0;
+                    if (a.logp) a.logp[(size_t)r * T] = 0.f;
+                }
                 apply(a0);
                 t = 1;
             }
@@ -426,51 +455,50 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                 const bool stop = consumers_all(fin);
                 if (warp == 1 && lane == 0) ms.stop = stop ? 1 : 0;
                 // masks of this step; finished / unused lanes keep one live column so that their rows stay finite
-                const Bits mk = make_bits(fin ? 1ull : al_lo, fin ? 0ull : al_hi);
+                const u64 mk_lo = fin ? 1ull : al_lo, mk_hi = fin ? 0ull : al_hi;
+                const Bits mk = make_bits(mk_lo, mk_hi);
                 MS_STAMP(0);
                 if (!stop) {
-                    // ---- query: scale * (gctx + ctx(cur) [+ ctx_first(first)]) [+ scaled capacity column * remaining]
-                    const float *c_row = a.tables + ((size_t)3 * Mrows + b * (int64_t)N + cur) * E;
-                    const float *f_row = a.tables + ((size_t)4 * Mrows + b * (int64_t)N + first) * E;
+                    // ---- this group's half of the query: scale * (gctx + ctx(cur) [+ ctx_first(first)]) [+ scaled capacity
+                    //      column * remaining capacity]; every load is issued before the first use
+                    const float *c_row = a.tables + ((size_t)3 * Mrows + b * (int64_t)N + cur) * E + 64 * grp;
+                    const float *f_row = a.tables + ((size_t)4 * Mrows + b * (int64_t)N + first) * E + 64 * grp;
                     const float rem = CVRP ? __fsub_rn(cap, used) : 0.f;
-#pragma unroll 1
-                    for (int g = 0; g < 2; ++g) {               // 64 dims per round, every load issued before the first use
-                        float4 x[16];
+                    float4 x[16];
 #pragma unroll
-                        for (int k = 0; k < 16; ++k) x[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (!fin) {
+                    for (int k = 0; k < 16; ++k) x[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!fin) {
 #pragma unroll
-                            for (int k = 0; k < 16; ++k) x[k] = __ldg(reinterpret_cast<const float4 *>(c_row + 64 * g + 4 * k));
-                            if (!CVRP) {
+                        for (int k = 0; k < 16; ++k) x[k] = __ldg(reinterpret_cast<const float4 *>(c_row + 4 * k));
+                        if (!CVRP) {
 #pragma unroll
-                                for (int k = 0; k < 16; ++k) {
-                                    const float4 f = __ldg(reinterpret_cast<const float4 *>(f_row + 64 * g + 4 * k));
-                                    x[k].x += f.x; x[k].y += f.y; x[k].z += f.z; x[k].w += f.w;
-                                }
+                            for (int k = 0; k < 16; ++k) {
+                                const float4 f = __ldg(reinterpret_cast<const float4 *>(f_row + 4 * k));
+                                x[k].x += f.x; x[k].y += f.y; x[k].z += f.z; x[k].w += f.w;
                             }
                         }
-                        const float qs = fin ? 0.f : 1.f;       // finished / unused lanes: a zero query
+                    }
+                    const float qs = fin ? 0.f : 1.f;           // finished / unused lanes: a zero query
 #pragma unroll
-                        for (int half = 0; half < 2; ++half) {
-                            uint32_t hi[16], lo[16];
+                    for (int half = 0; half < 2; ++half) {
+                        uint32_t hi[16], lo[16];
 #pragma unroll
-                            for (int k = 0; k < 8; ++k) {
-                                const int d = 64 * g + 32 * half + 4 * k;
-                                float4 v = x[8 * half + k];
-                                const float4 gq = *reinterpret_cast<const float4 *>(&ms.gq[d]);
-                                v.x = fmaf(v.x, kScoreScale, gq.x); v.y = fmaf(v.y, kScoreScale, gq.y);
-                                v.z = fmaf(v.z, kScoreScale, gq.z); v.w = fmaf(v.w, kScoreScale, gq.w);
-                                if (CVRP) {
-                                    const float4 w = *reinterpret_cast<const float4 *>(&ms.wc[d]);
-                                    v.x = fmaf(w.x, rem, v.x); v.y = fmaf(w.y, rem, v.y);
-                                    v.z = fmaf(w.z, rem, v.z); v.w = fmaf(w.w, rem, v.w);
-                                }
-                                split2(v.x * qs, v.y * qs, hi[2 * k], lo[2 * k]);
-                                split2(v.z * qs, v.w * qs, hi[2 * k + 1], lo[2 * k + 1]);
+                        for (int k = 0; k < 8; ++k) {
+                            const int dl = 32 * half + 4 * k;   // dim within this group's 64
+                            float4 v = x[8 * half + k];
+                            const float4 gq = *reinterpret_cast<const float4 *>(&ms.gq[64 * grp + dl]);
+                            v.x = fmaf(v.x, kScoreScale, gq.x); v.y = fmaf(v.y, kScoreScale, gq.y);
+                            v.z = fmaf(v.z, kScoreScale, gq.z); v.w = fmaf(v.w, kScoreScale, gq.w);
+                            if (CVRP) {
+                                const float4 w = *reinterpret_cast<const float4 *>(&ms.wc[64 * grp + dl]);
+                                v.x = fmaf(w.x, rem, v.x); v.y = fmaf(w.y, rem, v.y);
+                                v.z = fmaf(w.z, rem, v.z); v.w = fmaf(w.w, rem, v.w);
                             }
-                            tmem_st16(tl + C_QH + 32u * g + 16u * half, hi);
-                            tmem_st16(tl + C_QL + 32u * g + 16u * half, lo);
+                            split2(v.x * qs, v.y * qs, hi[2 * k], lo[2 * k]);
+                            split2(v.z * qs, v.w * qs, hi[2 * k + 1], lo[2 * k + 1]);
                         }
+                        tmem_st16(tl + C_QH + 32u * grp + 16u * half, hi);
+                        tmem_st16(tl + C_QL + 32u * grp + 16u * half, lo);
                     }
                 }
                 tmem_st_wait();
@@ -480,33 +508,20 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                 if (stop) break;
                 MS_STAMP(1);
 
-                // ---- glimpse: masked softmax of every head on this thread's row, glimpse back as the next A operand
-                auto drain = [&](int j, float l) {              // o_j = O[j & 1] / l_j -> columns of the dead q_j
-                    const int bb = j & 1;
-                    MS_ACC(9, mbar_wait_bounded(&bars[B_OFULL + bb], (ph_o >> bb) & 1u));
-                    ph_o ^= 1u << bb;
-                    tc_fence_after();
-                    uint32_t ov[16], hi[8], lo[8];
-                    tmem_ld16(tl + (bb ? C_O1 : C_O0), ov);
-                    const float inv = __fdividef(1.f, l);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k)
-                        split2(__uint_as_float(ov[2 * k]) * inv, __uint_as_float(ov[2 * k + 1]) * inv, hi[k], lo[k]);
-                    tmem_st8(tl + C_QH + 8u * j, hi);
-                    tmem_st8(tl + C_QL + 8u * j, lo);
-                };
-                float l_prev = 1.f;
+                // ---- glimpse: masked softmax of this group's heads on the thread's row; the normalised glimpse goes back
+                //      to tensor memory, over the dead query columns of the same head, as the A operand of the logits
 #pragma unroll 1
-                for (int j = 0; j < H; ++j) {
-                    const int bb = j & 1;
-                    MS_ACC(8, mbar_wait_bounded(&bars[B_SFULL + bb], (ph_s >> bb) & 1u));
-                    ph_s ^= 1u << bb;
+                for (int jj = 0; jj < HG; ++jj) {
+                    const int j = HG * grp + jj;
+                    MS_ACC(8, mbar_wait_bounded(&bars[B_SFULL + grp], ph_sg));
+                    ph_sg ^= 1u;
                     tc_fence_after();
-                    if (j == 0) MS_STAMP(2);
+                    if (jj == 0) MS_STAMP(2);
 #ifdef MS_TRACE
                     const long long soft0 = clock64();
 #endif
-                    const uint32_t sb = tl + (bb ? C_S1 : C_S0), plb = tl + (bb ? C_PL1 : C_PL0);
+                    // ONE read of the row: tcgen05.ld moves 64 B/clk per SM (a 128 x 112 fp32 tile = 900 clk), so the masked
+                    // scores stay in registers between the max pass and the exp pass (cold per-rollout state spills instead)
                     uint32_t sv[NK];
                     tmem_ld_row(sb, sv);
                     float mx = -INFINITY;
@@ -533,28 +548,41 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                     tmem_st_wait();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&bars[B_PFULL + bb]);
+                    if (lane == 0) mbar_arrive(&bars[B_PFULL + grp]);
 #ifdef MS_TRACE
                     if (trace_on) trace[(size_t)t * 16 + 10] += clock64() - soft0;
 #endif
-                    if (j >= 1) drain(j - 1, l_prev);
-                    l_prev = l;
+                    // o_j = O[group] / l_j (the other group's warps fill the wait for the P V)
+                    MS_ACC(9, mbar_wait_bounded(&bars[B_OFULL + grp], ph_og));
+                    ph_og ^= 1u;
+                    tc_fence_after();
+                    uint32_t ov[16], hi[8], lo[8];
+                    tmem_ld16(ob, ov);
+                    const float inv = __fdividef(1.f, l);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                        split2(__uint_as_float(ov[2 * k]) * inv, __uint_as_float(ov[2 * k + 1]) * inv, hi[k], lo[k]);
+                    tmem_st8(tl + C_QH + 8u * j, hi);
+                    tmem_st8(tl + C_QL + 8u * j, lo);
                 }
                 MS_STAMP(3);
-                drain(H - 1, l_prev);
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[B_OREADY]);
                 MS_STAMP(4);
 
-                // ---- pointer logits of this rollout (attention.py:280-282, decoding.py:141-191), selection, transition
+                // ---- pointer logits (attention.py:280-282, decoding.py:141-191): this group's NH columns, partial results
+                //      exchanged through shared memory, then selection and transition in both threads of the start
                 mbar_wait_bounded(&bars[B_LGFULL], ph_lg);
                 ph_lg ^= 1u;
                 tc_fence_after();
                 MS_STAMP(5);
-                uint32_t lv[NK];
-                tmem_ld_row(tl + C_LG, lv);
+                uint32_t lv[NH];
+                tmem_ld_half(tl + C_LG + (uint32_t)(NH * grp), lv);
+                // the group's 56 mask bits as a local set: bit n <-> node NH grp + n
+                const u64 loc = grp ? ((mk_lo >> NH) | (mk_hi << (64 - NH))) : mk_lo;
+                const Bits mkl = make_bits(loc, 0ull);
                 int given = -1;
                 if (MODE == RL4CO_MODE_EVALUATE && !fin) {
                     const int64_t gv = a.actions_in[(size_t)r * T + t];
@@ -562,18 +590,19 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                     status |= bad ? RL4CO_ST_ACTION_RANGE : 0;
                     given = bad ? 0 : (int)gv;
                 }
+                const int given_loc = given - NH * grp;         // index inside this group's columns (or outside [0, NH))
                 // x = clip tanh(z) = clip - 2 clip / (2^(2 log2(e) z) + 1), z = logit / sqrt(E); e = exp(x - clip) (the
                 // clip bound is the log-sum-exp shift: no max pass); masked: e = 0.  Strictly branch free: every start
                 // has its own mask, a branch per element would diverge on almost every one of them.
                 float sum = 0.f, best = -INFINITY, e_a = 0.f, nan_probe = 0.f;
                 int act = 0;
 #pragma unroll
-                for (int n = 0; n < NK; ++n) {
+                for (int n = 0; n < NH; ++n) {
                     const float v = __uint_as_float(lv[n]);
                     nan_probe = fmaf(v, 0.f, nan_probe);         // NaN / inf anywhere in the row -> NaN (pad columns are 0)
                     const float e2 = ex2f(v * (kInvSqrtE * 2.f * kLog2e));
                     const float x = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
-                    const bool alive = bit_at(mk, n);
+                    const bool alive = bit_at(mkl, n);
                     const float e = alive ? ex2f((x - clip) * kLog2e) : 0.f;
                     sum += e;
                     if (MODE == RL4CO_MODE_SAMPLING) lv[n] = __float_as_uint(e);
@@ -584,38 +613,60 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                         act = gt ? n : act;
                         e_a = gt ? e : e_a;
                     } else if (MODE == RL4CO_MODE_EVALUATE) {
-                        const bool hit = n == given;
-                        e_a = hit ? e : e_a;
+                        e_a = (n == given_loc) ? e : e_a;
                     }
                 }
                 status |= (nan_probe != nan_probe) ? RL4CO_ST_NAN_LOGITS : 0;
-                if (MODE == RL4CO_MODE_EVALUATE) {
+                ms.xch[grp][sidx] = make_float4(sum, best, __int_as_float(act + NH * grp), e_a);
+                consumers_sync();
+                const float4 p0 = ms.xch[0][sidx], p1 = ms.xch[1][sidx];
+                sum = p0.x + p1.x;                              // same order in both threads of the start
+                if (MODE == RL4CO_MODE_GREEDY) {
+                    const bool second = p1.y > p0.y;            // strict: the lower node index wins a tie
+                    act = __float_as_int(second ? p1.z : p0.z);
+                    e_a = second ? p1.w : p0.w;
+                } else if (MODE == RL4CO_MODE_EVALUATE) {
                     act = given < 0 ? 0 : given;
+                    e_a = given >= NH ? p1.w : p0.w;
                     status |= (!fin && e_a == 0.f) ? RL4CO_ST_INFEASIBLE_ACTION : 0;
-                }
-                if (MODE == RL4CO_MODE_SAMPLING) {
-                    // Categorical(exp(logp)) by inverse CDF over this thread's own row (decoding.py:383-397): one uniform
+                } else {
+                    // Categorical(exp(logp)) by inverse CDF over the start's whole row (decoding.py:383-397): one uniform
                     // per rollout and step; the first feasible node whose running sum of e passes u * sum (the last
-                    // feasible one if rounding leaves the running sum short)
-                    const float target = philox_uniform(a.seed, a.offset, (uint64_t)r, (uint32_t)t) * sum;
+                    // feasible one if rounding leaves the running sum short).  Each group scans its own columns (still in
+                    // registers) against its share of the target, the winner is agreed through shared memory.
+                    const float target = philox_uniform(a.seed, a.offset, (uint64_t)r, (uint32_t)t) * sum - (grp ? p0.x : 0.f);
                     float cum = 0.f;
                     bool found = false;
+                    int pick = -1;
+                    float e_pick = 0.f;
 #pragma unroll
-                    for (int n = 0; n < NK; ++n) {
+                    for (int n = 0; n < NH; ++n) {
                         const float e = __uint_as_float(lv[n]);
                         cum += e;
                         const bool pos = e > 0.f, take = pos && !found;
-                        act = take ? n : act;
-                        e_a = take ? e : e_a;
+                        pick = take ? n : pick;
+                        e_pick = take ? e : e_pick;
                         found = found || (pos && cum > target);
                     }
+                    consumers_sync();                           // everybody has read the first exchange
+                    ms.xch[grp][sidx] = make_float4(found ? 1.f : 0.f, e_pick, __int_as_float(pick < 0 ? -1 : pick + NH * grp), 0.f);
+                    consumers_sync();
+                    const float4 s0 = ms.xch[0][sidx], s1 = ms.xch[1][sidx];
+                    // group 0's columns come first: its hit wins; otherwise group 1's hit or, rounding, its last feasible
+                    // node; a group without feasible nodes (pick -1) defers to the other
+                    const bool use1 = !(s0.x > 0.f) && __float_as_int(s1.z) >= 0;
+                    const bool ok0 = __float_as_int(s0.z) >= 0;
+                    act = use1 || !ok0 ? __float_as_int(s1.z) : __float_as_int(s0.z);
+                    e_a = use1 || !ok0 ? s1.y : s0.y;
                 }
                 MS_STAMP(6);
                 if (!fin) {
                     const float lp = __logf(e_a) - __logf(sum);
                     if (!(lp > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
-                    a.actions[(size_t)r * T + t] = act;
-                    if (a.logp) a.logp[(size_t)r * T + t] = lp;
+                    if (writer) {
+                        a.actions[(size_t)r * T + t] = act;
+                        if (a.logp) a.logp[(size_t)r * T + t] = lp;
+                    }
                     llsum += lp;
                     apply(act);
                     MS_STAMP(7);
@@ -624,7 +675,7 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
             }
 
             // ---- outputs of this rollout
-            if (active) {
+            if (writer) {
                 const float2 home = CVRP ? ms.locs[0] : ms.locs[first];    // cvrp/env.py:151-160, tsp/env.py:157-163
                 len += leg(prev.x, prev.y, home.x, home.y);
                 a.reward[r] = -len;
@@ -634,8 +685,8 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                     a.actions[(size_t)r * T + q] = 0;
                     if (a.logp) a.logp[(size_t)r * T + q] = 0.f;
                 }
-                if (status) raise_status(a.status, status);
             }
+            if (active && status) raise_status(a.status, status);   // both threads of a start: each saw half of the logits
         }
     }
 
