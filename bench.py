@@ -196,6 +196,12 @@ def side_configs(dev, peak_hbm, peak_src, quick=False):
     torch.set_num_threads(threads)
     idx = dev.index or 0
     fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12      # TFLOP/s, nominal CUDA-core FMA peak (not in MEASURED_PEAKS.json)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak_tensor = float(json.load(f)["bf16_tflops_sustained"])
+        peak_tensor_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained; fp16 runs at the bf16 rate)"
+    except Exception:  # noqa: BLE001
+        peak_tensor, peak_tensor_src = 1590.0, "fallback (B200_PROFILING.md: 1.59 PFLOP/s dense bf16)"
     out = {}
 
     def pinned(x):
@@ -326,11 +332,18 @@ def side_configs(dev, peak_hbm, peak_src, quick=False):
                         "rollouts_per_s": Bc * S / (ms * 1e-3), "env_steps_per_s": Bc * S * T / (ms * 1e-3),
                         "with_encoder_rollouts_per_s": Bc * S / (ms_full * 1e-3),
                         "mean_reward": float(o["reward"].mean()), "launches_per_step": pol.last_launches, "clocks": clocks,
-                        "roofline": {"bound": "fp32-fma", "achieved": tf, "peak": fp32_peak, "unit": "TFLOP/s",
-                                     "frac": tf / fp32_peak, "traffic": None,
-                                     "flops": "2 x (129*128 + 3*N*E + E*E) MAC per start-step in the reference's op order, "
-                                              "all S*B rollouts stepped until the slowest is done (T steps)",
-                                     "peak_source": "nominal 148 SM x 128 FMA/clk x 1.965 GHz (SURVEY 8d)"}}
+                        "roofline": {"bound": "tensor", "kernel": "am_rollout_ms_tc_kernel<cvrp, sampling> (tcgen05 kind::f16, "
+                                     "starts = TMEM lanes)", "achieved": tf, "peak": peak_tensor, "unit": "TFLOP/s",
+                                     "frac": tf / peak_tensor, "traffic": None,
+                                     "flops": "ALGORITHMIC: 2 x (129*128 + 3*N*E + E*E) MAC per start-step in the reference's op "
+                                              "order, all S*B rollouts stepped until the slowest is done (T steps); the kernel "
+                                              "issues 3 fp16 MMAs per product (hi/lo split) on 128 x 112 padded tiles",
+                                     "peak_source": peak_tensor_src,
+                                     "vs_nominal_fp32_fma_peak": tf / fp32_peak,
+                                     "what_binds": "not the tensor pipe (ncu: sm__pipe_tensor_cycles_active 4.6 % with 64 of 148 SMs "
+                                                   "busy, profiles/r02_c4_pomo_rollout_tc_raw.csv): per score element one MUFU ex2 "
+                                                   "and one fp32->fp16 pack on the quarter-rate pipe, and tcgen05.ld at 64 B/clk/SM "
+                                                   "(900 clk per 128 x 112 fp32 tile) - DESIGN.md section 3"}}
     pol_cpu = R.POMOPolicy(env_name="cvrp").eval()
     pol_cpu.load_state_dict({k: v.cpu() for k, v in pol.state_dict().items()})
     W = oracle_weights_of(pol_cpu)
