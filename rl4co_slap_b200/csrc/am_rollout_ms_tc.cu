@@ -62,6 +62,7 @@ struct Misc {
     float2 locs[128];
     float wc[128];          // cvrp: remaining-capacity column of project_context, pre-scaled
     float gq[128];          // graph context, pre-scaled (0 without one)
+    float stage[kConsumerWarps][32 * 36];   // query build: 32 starts x 32 dims per warp and pass, rows padded to 36 floats
     float4 xch[kGroups][128];   // logit phase: each group's partial (sum of e, best logit, its node, its e) per start
     uint64_t bars[12];
     uint32_t tmem_slot;
@@ -461,31 +462,47 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                 if (!stop) {
                     // ---- this group's half of the query: scale * (gctx + ctx(cur) [+ ctx_first(first)]) [+ scaled capacity
                     //      column * remaining capacity]; every load is issued before the first use
-                    const float *c_row = a.tables + ((size_t)3 * Mrows + b * (int64_t)N + cur) * E + 64 * grp;
-                    const float *f_row = a.tables + ((size_t)4 * Mrows + b * (int64_t)N + first) * E + 64 * grp;
+                    // The rows are gathered by the WARP, not by the thread: 8 lanes fetch one start's 32 dims as a full
+                    // 128-byte line (4 starts per instruction) into a padded staging tile, from which every thread takes
+                    // its own row - 64 line requests per warp and step instead of 512 thread-private ones.
+                    const float *ctx_tab = a.tables + ((size_t)3 * Mrows + b * (int64_t)N) * E + 64 * grp + 4 * (lane & 7);
+                    const float *first_tab = a.tables + ((size_t)4 * Mrows + b * (int64_t)N) * E + 64 * grp + 4 * (lane & 7);
                     const float rem = CVRP ? __fsub_rn(cap, used) : 0.f;
-                    float4 x[16];
+                    const float qs = fin ? 0.f : 1.f;           // finished / unused lanes: a zero query
+                    float *stg = ms.stage[warp - 1];
+                    float4 g[2][8];                             // every load of both passes is in flight before the first use
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) x[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (!fin) {
+                    for (int it = 0; it < 8; ++it) {
+                        const int src = 4 * it + (lane >> 3);
+                        const int cur_s = __shfl_sync(0xffffffffu, cur, src);
+                        const int fin_s = __shfl_sync(0xffffffffu, (int)fin, src);
+                        const int first_s = CVRP ? 0 : __shfl_sync(0xffffffffu, first, src);
 #pragma unroll
-                        for (int k = 0; k < 16; ++k) x[k] = __ldg(reinterpret_cast<const float4 *>(c_row + 4 * k));
-                        if (!CVRP) {
+                        for (int pass = 0; pass < 2; ++pass) {
+                            g[pass][it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (!fin_s) g[pass][it] = __ldg(reinterpret_cast<const float4 *>(ctx_tab + (size_t)cur_s * E + 32 * pass));
+                        }
+                        if (!CVRP && !fin_s) {
 #pragma unroll
-                            for (int k = 0; k < 16; ++k) {
-                                const float4 f = __ldg(reinterpret_cast<const float4 *>(f_row + 4 * k));
-                                x[k].x += f.x; x[k].y += f.y; x[k].z += f.z; x[k].w += f.w;
+                            for (int pass = 0; pass < 2; ++pass) {
+                                const float4 f = __ldg(reinterpret_cast<const float4 *>(first_tab + (size_t)first_s * E + 32 * pass));
+                                g[pass][it].x += f.x; g[pass][it].y += f.y; g[pass][it].z += f.z; g[pass][it].w += f.w;
                             }
                         }
                     }
-                    const float qs = fin ? 0.f : 1.f;           // finished / unused lanes: a zero query
+                    MS_STAMP(11);
 #pragma unroll
-                    for (int half = 0; half < 2; ++half) {
+                    for (int pass = 0; pass < 2; ++pass) {      // 32 dims per pass through the staging tile
+#pragma unroll
+                        for (int it = 0; it < 8; ++it)
+                            *reinterpret_cast<float4 *>(stg + (4 * it + (lane >> 3)) * 36 + 4 * (lane & 7)) = g[pass][it];
+                        __syncwarp();
+                        if (pass == 0) MS_STAMP(12);
                         uint32_t hi[16], lo[16];
 #pragma unroll
                         for (int k = 0; k < 8; ++k) {
-                            const int dl = 32 * half + 4 * k;   // dim within this group's 64
-                            float4 v = x[8 * half + k];
+                            const int dl = 32 * pass + 4 * k;   // dim within this group's 64
+                            float4 v = *reinterpret_cast<const float4 *>(stg + lane * 36 + 4 * k);
                             const float4 gq = *reinterpret_cast<const float4 *>(&ms.gq[64 * grp + dl]);
                             v.x = fmaf(v.x, kScoreScale, gq.x); v.y = fmaf(v.y, kScoreScale, gq.y);
                             v.z = fmaf(v.z, kScoreScale, gq.z); v.w = fmaf(v.w, kScoreScale, gq.w);
@@ -497,11 +514,14 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
                             split2(v.x * qs, v.y * qs, hi[2 * k], lo[2 * k]);
                             split2(v.z * qs, v.w * qs, hi[2 * k + 1], lo[2 * k + 1]);
                         }
-                        tmem_st16(tl + C_QH + 32u * grp + 16u * half, hi);
-                        tmem_st16(tl + C_QL + 32u * grp + 16u * half, lo);
+                        __syncwarp();                           // the tile is rewritten by the next pass
+                        tmem_st16(tl + C_QH + 32u * grp + 16u * pass, hi);
+                        tmem_st16(tl + C_QL + 32u * grp + 16u * pass, lo);
                     }
+                    MS_STAMP(13);
                 }
                 tmem_st_wait();
+                MS_STAMP(14);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[B_QREADY]);

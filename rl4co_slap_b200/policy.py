@@ -300,11 +300,18 @@ class AttentionModelPolicy(nn.Module):
         launches = 0
 
         chunk = B if S > 0 else min(B, max(1, int(self.rollout_chunk)))
+        # train-mode batch norm takes its statistics over the batch it is given: a chunked encoder pass would normalise
+        # every chunk differently (and update the running statistics once per chunk), so in that case the encoder sees
+        # the whole batch once and only the projection / rollout kernels are chunked
+        whole_init = None
+        if hidden is None and chunk < B and self.encoder.training and any(
+                isinstance(m, nn.modules.batchnorm._BatchNorm) for m in self.encoder.modules()):
+            hidden, whole_init = self.encoder(td)
         for c0 in range(0, B, chunk):
             c1 = min(B, c0 + chunk)
             Bc = c1 - c0
             if hidden is not None:
-                h, init_h = hidden[c0:c1], None
+                h, init_h = hidden[c0:c1], (whole_init[c0:c1] if whole_init is not None else None)
             else:
                 h, init_h = self.encoder(td[c0:c1] if (c0, c1) != (0, B) else td)
             h = h.detach().float().contiguous()

@@ -583,3 +583,24 @@ def test_slap_large_batch_parity_on_a_subsample(dev):
     refs = port.am_rollout("slap", state(), h[idx].cpu(), W, actions=smp["actions"][idx].cpu())
     torch.testing.assert_close(smp["reward"][idx].cpu(), refs["reward"], rtol=RTOL, atol=1e-5)
     torch.testing.assert_close(smp["log_likelihood"][idx].cpu(), refs["log_likelihood"], rtol=RTOL, atol=2e-5)
+
+
+def test_train_mode_batch_norm_sees_the_whole_batch_once(dev):
+    """chunked rollouts must not chunk a train-mode batch-norm encoder: same hidden states (hence tours) as an unchunked
+    call, and the running statistics move exactly once per forward"""
+    torch.manual_seed(21)
+    env = R.TSPEnv(generator_params=dict(num_loc=20), device=dev)
+    td = env.reset(batch_size=[96])
+    pol = R.AttentionModelPolicy(env_name="tsp", num_encoder_layers=2).to(dev).train()
+    bn = next(m for m in pol.encoder.modules() if isinstance(m, torch.nn.BatchNorm1d))
+    sd = {k: v.clone() for k, v in pol.state_dict().items()}
+    with torch.no_grad():
+        whole = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True)
+        n1 = int(bn.num_batches_tracked)
+        pol.load_state_dict(sd)
+        pol.rollout_chunk = 32
+        parts = pol(td, env, decode_type="greedy", return_actions=True, return_hidden=True)
+        n2 = int(bn.num_batches_tracked)
+    assert n1 == n2 == int(sd[[k for k in sd if k.endswith("num_batches_tracked")][0]]) + 1
+    torch.testing.assert_close(parts["hidden"].node_embeddings, whole["hidden"].node_embeddings, rtol=0, atol=0)
+    assert torch.equal(parts["actions"], whole["actions"])

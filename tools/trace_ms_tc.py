@@ -60,4 +60,8 @@ print(f"{name}100 S={S}: rollout 0 ran {n} steps, status {int(status.item())}, m
 m = d.mean(0)
 print("per step: " + "  ".join(f"{k} {v:.0f}" for k, v in zip(names, m)))
 print(f"   inside the heads: waiting for scores {tr[:, 8].mean():.0f}  waiting for P V {tr[:, 9].mean():.0f}  softmax arithmetic {tr[:, 10].mean():.0f}")
+if tr[:, 11].any():
+    q = tr[:, [0, 11, 12, 13, 14, 1]]
+    print("   inside the query phase: " + "  ".join(f"{k} {v:.0f}" for k, v in zip(
+        ["shuffles + loads issued", "loads landed + staged", "two passes of math + tcgen05.st", "wait::st", "fence + arrive"], np.diff(q, axis=1).mean(0))))
 print("step start to next step start:", (tr[1:, 0] - tr[:-1, 0]).mean())
