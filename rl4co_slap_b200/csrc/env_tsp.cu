@@ -203,29 +203,32 @@ tsp_replay_persistent_kernel(int64_t B, int N, int T, const float *__restrict__ 
     const bool mask4 = mask != nullptr && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
     const unsigned un = (unsigned)N;
 
-    float4 l0, l1, nl0, nl1;
-    longlong2 a0, a1, na0, na1;
-    auto load = [&](int64_t b, float4 &x0, float4 &x1, longlong2 &y0, longlong2 &y1) {
-        x0 = x1 = make_float4(0.f, 0.f, 0.f, 0.f);
-        y0 = y1 = make_longlong2(0, 0);
-        if (b >= B) return;
-        const float4 *lv = reinterpret_cast<const float4 *>(locs + b * (int64_t)N * 2);
-        const longlong2 *av = reinterpret_cast<const longlong2 *>(actions + b * (int64_t)T);
-        if (lane < nl) x0 = __ldg(lv + lane);
-        if (lane + 32 < nl) x1 = __ldg(lv + lane + 32);
-        if (lane < na) y0 = __ldg(av + lane);
-        if (lane + 32 < na) y1 = __ldg(av + lane + 32);
+    // this lane's pieces of an instance's rows; the pointers advance by one warp stride per iteration (no 64-bit
+    // multiplies in the loop), lanes without a piece never use theirs
+    const bool has_l0 = lane < nl, has_l1 = lane + 32 < nl, has_a0 = lane < na, has_a1 = lane + 32 < na;
+    int64_t b = blockIdx.x * (int64_t)kWarpsPerCta + warp;
+    const float4 *lv = reinterpret_cast<const float4 *>(locs + b * (int64_t)N * 2) + lane;
+    const longlong2 *av = reinterpret_cast<const longlong2 *>(actions + b * (int64_t)T) + lane;
+    const int64_t lv_step = stride * (int64_t)nl, av_step = stride * (int64_t)na;
+    float4 l0 = make_float4(0.f, 0.f, 0.f, 0.f), l1 = l0, nl0 = l0, nl1 = l0;
+    longlong2 a0 = make_longlong2(0, 0), a1 = a0, na0 = a0, na1 = a0;
+    auto load = [&](bool valid, float4 &x0, float4 &x1, longlong2 &y0, longlong2 &y1) {
+        if (valid && has_l0) x0 = __ldg(lv);
+        if (valid && has_l1) x1 = __ldg(lv + 32);
+        if (valid && has_a0) y0 = __ldg(av);
+        if (valid && has_a1) y1 = __ldg(av + 32);
+        lv += lv_step;
+        av += av_step;
     };
     for (int q = lane; q < 136; q += 32) sa[q] = 0;  // the tail beyond T is read (never used) by the 16-byte action loads
-    int64_t b = blockIdx.x * (int64_t)kWarpsPerCta + warp;
-    load(b, l0, l1, a0, a1);
+    load(b < B, l0, l1, a0, a1);
     int st = 0;
     for (; b < B; b += stride) {
-        load(b + stride, nl0, nl1, na0, na1);       // next instance in flight
+        load(b + stride < B, nl0, nl1, na0, na1);   // next instance in flight
         __syncwarp();                               // the previous instance's gathers are done
         // ---- stage: coordinates as they come (two nodes per 16 bytes), the seen array cleared
-        if (lane < nl) reinterpret_cast<float4 *>(sl)[lane] = l0;
-        if (lane + 32 < nl) reinterpret_cast<float4 *>(sl)[lane + 32] = l1;
+        if (has_l0) reinterpret_cast<float4 *>(sl)[lane] = l0;
+        if (has_l1) reinterpret_cast<float4 *>(sl)[lane + 32] = l1;
         seen[lane] = 0u;
         __syncwarp();
         // ---- actions as int (range checked), one seen byte each
@@ -238,26 +241,23 @@ tsp_replay_persistent_kernel(int64_t B, int N, int T, const float *__restrict__ 
             seen8[ai] = 1;
             over |= ai >= T;
         };
-        if (lane < na) { put(2 * lane, a0.x); put(2 * lane + 1, a0.y); }
-        if (lane + 32 < na) { put(2 * lane + 64, a1.x); put(2 * lane + 65, a1.y); }
+        if (has_a0) { put(2 * lane, a0.x); put(2 * lane + 1, a0.y); }
+        if (has_a1) { put(2 * lane + 64, a1.x); put(2 * lane + 65, a1.y); }
         __syncwarp();
         const unsigned word = seen[lane];           // bytes 0 / 1 of nodes 4 lane .. 4 lane + 3
         const int visited = __reduce_add_sync(kFull, __popc(word));
         // validity: sort(actions) == arange(T) (tsp/env.py:165-173)  <=>  T distinct values, all < T
         const int bad = __any_sync(kFull, over) || visited != T;
         // ---- tour length (utils/ops.py:93-101): legs a_t -> a_{t+1}, closed; lane owns t = 4 lane .. 4 lane + 3
-        float len = 0.f;
+        // (branch free: entries of `sa` beyond T are 0, legs beyond T are computed and dropped)
         const int t0 = 4 * lane;
-        if (t0 < T) {
-            const int4 a4 = *reinterpret_cast<const int4 *>(sa + t0);
-            const float2 home = sl[sa[0]];
-            const float2 p0 = sl[a4.x], p1 = sl[a4.y], p2 = sl[a4.z], p3 = sl[a4.w], p4 = sl[sa[t0 + 4]];
-            // leg k runs from node t0 + k to its successor; the successor of step T - 1 is step 0
-            len = leg_fast(p0, t0 + 1 == T ? home : p1);
-            if (t0 + 1 < T) len += leg_fast(p1, t0 + 2 == T ? home : p2);
-            if (t0 + 2 < T) len += leg_fast(p2, t0 + 3 == T ? home : p3);
-            if (t0 + 3 < T) len += leg_fast(p3, t0 + 4 == T ? home : p4);
-        }
+        const int4 a4 = *reinterpret_cast<const int4 *>(sa + t0);
+        const float2 home = sl[sa[0]];
+        const float2 p0 = sl[a4.x], p1 = sl[a4.y], p2 = sl[a4.z], p3 = sl[a4.w], p4 = sl[sa[t0 + 4]];
+        // leg k runs from node t0 + k to its successor; the successor of step T - 1 is step 0
+        const float g0 = leg_fast(p0, t0 + 1 == T ? home : p1), g1 = leg_fast(p1, t0 + 2 == T ? home : p2);
+        const float g2 = leg_fast(p2, t0 + 3 == T ? home : p3), g3 = leg_fast(p3, t0 + 4 == T ? home : p4);
+        float len = ((t0 < T ? g0 : 0.f) + (t0 + 1 < T ? g1 : 0.f)) + ((t0 + 2 < T ? g2 : 0.f) + (t0 + 3 < T ? g3 : 0.f));
         len = warp_sum(len);
         // ---- final state after T steps (tsp/env.py:83-93)
         if (mask) {
