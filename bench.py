@@ -226,6 +226,20 @@ def side_configs(dev, peak_hbm, peak_src, quick=False):
 
     ms, reps, clocks = timed_region(c1_step, idx, 0.6 if quick else 1.5)
     gpu_mean = float(host_reward.mean())
+    # the same step with encoder + K3 + K2 captured as one CUDA graph (policy.graphed): B = 512 is launch bound
+    with torch.inference_mode():
+        td_static = env.reset(R.TensorDict({"locs": dlocs}, batch_size=[B]))
+        fast = pol.graphed(td_static, env, decode_type="greedy")
+
+    def c1_graph_step():
+        dlocs.copy_(host_locs, non_blocking=True)       # dlocs IS the captured input buffer
+        o = fast(td_static)
+        host_reward.copy_(o["reward"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    with torch.inference_mode():
+        ms_graph, reps_graph, _ = timed_region(c1_graph_step, idx, 0.4 if quick else 1.0)
+    graph_mean = float(host_reward.mean())
     W = oracle_weights_of(pol_cpu)
     ref = {}
 
@@ -241,6 +255,10 @@ def side_configs(dev, peak_hbm, peak_src, quick=False):
                     "(BASELINE configs[0]); GPU arm end to end from pinned host coordinates to host rewards",
         "batch": B, "ms_per_step": ms, "reps": reps, "rollouts_per_s": B / (ms * 1e-3), "env_steps_per_s": B * N / (ms * 1e-3),
         "mean_reward": gpu_mean, "launches_per_step": pol.last_launches, "clocks": clocks,
+        "cuda_graph": {"ms_per_step": ms_graph, "reps": reps_graph, "rollouts_per_s": B / (ms_graph * 1e-3),
+                       "mean_reward": graph_mean,
+                       "what": "policy.graphed(): the same end-to-end step (H2D, encoder, K3, K2, D2H) with the kernels "
+                               "replayed as one CUDA graph instead of ~27 eager launches"},
         "roofline": {"bound": "hbm", "achieved": B * algo / (ms * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
                      "frac": B * algo / (ms * 1e-3) / 1e9 / peak_hbm, "traffic": None,
                      "note": "512 instances are 3.5 per SM: launch / latency bound, not a bandwidth case"},

@@ -604,3 +604,37 @@ def test_train_mode_batch_norm_sees_the_whole_batch_once(dev):
     assert n1 == n2 == int(sd[[k for k in sd if k.endswith("num_batches_tracked")][0]]) + 1
     torch.testing.assert_close(parts["hidden"].node_embeddings, whole["hidden"].node_embeddings, rtol=0, atol=0)
     assert torch.equal(parts["actions"], whole["actions"])
+
+
+@pytest.mark.parametrize("name,num_loc,B", (("tsp", 50, 512), ("slap", None, 64)))
+def test_graphed_rollout_equals_eager_and_replays_on_new_data(name, num_loc, B, dev):
+    """policy.graphed(): encoder + projection + rollout captured as one CUDA graph; replays on fresh instances give exactly
+    the eager results, the captured output tensors are reused, and device-side assertions still surface"""
+    torch.manual_seed(31)
+    gp = dict(num_loc=num_loc) if name == "tsp" else {"n_aisles": 10, "n_locs": 10}
+    env = R.get_env(name, device=dev, generator_params=gp, check_solution=False)
+    pol = load_policy(name, dev)
+    td0 = env.reset(env.generator(B).to(dev))
+    with torch.inference_mode():
+        fast = pol.graphed(td0, env, decode_type="greedy", return_actions=True)
+        for seed in (1, 2):
+            torch.manual_seed(seed)
+            td = env.reset(env.generator(B).to(dev))
+            want = pol(td, env, decode_type="greedy", return_actions=True)
+            got = fast(td)
+            assert torch.equal(got["actions"], want["actions"])
+            assert torch.equal(got["reward"], want["reward"]) and torch.equal(got["log_likelihood"], want["log_likelihood"])
+        first_ptr = got["actions"].data_ptr()
+        assert fast(td)["actions"].data_ptr() == first_ptr
+    with pytest.raises(NotImplementedError):
+        pol.graphed(td0, env, decode_type="sampling")
+    if name == "tsp":   # a NaN coordinate -> NaN logits: the status word is read after the replay
+        bad = td.clone()
+        bad["locs"] = td["locs"].clone()
+        bad["locs"][3, 7, 0] = float("nan")
+        with pytest.raises(AssertionError, match="Logits contain NaNs|infeasible action selected"):
+            with torch.inference_mode():
+                fast(bad)
+        with torch.inference_mode():
+            again = fast(td)                    # and the next replay is clean again
+        assert torch.equal(again["actions"], want["actions"])
