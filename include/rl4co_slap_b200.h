@@ -335,6 +335,21 @@ typedef struct rl4co_am_rollout_args {
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);
 
+/* Backward of the teacher-forced log-likelihood: what REINFORCE.calculate_loss differentiates
+ * (rl4co/models/rl/reinforce/reinforce.py:73-115 through ConstructivePolicy.forward with decode_type="evaluate",
+ * models/common/constructive/base.py:206-207,253-265).  Recompute based - nothing is saved by the rollout:
+ *   args      as for rl4co_am_rollout in RL4CO_MODE_EVALUATE (tables, gctx, q0 / wcap, demand, vehicle_capacity,
+ *             actions_in [R,T], multistart / S / num_loc); tsp and cvrp, standard logit post-processing,
+ *             N <= rl4co_am_evaluate_backward_max_nodes() (the instance's gradient accumulators live in shared memory)
+ *   grad_ll   [R] dL / d log_likelihood of every rollout
+ * Outputs, all into CALLER-ZEROED buffers (small batches spread the starts of an instance over several CTAs that meet
+ * through atomics): g_tables [n_tables][B*N][128], g_gctx [B,128] (may be NULL), g_q0 [128] (tsp) and g_wcap [128]
+ * (cvrp) (may be NULL).  The gradients with respect to the encoder output and the decoder weights follow from the table
+ * projection, which stays with the caller (training.py keeps it as differentiable torch ops). */
+int rl4co_am_evaluate_backward_max_nodes(void);
+int rl4co_am_evaluate_backward(const rl4co_am_rollout_args *args, const float *grad_ll, float *g_tables,
+                               float *g_gctx, float *g_q0, float *g_wcap, rl4co_stream_t stream);
+
 /* rl4co_am_rollout with its scratch memory held by the library.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot allocate device memory around the call (code under CUDA-graph
  * capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch of the rollout path is the table block

@@ -91,6 +91,8 @@ _SIGNATURES = {
     "rl4co_am_graph_context": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_am_rollout": ([C.POINTER(AmRolloutArgs), _p], C.c_int),
     "rl4co_am_rollout_static": ([C.POINTER(AmRolloutArgs), _p, _p, _p], C.c_int),
+    "rl4co_am_evaluate_backward_max_nodes": ([], C.c_int),
+    "rl4co_am_evaluate_backward": ([C.POINTER(AmRolloutArgs), _p, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_set_rollout_impl": ([C.c_int], C.c_int),
     "rl4co_decode_step": ([_i64, _i32, _p, _p, _i32, _f32, _f32, _i32, _p, _u64, _u64, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_reward_stats": ([_i64, _p, _p, _p], C.c_int),

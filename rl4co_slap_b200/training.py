@@ -218,8 +218,101 @@ def teacher_forced_log_likelihood(policy, td, env_name: str, h: torch.Tensor, ac
     return logp.sum(1) if return_sum else logp
 
 
+# ---- the same log-likelihood through the kernels, differentiable -------------------------------------------------
+class _KernelLogLikelihood(torch.autograd.Function):
+    """ll [R] of given tours from the rollout tables: forward = the rollout kernel in evaluate mode, backward =
+    rl4co_am_evaluate_backward (csrc/am_backward.cu, recompute based).  Differentiable inputs: tables
+    [n_tables, B*N, 128], gctx [B,128] or None, q0 [128] (tsp) or None, wcap [128] (cvrp) or None."""
+
+    @staticmethod
+    def _args(meta, tables, gctx, q0, wcap):
+        from . import _lib
+        a = _lib.AmRolloutArgs()
+        a.env, a.mode = _lib.ENV_IDS[meta["env"]], _lib.MODE_EVALUATE
+        a.B, a.S, a.multistart, a.num_loc = meta["B"], meta["S"], int(meta["S"] > 0), meta["num_loc"]
+        a.N, a.T, a.n_tables = meta["N"], meta["T"], tables.shape[0]
+        a.temperature, a.tanh_clipping, a.mask_logits = 1.0, meta["clip"], 1
+        a.tables, a.gctx, a.q0, a.wcap = _lib.ptr(tables), _lib.ptr(gctx), _lib.ptr(q0), _lib.ptr(wcap)
+        a.locs = _lib.ptr(meta["locs"])
+        a.demand, a.vehicle_capacity = _lib.ptr(meta.get("demand")), _lib.ptr(meta.get("capacity"))
+        a.actions_in = _lib.ptr(meta["actions"])
+        return a
+
+    @staticmethod
+    def forward(ctx, tables, gctx, q0, wcap, meta):
+        from . import _lib
+        dev, R, T = tables.device, meta["actions"].shape[0], meta["T"]
+        tables, gctx = tables.contiguous(), (gctx.contiguous() if gctx is not None else None)
+        q0, wcap = (q0.contiguous() if q0 is not None else None), (wcap.contiguous() if wcap is not None else None)
+        out = {"actions": torch.empty(R, T, dtype=torch.int64, device=dev), "ll": torch.empty(R, device=dev),
+               "reward": torch.empty(R, device=dev), "status": _lib.new_status(dev)}
+        a = _KernelLogLikelihood._args(meta, tables, gctx, q0, wcap)
+        a.actions, a.ll, a.reward, a.status = _lib.ptr(out["actions"]), _lib.ptr(out["ll"]), _lib.ptr(out["reward"]), _lib.ptr(out["status"])
+        _lib.check(_lib.load().rl4co_am_rollout(a, _lib.stream_ptr(dev)), "rl4co_am_rollout")
+        _lib.raise_for_status(out["status"])
+        ctx.meta = meta
+        ctx.save_for_backward(tables, *(x for x in (gctx, q0, wcap) if x is not None))
+        ctx.have = (gctx is not None, q0 is not None, wcap is not None)
+        return out["ll"]
+
+    @staticmethod
+    def backward(ctx, grad_ll):
+        from . import _lib
+        saved = list(ctx.saved_tensors)
+        tables = saved.pop(0)
+        gctx, q0, wcap = (saved.pop(0) if have else None for have in ctx.have)
+        dev = tables.device
+        g_tables = torch.zeros_like(tables)
+        g_gctx = torch.zeros_like(gctx) if gctx is not None else None
+        g_q0 = torch.zeros_like(q0) if q0 is not None else None
+        g_wcap = torch.zeros_like(wcap) if wcap is not None else None
+        a = _KernelLogLikelihood._args(ctx.meta, tables, gctx, q0, wcap)
+        _lib.check(_lib.load().rl4co_am_evaluate_backward(
+            a, _lib.ptr(grad_ll.contiguous().float()), _lib.ptr(g_tables), _lib.ptr(g_gctx), _lib.ptr(g_q0), _lib.ptr(g_wcap),
+            _lib.stream_ptr(dev)), "rl4co_am_evaluate_backward")
+        return g_tables, g_gctx, g_q0, g_wcap, None
+
+
+def kernel_backward_supported(policy, env_name: str, h: torch.Tensor) -> bool:
+    from . import _lib
+    return (h.is_cuda and env_name in ("tsp", "cvrp") and policy.tanh_clipping > 0 and policy.temperature == 1.0
+            and bool(policy.mask_logits) and h.shape[1] <= int(_lib.load().rl4co_am_evaluate_backward_max_nodes()))
+
+
+def kernel_log_likelihood(policy, td, env_name: str, h: torch.Tensor, actions: torch.Tensor, num_starts: int = 0) -> torch.Tensor:
+    """The log-likelihood of :func:`teacher_forced_log_likelihood`, [R], with forward AND backward in the kernels.
+    The table projection (am/decoder.py:208-237 with project_out and the context projection folded in, as in
+    policy.AttentionModelDecoder._fold_weights) is built here with differentiable torch ops, so autograd carries the
+    kernel's table gradients on into ``h`` (the encoder) and every decoder weight."""
+    dec = policy.decoder
+    E = dec.embed_dim
+    B, N, _ = h.shape
+    Wn = dec.project_node_embeddings.weight
+    Wc = dec.context_embedding.project_context.weight
+    parts = [Wn[:E], Wn[E:2 * E], dec.pointer.project_out.weight.t() @ Wn[2 * E:]]
+    q0 = wcap = None
+    if env_name == "tsp":
+        parts += [Wc[:, E:], Wc[:, :E]]
+        q0 = Wc @ dec.context_embedding.W_placeholder
+    else:
+        parts += [Wc[:, :E]]
+        wcap = Wc[:, E]
+    nt = len(parts)
+    tables = F.linear(h.float(), torch.cat(parts, 0)).view(B * N, nt, E).permute(1, 0, 2).contiguous()
+    gctx = dec.project_fixed_context(h.float().mean(1)) if dec.use_graph_context else None
+    S = int(num_starts)
+    meta = {"env": env_name, "B": B, "S": S, "N": N, "T": actions.shape[1], "clip": float(policy.tanh_clipping),
+            "num_loc": N - (0 if env_name == "tsp" else 1), "locs": td["locs"].float().contiguous(),
+            "actions": actions.contiguous()}
+    if env_name == "cvrp":
+        meta["demand"] = td["demand"].float().contiguous()
+        meta["capacity"] = td["vehicle_capacity"].float().contiguous()
+    return _KernelLogLikelihood.apply(tables, gctx, q0, wcap, meta)
+
+
 def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: Optional[str] = None,
-                   num_starts: Optional[int] = None, max_grad_norm: Optional[float] = 1.0) -> dict:
+                   num_starts: Optional[int] = None, max_grad_norm: Optional[float] = 1.0,
+                   backward: str = "auto") -> dict:
     """One REINFORCE training step (reinforce.py:62-115, pomo/model.py:87-111): roll out with the fused kernel
     (no autograd), re-evaluate the sampled trajectories' log-likelihood differentiably, loss
     ``((reward - baseline) * log_likelihood).mean()`` on the negated... exactly ``-(advantage * ll).mean()`` as in
@@ -238,7 +331,13 @@ def reinforce_step(policy, env, td, optimizer=None, baseline=None, decode_type: 
     actions, reward = out["actions"], out["reward"]
     B = td["locs"].shape[0]
     S = actions.shape[0] // B if multistart else 0
-    ll = teacher_forced_log_likelihood(policy, td, env.name, h.float(), actions, num_starts=S)
+    # differentiable re-evaluation of the sampled tours: the backward kernel where it applies (tsp / cvrp, standard logit
+    # post-processing), the batched PyTorch pass otherwise; ``backward`` = "kernel" / "torch" forces one of them
+    use_kernel = backward == "kernel" or (backward == "auto" and kernel_backward_supported(policy, env.name, h))
+    if use_kernel:
+        ll = kernel_log_likelihood(policy, td, env.name, h, actions, num_starts=S)
+    else:
+        ll = teacher_forced_log_likelihood(policy, td, env.name, h.float(), actions, num_starts=S)
     if baseline is None:
         bl = torch.zeros_like(reward)
     elif isinstance(baseline, str) and baseline == "shared":
