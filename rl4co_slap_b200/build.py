@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librl4co_slap_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["abi.cu", "env_tsp.cu", "env_atsp.cu", "env_cvrp.cu", "env_sdvrp.cu", "env_slap.cu", "env_op.cu", "env_pctsp.cu", "am_project.cu", "am_project_tc.cu", "am_rollout.cu", "am_rollout_rf.cu", "am_rollout_tsp.cu", "am_rollout_static.cu", "am_rollout_ms_tc.cu", "am_backward.cu",
+SOURCES = ["abi.cu", "env_tsp.cu", "env_atsp.cu", "env_cvrp.cu", "env_sdvrp.cu", "env_slap.cu", "env_op.cu", "env_pctsp.cu", "am_project.cu", "am_project_tc.cu", "am_rollout.cu", "am_rollout_rf.cu", "am_rollout_tsp.cu", "am_rollout_slap.cu", "am_rollout_static.cu", "am_rollout_ms_tc.cu", "am_backward.cu",
            "decode_reduce.cu", "pomo_epilogue.cu", "encoder_attention.cu", "encoder_attention_tc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]

@@ -545,6 +545,8 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     if (g_rollout_impl == 0 && rollout_ms_tc_supports(a)) return launch_rollout_ms_tc(a, (cudaStream_t)stream);
     // TSP greedy single start: register-file kernel with node compaction (am_rollout_tsp.cu)
     if (g_rollout_impl == 0 && rollout_tsp_greedy_supports(a)) return launch_rollout_tsp_greedy(a, (cudaStream_t)stream);
+    // slap: the query never changes, so the glimpse is maintained incrementally (am_rollout_slap.cu)
+    if (g_rollout_impl == 0 && rollout_slap_supports(a)) return launch_rollout_slap(a, (cudaStream_t)stream);
     // single-start rollouts: register-file resident kernel (am_rollout_rf.cu)
     if (g_rollout_impl != 1 && rollout_rf_supports(a)) return launch_rollout_rf(a, (cudaStream_t)stream);
 

@@ -109,4 +109,9 @@ bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a);
 int launch_rollout_ms_tc(const rl4co_am_rollout_args &a, cudaStream_t stream);
 bool rollout_ms_tc_supports(const rl4co_am_rollout_args &a);
 
+
+// slap: constant query, incrementally maintained glimpse, two CTAs per SM (am_rollout_slap.cu)
+int launch_rollout_slap(const rl4co_am_rollout_args &a, cudaStream_t stream);
+bool rollout_slap_supports(const rl4co_am_rollout_args &a);
+
 }  // namespace rl4co
