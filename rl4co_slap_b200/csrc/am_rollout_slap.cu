@@ -2,28 +2,46 @@
 //
 // What SLAP allows that the routing envs do not: its context embedding returns zeros (`SLAPContext`,
 // examples/slap.py:11-84 - the wiring BASELINE.json names), so the decoder query is the projected graph context
-// alone (am/decoder.py:141-142) and the glimpse QUERY IS THE SAME AT EVERY STEP
-// of a trajectory and so are the glimpse scores s[h][n] = <q_h, K[n]_h>.  Only the mask changes, and it only
-// ever loses the one node that was just assigned (slap/env.py:38-93).  The per-step glimpse (attention.py:289-306)
-//     o_h = sum_{n alive} 2^(s[n] - m) V[n]_h / sum_{n alive} 2^(s[n] - m),      m = max_{n alive} s[n]
-// is therefore maintained INCREMENTALLY: numerator O_h and denominator Z_h are kept in fp64 and lose the term of
-// the assigned node, O_h -= e_a V[a]_h, Z_h -= e_a.  As long as the node that holds the maximum is alive, m is the
-// value the reference's softmax subtracts too, every e_n is bit-identical to the one the step-by-step kernel
-// forms, Z >= 1, and a subtraction cancels at most half of the magnitude (fp64 keeps the accumulated error
-// ~1e-15).  When the maximum node itself is assigned (its e is exactly 1.0f) the head is recomputed from its
-// stored scores with the new maximum - one pass over the V rows, from L2.
+// alone (am/decoder.py:141-142) and the glimpse QUERY IS THE SAME AT EVERY STEP of a trajectory, and so are the
+// glimpse scores s[h][n] = <q_h, K[n]_h>.  Only the mask changes, and it only ever loses the one location that
+// was just assigned (slap/env.py:38-93).  The per-step glimpse (attention.py:289-306)
+//     o_h = sum_{n alive} 2^(s[n] - m) V[n]_h / sum_{n alive} 2^(s[n] - m)
+// is therefore maintained INCREMENTALLY.  The numerator is defined as the sum of the individually rounded products
+// fl(e_n V[n]) (what an fp32 implementation adds up anyway) and, like the denominator, is held as a two-float value
+// hi + lo: built with error-free TwoSum additions, and reduced at every step by adding -fl(e_a V[a]), -e_a of the
+// assigned location the same way - which removes exactly what the build put in.  What remains is therefore the sum
+// over the alive locations to ~2^-44 of the sum it STARTED from, i.e. still to fp32 accuracy after the remainder
+// has shrunk by many orders of magnitude (a plain fp32 starting sum would not do: its rounding error is small
+// against the full sum only, and the first dominant location to leave would expose it).  When what is left of a
+// head's denominator falls below 2^-16 of its value at the last scaling (the head was concentrated on locations that
+// are gone; exponentials of the others may have been flushed to zero), every head is rebuilt from the stored scores
+// with the maximum of the nodes still alive - the softmax shift the reference uses at that step.  Any shift gives the
+// same quotient; the exponentials differ from the step-by-step kernel's by the rounding of ex2.approx (2^-22), the
+// same class of error that kernel has.
 //
 // Per step that leaves ONE mat-vec, the pointer logits <o, L'[n]> (project_out folded into L', attention.py:
-// 276-282), instead of three; only L' stays in registers (56 per thread at N <= 112), so TWO CTAs fit an SM and
-// cover each other's barrier and shuffle latency.  K and V stream through once per instance.
+// 276-282), and a step is a latency chain, not arithmetic.  Ownership is therefore NODE-major, so that a step has
+// a single block barrier and no exchange of partial logits through shared memory:
+//   warp w owns the NW consecutive nodes w NW .. w NW + NW - 1; lane l owns dims 4l .. 4l+3 (head l >> 2) of their
+//   logit keys, in registers for the whole trajectory (NW = 13 at N = 100: 52 registers);
+//   every warp keeps the whole glimpse state redundantly, lane l its own 4 dims of O and its head's Z;
+//   logits: NW register dot products per lane, one 32-lane transposing butterfly (16 shuffles) that leaves the
+//   full logit of node w NW + (l >> 1) in lane l; tanh clip, mask, (Gumbel noise), warp arg-max by two redux;
+//   the 8 warp winners meet in shared memory (double buffered), ONE barrier, every warp picks the block winner;
+//   update of O, Z from shared memory: e[h][a] (formed once per scaling) and the value row V[a] (the instance's
+//   value table is landed in shared memory by TMA one instance ahead; logit keys are loaded one instance ahead
+//   into the registers the finished instance no longer needs).
+// Two CTAs per SM (about 84 KB of shared memory and 128 registers each) cover each other's chains.
 //
-// Ownership as in am_rollout_rf.cu: warp = head, lane = (hh, g), the thread owns nodes g + 16 j and 8 dims.
-// Selection, Gumbel noise keying, log-prob bookkeeping and outputs are the same as in that kernel, so for the
-// same seed a sampled rollout picks the same nodes unless a logit differs in the last bits.
+// Selection, Gumbel noise keying, log-prob bookkeeping and outputs follow am_rollout_rf.cu, so for the same seed a
+// sampled rollout picks the same locations unless a logit differs in the last bits.  Restricted to the standard
+// logit post-processing (tanh clipping, temperature 1, masked logits); anything else runs on am_rollout_rf.cu.
 //
 // Reference op order being reproduced: SURVEY.md appendix A; rl4co/models/zoo/am/decoder.py:134-200,
 // rl4co/models/nn/attention.py:263-309, rl4co/utils/decoding.py:141-191,327-397,
 // rl4co/envs/warehousing/slap/env.py:38-143.
+#include <stdlib.h>
+
 #include "rollout_util.cuh"
 
 namespace rl4co {
@@ -37,27 +55,28 @@ constexpr int kWarps = 8;
 constexpr float kScoreScale = 0.25f * 1.4426950408889634f;   // 1/sqrt(16) * log2(e)
 constexpr float kInvSqrtE = 0.08838834764831845f;             // 1/sqrt(128)
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int PLS = 144;              // row stride of the partial-logit matrix [head][node]
 constexpr size_t kSmemLimit = 112 * 1024;   // two CTAs per SM
 
 struct Layout {
-    size_t off_pl, off_xs, off_sc, off_e, off_o, off_mw, off_act, off_ain, off_lp, off_locs, off_noise, off_part, off_pick, off_bar, off_v, total;
+    size_t off_xs, off_sc, off_e, off_po, off_z, off_best, off_mw, off_act, off_ain, off_lp, off_locs, off_noise,
+        off_part, off_pick, off_bar, off_v, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline Layout make_layout(int N, int P, int M, int n_pick) {
+__host__ __device__ inline Layout make_layout(int N, int P, int n_pick) {
     Layout L;
     size_t o = 0;
-    L.off_pl = o;    o += (size_t)kWarps * PLS * 4;          // partial logits [head][node]
     L.off_xs = o;    o += (size_t)P * 128 * 4;               // processed logits, one row per step
-    L.off_sc = o;    o += (size_t)M * kThreads * 4;          // glimpse scores of the own nodes [j][thread]
-    L.off_e = o;     o += (size_t)kWarps * 128 * 4;          // e[head][node] = 2^(s - m), 0 once assigned
-    L.off_o = o;     o += E * 4;                             // glimpse numerators after a recompute (warp private)
+    L.off_sc = o;    o += (size_t)kWarps * 128 * 4;          // glimpse scores [head][node]
+    L.off_e = o;     o += (size_t)kWarps * 128 * 4;          // e[head][node] = 2^(s - m) at the last scaling
+    L.off_po = o;    o += (size_t)2 * kWarps * E * 4;        // per-warp partial glimpse numerators, hi and lo parts
+    L.off_z = o;     o += 16 * 4;                            // glimpse denominators [head], (hi, lo)
+    L.off_best = o;  o += 2 * kWarps * 8;                    // warp winners (value, node), double buffered
     L.off_mw = o;    o += up16((size_t)P * 4);
     L.off_act = o;   o += up16((size_t)P * 4);
     L.off_ain = o;   o += up16((size_t)P * 4);
     L.off_lp = o;    o += up16((size_t)P * 4);
     L.off_locs = o;  o += up16((size_t)N * 8);
-    L.off_noise = o; o += 16 * 128 * 4;                      // sampling: Gumbel noise of 16 steps
+    L.off_noise = o; o += 16 * 128 * 4;                      // sampling: Gumbel noise of 16 steps [16][node]
     L.off_part = o;  o += 64 * 4;
     L.off_pick = o;  o += up16((size_t)n_pick * 4);          // picklist as int
     L.off_bar = o;   o += 16;
@@ -77,10 +96,6 @@ __device__ __forceinline__ float rcpf(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
-__device__ __forceinline__ float fast_tanh(float x) {
-    const float t = ex2f(x * 2.8853900817779268f);
-    return 1.f - __fdividef(2.f, t + 1.f);
-}
 __device__ __forceinline__ float redux_max(float v) {
     float r;
     asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
@@ -96,30 +111,56 @@ __device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+    u64 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 __device__ __forceinline__ u64 pack2(float lo, float hi) {
     u64 d;
     asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
     return d;
 }
-__device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi) {
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
 __device__ __forceinline__ float hsum2(u64 v) {
     float lo, hi;
-    unpack2(v, lo, hi);
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
     return lo + hi;
 }
-__device__ __forceinline__ void ldg_256(const float *p, u64 (&v)[4]) {
-    asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
+// a lane's 4 dims of one table row: 16 bytes, a warp reads the whole 512 B row in one request
+__device__ __forceinline__ void ldg_128(const float *p, u64 (&v)[2]) {
+    asm volatile("ld.global.nc.v2.u64 {%0, %1}, [%2];" : "=l"(v[0]), "=l"(v[1]) : "l"(p));
 }
 __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+// error-free pieces of the compensated (two-float) accumulators: value = hi + lo
+__device__ __forceinline__ void two_sum(float a, float b, float &s, float &err) {
+    s = __fadd_rn(a, b);
+    const float bb = __fsub_rn(s, a);
+    err = __fadd_rn(__fsub_rn(a, __fsub_rn(s, bb)), __fsub_rn(b, bb));
+}
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b) {
+    u64 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// (hi, lo) += q on two dims at once (packed fp32 pairs, m1 = (-1, -1)): TwoSum, with a - b written fma(b, -1, a), which is
+// exact.  The glimpse numerator is DEFINED as the sum of the individually rounded products fl(e_n V_n): a location is
+// taken out by adding -fl(e_a V_a), which removes exactly what the build put in
+__device__ __forceinline__ void add_term2(u64 &hi, u64 &lo, u64 q, u64 m1) {
+    const u64 s = fadd2(hi, q);
+    const u64 bb = ffma2(hi, m1, s);                // s - hi
+    const u64 t1 = ffma2(bb, m1, s);                // s - bb
+    const u64 t2 = ffma2(t1, m1, hi);               // hi - (s - bb)
+    const u64 t3 = ffma2(bb, m1, q);                // q - bb
+    hi = s;
+    lo = fadd2(lo, fadd2(t2, t3));
+}
 
-#ifdef SLAPK_TRACE
 // -DSLAPK_TRACE (tools/trace_slap.py): thread 0 of CTA 0 stamps clock64() into a.logp_all, reused as a [P + 1][8] int64
-// buffer, during its SECOND instance (the other CTA of the SM is then in flight): six points per step, and in row P the
+// buffer, during its SECOND instance (the other CTA of the SM is then in flight): five points per step, and in row P the
 // phases of the instance
+#ifdef SLAPK_TRACE
 #define SLAPK_TRACE_AT(k) do { if (tid == 0 && blockIdx.x == 0 && it == 1) reinterpret_cast<long long *>(a.logp_all)[t * 8 + (k)] = clock64(); } while (0)
 #define SLAPK_TRACE_INST(k) do { if (tid == 0 && blockIdx.x == 0 && it == 1) reinterpret_cast<long long *>(a.logp_all)[P * 8 + (k)] = clock64(); } while (0)
 #else
@@ -127,33 +168,24 @@ __device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
 #define SLAPK_TRACE_INST(k) do { } while (0)
 #endif
 
-// error-free pieces of the compensated (two-float) accumulators: value = hi + lo
-__device__ __forceinline__ void two_sum(float a, float b, float &s, float &err) {
-    s = __fadd_rn(a, b);
-    const float bb = __fsub_rn(s, a);
-    err = __fadd_rn(__fsub_rn(a, __fsub_rn(s, bb)), __fsub_rn(b, bb));
-}
-// (hi, lo) -= e * v, with the product's rounding error recovered by an FMA
-__device__ __forceinline__ void sub_product(float &hi, float &lo, float e, float v) {
-    const float p = __fmul_rn(e, v);
-    const float pe = __fmaf_rn(e, v, -p);
-    float s, err;
-    two_sum(hi, -p, s, err);
-    hi = s;
-    lo = __fadd_rn(lo, __fsub_rn(err, pe));
-}
+constexpr int pow2_at_least(int v) { return v <= 4 ? 4 : v <= 8 ? 8 : 16; }
+constexpr int log2_of(int v) { return v == 4 ? 2 : v == 8 ? 3 : 4; }
 
-template <int M>
+template <int NW>
 __global__ void __launch_bounds__(kThreads, 2)
 am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
+    constexpr int PADV = pow2_at_least(NW);         // butterfly width
+    constexpr int SH = 5 - log2_of(PADV);           // lane l ends up with the logit of the warp's node l >> SH
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T, P = a.P < a.T ? a.P : a.T;
-    const Layout L = make_layout(N, P, M, a.O * a.K);
-    float *spl = reinterpret_cast<float *>(smem + L.off_pl);
+    const int n_pick = a.O * a.K;
+    const Layout L = make_layout(N, P, n_pick);
     float *sxs = reinterpret_cast<float *>(smem + L.off_xs);
     float *s_sc = reinterpret_cast<float *>(smem + L.off_sc);
     float *s_e = reinterpret_cast<float *>(smem + L.off_e);
-    float *so = reinterpret_cast<float *>(smem + L.off_o);
+    float *s_po = reinterpret_cast<float *>(smem + L.off_po);
+    float *s_z = reinterpret_cast<float *>(smem + L.off_z);
+    float2 *s_best = reinterpret_cast<float2 *>(smem + L.off_best);
     float *s_mw = reinterpret_cast<float *>(smem + L.off_mw);
     int *s_act = reinterpret_cast<int *>(smem + L.off_act);
     int *s_ain = reinterpret_cast<int *>(smem + L.off_ain);
@@ -166,23 +198,25 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
     float *sV = reinterpret_cast<float *>(smem + L.off_v);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int hh = lane >> 4, g = lane & 15;
-    const int dim0 = 16 * warp + 8 * hh;            // first of the 8 dims this thread multiplies
-    // the ONE of those dims whose glimpse numerator this lane keeps (where the butterfly below leaves it)
-    const int kd = ((g & 8) ? 4 : 0) + ((g & 4) ? 2 : 0) + ((g & 2) ? 1 : 0);
+    const int d0 = 4 * lane;                        // first of the 4 dims this lane owns
+    const int hl = lane >> 2;                       // their head
+    const int n0 = warp * NW;                       // first node of this warp
+    const int vi = lane >> SH;                      // the warp's node whose logit the butterfly leaves in this lane
+    const int n_me = n0 + vi;
+    const bool valid_me = vi < NW && n_me < N;
+    const bool writer_me = valid_me && (lane & ((1 << SH) - 1)) == 0;
     const int64_t Mrows = a.B * (int64_t)N;         // rows per table
     const size_t tab_bytes = (size_t)N * E * 4;
-    const bool std_logits = a.tanh_clipping > 0.f && a.temperature == 1.f && a.mask_logits != 0;
     const float clip = a.tanh_clipping;
-    const bool sampling = a.mode == RL4CO_MODE_SAMPLING;
-    const int n_pick = a.O * a.K;
+    const bool sampling = a.mode == RL4CO_MODE_SAMPLING, greedy = a.mode == RL4CO_MODE_GREEDY;
 
-    unsigned own = 0, rown = 0;
-#pragma unroll
-    for (int j = 0; j < M; ++j) own |= (g + 16 * j < N) ? (1u << j) : 0u;
+    unsigned rown = 0;                              // reader layout: bit k of lane l <-> node 4 l + k
 #pragma unroll
     for (int k = 0; k < 4; ++k) rown |= (4 * lane + k < N) ? (1u << k) : 0u;
 
+    // pad columns of the logit rows are never written again: -inf once
+    for (int q = tid; q < P * 128; q += kThreads)
+        if ((q & 127) >= N) sxs[q] = -INFINITY;
     if (tid == 0) {
         mbar_init(bar, 1);
         fence_barrier_init();
@@ -196,79 +230,70 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
         for (size_t off = 0; off < tab_bytes; off += 16384)
             tma_load_1d(dst + off, src + off, (unsigned)(tab_bytes - off < 16384 ? tab_bytes - off : 16384), bar);
     };
-    u64 L2[M][4];                                   // logit keys of the current instance, loaded one instance ahead
+    u64 L2[NW][2];                                  // logit keys of the current instance, loaded one instance ahead
     auto load_logit_keys = [&](int64_t b) {
-        const float *lb = a.tables + ((size_t)2 * Mrows + b * (int64_t)N) * E + dim0;
+        const float *lb = a.tables + ((size_t)2 * Mrows + b * (int64_t)N) * E + d0;
 #pragma unroll
-        for (int j = 0; j < M; ++j) {
-            const int n = g + 16 * j;
-            if (n < N) ldg_256(lb + (size_t)n * E, L2[j]);
-            else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) L2[j][i] = 0ull;
-            }
+        for (int i = 0; i < NW; ++i) {
+            if (n0 + i < N) ldg_128(lb + (size_t)(n0 + i) * E, L2[i]);
+            else { L2[i][0] = 0ull; L2[i][1] = 0ull; }
         }
+    };
+    // small per-instance inputs, also fetched one instance ahead: location of node tid, picklist entry tid, this lane's 4 dims
+    // of the graph context
+    float2 nx_loc = make_float2(0.f, 0.f);
+    long long nx_pick = 0;
+    float4 nx_g = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto load_small = [&](int64_t b) {
+        if (tid < N) nx_loc = __ldg(reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2) + tid);
+        if (tid < n_pick) nx_pick = __ldg(a.picklist + b * (int64_t)n_pick + tid);
+        if (a.gctx) nx_g = __ldg(reinterpret_cast<const float4 *>(a.gctx + b * E + d0));
     };
     if ((int64_t)blockIdx.x < a.B) {
         if (tid == 0) stage_values(blockIdx.x);
         load_logit_keys(blockIdx.x);
+        load_small(blockIdx.x);
     }
 
     int it = 0;
     for (int64_t b = blockIdx.x; b < a.B; b += gridDim.x, ++it) {
         const int64_t r = b;
         int t = 0, status = 0;
+#ifdef SLAPK_TRACE
+        int n_rebuilds = 0;
+#endif
         SLAPK_TRACE_INST(0);
-        const float *kb = a.tables + ((size_t)0 * Mrows + b * (int64_t)N) * E + dim0;
-        const float *vb = a.tables + ((size_t)1 * Mrows + b * (int64_t)N) * E + dim0;
-        // ------------------------------------------------ the one query of the trajectory, pre-scaled
-        u64 q2[4];
-        {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = 0.f;
-            if (a.gctx) {
-                const float4 g0 = __ldg(reinterpret_cast<const float4 *>(a.gctx + b * E + dim0));
-                const float4 g1 = __ldg(reinterpret_cast<const float4 *>(a.gctx + b * E + dim0) + 1);
-                v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; v[3] = g0.w; v[4] = g1.x; v[5] = g1.y; v[6] = g1.z; v[7] = g1.w;
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) q2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
-        }
         // ------------------------------------------------ glimpse scores, once (attention.py:289-306), base-2 scaled
-        float s[M];
         {
-            u64 kr[M][4];
+            // the one query of the trajectory, pre-scaled (zero without a graph context)
+            const u64 q2[2] = {pack2(nx_g.x * kScoreScale, nx_g.y * kScoreScale), pack2(nx_g.z * kScoreScale, nx_g.w * kScoreScale)};
+            const float *kb = a.tables + ((size_t)0 * Mrows + b * (int64_t)N) * E + d0;
+            u64 kr[NW][2];
 #pragma unroll
-            for (int j = 0; j < M; ++j) {
-                const int n = g + 16 * j;
-                if (n < N) ldg_256(kb + (size_t)n * E, kr[j]);
-                else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) kr[j][i] = 0ull;
-                }
+            for (int i = 0; i < NW; ++i) {
+                if (n0 + i < N) ldg_128(kb + (size_t)(n0 + i) * E, kr[i]);
+                else { kr[i][0] = 0ull; kr[i][1] = 0ull; }
             }
-            u64 acc[M];
+            float sv[NW];
 #pragma unroll
-            for (int j = 0; j < M; ++j) acc[j] = 0ull;
+            for (int i = 0; i < NW; ++i) sv[i] = hsum2(ffma2(kr[i][1], q2[1], fmul2(kr[i][0], q2[0])));
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < NW; ++i) sv[i] += __shfl_xor_sync(kFull, sv[i], 1);
 #pragma unroll
-                for (int j = 0; j < M; ++j) acc[j] = ffma2(kr[j][i], q2[i], acc[j]);
+            for (int i = 0; i < NW; ++i) sv[i] += __shfl_xor_sync(kFull, sv[i], 2);
+            if ((lane & 3) == 0) {
 #pragma unroll
-            for (int j = 0; j < M; ++j) s[j] = hsum2(acc[j]);
-#pragma unroll
-            for (int j = 0; j < M; ++j) s[j] += __shfl_xor_sync(kFull, s[j], 16);
+                for (int i = 0; i < NW; ++i)
+                    if (n0 + i < N) s_sc[hl * 128 + n0 + i] = sv[i];
+            }
         }
         SLAPK_TRACE_INST(1);
         // small per-instance state -> shared memory (the previous instance's epilogue ended with a barrier)
-#pragma unroll
-        for (int j = 0; j < M; ++j) s_sc[j * kThreads + tid] = s[j];
         {
-            const float2 *lrow = reinterpret_cast<const float2 *>(a.locs + b * (int64_t)N * 2);
-            for (int n = tid; n < N; n += kThreads) s_locs[n] = lrow[n];
+            if (tid < N) s_locs[tid] = nx_loc;
+            if (tid < n_pick) s_pick[tid] = (int)nx_pick;
             const int64_t *pl = a.picklist + b * (int64_t)n_pick;
-            for (int q = tid; q < n_pick; q += kThreads) s_pick[q] = (int)pl[q];
+            for (int q = tid + kThreads; q < n_pick; q += kThreads) s_pick[q] = (int)pl[q];     // more than 256 entries
         }
         if (tid == 0 && b + gridDim.x < a.B) {      // next instance: its three tables -> L2
             const int64_t nb = b + gridDim.x;
@@ -295,220 +320,174 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
         }
 
         // ------------------------------------------------ env state (slap/env.py:95-129): node 0 is never assignable
-        unsigned alive = own, ralive = rown;
-        if (g == 0) alive &= ~1u;
+        unsigned ralive = rown;
         if (lane == 0) ralive &= ~1u;
+        bool alive_me = valid_me && n_me != 0;
 
-        // ------------------------------------------------ glimpse state of this head.  Numerator of dim dim0 + kd and the
-        // denominator as two-float sums (hi + lo); zref = denominator when the exponentials were last formed
-        float Ohi, Olo, Zhi, Zlo, zref;
-        // butterfly over the 16 node groups, same order as am_rollout_rf.cu: leaves dim kd of the half head in this lane
-        auto reduce_head = [&](const u64 (&oacc)[4], float psum) {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) unpack2(oacc[i], v[2 * i], v[2 * i + 1]);
-#pragma unroll
-            for (int o = 8; o > 0; o >>= 1) psum += __shfl_xor_sync(kFull, psum, o);
-            const bool b3 = g & 8, b2 = g & 4, b1 = g & 2;
-            float w4[4], w2[2], w1;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float send = b3 ? v[k] : v[k + 4], keep = b3 ? v[k + 4] : v[k];
-                w4[k] = keep + __shfl_xor_sync(kFull, send, 8);
-            }
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const float send = b2 ? w4[k] : w4[k + 2], keep = b2 ? w4[k + 2] : w4[k];
-                w2[k] = keep + __shfl_xor_sync(kFull, send, 4);
-            }
+        // ------------------------------------------------ glimpse state, replicated in every warp: this lane's 4 dims of
+        // the numerator and its head's denominator as two-float sums; zref = denominator at the last scaling
+        u64 Ohi[2], Olo[2];                         // dims (4l, 4l+1) and (4l+2, 4l+3), packed
+        float Zhi, Zlo, zref;
+        // (re)build it from the scores with the maximum of the alive nodes as the shift.  Block-wide: warp w = head w forms
+        // the exponentials and the denominator, then every warp sums e V over its own nodes, then all partials are added
+        // Everything is summed as two-float values: the state is later REDUCED by exact subtractions, so an error that is
+        // small against the full sum would not be small against what remains once the dominant locations are gone
+        auto build_state = [&]() {
+            const u64 m1 = pack2(-1.f, -1.f);
             {
-                const float send = b1 ? w2[0] : w2[1], keep = b1 ? w2[1] : w2[0];
-                w1 = keep + __shfl_xor_sync(kFull, send, 2);
-            }
-            w1 += __shfl_xor_sync(kFull, w1, 1);
-            Ohi = w1; Olo = 0.f;
-            Zhi = psum; Zlo = 0.f; zref = psum;
-            if ((g & 1) == 0) so[dim0 + kd] = w1;
-        };
-        {   // first glimpse state: the value rows pass through registers once (shared memory gets its own copy by TMA)
-            float mx = -INFINITY;
+                const float4 s4 = *reinterpret_cast<const float4 *>(s_sc + warp * 128 + 4 * lane);
+                const float s0 = (ralive & 1u) ? s4.x : -INFINITY, s1 = (ralive & 2u) ? s4.y : -INFINITY;
+                const float s2 = (ralive & 4u) ? s4.z : -INFINITY, s3 = (ralive & 8u) ? s4.w : -INFINITY;
+                const float mx = redux_max(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)));
+                const float4 e4 = make_float4(ex2f(s0 - mx), ex2f(s1 - mx), ex2f(s2 - mx), ex2f(s3 - mx));   // 2^-inf = 0
+                *reinterpret_cast<float4 *>(s_e + warp * 128 + 4 * lane) = e4;
+                float zh, zl, err;
+                two_sum(e4.x, e4.y, zh, zl);
+                two_sum(zh, e4.z, zh, err); zl += err;
+                two_sum(zh, e4.w, zh, err); zl += err;
 #pragma unroll
-            for (int j = 0; j < M; ++j) {
-                s[j] = ((alive >> j) & 1u) ? s[j] : -INFINITY;
-                mx = fmaxf(mx, s[j]);
-            }
-            mx = redux_max(mx);
-            u64 vr[M][4];
-#pragma unroll
-            for (int j = 0; j < M; ++j) {
-                const int n = g + 16 * j;
-                if (n < N) ldg_256(vb + (size_t)n * E, vr[j]);
-                else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) vr[j][i] = 0ull;
+                for (int o = 16; o > 0; o >>= 1) {      // symmetric, so every lane ends with the same pair
+                    const float oh = __shfl_xor_sync(kFull, zh, o), ol = __shfl_xor_sync(kFull, zl, o);
+                    two_sum(zh, oh, zh, err);
+                    zl = (zl + ol) + err;
                 }
+                if (lane == 0) reinterpret_cast<float2 *>(s_z)[warp] = make_float2(zh, zl);
             }
-            float psum = 0.f;
-            u64 oacc[4] = {0ull, 0ull, 0ull, 0ull};
+            __syncthreads();
+            {
+                u64 ph[2] = {0ull, 0ull}, pl[2] = {0ull, 0ull};
 #pragma unroll
-            for (int j = 0; j < M; ++j) {
-                const float p = ex2f(s[j] - mx);        // node 0 / absent: 2^-inf = 0
-                psum += p;
-                if (hh == 0) s_e[warp * 128 + g + 16 * j] = p;
-                const u64 pp = pack2(p, p);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) oacc[i] = ffma2(vr[j][i], pp, oacc[i]);
+                for (int i = 0; i < NW; ++i) {
+                    const int n = n0 + i < N ? n0 + i : N - 1;      // absent nodes: e = 0, any row
+                    const float e = s_e[hl * 128 + n0 + i];
+                    const ulonglong2 v4 = *reinterpret_cast<const ulonglong2 *>(sV + (size_t)n * E + d0);
+                    const u64 e2 = pack2(e, e);
+                    add_term2(ph[0], pl[0], fmul2(e2, v4.x), m1);
+                    add_term2(ph[1], pl[1], fmul2(e2, v4.y), m1);
+                }
+                *reinterpret_cast<ulonglong2 *>(s_po + warp * E + d0) = make_ulonglong2(ph[0], ph[1]);
+                *reinterpret_cast<ulonglong2 *>(s_po + (kWarps + warp) * E + d0) = make_ulonglong2(pl[0], pl[1]);
             }
-            reduce_head(oacc, psum);
-        }
-        // the same from shared memory, with the maximum of the nodes that are still alive (rare, see the header)
-        auto recompute = [&]() {
-            float sj[M], mx = -INFINITY;
+            __syncthreads();
+            Ohi[0] = Ohi[1] = Olo[0] = Olo[1] = 0ull;
 #pragma unroll
-            for (int j = 0; j < M; ++j) {
-                sj[j] = ((alive >> j) & 1u) ? s_sc[j * kThreads + tid] : -INFINITY;
-                mx = fmaxf(mx, sj[j]);
+            for (int w = 0; w < kWarps; ++w) {
+                const ulonglong2 h4 = *reinterpret_cast<const ulonglong2 *>(s_po + w * E + d0);
+                const ulonglong2 l4 = *reinterpret_cast<const ulonglong2 *>(s_po + (kWarps + w) * E + d0);
+                add_term2(Ohi[0], Olo[0], h4.x, m1);
+                add_term2(Ohi[1], Olo[1], h4.y, m1);
+                Olo[0] = fadd2(Olo[0], l4.x);
+                Olo[1] = fadd2(Olo[1], l4.y);
             }
-            mx = redux_max(mx);
-            float psum = 0.f;
-            u64 oacc[4] = {0ull, 0ull, 0ull, 0ull};
-#pragma unroll
-            for (int j = 0; j < M; ++j) {
-                const float p = ex2f(sj[j] - mx);
-                psum += p;
-                if (hh == 0) s_e[warp * 128 + g + 16 * j] = p;
-                const u64 pp = pack2(p, p);
-                const int n = g + 16 * j < N ? g + 16 * j : N - 1;      // absent nodes: p = 0, any row
-                const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(sV + (size_t)n * E + dim0);
-                const ulonglong2 v1 = *(reinterpret_cast<const ulonglong2 *>(sV + (size_t)n * E + dim0) + 1);
-                oacc[0] = ffma2(v0.x, pp, oacc[0]);
-                oacc[1] = ffma2(v0.y, pp, oacc[1]);
-                oacc[2] = ffma2(v1.x, pp, oacc[2]);
-                oacc[3] = ffma2(v1.y, pp, oacc[3]);
-            }
-            reduce_head(oacc, psum);
+            const float2 z2 = reinterpret_cast<const float2 *>(s_z)[hl];
+            Zhi = z2.x; Zlo = z2.y; zref = Zhi;
         };
         SLAPK_TRACE_INST(2);
         mbar_wait(bar, par);                        // value table landed in shared memory
         par ^= 1u;
-        __syncthreads();                            // noise / given actions visible to every warp
+        __syncthreads();                            // scores / noise / given actions visible to every warp
+        build_state();
         SLAPK_TRACE_INST(3);
 
         // ================================================== decode loop ==================
         while (t < P) {
             SLAPK_TRACE_AT(0);
-            float G[4] = {0.f, 0.f, 0.f, 0.f};
-            if (sampling) {                             // noise ring as in am_rollout_rf.cu
+            float Gn = 0.f;
+            if (sampling) {                             // noise ring as in am_rollout_rf.cu, read by node
                 if ((t & 7) == 0 && t > 0) gen_noise(t + 8 + warp);
-                const float4 g4 = s_noise[(t & 15) * 32 + lane];
-                G[0] = g4.x; G[1] = g4.y; G[2] = g4.z; G[3] = g4.w;
+                Gn = reinterpret_cast<const float *>(s_noise)[(t & 15) * 128 + (valid_me ? n_me : 0)];
             }
-            // ---- partial pointer logits of this head, project_out folded (attention.py:276-282)
-            __syncwarp();                               // the glimpse numerators of all 8 dims are in `so`
+            // ---- pointer logits of the own nodes, project_out folded (attention.py:276-282): o = O / Z, then <o, L'[n]>
+            float tot;
             {
-                const ulonglong2 o0 = *reinterpret_cast<const ulonglong2 *>(so + dim0);
-                const ulonglong2 o1 = *(reinterpret_cast<const ulonglong2 *>(so + dim0) + 1);
-                const u64 o2[4] = {o0.x, o0.y, o1.x, o1.y};
-                u64 acc[M];
+                const float inv = rcpf(Zhi + Zlo);          // softmax normaliser of this lane's head
+                const u64 inv2 = pack2(inv, inv);
+                const u64 o2[2] = {fmul2(fadd2(Ohi[0], Olo[0]), inv2), fmul2(fadd2(Ohi[1], Olo[1]), inv2)};
+                float v[PADV];
 #pragma unroll
-                for (int j = 0; j < M; ++j) acc[j] = 0ull;
+                for (int i = 0; i < PADV; ++i) v[i] = i < NW ? hsum2(ffma2(L2[i < NW ? i : 0][1], o2[1], fmul2(L2[i < NW ? i : 0][0], o2[0]))) : 0.f;
+                // transposing butterfly: after the stage with offset o a lane keeps the half of the values selected by
+                // its bit o; the last stages are plain exchanges.  Lane l ends with the total of value l >> SH
+                int half = PADV / 2;
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int o = 16; o >= 1; o >>= 1) {
+                    if (half >= 1) {
+                        const bool up = (lane & o) != 0;
 #pragma unroll
-                    for (int j = 0; j < M; ++j) acc[j] = ffma2(L2[j][i], o2[i], acc[j]);
-                const float inv = __fdividef(1.f, Zhi + Zlo);     // softmax normaliser of this head
-                float pl[M];
-#pragma unroll
-                for (int j = 0; j < M; ++j) pl[j] = hsum2(acc[j]) * inv;
-#pragma unroll
-                for (int j = 0; j < M; ++j) pl[j] += __shfl_xor_sync(kFull, pl[j], 16);
-                float *row = spl + warp * PLS + g;
-                if (hh == 0) {
-#pragma unroll
-                    for (int j = 0; j < M; ++j) row[16 * j] = pl[j];
+                        for (int k = 0; k < PADV / 2; ++k) {
+                            if (k < half) {
+                                const float send = up ? v[k] : v[k + half], keep = up ? v[k + half] : v[k];
+                                v[k] = keep + __shfl_xor_sync(kFull, send, o);
+                            }
+                        }
+                        half >>= 1;
+                    } else {
+                        v[0] += __shfl_xor_sync(kFull, v[0], o);
+                    }
                 }
+                tot = v[0];
             }
             SLAPK_TRACE_AT(1);
-            __syncthreads();
-            SLAPK_TRACE_AT(2);
-            float *sxrow = sxs + t * 128;
-            // ---- warps 0-3, thread = node 32 warp + lane = g + 16 (2 warp + hh): logit = sum_h pl_h / sqrt(E),
-            //      then process_logits (utils/decoding.py:141-191)
-            if (warp < 4) {
-                const float *col = spl + tid;
-                const float sum = ((col[0] + col[2 * PLS]) + (col[4 * PLS] + col[6 * PLS])) +
-                                  ((col[PLS] + col[3 * PLS]) + (col[5 * PLS] + col[7 * PLS]));
-                const int jb = 2 * warp + hh;
-                const bool exists = (own >> jb) & 1u, feasible = (alive >> jb) & 1u;
-                float xv;
-                if (std_logits) {
-                    const float e2 = ex2f(sum * (kInvSqrtE * 2.f * kLog2e));
-                    xv = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
-                    if (exists && sum != sum) status |= RL4CO_ST_NAN_LOGITS;
-                    xv = feasible ? xv : -INFINITY;
-                } else {
-                    xv = sum * kInvSqrtE;
-                    if (exists && xv != xv) status |= RL4CO_ST_NAN_LOGITS;
-                    if (clip > 0.f) xv = fast_tanh(xv) * clip;
-                    xv = __fdiv_rn(xv, a.temperature);
-                    xv = (exists && (feasible || !a.mask_logits)) ? xv : -INFINITY;
-                }
-                sxrow[tid] = xv;
-            }
-            SLAPK_TRACE_AT(3);
-            __syncthreads();
-            SLAPK_TRACE_AT(4);
-            // ---- every warp: all logits, lane = nodes 4 lane .. 4 lane + 3
-            float x[4];
+            // ---- process_logits (utils/decoding.py:141-191): clip * tanh(z) = clip - 2 clip / (2^(2 log2(e) z) + 1), mask
+            float xv;
             {
-                const float4 xv = *reinterpret_cast<const float4 *>(sxrow + 4 * lane);
-                x[0] = xv.x; x[1] = xv.y; x[2] = xv.z; x[3] = xv.w;
+                const float e2 = ex2f(tot * (kInvSqrtE * 2.f * kLog2e));
+                xv = fmaf(-2.f * clip, rcpf(e2 + 1.f), clip);
+                if (valid_me && tot != tot) status |= RL4CO_ST_NAN_LOGITS;
+                xv = alive_me ? xv : -INFINITY;
             }
-            const float gm = (sampling && std_logits) ? clip : redux_max(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])));
+            if (writer_me) sxs[t * 128 + n_me] = xv;    // the step's log-prob is formed after the loop
             // ---- selection (utils/decoding.py:371-397,410-499)
             int act;
-            if (a.mode == RL4CO_MODE_GREEDY) {
-                unsigned cand = 0x7fffffffu;            // argmax, lowest index on ties
-                cand = x[3] == gm ? 4u * lane + 3u : cand;
-                cand = x[2] == gm ? 4u * lane + 2u : cand;
-                cand = x[1] == gm ? 4u * lane + 1u : cand;
-                cand = x[0] == gm ? 4u * lane : cand;
-                const unsigned win = redux_min_u32(cand);
-                act = win < (unsigned)N ? (int)win : 0;
-            } else if (a.mode == RL4CO_MODE_EVALUATE) {
+            float gm = clip;                            // log-sum-exp shift: the bound of the clipped logits, or their maximum
+            if (a.mode == RL4CO_MODE_EVALUATE) {
                 act = s_ain[t];
                 if (act < 0) { status |= RL4CO_ST_ACTION_RANGE; act = 0; }
-            } else {                                    // Gumbel-max sample (rollout_util.cuh)
-                const float y0 = x[0] + G[0], y1 = x[1] + G[1], y2 = x[2] + G[2], y3 = x[3] + G[3];
-                const float ym = redux_max(fmaxf(fmaxf(y0, y1), fmaxf(y2, y3)));
-                unsigned cand = 0x7fffffffu;
-                cand = y3 == ym ? 4u * lane + 3u : cand;
-                cand = y2 == ym ? 4u * lane + 2u : cand;
-                cand = y1 == ym ? 4u * lane + 1u : cand;
-                cand = y0 == ym ? 4u * lane : cand;
-                const unsigned win = redux_min_u32(cand);
-                act = win < (unsigned)N ? (int)win : 0;
+            } else {
+                // greedy: arg-max of the logits; sampling: Gumbel-max, arg-max of logits + noise (rollout_util.cuh); lowest
+                // node on ties.  Warp winner by two redux, block winner after the step's only barrier
+                const float y = valid_me ? xv + Gn : -INFINITY;
+                const float ym = redux_max(y);
+                const unsigned win = redux_min_u32((valid_me && y == ym) ? (unsigned)n_me : 0x7fffffffu);
+                float2 *slot = s_best + (t & 1) * kWarps;
+                if (lane == 0) slot[warp] = make_float2(ym, __uint_as_float(win));
+                SLAPK_TRACE_AT(2);
+                __syncthreads();
+                SLAPK_TRACE_AT(3);
+                // lane w < 8 takes warp w's winner: the largest value, the lowest node among equals
+                const float2 mine = slot[lane & 7];
+                const float best = redux_max(mine.x);
+                const unsigned bi = redux_min_u32(mine.x == best ? __float_as_uint(mine.y) : 0x7fffffffu);
+                act = bi < (unsigned)N ? (int)bi : 0;
+                if (greedy) gm = best;
             }
-            if (lane == (act >> 2) && !((ralive >> (act & 3)) & 1u)) status |= RL4CO_ST_INFEASIBLE_ACTION;
+            // feasibility of the chosen action (utils/decoding.py:377-379,393-395): the lane that holds its logit checks
+            if ((n_me == act && vi < NW && !alive_me) || act >= N) status |= RL4CO_ST_INFEASIBLE_ACTION;
             if (tid == 0) { s_act[t] = act; s_mw[t] = gm; }
-            // ---- transition (slap/env.py:38-93): the location leaves the mask and this head's glimpse state
-            alive &= ~((g == (act & 15)) ? (1u << (act >> 4)) : 0u);
+            // ---- transition (slap/env.py:38-93): the location leaves the mask and every head's glimpse state
+            alive_me = alive_me && n_me != act;
             ralive &= ~((lane == (act >> 2)) ? (1u << (act & 3)) : 0u);
             if (t + 1 < P) {
-                const float e_a = s_e[warp * 128 + act];
-                const float v_a = sV[(size_t)act * E + dim0 + kd];
-                sub_product(Ohi, Olo, e_a, v_a);
+                const float e_a = s_e[hl * 128 + act];
+                const ulonglong2 va = *reinterpret_cast<const ulonglong2 *>(sV + (size_t)act * E + d0);
+                const u64 ne2 = pack2(-e_a, -e_a), m1 = pack2(-1.f, -1.f);
+                add_term2(Ohi[0], Olo[0], fmul2(ne2, va.x), m1);    // -fl(e_a V_a): the term the build added, negated
+                add_term2(Ohi[1], Olo[1], fmul2(ne2, va.y), m1);
                 float zs, ze;
                 two_sum(Zhi, -e_a, zs, ze);
                 Zhi = zs;
                 Zlo = __fadd_rn(Zlo, ze);
-                __syncwarp();                           // every lane has read e_a
-                if (lane == 0) s_e[warp * 128 + act] = 0.f;     // a repeated (infeasible) action subtracts nothing
-                // what is left is a sliver of what the exponentials were scaled for (or cancelled altogether): rescale
-                if (!(Zhi > zref * 1.52587890625e-05f)) recompute();
-                else if ((g & 1) == 0) so[dim0 + kd] = __fadd_rn(Ohi, Olo);
+                // what is left of some head is a sliver (2^-16) of what its exponentials were scaled for, or cancelled
+                // altogether: rebuild with the maximum of what is alive.  Every warp holds the same state, so all of them take the branch together
+                if (__any_sync(kFull, !(Zhi > zref * 1.52587890625e-05f))) {
+                    __syncthreads();                    // everyone is done with e[] and the partials of the last build
+                    build_state();
+#ifdef SLAPK_TRACE
+                    ++n_rebuilds;
+#endif
+                }
             }
-            SLAPK_TRACE_AT(5);
+            SLAPK_TRACE_AT(4);
             ++t;
         }
 
@@ -521,34 +500,29 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
                 stage_values(b + gridDim.x);
             }
             load_logit_keys(b + gridDim.x);
+            load_small(b + gridDim.x);
         }
         const int nact = t;
-        // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368)
-        for (int qb = warp; qb < nact; qb += 16 * kWarps) {
-            float es[16], mm[16];
+        // chosen log-probs: logp = (x_a - m) - log(sum exp(x - m))   (utils/decoding.py:191,364-368): 8 threads per step, 16 nodes
+        // each, 32 steps per pass
+        for (int q0 = 0; q0 < nact; q0 += kThreads / 8) {
+            const int q = q0 + (tid >> 3), part = tid & 7;
+            float es = 0.f, m = 0.f;
+            if (q < nact) {
+                m = s_mw[q];
+                const float4 *row = reinterpret_cast<const float4 *>(sxs + q * 128 + 16 * part);
 #pragma unroll
-            for (int u = 0; u < 16; ++u) {
-                const int q = qb + u * kWarps;
-                es[u] = 0.f;
-                mm[u] = 0.f;
-                if (q < nact) {
-                    const float4 xv = *reinterpret_cast<const float4 *>(sxs + q * 128 + 4 * lane);
-                    mm[u] = s_mw[q];
-                    es[u] = (ex2f((xv.x - mm[u]) * kLog2e) + ex2f((xv.y - mm[u]) * kLog2e)) +
-                            (ex2f((xv.z - mm[u]) * kLog2e) + ex2f((xv.w - mm[u]) * kLog2e));
+                for (int u = 0; u < 4; ++u) {
+                    const float4 x4 = row[u];
+                    es += (ex2f((x4.x - m) * kLog2e) + ex2f((x4.y - m) * kLog2e)) +
+                          (ex2f((x4.z - m) * kLog2e) + ex2f((x4.w - m) * kLog2e));     // masked logits: 2^-inf = 0
                 }
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-                for (int u = 0; u < 16; ++u) es[u] += __shfl_xor_sync(kFull, es[u], o);
-            float my_es = 1.f, my_m = 0.f;
-#pragma unroll
-            for (int u = 0; u < 16; ++u)
-                if (lane == u) { my_es = es[u]; my_m = mm[u]; }
-            const int q = qb + lane * kWarps;
-            if (lane < 16 && q < nact) {
-                const float lpa = (sxs[q * 128 + s_act[q]] - my_m) - logf(my_es);
+            es += __shfl_xor_sync(kFull, es, 1);
+            es += __shfl_xor_sync(kFull, es, 2);
+            es += __shfl_xor_sync(kFull, es, 4);
+            if (q < nact && part == 0) {
+                const float lpa = (sxs[q * 128 + s_act[q]] - m) - logf(es);
                 s_lp[q] = lpa;
                 if (!(lpa > -1000.f)) status |= RL4CO_ST_NEG_INF_LOGP;
             }
@@ -556,17 +530,10 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
         SLAPK_TRACE_INST(5);
         // slap/env.py:131-143: closed tour through the locations of every order (assignment[t] = s_act[t])
         float part = 0.f;
-        for (int o = tid; o < a.O; o += kThreads) {
-            const int *ord = s_pick + o * a.K;
-            const float2 first = s_locs[s_act[ord[0]]];
-            float2 prev = first;
-            float len = 0.f;
-            for (int k = 1; k < a.K; ++k) {
-                const float2 cur = s_locs[s_act[ord[k]]];
-                len += leg(prev.x, prev.y, cur.x, cur.y);
-                prev = cur;
-            }
-            part += len + leg(prev.x, prev.y, first.x, first.y);
+        for (int idx = tid; idx < n_pick; idx += kThreads) {    // one leg per thread: entry k of its order -> entry k + 1 (cyclic)
+            const int k = idx % a.K, nxt = k + 1 == a.K ? idx - k : idx + 1;
+            const float2 p = s_locs[s_act[s_pick[idx]]], w = s_locs[s_act[s_pick[nxt]]];
+            part += leg(p.x, p.y, w.x, w.y);
         }
         part = warp_sum(part);
         if (lane == 0) spart[warp] = part;
@@ -583,7 +550,11 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
                 for (int w = 0; w < kWarps; ++w) { len += spart[w]; st |= __float_as_int(spart[40 + w]); }
                 a.reward[r] = -len;
                 a.ll[r] = llp;
+#ifdef SLAPK_TRACE
+                if (a.steps) a.steps[r] = nact + (n_rebuilds << 8);     // tools/trace_slap.py: rebuilds per instance
+#else
                 if (a.steps) a.steps[r] = nact;
+#endif
                 if (st) raise_status(a.status, st);
             }
         }
@@ -594,13 +565,15 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
         if (a.assignment)
             for (int q = tid; q < a.P; q += kThreads) a.assignment[(size_t)r * a.P + q] = q < nact ? s_act[q] : -1;
         SLAPK_TRACE_INST(6);
-        __syncthreads();                         // the next instance rewrites the small arrays
+        // no barrier here: what the next instance writes before its own barriers (scores, locations, picklist, noise, given
+        // actions) is not read by the output loops above, and the reward loop that reads locations / picklist ended before
+        // the barrier in the middle of this epilogue
     }
 }
 
-__host__ inline int nodes_per_thread(int N) { return N <= 32 ? 2 : N <= 64 ? 4 : N <= 112 ? 7 : 8; }
+__host__ inline int nodes_per_warp(int N) { return N <= 32 ? 4 : N <= 64 ? 8 : N <= 104 ? 13 : 16; }
 
-template <int M>
+template <int NW>
 static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -609,15 +582,26 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    const Layout L = make_layout(a.N, a.P < a.T ? a.P : a.T, M, a.O * a.K);
-    cudaError_t e = cudaFuncSetAttribute(am_rollout_slap_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+    const Layout L = make_layout(a.N, a.P < a.T ? a.P : a.T, a.O * a.K);
+    cudaError_t e = cudaFuncSetAttribute(am_rollout_slap_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+    if (e == cudaSuccess)   // two CTAs of ~84 KB: ask for the largest shared-memory carve-out
+        e = cudaFuncSetAttribute(am_rollout_slap_kernel<NW>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) {
         set_error("am_rollout(slap): cannot reserve %zu B of shared memory: %s", L.total, cudaGetErrorString(e));
         return 2;
     }
-    const int64_t cap = (int64_t)2 * sm_count;               // persistent: two CTAs per SM
+    if (getenv("RL4CO_DEBUG_OCCUPANCY")) {
+        int nb = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, am_rollout_slap_kernel<NW>, kThreads, L.total);
+        cudaFuncAttributes fa;
+        cudaFuncGetAttributes(&fa, am_rollout_slap_kernel<NW>);
+        fprintf(stderr, "am_rollout(slap)<%d>: %d CTAs/SM, %d regs, %zu B dynamic smem, carveout %d\n", NW, nb, fa.numRegs, L.total,
+                fa.preferredShmemCarveout);
+    }
+    int64_t cap = (int64_t)2 * sm_count;                     // persistent: two CTAs per SM
+    if (const char *dbg = getenv("RL4CO_DEBUG_SLAP_GRID")) cap = atoll(dbg) > 0 ? atoll(dbg) : cap;   // timing experiments only
     const int64_t grid = a.B < cap ? a.B : cap;
-    am_rollout_slap_kernel<M><<<(unsigned)grid, kThreads, L.total, stream>>>(a);
+    am_rollout_slap_kernel<NW><<<(unsigned)grid, kThreads, L.total, stream>>>(a);
     RL4CO_CHECK_LAUNCH("am_rollout(slap)");
     return 0;
 }
@@ -630,16 +614,17 @@ bool rollout_slap_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
+    if (!(a.tanh_clipping > 0.f && a.temperature == 1.f && a.mask_logits != 0)) return false;
     const int P = a.P < a.T ? a.P : a.T;
-    return slapk::make_layout(a.N, P, slapk::nodes_per_thread(a.N), a.O * a.K).total <= slapk::kSmemLimit;
+    return slapk::make_layout(a.N, P, a.O * a.K).total <= slapk::kSmemLimit;
 }
 
 int launch_rollout_slap(const rl4co_am_rollout_args &a, cudaStream_t stream) {
-    switch (slapk::nodes_per_thread(a.N)) {
-        case 2: return slapk::launch<2>(a, stream);
+    switch (slapk::nodes_per_warp(a.N)) {
         case 4: return slapk::launch<4>(a, stream);
-        case 7: return slapk::launch<7>(a, stream);
-        default: return slapk::launch<8>(a, stream);
+        case 8: return slapk::launch<8>(a, stream);
+        case 13: return slapk::launch<13>(a, stream);
+        default: return slapk::launch<16>(a, stream);
     }
 }
 

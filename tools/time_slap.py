@@ -46,6 +46,9 @@ with torch.inference_mode():
             for mode in ("greedy", "sampling"):
                 ga, gb = res[("slap", mode)], res[("rf", mode)]
                 same = (ga["actions"] == gb["actions"]).all(1)
+                if not bool(same.any()):
+                    print(f"   {mode}: assignments equal 0/{same.numel()}")
+                    continue
                 print(f"   {mode}: assignments equal {int(same.sum())}/{same.numel()}  max |ll diff| on equal "
                       f"{(ga['log_likelihood'] - gb['log_likelihood'])[same].abs().max().item():.2e} (|ll| up to "
                       f"{gb['log_likelihood'].abs().max().item():.1f})  reward diff "

@@ -3,9 +3,9 @@
     python tools/trace_slap.py build      # here (nvcc, no GPU): tools/_trace_slap/librl4co_trace.so
     python tools/trace_slap.py            # on the GPU box: per-phase cycles of one trajectory
 
-Thread 0 of CTA 0 stamps clock64() during its second instance: per step 0 start | 1 partial logits stored |
-2 past barrier 1 | 3 slice done | 4 past barrier 2 | 5 selection + transition + glimpse update done; per instance
-0 start | 1 scores in registers | 2 V in shared memory, past the barrier | 3 first glimpse state | 4 decode done |
+Thread 0 of CTA 0 stamps clock64() during its second instance: per step 0 start | 1 logits of the own nodes (butterfly
+done) | 2 warp winner stored | 3 past the barrier | 4 block winner + transition + glimpse update done; per instance
+0 start | 1 scores stored | 2 small state staged | 3 value table landed + first glimpse state | 4 decode done |
 5 log-probs | 6 reward + outputs.
 """
 import os, sys
@@ -27,7 +27,11 @@ torch.manual_seed(1234)
 N, P = 100, 20
 B = 148 * 2 * 4
 env = R.SLAPEnv(generator_params={"n_aisles": 10, "n_locs": 10}, device=dev)
-pol = R.AttentionModelPolicy(env_name="slap").to(dev).eval()
+if os.environ.get("SLAP_FIXTURE_POLICY"):        # the reference-initialised fixture weights of the parity tests
+    from tests.helpers import load_policy
+    pol = load_policy("slap", dev)
+else:
+    pol = R.AttentionModelPolicy(env_name="slap").to(dev).eval()
 with torch.inference_mode():
     td = env.reset(env.generator(B).to(dev))
     h = pol.encoder(td)[0].float().contiguous()
@@ -57,15 +61,17 @@ a.steps, a.status = _lib.ptr(steps), _lib.ptr(status)
 for _ in range(2):
     _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
 torch.cuda.synchronize()
+rb = (steps.cpu().numpy() >> 8)
+print("glimpse rebuilds per instance: mean %.2f  max %d  histogram %s" % (rb.mean(), rb.max(), np.bincount(rb)[:21].tolist()))
 full = trace.cpu().numpy().reshape(P + 1, 8)
-tr = full[:P, :6]
+tr = full[:P, :5]
 d = np.diff(tr, axis=1)
-names = ["L+store", "barrier1", "slice", "barrier2", "select+transition+update"]
+names = ["logits+butterfly", "tanh+warp argmax", "barrier", "winner+update"]
 print("mean reward", rew.mean().item())
 m = d[1:].mean(0)
 print("per step: " + "  ".join(f"{n} {v:.0f}" for n, v in zip(names, m)), "| step total", (tr[1:, 0] - tr[:-1, 0]).mean())
 print("cycles from step start to next step start:", " ".join(str(int(v)) for v in (tr[1:, 0] - tr[:-1, 0])))
-print("update phase per step:", " ".join(str(int(v)) for v in d[:, 4]))
+print("update phase per step:", " ".join(str(int(v)) for v in d[:, 3]))
 v = full[P]
-print(f"instance: L'/K loads + scores {v[1]-v[0]}  V -> smem + barriers {v[2]-v[1]}  first glimpse {v[3]-v[2]}  decode {v[4]-v[3]}  "
+print(f"instance: K loads + scores {v[1]-v[0]}  small state {v[2]-v[1]}  V wait + first glimpse {v[3]-v[2]}  decode {v[4]-v[3]}  "
       f"log-probs {v[5]-v[4]}  reward + outputs {v[6]-v[5]}  total {v[6]-v[0]}")
