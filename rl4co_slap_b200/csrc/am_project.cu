@@ -129,7 +129,7 @@ am_graph_context_kernel(int64_t B, int N, const float *__restrict__ h,
 }  // namespace rl4co
 
 namespace rl4co {
-int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream);
+int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, bool f16, cudaStream_t stream);
 int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, const float *image, float *tables,
                       int64_t table_stride, int64_t ldo, const float *bias, int relu, int64_t ldx, int accumulate,
                       const float *residual, const float *scale, const float *shift, cudaStream_t stream);
@@ -143,7 +143,7 @@ extern "C" int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *im
     RL4CO_REQUIRE(n_tables >= 1 && n_tables <= 16, "am_pack_weights: bad n_tables=%d", n_tables);
     RL4CO_REQUIRE(W && image, "am_pack_weights: null pointer");
     RL4CO_REQUIRE(((uintptr_t)W & 15) == 0 && ((uintptr_t)image & 15) == 0, "am_pack_weights: pointers must be 16-byte aligned");
-    return launch_pack_weights(n_tables, W, 128, image, (cudaStream_t)stream);
+    return launch_pack_weights(n_tables, W, 128, image, true, (cudaStream_t)stream);
 }
 
 extern "C" int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,
@@ -164,7 +164,7 @@ extern "C" int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, fl
     RL4CO_REQUIRE(((uintptr_t)W & 15) == 0 && ((uintptr_t)image & 15) == 0, "linear_pack: pointers must be 16-byte aligned");
     const int nb = n_out / 128;
     for (int kc = 0; kc < n_in / 128; ++kc) {       // one image set per 128-wide K chunk
-        int rc = launch_pack_weights(nb, W + kc * 128, n_in, image + (size_t)kc * nb * 32768, (cudaStream_t)stream);
+        int rc = launch_pack_weights(nb, W + kc * 128, n_in, image + (size_t)kc * nb * 32768, n_in == 128, (cudaStream_t)stream);
         if (rc) return rc;
     }
     return 0;

@@ -1,7 +1,17 @@
 // K3 (tensor-core path) - projection of the encoder's node embeddings into the rollout tables
 // on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM), fp32-accurate through
-// a 3-term TF32 split:   a*w = a_hi*w_hi + a_hi*w_lo + a_lo*w_hi  (+ O(2^-22) dropped),
-// with a_hi = rna_tf32(a), a_lo = rna_tf32(a - a_hi), products accumulated in fp32 in TMEM.
+// a 3-term split:   a*w = a_hi*w_hi + a_hi*w_lo + a_lo*w_hi  (+ O(2^-22) dropped), products accumulated in
+// fp32 in TMEM.  Two operand formats:
+//   K = 128 (the table projection, every 128-wide linear layer): FP16 halves, a_hi = fp16(a), a_lo = fp16(a - a_hi)
+//     (11 + 11 significant bits), kind::f16 MMAs of K = 16 - half the MMA count and half the operand bytes of the
+//     TF32 form, which was tensor-pipe bound.  fp16 has 5 exponent bits, so both operands are brought into range by
+//     exact powers of two: every 128-row tile of h by 2^(13 - e), e the exponent of the tile's largest |a| (found by
+//     the producer warps before they convert), every weight table by the same rule at pack time; the epilogue
+//     multiplies the accumulator by the product of the two inverse scales.  Nothing overflows or falls into the
+//     subnormals whatever the magnitude of the inputs, inf / NaN propagate.
+//   K > 128 (K chunks accumulated in TMEM, e.g. the 512 -> 128 feed-forward layer): TF32 halves as before
+//     (a_hi = top 19 bits, a_lo = a - a_hi), since a common scale for all chunks of a row tile is not known when the
+//     first chunk is converted.
 // Replaces AttentionModelDecoder._precompute_cache (rl4co/models/zoo/am/decoder.py:208-237) and
 // the per-node halves of the context projection (rl4co/models/nn/env_embeddings/context.py:67-71).
 //
@@ -19,6 +29,8 @@
 //              2 x 128 columns) and store it to the table.
 // The tables of one instance are read back by the rollout kernel row by row, so the output stays
 // row-major [t][m][128].
+#include <type_traits>
+
 #include "common.cuh"
 #include "rollout_util.cuh"
 #include "tc_util.cuh"
@@ -45,29 +57,73 @@ constexpr uint32_t kTmemCols = TB * BN;  // 512 columns: four 128-column accumul
 // instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = F32 (bits 4-5 = 1),
 // A = B = TF32 (bits 7-9, 10-12 = 2), both K-major, N/8 at bit 17, M/16 at bit 24
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((BN >> 3) << 17) | ((BM >> 4) << 24);
+constexpr uint32_t kIdescH = tcu::make_idesc_f16(BM, BN);     // FP16 operands, K = 16 per instruction
 
-// weights -> the shared-memory image of one table: [hi|lo][kb][row j = output feature][32 k], swizzled
+// weights -> the shared-memory image of one table.  TF32: [hi|lo][kb 0..3][row j = output feature][32 k], swizzled, 128 KB.
+// FP16: W 2^(13 - e_w) as [hi|lo][kb 0..1][row j][64 k], swizzled, 64 KB, and the float 2^(e_w - 13) at byte 65536.
+constexpr int kImageFloats = 32768;     // per table and K chunk, either format
+constexpr int kScaleAt = 16384;         // float index of the inverse weight scale in an FP16 image
+// exponent-based power-of-two scale: amax = largest |x| as raw bits (sign cleared); returns 2^(13 - e) and its inverse
+__device__ __forceinline__ void range_scale(uint32_t amax_bits, float &scale, float &inv) {
+    int e = (int)(amax_bits >> 23) - 127;               // amax in [2^e, 2^(e+1)); zeros / subnormals: -127
+    if (e >= -2 && e <= 14) {                           // comfortably inside fp16's range already: no scaling (the usual case,
+        scale = inv = 1.f;                              // and the conversion then skips the multiplications)
+        return;
+    }
+    e = e < -100 ? -100 : e;                            // keeps 2^(13 - e) finite; inf / NaN (e = 128) stay inf / NaN
+    scale = __uint_as_float((uint32_t)(13 - e + 127) << 23);
+    inv = __uint_as_float((uint32_t)(e - 13 + 127) << 23);
+}
+template <bool F16>
 __global__ void __launch_bounds__(256) pack_weights_kernel(int n_tables, const float *__restrict__ W, int64_t ldw,
                                                            float *__restrict__ image) {
     const int t = blockIdx.x;
     const float *Wt = W + (size_t)t * BN * ldw;
     char *img = reinterpret_cast<char *>(image) + (size_t)t * W_BYTES;
-    for (int idx = threadIdx.x; idx < BN * (E / 4); idx += blockDim.x) {
-        const int j = idx / (E / 4), c4 = idx % (E / 4);        // row j, float4 chunk c4 of the row
-        const float4 w = *reinterpret_cast<const float4 *>(Wt + (size_t)j * ldw + 4 * c4);
-        const int kb = c4 / 8, c = c4 % 8;
+    if (!F16) {
+        for (int idx = threadIdx.x; idx < BN * (E / 4); idx += blockDim.x) {
+            const int j = idx / (E / 4), c4 = idx % (E / 4);        // row j, float4 chunk c4 of the row
+            const float4 w = *reinterpret_cast<const float4 *>(Wt + (size_t)j * ldw + 4 * c4);
+            const int kb = c4 / 8, c = c4 % 8;
+            uint4 hi, lo;
+            hi.x = to_tf32(w.x); hi.y = to_tf32(w.y); hi.z = to_tf32(w.z); hi.w = to_tf32(w.w);
+            lo.x = to_tf32(w.x - __uint_as_float(hi.x)); lo.y = to_tf32(w.y - __uint_as_float(hi.y));
+            lo.z = to_tf32(w.z - __uint_as_float(hi.z)); lo.w = to_tf32(w.w - __uint_as_float(hi.w));
+            *reinterpret_cast<uint4 *>(img + (size_t)kb * KB_BYTES + swz(j, c)) = hi;
+            *reinterpret_cast<uint4 *>(img + (size_t)(NKB + kb) * KB_BYTES + swz(j, c)) = lo;
+        }
+        return;
+    }
+    __shared__ uint32_t s_max[8];
+    uint32_t amax = 0;
+    for (int idx = threadIdx.x; idx < BN * E; idx += blockDim.x)
+        amax = max(amax, __float_as_uint(Wt[(size_t)(idx / E) * ldw + idx % E]) & 0x7fffffffu);
+    amax = __reduce_max_sync(0xffffffffu, amax);
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = amax;
+    __syncthreads();
+    for (int w = 0; w < 8; ++w) amax = max(amax, s_max[w]);
+    float sc, inv;
+    range_scale(amax, sc, inv);
+    if (threadIdx.x == 0) reinterpret_cast<float *>(img)[kScaleAt] = inv;
+    for (int idx = threadIdx.x; idx < BN * (E / 8); idx += blockDim.x) {
+        const int j = idx / (E / 8), c8 = idx % (E / 8);        // row j, chunk of 8 k-elements
+        const float4 w0 = *reinterpret_cast<const float4 *>(Wt + (size_t)j * ldw + 8 * c8);
+        const float4 w1 = *reinterpret_cast<const float4 *>(Wt + (size_t)j * ldw + 8 * c8 + 4);
+        const int kb = c8 / 8, c = c8 % 8;
         uint4 hi, lo;
-        hi.x = to_tf32(w.x); hi.y = to_tf32(w.y); hi.z = to_tf32(w.z); hi.w = to_tf32(w.w);
-        lo.x = to_tf32(w.x - __uint_as_float(hi.x)); lo.y = to_tf32(w.y - __uint_as_float(hi.y));
-        lo.z = to_tf32(w.z - __uint_as_float(hi.z)); lo.w = to_tf32(w.w - __uint_as_float(hi.w));
+        split_f16x2(w0.x * sc, w0.y * sc, hi.x, lo.x);
+        split_f16x2(w0.z * sc, w0.w * sc, hi.y, lo.y);
+        split_f16x2(w1.x * sc, w1.y * sc, hi.z, lo.z);
+        split_f16x2(w1.z * sc, w1.w * sc, hi.w, lo.w);
         *reinterpret_cast<uint4 *>(img + (size_t)kb * KB_BYTES + swz(j, c)) = hi;
-        *reinterpret_cast<uint4 *>(img + (size_t)(NKB + kb) * KB_BYTES + swz(j, c)) = lo;
+        *reinterpret_cast<uint4 *>(img + (size_t)(2 + kb) * KB_BYTES + swz(j, c)) = lo;
     }
 }
 
 // RES: the epilogue adds skip rows (`residual`).  A compile-time switch: the 32 registers of the prefetched skip rows
 // push the drain over the 128-register cap, and its spilled loop state reloads behind the row stores.
-template <bool RES>
+// F16: FP16 operand halves with per-tile / per-table range scales (single K chunk only), see the header.
+template <bool RES, bool F16>
 __global__ void __launch_bounds__(kThreads, 1)
 am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_groups, int n_chunks, int tb,
                      const float *__restrict__ h,
@@ -85,7 +141,13 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
     uint64_t *acc_full = a_empty + A_STAGES, *acc_empty = acc_full + TB;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + TB);
     float *s_bias = reinterpret_cast<float *>(sO + 2 * OUT_BYTES + 256);   // this table's 128 bias values (zeros if none)
-    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 + 4 * 4 <= 256, "barrier block (+ tmem slot + 4 tile-count slots)");
+    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 + 4 * 4 <= 144, "barrier block (+ tmem slot + 4 tile-count slots)");
+    // FP16 form: largest |a| of the tile being converted, one slot per producer warp, double buffered by tile parity;
+    // inverse tile scales for the epilogue, a ring of 8 tiles (the producers run at most TB + 2 tiles ahead of it)
+    uint32_t *s_amax = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(bars) + 144);
+    float *s_ascale = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(bars) + 208);
+    constexpr int NKBX = F16 ? 2 : NKB;                 // k-blocks (128-byte swizzle rows) per K chunk
+    constexpr unsigned kWLoad = 2 * NKBX * KB_BYTES;    // bytes of the weight image the MMAs read
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int table = blockIdx.x % n_tables, group = blockIdx.x / n_tables;
@@ -139,21 +201,39 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                         we_phase ^= 1u;
                     }
                     if (lane == 0) {
-                        mbar_expect_tx(w_full, (unsigned)W_BYTES);
+                        mbar_expect_tx(w_full, kWLoad);
                         const char *src = reinterpret_cast<const char *>(image) + ((size_t)kc * n_tables + table) * W_BYTES;
-                        for (int off = 0; off < W_BYTES; off += KB_BYTES) tma_load_1d(sW + off, src + off, KB_BYTES, w_full);
+                        for (unsigned off = 0; off < kWLoad; off += KB_BYTES) tma_load_1d(sW + off, src + off, KB_BYTES, w_full);
                     }
                     __syncwarp();
                     mbar_wait_bounded(w_full, w_phase);
                     w_phase ^= 1u;
                 }
                 for (int t = 0; t < nt; ++t) {
+                    if (F16 && ldx == E && lane == 0) {
+                        // the tile after next of this CTA's walk -> L2 (rows of a tile are contiguous when ldx = 128): the
+                        // producers can only issue the register loads of a tile once the previous one is converted, so
+                        // these should return from L2.  Issued here because this warp has the time (a bulk prefetch takes
+                        // ~600 clk to issue, which the producers' critical path cannot afford)
+                        int pb = blk, pt = t + 2;
+                        while (pb < n_blocks && pt >= tiles_in(pb)) { pt -= tiles_in(pb); pb += n_groups; }
+                        const int64_t m = ((int64_t)pb * tb + pt) * BM;
+                        if (pb < n_blocks && m < M) {
+                            const int64_t rows = M - m < BM ? M - m : BM;
+                            const char *src = reinterpret_cast<const char *>(h + m * E);
+                            const unsigned bytes = (unsigned)rows * E * 4;
+                            for (unsigned off = 0; off < bytes; off += 32768)
+                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + off),
+                                             "r"(bytes - off < 32768u ? bytes - off : 32768u) : "memory");
+                        }
+                    }
+                    __syncwarp();
                     if (kc == 0) mbar_wait_bounded(&acc_empty[t], (unsigned)(bi & 1) ^ 1u);   // drained by the epilogue
                     tc_fence_after();
                     const uint32_t d = tmem_u + (uint32_t)(t * BN);
                     const bool last = kc == n_chunks - 1;
 #pragma unroll
-                    for (int kb = 0; kb < NKB; ++kb) {
+                    for (int kb = 0; kb < NKBX; ++kb) {
                         const int stage = kb & 1;
                         mbar_wait_bounded(&a_full[stage], a_phase);
 #ifndef TC_PRODUCER_FENCE
@@ -166,18 +246,24 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
 #endif
                         tc_fence_after();
                         const uint32_t a_hi = dA + (uint32_t)((stage * A_STAGE_BYTES) >> 4), a_lo = a_hi + (KB_BYTES >> 4);
-                        const uint32_t b_hi = dW + (uint32_t)((kb * KB_BYTES) >> 4), b_lo = b_hi + ((NKB * KB_BYTES) >> 4);
+                        const uint32_t b_hi = dW + (uint32_t)((kb * KB_BYTES) >> 4), b_lo = b_hi + ((NKBX * KB_BYTES) >> 4);
                         if (elect_one()) {
 #pragma unroll
-                            for (int k8 = 0; k8 < KB / 8; ++k8) {   // K = 8 tf32 = 32 bytes = 2 address units per instruction
-                                umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, kIdesc, (unsigned)((kb | k8) != 0 || kc != 0));
+                            for (int k8 = 0; k8 < KB / 8; ++k8) {   // 32 bytes of K (8 tf32 / 16 fp16) = 2 address units per instruction
+                                if (F16) {
+                                    umma_f16(d, a_lo + 2 * k8, b_hi + 2 * k8, kIdescH, (unsigned)((kb | k8) != 0));
+                                    umma_f16(d, a_hi + 2 * k8, b_lo + 2 * k8, kIdescH, 1u);
+                                    umma_f16(d, a_hi + 2 * k8, b_hi + 2 * k8, kIdescH, 1u);
+                                } else {
+                                    umma_tf32(d, a_lo + 2 * k8, b_hi + 2 * k8, kIdesc, (unsigned)((kb | k8) != 0 || kc != 0));
 #ifndef TC_EXP_ONE_MMA
-                                umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, kIdesc, 1u);
-                                umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, kIdesc, 1u);
+                                    umma_tf32(d, a_hi + 2 * k8, b_lo + 2 * k8, kIdesc, 1u);
+                                    umma_tf32(d, a_hi + 2 * k8, b_hi + 2 * k8, kIdesc, 1u);
 #endif
+                                }
                             }
                             umma_commit(&a_empty[stage]);           // smem slot free once these MMAs have read it
-                            if (kb == NKB - 1 && last) umma_commit(&acc_full[t]);   // accumulator complete
+                            if (kb == NKBX - 1 && last) umma_commit(&acc_full[t]);  // accumulator complete
                         }
                         __syncwarp();
                         if (stage == A_STAGES - 1) a_phase ^= 1u;
@@ -191,6 +277,112 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
         }
         __syncwarp();
     } else if (warp <= kProducerWarps) {
+        if constexpr (F16) {
+        // ================================================= producers, FP16 form: h tile -> range scale -> hi / lo halves
+        // thread = (row r0 + 32 i, 16-byte chunk c of the k-block's 128-byte row = 8 k-elements = two float4 of h)
+        const int p = tid - 32;                                 // 0..255
+        const int c = p & 7, r0 = p >> 3;
+        constexpr int RPT = BM / (kProducerWarps * 4);          // rows per thread and k-block (4)
+        int stage = 0;
+        unsigned phase = 0, cnt = 0;
+        float4 v[2][RPT][2];                                    // one tile of h: 16 LDG.128 per thread in flight
+        auto load_kb = [&](int blk, int t, int kb) {
+#pragma unroll
+            for (int i = 0; i < RPT; ++i) {
+                const int64_t m = (int64_t)(blk * tb + t) * BM + r0 + 32 * i;
+                if (blk < n_blocks && m < M) {
+                    const float4 *src = reinterpret_cast<const float4 *>(h + m * ldx + kb * 64) + 2 * c;
+                    v[kb][i][0] = __ldg(src);
+                    v[kb][i][1] = __ldg(src + 1);
+                } else {
+                    v[kb][i][0] = v[kb][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+        };
+        auto advance = [&](int &blk, int &t) {                  // next (block, tile) of the walk
+            if (blk >= n_blocks) return;
+            if (++t >= tiles_in(blk)) { t = 0; blk += n_groups; }
+        };
+        int blk = group, nblk = group;
+        int t = 0, ntl = 0;
+        advance(nblk, ntl);
+        load_kb(blk, t, 0);
+        load_kb(blk, t, 1);
+#ifdef TC_PTRACE
+        long long tr[6] = {0, 0, 0, 0, 0, 0}, t0 = clock64(), t1;
+#define PT(k) do { t1 = clock64(); tr[k] += t1 - t0; t0 = t1; } while (0)
+#else
+#define PT(k) do { } while (0)
+#endif
+        while (blk < n_blocks) {
+            PT(0);
+            // largest |a| of the tile: thread -> warp -> the eight producer warps
+            float fm = 0.f;
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+                for (int i = 0; i < RPT; ++i)
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const float4 a4 = v[kb][i][u];
+                        fm = fmaxf(fmaxf(fm, fmaxf(fabsf(a4.x), fabsf(a4.y))), fmaxf(fabsf(a4.z), fabsf(a4.w)));
+                    }
+            // (fmaxf drops NaNs: a NaN entry still reaches the output through the MMA, only the scale ignores it)
+            uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(fm));
+            PT(1);
+            uint32_t *slot = s_amax + (cnt & 1u) * 8;
+            if (lane == 0) slot[warp - 1] = am;
+            asm volatile("bar.sync 2, 256;" ::: "memory");         // the eight producer warps
+            PT(2);
+            {
+                const uint4 m0 = *reinterpret_cast<const uint4 *>(slot), m1 = *reinterpret_cast<const uint4 *>(slot + 4);
+                am = max(max(max(m0.x, m0.y), max(m0.z, m0.w)), max(max(m1.x, m1.y), max(m1.z, m1.w)));
+            }
+            float sc, inv;
+            range_scale(am, sc, inv);
+            if (p == 0) s_ascale[cnt & 7u] = inv;               // read by the epilogue behind a_full -> commit -> acc_full
+            auto convert = [&](auto scaled) {
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb) {
+                    PT(5);
+                    mbar_wait_bounded(&a_empty[stage], phase ^ 1u);
+                    PT(3);
+                    unsigned char *hi_img = sA + stage * A_STAGE_BYTES, *lo_img = hi_img + KB_BYTES;
+#pragma unroll
+                    for (int i = 0; i < RPT; ++i) {
+                        const int r = r0 + 32 * i;
+                        float4 a0 = v[kb][i][0], a1 = v[kb][i][1];
+                        if (decltype(scaled)::value) {
+                            a0.x *= sc; a0.y *= sc; a0.z *= sc; a0.w *= sc;
+                            a1.x *= sc; a1.y *= sc; a1.z *= sc; a1.w *= sc;
+                        }
+                        uint4 hi, lo;
+                        split_f16x2_trunc(a0.x, a0.y, hi.x, lo.x);
+                        split_f16x2_trunc(a0.z, a0.w, hi.y, lo.y);
+                        split_f16x2_trunc(a1.x, a1.y, hi.z, lo.z);
+                        split_f16x2_trunc(a1.z, a1.w, hi.w, lo.w);
+                        *reinterpret_cast<uint4 *>(hi_img + swz(r, c)) = hi;
+                        *reinterpret_cast<uint4 *>(lo_img + swz(r, c)) = lo;
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&a_full[stage]);
+                    PT(4);
+                    load_kb(nblk, ntl, kb);                     // refill for the next tile (see the TF32 form below)
+                    if (++stage == A_STAGES) { stage = 0; phase ^= 1u; }
+                }
+            };
+            if (sc == 1.f) convert(std::false_type{});
+            else convert(std::true_type{});
+            blk = nblk; t = ntl;
+            advance(nblk, ntl);
+            ++cnt;
+        }
+#ifdef TC_PTRACE
+        if (blockIdx.x == 0 && p == 0)
+            printf("producer clocks per tile over %u tiles: top %lld | amax (load wait) %lld | barrier %lld | a_empty wait %lld | convert+arrive %lld | refill issue %lld\n",
+                   cnt, tr[0] / cnt, tr[1] / cnt, tr[2] / cnt, tr[3] / cnt, tr[4] / cnt, tr[5] / cnt);
+#endif
+        } else {
         // ================================================= producers: h tile -> hi / lo swizzled images
         const int p = tid - 32;                                 // 0..255
         const int c = p & 7, r0 = p >> 3;                       // 16-byte chunk of the k-block row, first row
@@ -261,10 +453,15 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
             blk = nblk; kc = nkc; t = ntl;
             advance(nblk, nkc, ntl);
         }
+        }
     } else {
         // ================================================= epilogue: TMEM -> registers -> table rows
         // Per 32-column block: tcgen05.ld (thread = row) -> swizzled staging -> thread = (row group, 16-byte
-        // chunk) -> 512-byte coalesced row stores.  All addresses are hoisted: a thread's eight staging reads
+        // chunk) -> 512-byte coalesced row stores.  (Storing straight from the tcgen05.ld registers - thread = row, four
+        // 32-byte st.global.v8 per column block, no staging - was measured 25 % SLOWER, 1.76 vs 1.41 ms on 1 638 400 rows x 5
+        // tables: 32 separate sectors per store instruction cost the L1 more than the staging traffic saves.  Staging
+        // thread = row into padded rows and one 512-byte cp.async.bulk store per row - no LDS / STG / barrier - was measured
+        // EQUAL, 1.40 ms: the staging is not what bounds this kernel.)  All addresses are hoisted: a thread's eight staging reads
         // are 2 KB apart (same swizzle phase) and its eight rows 16 * ldo apart.
         const int q = warp & 3;                                 // TMEM lane quarter this warp may access
         const int row = 32 * q + lane;
@@ -293,6 +490,9 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
             asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(s_nt) : "memory");
             return v;
         };
+        // FP16 form: inverse scale of the table's weights (constant) times the inverse scale of each tile of h
+        const float w_inv = F16 ? __ldg(image + (size_t)table * kImageFloats + kScaleAt) : 1.f;
+        unsigned cnt = 0;
         int bi = 0;
         for (int blk = group; blk < n_blocks; blk += n_groups, ++bi) {
         __syncwarp();
@@ -312,6 +512,11 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
             const float *r_ptr = (RES && residual) ? residual + m0 * ldo + table * BN + ch * 4 : nullptr;
             mbar_wait_bounded(&acc_full[t], (unsigned)(bi & 1));
             tc_fence_after();
+            float unscale = 1.f;
+            if (F16) {
+                unscale = w_inv * s_ascale[cnt & 7u];
+                ++cnt;
+            }
 #pragma unroll
             for (int cb = 0; cb < BN / 32; ++cb) {
                 float4 rs[8];
@@ -333,6 +538,10 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                       "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                     : "r"(taddr));
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (F16) {
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) * unscale);
+                }
                 if (cb == BN / 32 - 1) {                        // accumulator drained: hand it back to the MMA warp
                     tc_fence_before();
                     __syncwarp();
@@ -406,8 +615,10 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
 
 }  // namespace tc
 
-int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, cudaStream_t stream) {
-    tc::pack_weights_kernel<<<n_tables, 256, 0, stream>>>(n_tables, W, ldw, image);
+// f16: the image of a single-K-chunk product (K = 128), see the header
+int launch_pack_weights(int n_tables, const float *W, int64_t ldw, float *image, bool f16, cudaStream_t stream) {
+    if (f16) tc::pack_weights_kernel<true><<<n_tables, 256, 0, stream>>>(n_tables, W, ldw, image);
+    else tc::pack_weights_kernel<false><<<n_tables, 256, 0, stream>>>(n_tables, W, ldw, image);
     RL4CO_CHECK_LAUNCH("am_pack_weights");
     return 0;
 }
@@ -423,10 +634,10 @@ int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, con
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    cudaError_t e = cudaFuncSetAttribute(tc::am_project_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         tc::SMEM_BYTES);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(tc::am_project_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
+    const bool f16 = n_chunks == 1;                             // must match the image: launch_pack_weights(.., f16, ..)
+    auto kernel = f16 ? (residual ? tc::am_project_tc_kernel<true, true> : tc::am_project_tc_kernel<false, true>)
+                      : (residual ? tc::am_project_tc_kernel<true, false> : tc::am_project_tc_kernel<false, false>);
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SMEM_BYTES);
     if (e != cudaSuccess) {
         set_error("am_project(tc): cannot reserve %d B of shared memory: %s", tc::SMEM_BYTES, cudaGetErrorString(e));
         return 2;
@@ -443,7 +654,6 @@ int launch_project_tc(int64_t M, int n_tables, int n_chunks, const float *h, con
     int64_t tb = n_tiles / groups;
     if (tb > tc::TB) tb = tc::TB;
     if (tb < 1) tb = 1;
-    auto kernel = residual ? tc::am_project_tc_kernel<true> : tc::am_project_tc_kernel<false>;
     kernel<<<(unsigned)(groups * n_tables), tc::kThreads, tc::SMEM_BYTES, stream>>>(
         M, (int)n_tiles, (int)((n_tiles + tb - 1) / tb), n_tables, (int)groups, n_chunks, (int)tb, h, image, tables, table_stride,
         ldo, bias, relu, ldx, accumulate, residual, scale, shift);

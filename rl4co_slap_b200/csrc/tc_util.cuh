@@ -56,6 +56,42 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint32_t a_lo32, uint
         "}\n" ::"r"(tmem_d), "r"(a_lo32), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHi)
         : "memory");
 }
+// the same for fp16 operands (kind::f16: A = B = F16 = format 0, K = 16 per instruction), fp32 accumulation
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint32_t a_lo32, uint32_t b_lo32, uint32_t idesc,
+                                         uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b64 da, {%1, %5};\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(a_lo32), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHi)
+        : "memory");
+}
+// the same split by truncation: hi = the top 11 significant bits of x (exactly representable in fp16 while |x| is in fp16's
+// normal range), lo = fp16(x - hi) with x - hi exact - no conversion back to fp32; x = hi + lo to 21-22 significant bits
+__device__ __forceinline__ void split_f16x2_trunc(float x0, float x1, uint32_t &hi, uint32_t &lo) {
+    const float h0 = __uint_as_float(__float_as_uint(x0) & 0xffffe000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xffffe000u);
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(h1), "f"(h0));     // first source -> upper half
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - h1), "f"(x0 - h0));
+}
+// two fp32 -> fp16 pairs hi, lo with x = hi + lo to 22 significant bits (lo = fp16(x - hi), exact difference)
+__device__ __forceinline__ void split_f16x2(float x0, float x1, uint32_t &hi, uint32_t &lo) {
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(x1), "f"(x0));     // first source -> upper half
+    float b0, b1;
+    asm("{\n\t"
+        ".reg .b16 l, h;\n\t"
+        "mov.b32 {l, h}, %2;\n\t"
+        "cvt.f32.f16 %0, l;\n\t"
+        "cvt.f32.f16 %1, h;\n\t"
+        "}\n" : "=f"(b0), "=f"(b1) : "r"(hi));
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - b1), "f"(x0 - b0));
+}
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {    // arrives when all prior MMAs are done
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
