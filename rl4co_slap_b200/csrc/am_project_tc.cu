@@ -21,10 +21,12 @@
 // split into hi / lo and laid out in the 128-byte-swizzled K-major image the MMA reads
 // (rl4co_am_pack_weights) - resident in shared memory (128 KB, one TMA bulk load), and streams
 // 128-row tiles of h:
-//   warps 1-8  producers: coalesced LDG of a 128 x 32 fp32 k-block, hi / lo split, swizzled
-//              st.shared into a 2-stage ring, mbarrier full / empty;
-//   warp 0     one elected lane issues 48 tcgen05.mma (M128 N128 K8, kind::tf32) per tile and
-//              commits to the mbarriers;
+//   warps 1-8  producers: TF32 form - coalesced LDG of a 128 x 32 fp32 k-block, hi / lo split, swizzled
+//              st.shared into a 2-stage ring, mbarrier full / empty; FP16 form - the raw fp32 tile is landed in
+//              shared memory by TMA a tile ahead (the image is half the size, which frees the room), the
+//              warps read it, find the tile's range, and write the two 128 x 64 fp16 k-block images;
+//   warp 0     one elected lane issues 48 tcgen05.mma (M128 N128 K8, kind::tf32) or 24 (K16, kind::f16) per
+//              tile and commits to the mbarriers;
 //   warps 9-12 epilogue: tcgen05.ld the 128 x 128 fp32 accumulator (double buffered in TMEM,
 //              2 x 128 columns) and store it to the table.
 // The tables of one instance are read back by the rollout kernel row by row, so the output stays
@@ -141,11 +143,13 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
     uint64_t *acc_full = a_empty + A_STAGES, *acc_empty = acc_full + TB;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + TB);
     float *s_bias = reinterpret_cast<float *>(sO + 2 * OUT_BYTES + 256);   // this table's 128 bias values (zeros if none)
-    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 + 4 * 4 <= 144, "barrier block (+ tmem slot + 4 tile-count slots)");
+    static_assert((2 + 2 * A_STAGES + 2 * TB) * 8 + 4 + 4 * 4 <= 136, "barrier block (+ tmem slot + 4 tile-count slots)");
     // FP16 form: largest |a| of the tile being converted, one slot per producer warp, double buffered by tile parity;
     // inverse tile scales for the epilogue, a ring of 8 tiles (the producers run at most TB + 2 tiles ahead of it)
-    uint32_t *s_amax = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(bars) + 144);
-    float *s_ascale = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(bars) + 208);
+    uint32_t *s_amax = reinterpret_cast<uint32_t *>(reinterpret_cast<unsigned char *>(bars) + 160);
+    float *s_ascale = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(bars) + 224);
+    // FP16 form: the raw fp32 tile of h in shared memory (upper half of the weight region) is complete
+    uint64_t *raw_full = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(bars) + 136);
     constexpr int NKBX = F16 ? 2 : NKB;                 // k-blocks (128-byte swizzle rows) per K chunk
     constexpr unsigned kWLoad = 2 * NKBX * KB_BYTES;    // bytes of the weight image the MMAs read
 
@@ -164,6 +168,7 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
         mbar_init(w_empty, 1);
         for (int s = 0; s < A_STAGES; ++s) { mbar_init(&a_full[s], kProducerWarps); mbar_init(&a_empty[s], 1); }
         for (int s = 0; s < TB; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4); }
+        mbar_init(raw_full, 1);
         fence_barrier_init();
     }
     if (tid < BN) {                                             // per-column epilogue vectors of this table
@@ -210,24 +215,6 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                     w_phase ^= 1u;
                 }
                 for (int t = 0; t < nt; ++t) {
-                    if (F16 && ldx == E && lane == 0) {
-                        // the tile after next of this CTA's walk -> L2 (rows of a tile are contiguous when ldx = 128): the
-                        // producers can only issue the register loads of a tile once the previous one is converted, so
-                        // these should return from L2.  Issued here because this warp has the time (a bulk prefetch takes
-                        // ~600 clk to issue, which the producers' critical path cannot afford)
-                        int pb = blk, pt = t + 2;
-                        while (pb < n_blocks && pt >= tiles_in(pb)) { pt -= tiles_in(pb); pb += n_groups; }
-                        const int64_t m = ((int64_t)pb * tb + pt) * BM;
-                        if (pb < n_blocks && m < M) {
-                            const int64_t rows = M - m < BM ? M - m : BM;
-                            const char *src = reinterpret_cast<const char *>(h + m * E);
-                            const unsigned bytes = (unsigned)rows * E * 4;
-                            for (unsigned off = 0; off < bytes; off += 32768)
-                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + off),
-                                             "r"(bytes - off < 32768u ? bytes - off : 32768u) : "memory");
-                        }
-                    }
-                    __syncwarp();
                     if (kc == 0) mbar_wait_bounded(&acc_empty[t], (unsigned)(bi & 1) ^ 1u);   // drained by the epilogue
                     tc_fence_after();
                     const uint32_t d = tmem_u + (uint32_t)(t * BN);
@@ -279,35 +266,40 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
     } else if (warp <= kProducerWarps) {
         if constexpr (F16) {
         // ================================================= producers, FP16 form: h tile -> range scale -> hi / lo halves
+        // The raw fp32 tile (128 rows x 512 B, contiguous: ldx = 128 whenever K = 128) is landed in shared memory by TMA
+        // bulk copies, a tile ahead, into the half of the weight region the FP16 image leaves free; the producers read
+        // their elements from there.  (Loading them straight into registers - 16 LDG.128 per thread - had the whole tile's
+        // load latency in front of every conversion, since the range scale needs the complete tile, plus ~1.4k clk per
+        // tile of stalled load ISSUE: 1.40 vs 1.20 ms on 1 638 400 rows x 5 tables, -DTC_PTRACE.)
         // thread = (row r0 + 32 i, 16-byte chunk c of the k-block's 128-byte row = 8 k-elements = two float4 of h)
         const int p = tid - 32;                                 // 0..255
         const int c = p & 7, r0 = p >> 3;
         constexpr int RPT = BM / (kProducerWarps * 4);          // rows per thread and k-block (4)
+        const unsigned char *raw = sW + 65536;                  // [128][128] fp32
         int stage = 0;
-        unsigned phase = 0, cnt = 0;
-        float4 v[2][RPT][2];                                    // one tile of h: 16 LDG.128 per thread in flight
-        auto load_kb = [&](int blk, int t, int kb) {
-#pragma unroll
-            for (int i = 0; i < RPT; ++i) {
-                const int64_t m = (int64_t)(blk * tb + t) * BM + r0 + 32 * i;
-                if (blk < n_blocks && m < M) {
-                    const float4 *src = reinterpret_cast<const float4 *>(h + m * ldx + kb * 64) + 2 * c;
-                    v[kb][i][0] = __ldg(src);
-                    v[kb][i][1] = __ldg(src + 1);
-                } else {
-                    v[kb][i][0] = v[kb][i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            }
-        };
+        unsigned phase = 0, cnt = 0, rphase = 0;
         auto advance = [&](int &blk, int &t) {                  // next (block, tile) of the walk
             if (blk >= n_blocks) return;
             if (++t >= tiles_in(blk)) { t = 0; blk += n_groups; }
         };
+        auto rows_of = [&](int blk, int t) {                    // valid rows of a tile (0 past the end of the walk)
+            if (blk >= n_blocks) return (int64_t)0;
+            const int64_t left = M - (int64_t)(blk * tb + t) * BM;
+            return left < 0 ? (int64_t)0 : (left < BM ? left : (int64_t)BM);
+        };
+        auto stage_raw = [&](int blk, int t) {                  // thread 0: TMA the tile's rows
+            const int64_t rows = rows_of(blk, t);
+            if (rows == 0) return;
+            const char *src = reinterpret_cast<const char *>(h + (int64_t)(blk * tb + t) * BM * E);
+            const unsigned bytes = (unsigned)rows * E * 4;
+            mbar_expect_tx(raw_full, bytes);
+            for (unsigned off = 0; off < bytes; off += 16384)
+                tma_load_1d(const_cast<unsigned char *>(raw) + off, src + off, bytes - off < 16384u ? bytes - off : 16384u, raw_full);
+        };
         int blk = group, nblk = group;
         int t = 0, ntl = 0;
         advance(nblk, ntl);
-        load_kb(blk, t, 0);
-        load_kb(blk, t, 1);
+        if (p == 0) stage_raw(blk, t);
 #ifdef TC_PTRACE
         long long tr[6] = {0, 0, 0, 0, 0, 0}, t0 = clock64(), t1;
 #define PT(k) do { t1 = clock64(); tr[k] += t1 - t0; t0 = t1; } while (0)
@@ -316,6 +308,24 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
 #endif
         while (blk < n_blocks) {
             PT(0);
+            const int rows_ok = (int)rows_of(blk, t);
+            mbar_wait_bounded(raw_full, rphase);
+            rphase ^= 1u;
+            float4 v[2][RPT][2];                                // this thread's 64 elements of the tile
+            // a lane reads its 32 bytes as two 16-byte halves, lanes c >= 4 the upper half first: the 8 lanes of a
+            // quarter-warp phase then touch all 32 banks once
+            const int swap = (c >> 2) & 1;
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb)
+#pragma unroll
+                for (int i = 0; i < RPT; ++i) {
+                    const int r = r0 + 32 * i;
+                    const float4 *src = reinterpret_cast<const float4 *>(raw + (size_t)r * 512 + kb * 256 + c * 32);
+                    const float4 x = src[swap], y = src[swap ^ 1];
+                    const bool ok = r < rows_ok;
+                    v[kb][i][0] = ok ? (swap ? y : x) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[kb][i][1] = ok ? (swap ? x : y) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
             // largest |a| of the tile: thread -> warp -> the eight producer warps
             float fm = 0.f;
 #pragma unroll
@@ -332,8 +342,13 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
             PT(1);
             uint32_t *slot = s_amax + (cnt & 1u) * 8;
             if (lane == 0) slot[warp - 1] = am;
-            asm volatile("bar.sync 2, 256;" ::: "memory");         // the eight producer warps
+            asm volatile("bar.sync 2, 256;" ::: "memory");         // the eight producer warps; everyone has read the raw tile
             PT(2);
+            // ... so the next one may land on it.  (Issued from here although a bulk copy takes a few hundred cycles to issue:
+            // handing it to the MMA warp or to a warp of its own, which wait for a signal first, was measured slower,
+            // 1.28 vs 1.20 ms; so was a cluster of the n_tables CTAs multicasting the tile to each other, 1.75 ms - with one
+            // buffer the whole cluster waits for its slowest member before anything can be fetched.)
+            if (p == 0) stage_raw(nblk, ntl);
             {
                 const uint4 m0 = *reinterpret_cast<const uint4 *>(slot), m1 = *reinterpret_cast<const uint4 *>(slot + 4);
                 am = max(max(max(m0.x, m0.y), max(m0.z, m0.w)), max(max(m1.x, m1.y), max(m1.z, m1.w)));
@@ -367,7 +382,6 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&a_full[stage]);
                     PT(4);
-                    load_kb(nblk, ntl, kb);                     // refill for the next tile (see the TF32 form below)
                     if (++stage == A_STAGES) { stage = 0; phase ^= 1u; }
                 }
             };
@@ -379,7 +393,7 @@ am_project_tc_kernel(int64_t M, int n_tiles, int n_blocks, int n_tables, int n_g
         }
 #ifdef TC_PTRACE
         if (blockIdx.x == 0 && p == 0)
-            printf("producer clocks per tile over %u tiles: top %lld | amax (load wait) %lld | barrier %lld | a_empty wait %lld | convert+arrive %lld | refill issue %lld\n",
+            printf("producer clocks per tile over %u tiles: top %lld | raw wait + LDS + amax %lld | barrier %lld | a_empty wait %lld | convert+arrive %lld | between k-blocks %lld\n",
                    cnt, tr[0] / cnt, tr[1] / cnt, tr[2] / cnt, tr[3] / cnt, tr[4] / cnt, tr[5] / cnt);
 #endif
         } else {
