@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RL4CO_ABI_VERSION 2
+#define RL4CO_ABI_VERSION 3
 
 /* status bits (device int32 word) */
 #define RL4CO_ST_INVALID_TOUR      1   /* tsp/env.py:173, cvrp/env.py:175 */
@@ -331,6 +331,10 @@ typedef struct rl4co_am_rollout_args {
      * (nn/env_embeddings/dynamic.py:61-79) as wdyn [3][E] = its Linear(1, 3E) weight split into the glimpse-key and
      * glimpse-value columns and Wout^T times the logit-key column (project_out folded as for table 2) */
     const float *wdyn;
+    /* multistart with caller-chosen start nodes (appended, ABI 3): start_nodes [R] int32, rollout r = s*B + b starts at
+     * start_nodes[r] instead of s % num_loc (+1) - what a select_start_nodes_fn returned (utils/decoding.py:287-291), e.g.
+     * the op branch of utils/ops.py:166-176 that resamples the starts from the feasible nodes.  NULL: the default rule. */
+    const int32_t *start_nodes;
 } rl4co_am_rollout_args;
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);

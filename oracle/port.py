@@ -548,6 +548,11 @@ def pointer_logits(q, cache, mask, W):
 def decoder_forward(env_name, td_flat: State, cache, W, num_starts: int):
     """am/decoder.py:162-200: returns (logits, mask), flattened start-major for multistart."""
     td = td_flat
+    if env_name == "sdvrp" and num_starts > 1:
+        # has_dyn_emb_multi_start, am/decoder.py:176-187: keys and values are not shared across starts (the episodes modify
+        # them), so the CACHE is batchified to [S*B, ...] and the state stays flat - S*B independent single-start rows
+        cache = {k: (batchify(v, num_starts) if isinstance(v, torch.Tensor) else v) for k, v in cache.items()}
+        num_starts = 0
     if num_starts > 1:
         td = {k: unbatchify(v, num_starts) for k, v in td_flat.items() if isinstance(v, torch.Tensor)}
     gctx = cache["gctx"]
@@ -558,7 +563,6 @@ def decoder_forward(env_name, td_flat: State, cache, W, num_starts: int):
         q = q.unsqueeze(1)
     mask = td["action_mask"]
     if env_name == "sdvrp":     # SDVRPDynamicEmbedding, dynamic.py:61-79 + _compute_kvl, am/decoder.py:148-160
-        assert num_starts <= 1, "sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not restated"
         d = td["demand_with_depot"][..., None].clone().to(cache["gk"].dtype)
         d[..., 0, :] = 0
         k_dyn, v_dyn, l_dyn = F.linear(d, W["Wdyn"]).chunk(3, dim=-1)
@@ -603,7 +607,7 @@ def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
                num_starts: Optional[int] = None, actions=None, temperature: float = 1.0,
                tanh_clipping: float = 10.0, use_graph_context: bool = True,
                num_loc: Optional[int] = None, return_all_logp: bool = False,
-               check_solution: bool = True, max_steps: int = 1_000_000):
+               check_solution: bool = True, max_steps: int = 1_000_000, start_nodes=None):
     """models/common/constructive/base.py:196-276 with the decoding hooks of
     utils/decoding.py:265-369.  ``td`` is a reset state (tsp_reset / cvrp_reset /
     slap_reset); ``h`` the encoder output [B,N,E]."""
@@ -617,7 +621,9 @@ def am_rollout(env_name: str, td: State, h, W, decode_type: str = "greedy",
         S = num_starts if num_starts is not None else num_starts_for(env_name, td["action_mask"])
         B0 = td["action_mask"].shape[0]
         nl = num_loc if num_loc is not None else (td["locs"].shape[1] - (0 if env_name == "tsp" else 1))
-        a0 = select_start_nodes(env_name, B0, S, nl)
+        # start_nodes [S*B]: what select_start_nodes_fn returned (utils/decoding.py:287-291), e.g. the op branch of
+        # utils/ops.py:166-176 that resamples the starts from the feasible nodes with torch.multinomial
+        a0 = select_start_nodes(env_name, B0, S, nl) if start_nodes is None else torch.as_tensor(start_nodes, dtype=torch.int64)
         td = {k: (batchify(v, S) if isinstance(v, torch.Tensor) else v) for k, v in td.items()}
         td["action"] = a0
         td = _STEP[env_name](td)

@@ -219,7 +219,7 @@ am_rollout_kernel(const rl4co_am_rollout_args a, const int n_smem_tab, const int
         if (warp == 0) {
             if (ENV == RL4CO_ENV_CVRP) cvrp_mask(0, 0.f);
             if (a.multistart) {     // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
-                int a0 = s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
+                int a0 = a.start_nodes ? (int)a.start_nodes[r] : s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
                 if (lane == 0) { s_act[0] = a0; s_lp[0] = 0.f; misc[M_NACT] = 1; }
                 if (a.logp_all)
                     for (int n = lane; n < N; n += 32) a.logp_all[((size_t)r * T) * N + n] = 0.f;
@@ -522,14 +522,14 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         RL4CO_REQUIRE(a.picklist && a.P >= 1 && a.O >= 0 && a.K >= 1 && a.T >= a.P, "am_rollout: slap needs picklist and T>=P");
     if (a.env == RL4CO_ENV_OP) {
         RL4CO_REQUIRE(a.wcap && a.prize && a.max_length, "am_rollout: op needs wcap/prize/max_length");
-        // multistart: the caller guarantees that the reference would not resample the start nodes (utils/ops.py:166-176)
+        // multistart: where the reference resamples the start nodes (utils/ops.py:166-176) the caller passes them in start_nodes
         RL4CO_REQUIRE(!a.multistart || a.num_loc >= 1, "am_rollout: bad multistart setup");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: op runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
     if (a.env == RL4CO_ENV_SDVRP) {
         RL4CO_REQUIRE(a.wcap && a.demand && a.vehicle_capacity && a.wdyn, "am_rollout: sdvrp needs wcap/demand/capacity/wdyn");
-        RL4CO_REQUIRE(!a.multistart, "am_rollout: sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not implemented");
+        RL4CO_REQUIRE(!a.multistart || a.num_loc >= 1, "am_rollout: bad multistart setup");
         RL4CO_REQUIRE(rollout_rf_supports(a), "am_rollout: sdvrp runs on the register-file kernel only (N <= 128, no logp_all)");
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
@@ -540,6 +540,7 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
         return launch_rollout_rf(a, (cudaStream_t)stream);
     }
     if (a.multistart) RL4CO_REQUIRE(a.num_loc >= 1 && a.env != RL4CO_ENV_SLAP, "am_rollout: bad multistart setup");
+    RL4CO_REQUIRE(a.start_nodes == nullptr || a.multistart, "am_rollout: start_nodes without multistart");
 
     // multistart (POMO) tsp / cvrp: tensor-core kernel, starts = TMEM lanes (am_rollout_ms_tc.cu)
     if (g_rollout_impl == 0 && rollout_ms_tc_supports(a)) return launch_rollout_ms_tc(a, (cudaStream_t)stream);

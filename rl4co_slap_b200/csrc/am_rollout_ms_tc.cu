@@ -722,6 +722,7 @@ am_rollout_ms_tc_kernel(const rl4co_am_rollout_args a) {
 
 bool rollout_ms_tc_supports(const rl4co_am_rollout_args &a) {
     if (!a.multistart || a.S < 1 || a.S > 128) return false;
+    if (a.start_nodes != nullptr) return false;      // caller-chosen start nodes: the register-file kernel
     if (a.env != RL4CO_ENV_TSP && a.env != RL4CO_ENV_CVRP) return false;
 #ifndef MS_TRACE
     if (a.logp_all != nullptr) return false;

@@ -236,7 +236,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         const float *C = cbuf + (size_t)buf * N * E;
         // ------------------------------------------------ registers <- tables (global / L2)
         u64 K2[M][4], V2[M][4], L2[M][4];
-        {
+        auto load_tables = [&]() {
             const float *kb = a.tables + ((size_t)0 * Mrows + b * (int64_t)N) * E + dim0;
             const float *vb = a.tables + ((size_t)1 * Mrows + b * (int64_t)N) * E + dim0;
             const float *lb = a.tables + ((size_t)2 * Mrows + b * (int64_t)N) * E + dim0;
@@ -252,7 +252,8 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                     for (int i = 0; i < 4; ++i) K2[j][i] = V2[j][i] = L2[j][i] = 0ull;
                 }
             }
-        }
+        };
+        load_tables();
         // constant part of the query, pre-scaled: qbs = scale * (gctx [+ step-0 placeholder])
         u64 qbs2[4];
         auto set_qb = [&](const float *extra) {      // extra: 8 floats at this thread's dims, or null
@@ -546,6 +547,9 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         }
         if (ENV == RL4CO_ENV_CVRP) cvrp_masks(0);
         if (ENV == RL4CO_ENV_SDVRP) {               // remaining demands = demands, every row gets its dynamic term
+            // several starts per instance (am/decoder.py:176-187: keys and values are NOT shared across starts, the
+            // episodes modify them): the previous start left its own dynamic terms in the registers - static rows again
+            if (s != s_begin) load_tables();
             *reinterpret_cast<float4 *>(rem_w + 4 * lane) = *reinterpret_cast<const float4 *>(s_dem + 4 * lane);
             __syncwarp();
             sdvrp_masks(0);
@@ -562,7 +566,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         cur = 0; t = 0; status = 0; done = false; use_c = CAPCOL;
         set_qb(ENV == RL4CO_ENV_TSP ? a.q0 + dim0 : nullptr);   // tsp step 0: context.py:111-121
         if (a.multistart) {                         // forced POMO start node, log-prob 0 (utils/decoding.py:287-305)
-            const int a0 = s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
+            const int a0 = a.start_nodes ? (int)a.start_nodes[r] : s % a.num_loc + (ENV == RL4CO_ENV_TSP ? 0 : 1);
             if (tid == 0) { s_act[0] = a0; s_lp[0] = 0.f; }
             apply(a0);
             t = 1;
@@ -936,7 +940,7 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
-    if (a.multistart && (a.env == RL4CO_ENV_SLAP || a.env == RL4CO_ENV_SDVRP)) return false;
+    if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP, a.env == RL4CO_ENV_SDVRP).total <= (size_t)227 * 1024;
 }
 

@@ -745,6 +745,7 @@ bool rollout_tsp_greedy_supports(const rl4co_am_rollout_args &a) {
 #endif
     if (a.env != RL4CO_ENV_TSP || a.mode == RL4CO_MODE_EVALUATE) return false;
     if (a.S > 1 && !a.multistart) return false;      // several free starts per instance: the generic kernel
+    if (a.start_nodes != nullptr) return false;      // caller-chosen start nodes: the generic kernel
     if (!(a.tanh_clipping > 0.f) || a.temperature != 1.f || a.mask_logits == 0) return false;
     if (a.N > 112 || a.T > tspg::kMaxT || a.N < 2) return false;
     return tspg::smem_total(a.N, a.T) <= (size_t)227 * 1024;

@@ -241,9 +241,6 @@ class AttentionModelPolicy(nn.Module):
         if name != self.decoder.env_name:
             raise ValueError(f"policy was built for {self.decoder.env_name!r}, env is {name!r}")
         multistart = "multistart" in decode_type
-        if multistart and start_fn is not None:
-            raise NotImplementedError("select_start_nodes_fn with multistart decoding: the kernel forces start node "
-                                      "s % num_loc (+1 past a depot), utils/ops.py:139-163")
         if multisample and multistart:
             multisample = False                         # decoding.py:286: the multistart branch wins
         S = 0
@@ -264,22 +261,34 @@ class AttentionModelPolicy(nn.Module):
         elif name == "sdvrp":
             # a customer visit either completes the customer or fills the vehicle, every fill costs one depot visit
             T = 3 * N
-            if multistart or multisample:
-                raise NotImplementedError("sdvrp multistart (dynamic embedding x starts, am/decoder.py:176-187) is not implemented")
             if store_all_logp:
                 raise NotImplementedError("sdvrp: per-node log-probs (return_entropy / store_all_logp) are not "
                                           "produced by the register-file rollout kernel")
         elif name in ("op", "pctsp", "spctsp"):
             # op at worst: depot first (not done at step 0), ..., every customer, depot; pctsp: every customer, depot
             T = N + 1 if name == "op" else N
-            if multistart and name == "op" and bool((td["action_mask"][..., 1:].sum(-1) < S).any()):
-                raise NotImplementedError("op multistart with fewer feasible start nodes than starts: the reference "
-                                          "resamples them with torch.multinomial (utils/ops.py:166-176); not implemented")
             if store_all_logp:
                 raise NotImplementedError(f"{name}: per-node log-probs (return_entropy / store_all_logp) are not "
                                           "produced by the register-file rollout kernel")
         else:  # every customer may be followed by a depot return
             T = 2 * (N - 1) + 1
+        # multistart start nodes (utils/decoding.py:286-291): a caller-supplied select_start_nodes_fn(td, env, num_starts),
+        # or - op with fewer feasible nodes than starts in some instance - the reference's own resampling of the starts
+        # from the feasible nodes (utils/ops.py:166-176, torch.multinomial with replacement).  Otherwise the kernel's
+        # built-in rule s % num_loc (+1 past a depot), which is the rest of utils/ops.py:139-163.
+        start_nodes = None
+        if multistart and start_fn is not None:
+            start_nodes = start_fn(td, env, S)
+        elif multistart and name == "op" and bool((td["action_mask"][..., 1:].float().sum(-1) < S).any()):
+            sel = torch.multinomial(td["action_mask"][..., 1:].float(), S, replacement=True) + 1     # [B,S], depot re-added
+            start_nodes = sel.t().reshape(-1)                                                        # "b n -> (n b)"
+        if start_nodes is not None:
+            start_nodes = torch.as_tensor(start_nodes, device=dev).reshape(-1)
+            if start_nodes.numel() != R:
+                raise ValueError(f"select_start_nodes_fn returned {start_nodes.numel()} nodes for {R} rollouts")
+            if bool(((start_nodes < 0) | (start_nodes >= N)).any()):
+                raise ValueError("select_start_nodes_fn returned a node outside [0, N)")
+            start_nodes = start_nodes.to(torch.int32).contiguous()
         if actions is not None:
             T = actions.shape[-1]
             actions = actions.contiguous()
@@ -364,6 +373,7 @@ class AttentionModelPolicy(nn.Module):
             a.logp_all = _lib.ptr(logp_all[sl]) if logp_all is not None else None
             a.ll, a.reward, a.steps = _lib.ptr(out_ll[sl]), _lib.ptr(out_reward[sl]), _lib.ptr(out_steps[sl])
             a.assignment = _lib.ptr(assign[sl]) if assign is not None else None
+            a.start_nodes = _lib.ptr(start_nodes, torch.int32) if start_nodes is not None else None
             a.status = _lib.ptr(status)
             _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
             launches += 1

@@ -127,10 +127,55 @@ def test_invalid_tours_raise_reference_messages(dev):
         env.check_solution_validity(td, long)
     with pytest.raises(AssertionError, match="Max length exceeded"):     # get_reward's validity check, as the reference
         pol(td, env, actions=long, hidden=t(fx["hidden"], dev))
-    # op10 has instances with fewer than 8 feasible start nodes: the reference would resample them
+
+
+def test_multistart_start_nodes_are_resampled_like_the_reference(dev):
+    """op10 has instances with fewer feasible nodes than starts: the reference draws the start nodes from the feasible
+    ones with torch.multinomial (utils/ops.py:166-176).  The policy does the same draw (same call, torch's generator) and
+    hands the nodes to the kernel; the oracle given the SAME nodes must produce the same tours."""
     fx, pol, env, td = _setup("op10", dev)
-    with pytest.raises(NotImplementedError, match="multistart"):
-        pol(td, env, decode_type="multistart_greedy", num_starts=10, hidden=t(fx["hidden"], dev))
+    S, B = 10, td["locs"].shape[0]
+    feasible = td["action_mask"][..., 1:]
+    assert bool((feasible.sum(-1) < S).any()), "the fixture is meant to have instances with too few feasible starts"
+    torch.manual_seed(5)
+    out = pol(td, env, decode_type="multistart_greedy", num_starts=S, hidden=t(fx["hidden"], dev), return_actions=True)
+    torch.manual_seed(5)        # the draw the policy made
+    sel = (torch.multinomial(feasible.float(), S, replacement=True) + 1).t().reshape(-1)
+    assert torch.equal(out["actions"][:, 0], sel)
+    assert feasible[torch.arange(B, device=dev).repeat(S), sel - 1].all(), "a start node is infeasible"
+    ref = port.am_rollout("op", oracle_reset("op", fx), t(fx["hidden"]), oracle_weights("op"), "multistart_greedy",
+                          num_starts=S, start_nodes=sel.cpu())
+    got = out["actions"].cpu()
+    Tm = max(got.shape[1], ref["actions"].shape[1])
+    pad = lambda x: torch.nn.functional.pad(x, (0, Tm - x.shape[1]))
+    assert torch.equal(pad(got), pad(ref["actions"]))
+    torch.testing.assert_close(out["reward"].cpu(), ref["reward"], rtol=RTOL, atol=1e-6)
+    torch.testing.assert_close(out["log_likelihood"].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
+
+
+def test_select_start_nodes_fn_is_honoured(dev):
+    """utils/decoding.py:286-291: a caller's select_start_nodes_fn(td, env, num_starts) replaces the default rule"""
+    fx, pol, env, td = _setup("op20", dev)
+    S, B = 6, td["locs"].shape[0]
+    calls = []
+
+    def backwards(td_, env_, n):
+        calls.append(n)
+        return (20 - torch.arange(n, device=dev).repeat_interleave(td_["locs"].shape[0]) % 20)   # customers 20, 19, ...
+
+    out = pol(td, env, decode_type="multistart_greedy", num_starts=S, hidden=t(fx["hidden"], dev), return_actions=True,
+              select_start_nodes_fn=backwards)
+    assert calls == [S]
+    assert torch.equal(out["actions"][:, 0].view(S, B), (20 - torch.arange(S, device=dev))[:, None].expand(S, B))
+    ref = port.am_rollout("op", oracle_reset("op", fx), t(fx["hidden"]), oracle_weights("op"), "multistart_greedy",
+                          num_starts=S, start_nodes=out["actions"][:, 0].cpu(), check_solution=False)
+    Tm = max(out["actions"].shape[1], ref["actions"].shape[1])
+    pad = lambda x: torch.nn.functional.pad(x, (0, Tm - x.shape[1]))
+    assert torch.equal(pad(out["actions"].cpu()), pad(ref["actions"]))
+    torch.testing.assert_close(out["log_likelihood"].cpu(), ref["log_likelihood"], rtol=RTOL, atol=2e-5)
+    with pytest.raises(ValueError, match="rollouts"):
+        pol(td, env, decode_type="multistart_greedy", num_starts=S, hidden=t(fx["hidden"], dev),
+            select_start_nodes_fn=lambda a, b, n: torch.ones(3, dtype=torch.int64, device=dev))
 
 
 @pytest.mark.parametrize("case", ("op20", "op50", "op100"))
