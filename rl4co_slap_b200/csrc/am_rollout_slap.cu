@@ -57,34 +57,30 @@ constexpr float kInvSqrtE = 0.08838834764831845f;             // 1/sqrt(128)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr size_t kSmemLimit = 112 * 1024;   // two CTAs per SM
 
+// Shared-memory layout with COMPILE-TIME offsets (sized for the limits below): with run-time offsets the decode loop spent
+// ~50 of its 284 instructions per step rebuilding shared-memory addresses the 128-register cap would not let it keep
+constexpr int kMaxSteps = 32;        // P: products = decode steps
+constexpr int kMaxPick = 256;        // O * K: picklist entries
 struct Layout {
-    size_t off_xs, off_sc, off_e, off_po, off_z, off_best, off_mw, off_act, off_ain, off_lp, off_locs, off_noise,
-        off_part, off_pick, off_bar, off_v, total;
+    static constexpr size_t off_xs = 0;                                          // processed logits, one row per step
+    static constexpr size_t off_sc = off_xs + (size_t)kMaxSteps * 128 * 4;      // glimpse scores [head][node]
+    static constexpr size_t off_e = off_sc + (size_t)kWarps * 128 * 4;          // e[head][node] = 2^(s - m) at the last scaling
+    static constexpr size_t off_po = off_e + (size_t)kWarps * 128 * 4;          // per-warp partial numerators, hi and lo parts
+    static constexpr size_t off_z = off_po + (size_t)2 * kWarps * E * 4;        // glimpse denominators [head], (hi, lo)
+    static constexpr size_t off_best = off_z + 16 * 4;                          // warp winners (value, node), double buffered
+    static constexpr size_t off_mw = off_best + 2 * kWarps * 8;
+    static constexpr size_t off_act = off_mw + kMaxSteps * 4;
+    static constexpr size_t off_ain = off_act + kMaxSteps * 4;
+    static constexpr size_t off_lp = off_ain + kMaxSteps * 4;
+    static constexpr size_t off_locs = off_lp + kMaxSteps * 4;
+    static constexpr size_t off_noise = off_locs + 128 * 8;                     // sampling: Gumbel noise of 16 steps [16][node]
+    static constexpr size_t off_part = off_noise + 16 * 128 * 4;
+    static constexpr size_t off_pick = off_part + 64 * 4;                       // picklist as int
+    static constexpr size_t off_bar = off_pick + kMaxPick * 4;
+    static constexpr size_t off_v = (off_bar + 16 + 127) / 128 * 128;           // glimpse values [node][128], landed by TMA
+    static constexpr size_t total = off_v + (size_t)128 * E * 4;
 };
-__host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline Layout make_layout(int N, int P, int n_pick) {
-    Layout L;
-    size_t o = 0;
-    L.off_xs = o;    o += (size_t)P * 128 * 4;               // processed logits, one row per step
-    L.off_sc = o;    o += (size_t)kWarps * 128 * 4;          // glimpse scores [head][node]
-    L.off_e = o;     o += (size_t)kWarps * 128 * 4;          // e[head][node] = 2^(s - m) at the last scaling
-    L.off_po = o;    o += (size_t)2 * kWarps * E * 4;        // per-warp partial glimpse numerators, hi and lo parts
-    L.off_z = o;     o += 16 * 4;                            // glimpse denominators [head], (hi, lo)
-    L.off_best = o;  o += 2 * kWarps * 8;                    // warp winners (value, node), double buffered
-    L.off_mw = o;    o += up16((size_t)P * 4);
-    L.off_act = o;   o += up16((size_t)P * 4);
-    L.off_ain = o;   o += up16((size_t)P * 4);
-    L.off_lp = o;    o += up16((size_t)P * 4);
-    L.off_locs = o;  o += up16((size_t)N * 8);
-    L.off_noise = o; o += 16 * 128 * 4;                      // sampling: Gumbel noise of 16 steps [16][node]
-    L.off_part = o;  o += 64 * 4;
-    L.off_pick = o;  o += up16((size_t)n_pick * 4);          // picklist as int
-    L.off_bar = o;   o += 16;
-    o = (o + 127) & ~(size_t)127;
-    L.off_v = o;     o += (size_t)N * E * 4;                 // glimpse values [node][128], landed by TMA
-    L.total = o;
-    return L;
-}
+static_assert(Layout::total <= kSmemLimit, "two CTAs per SM");
 
 __device__ __forceinline__ float ex2f(float x) {
     float r;
@@ -179,23 +175,23 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int N = a.N, T = a.T, P = a.P < a.T ? a.P : a.T;
     const int n_pick = a.O * a.K;
-    const Layout L = make_layout(N, P, n_pick);
-    float *sxs = reinterpret_cast<float *>(smem + L.off_xs);
-    float *s_sc = reinterpret_cast<float *>(smem + L.off_sc);
-    float *s_e = reinterpret_cast<float *>(smem + L.off_e);
-    float *s_po = reinterpret_cast<float *>(smem + L.off_po);
-    float *s_z = reinterpret_cast<float *>(smem + L.off_z);
-    float2 *s_best = reinterpret_cast<float2 *>(smem + L.off_best);
-    float *s_mw = reinterpret_cast<float *>(smem + L.off_mw);
-    int *s_act = reinterpret_cast<int *>(smem + L.off_act);
-    int *s_ain = reinterpret_cast<int *>(smem + L.off_ain);
-    float *s_lp = reinterpret_cast<float *>(smem + L.off_lp);
-    float2 *s_locs = reinterpret_cast<float2 *>(smem + L.off_locs);
-    float4 *s_noise = reinterpret_cast<float4 *>(smem + L.off_noise);
-    float *spart = reinterpret_cast<float *>(smem + L.off_part);
-    int *s_pick = reinterpret_cast<int *>(smem + L.off_pick);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L.off_bar);
-    float *sV = reinterpret_cast<float *>(smem + L.off_v);
+    using L = Layout;
+    float *sxs = reinterpret_cast<float *>(smem + L::off_xs);
+    float *s_sc = reinterpret_cast<float *>(smem + L::off_sc);
+    float *s_e = reinterpret_cast<float *>(smem + L::off_e);
+    float *s_po = reinterpret_cast<float *>(smem + L::off_po);
+    float *s_z = reinterpret_cast<float *>(smem + L::off_z);
+    float2 *s_best = reinterpret_cast<float2 *>(smem + L::off_best);
+    float *s_mw = reinterpret_cast<float *>(smem + L::off_mw);
+    int *s_act = reinterpret_cast<int *>(smem + L::off_act);
+    int *s_ain = reinterpret_cast<int *>(smem + L::off_ain);
+    float *s_lp = reinterpret_cast<float *>(smem + L::off_lp);
+    float2 *s_locs = reinterpret_cast<float2 *>(smem + L::off_locs);
+    float4 *s_noise = reinterpret_cast<float4 *>(smem + L::off_noise);
+    float *spart = reinterpret_cast<float *>(smem + L::off_part);
+    int *s_pick = reinterpret_cast<int *>(smem + L::off_pick);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L::off_bar);
+    float *sV = reinterpret_cast<float *>(smem + L::off_v);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int d0 = 4 * lane;                        // first of the 4 dims this lane owns
@@ -291,9 +287,7 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
         // small per-instance state -> shared memory (the previous instance's epilogue ended with a barrier)
         {
             if (tid < N) s_locs[tid] = nx_loc;
-            if (tid < n_pick) s_pick[tid] = (int)nx_pick;
-            const int64_t *pl = a.picklist + b * (int64_t)n_pick;
-            for (int q = tid + kThreads; q < n_pick; q += kThreads) s_pick[q] = (int)pl[q];     // more than 256 entries
+            if (tid < n_pick) s_pick[tid] = (int)nx_pick;       // n_pick <= kMaxPick = kThreads
         }
         if (tid == 0 && b + gridDim.x < a.B) {      // next instance: its three tables -> L2
             const int64_t nb = b + gridDim.x;
@@ -582,26 +576,26 @@ static int launch(const rl4co_am_rollout_args &a, cudaStream_t stream) {
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
         if (sm_count <= 0) sm_count = 148;
     }
-    const Layout L = make_layout(a.N, a.P < a.T ? a.P : a.T, a.O * a.K);
-    cudaError_t e = cudaFuncSetAttribute(am_rollout_slap_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total);
+    using L = Layout;
+    cudaError_t e = cudaFuncSetAttribute(am_rollout_slap_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::total);
     if (e == cudaSuccess)   // two CTAs of ~84 KB: ask for the largest shared-memory carve-out
         e = cudaFuncSetAttribute(am_rollout_slap_kernel<NW>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) {
-        set_error("am_rollout(slap): cannot reserve %zu B of shared memory: %s", L.total, cudaGetErrorString(e));
+        set_error("am_rollout(slap): cannot reserve %zu B of shared memory: %s", L::total, cudaGetErrorString(e));
         return 2;
     }
     if (getenv("RL4CO_DEBUG_OCCUPANCY")) {
         int nb = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, am_rollout_slap_kernel<NW>, kThreads, L.total);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, am_rollout_slap_kernel<NW>, kThreads, L::total);
         cudaFuncAttributes fa;
         cudaFuncGetAttributes(&fa, am_rollout_slap_kernel<NW>);
-        fprintf(stderr, "am_rollout(slap)<%d>: %d CTAs/SM, %d regs, %zu B dynamic smem, carveout %d\n", NW, nb, fa.numRegs, L.total,
+        fprintf(stderr, "am_rollout(slap)<%d>: %d CTAs/SM, %d regs, %zu B dynamic smem, carveout %d\n", NW, nb, fa.numRegs, L::total,
                 fa.preferredShmemCarveout);
     }
     int64_t cap = (int64_t)2 * sm_count;                     // persistent: two CTAs per SM
     if (const char *dbg = getenv("RL4CO_DEBUG_SLAP_GRID")) cap = atoll(dbg) > 0 ? atoll(dbg) : cap;   // timing experiments only
     const int64_t grid = a.B < cap ? a.B : cap;
-    am_rollout_slap_kernel<NW><<<(unsigned)grid, kThreads, L.total, stream>>>(a);
+    am_rollout_slap_kernel<NW><<<(unsigned)grid, kThreads, L::total, stream>>>(a);
     RL4CO_CHECK_LAUNCH("am_rollout(slap)");
     return 0;
 }
@@ -616,7 +610,7 @@ bool rollout_slap_supports(const rl4co_am_rollout_args &a) {
     if (a.N > 128) return false;
     if (!(a.tanh_clipping > 0.f && a.temperature == 1.f && a.mask_logits != 0)) return false;
     const int P = a.P < a.T ? a.P : a.T;
-    return slapk::make_layout(a.N, P, a.O * a.K).total <= slapk::kSmemLimit;
+    return P <= slapk::kMaxSteps && a.O * a.K <= slapk::kMaxPick;     // the limits of the fixed shared-memory layout
 }
 
 int launch_rollout_slap(const rl4co_am_rollout_args &a, cudaStream_t stream) {
