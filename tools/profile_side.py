@@ -1,6 +1,7 @@
 """Workloads of the side configurations for ncu captures (one kernel each, run under `ncu -k regex:...`):
     python tools/profile_side.py c2      TSP100 env-only replay, B = 2^20           (kernel: tsp_replay)
-    python tools/profile_side.py c5      SLAP greedy rollout, B = 16 384            (kernel: am_rollout_rf)
+    python tools/profile_side.py c5      SLAP greedy rollout, B = 16 384            (kernel: am_rollout_slap)
+    python tools/profile_side.py k3 [nt] K3 projection, 1 638 400 rows x nt tables  (kernel: am_project_tc)
     python tools/profile_side.py c4      CVRP100 POMO multistart sampling, B = 64   (kernel: the multistart rollout)
 """
 import os, sys
@@ -10,7 +11,7 @@ import rl4co_slap_b200 as R
 
 dev = torch.device("cuda:0")
 which = sys.argv[1]
-reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+reps = int(sys.argv[2]) if len(sys.argv) > 2 and which != "k3" else 3
 with torch.inference_mode():
     torch.manual_seed(1234)
     if which == "c2":
@@ -28,6 +29,17 @@ with torch.inference_mode():
         h = torch.cat([pol.encoder(td[i:i + 8192])[0] for i in range(0, Bs, 8192)])
         for _ in range(reps):
             pol(td, env, decode_type="greedy", hidden=h)
+    elif which == "k3":
+        from rl4co_slap_b200 import _lib
+        M, nt = 1638400, int(sys.argv[2]) if len(sys.argv) > 2 else 5
+        h = torch.randn(M, 128, device=dev) * 3
+        W = torch.randn(nt * 128, 128, device=dev) * 0.1
+        s = _lib.stream_ptr(dev)
+        image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(nt)), device=dev)
+        _lib.call("rl4co_am_pack_weights", nt, _lib.ptr(W), _lib.ptr(image), s)
+        out = torch.zeros(nt, M, 128, device=dev)
+        for _ in range(3):
+            _lib.call("rl4co_am_project_tc", M, nt, _lib.ptr(h), _lib.ptr(image), _lib.ptr(out), s)
     elif which == "c4":
         Bc = 64
         env = R.CVRPEnv(generator_params=dict(num_loc=100), device=dev, check_solution=False)
