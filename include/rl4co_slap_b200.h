@@ -226,10 +226,14 @@ int rl4co_slap_replay(int64_t B, int32_t N, int32_t P, int32_t O, int32_t K,
 int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, const float *W,
                      float *tables, rl4co_stream_t stream);
 
-/* K3 on the tensor cores (tcgen05.mma kind::tf32, 3-term hi/lo split, fp32 accumulation in TMEM;
- * same result as rl4co_am_project to fp32 rounding level).  The weights are first packed once per
- * weight update into the shared-memory image the MMA reads:
- *   image: rl4co_am_weight_image_floats(n_tables) floats (128 KB per table), caller owned. */
+/* K3 on the tensor cores (tcgen05.mma, 3-term hi/lo split a w = a_hi w_hi + a_hi w_lo + a_lo w_hi, fp32 accumulation in
+ * TMEM; same result as rl4co_am_project to fp32 rounding level: max error 1.5e-5 on values of size 18 against 1.0e-5 for the
+ * fp32 SIMT kernel).  K = 128 products - this entry point, and rl4co_linear_tc with n_in = 128 - use FP16 halves
+ * (kind::f16) with exact power-of-two range scales per 128-row tile of the input and per weight table, so that inputs of
+ * any magnitude are safe; K > 128 uses TF32 halves (kind::tf32).  The weights are first packed once per weight update into
+ * the shared-memory image the MMA reads; the image is OPAQUE (its format follows the rule above) and must be consumed by the
+ * same library version that packed it:
+ *   image: rl4co_am_weight_image_floats(n_tables) floats (a 128 KB slot per table), caller owned. */
 int64_t rl4co_am_weight_image_floats(int32_t n_tables);
 int rl4co_am_pack_weights(int32_t n_tables, const float *W, float *image, rl4co_stream_t stream);
 int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float *image,

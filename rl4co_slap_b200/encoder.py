@@ -114,7 +114,7 @@ def linear128(x: torch.Tensor, lin: nn.Linear, relu: bool = False, residual: tor
               norm: nn.BatchNorm1d = None) -> torch.Tensor:
     """``norm(act(lin(x)) + residual)`` (residual / norm optional).  On a CUDA device, outside autograd, a
     Linear whose input and output widths are multiples of 128 runs on the library's fp32-accurate tensor-core
-    kernel (rl4co_linear_tc[_ex]: tcgen05, 3-term TF32 split, fp32 accumulation - the K3 projection kernel
+    kernel (rl4co_linear_tc[_ex]: tcgen05, 3-term hi / lo split - FP16 halves for K = 128, TF32 for K > 128 -, fp32 accumulation - the K3 projection kernel
     with a bias / ReLU / skip / eval-batch-norm epilogue); everything else is the plain PyTorch ops.  The
     packed weight image is cached on the module.  ``norm`` must be an eval-mode BatchNorm1d."""
     w = lin.weight

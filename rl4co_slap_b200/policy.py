@@ -111,7 +111,7 @@ class AttentionModelDecoder(nn.Module):
         return self._fold
 
     def weight_image(self):
-        """The folded table weights as the pre-split (TF32 hi / lo), pre-swizzled shared-memory image
+        """The folded table weights as the pre-split (hi / lo halves), pre-swizzled shared-memory image
         the tensor-core projection reads (csrc/am_project_tc.cu); packed once per weight update."""
         W = self.folded_weights()[0]
         if getattr(self, "_image", None) is None:
@@ -331,7 +331,7 @@ class AttentionModelPolicy(nn.Module):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if prof is not None else None
             if ev:
                 ev[0].record()
-            if self.projection == "tensor":     # tcgen05 3xTF32, fp32-accurate
+            if self.projection == "tensor":     # tcgen05, 3-term FP16 split with range scales, fp32-accurate
                 _lib.call("rl4co_am_project_tc", Bc * N, n_tables, _lib.ptr(h), _lib.ptr(W_image), _lib.ptr(tables), stream)
             else:                               # fp32 SIMT kernel (kept as the in-library cross-check)
                 _lib.call("rl4co_am_project", Bc * N, n_tables, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
