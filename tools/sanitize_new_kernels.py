@@ -1,4 +1,5 @@
-"""Small workloads of the round-2 kernels for compute-sanitizer (memcheck / racecheck / synccheck):
+"""Small workloads of the round-2 kernels for compute-sanitizer (memcheck / racecheck / synccheck), for machines where the
+sanitizer may be used (it is closed on the pool this repository was built on, so no log of it is committed):
     compute-sanitizer --tool racecheck python tools/sanitize_new_kernels.py slap
     compute-sanitizer --tool memcheck  python tools/sanitize_new_kernels.py k3
 slap: B = 700 instances (296 persistent CTAs, so most CTAs run more than two instances: the carry-over of registers /
