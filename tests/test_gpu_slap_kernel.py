@@ -30,7 +30,10 @@ def _setup(dev, n_aisles, n_locs, B, scale, seed=5):
     gen = env.generator(B)
     td = env.reset(gen.to(dev))
     with torch.inference_mode():
-        h = pol.encoder(td)[0].float() * scale
+        h = pol.encoder(td)[0].float()
+        # every generated instance has the same warehouse grid and therefore the same encoder output; the rollout takes any
+        # `hidden`, so give every instance its own: per-node noise of a quarter of the embeddings' spread
+        h = (h + 0.25 * h.std() * torch.randn_like(h)) * scale
     return env, pol, gen, td, h.contiguous()
 
 
@@ -147,3 +150,42 @@ def test_two_launches_agree_and_do_not_depend_on_the_batch_position(dev):
     assert torch.equal(full["actions"][perm], shuf["actions"])
     assert torch.equal(full["log_likelihood"][perm], shuf["log_likelihood"])
     assert torch.equal(full["reward"][perm], shuf["reward"])
+
+
+@pytest.mark.parametrize("n_aisles,n_locs,P,O,K,graph_context", ((37, 1, 20, 20, 5, True), (8, 16, 32, 64, 4, True),
+                                                                 (10, 10, 20, 20, 5, False), (2, 3, 5, 3, 2, True),
+                                                                 (10, 10, 33, 20, 5, True)))
+def test_limits_of_the_fixed_layout_and_odd_shapes(dev, n_aisles, n_locs, P, O, K, graph_context):
+    """N = 37 (a prime), the largest shape the kernel's fixed shared-memory layout takes (N = 128, P = 32 steps, 256 picklist
+    entries), no graph context (the query is zero: uniform attention), a tiny warehouse, and P = 33 - one step beyond the
+    layout, which must fall through to the generic kernel with the same results: greedy assignments and evaluate
+    log-likelihoods against the oracle"""
+    B = 48
+    torch.manual_seed(31)
+    env = R.SLAPEnv(generator_params={"n_aisles": n_aisles, "n_locs": n_locs, "n_products": P, "max_orders": O,
+                                      "max_products_in_order": K}, device=dev)
+    pol = R.AttentionModelPolicy(env_name="slap", num_encoder_layers=1, feedforward_hidden=128,
+                                 use_graph_context=graph_context).to(dev).eval()
+    sd = {k: v for k, v in __import__("tests.helpers", fromlist=["policy_state"]).policy_state("slap").items()
+          if not (k.endswith("project_fixed_context.weight") and not graph_context)}
+    pol.load_state_dict(sd, strict=False)
+    gen = env.generator(B)
+    td = env.reset(gen.to(dev))
+    with torch.inference_mode():
+        h = pol.encoder(td)[0].float().contiguous()
+        out = pol(td, env, decode_type="greedy", hidden=h, return_actions=True)
+    W = oracle_weights("slap")
+    state = _oracle_state(gen, slice(None), P)
+    ref = port.am_rollout("slap", state, h.cpu(), W, "greedy", use_graph_context=graph_context)
+    # (every instance of a generated batch has the same warehouse grid, hence the same encoder output: a verified near tie is the
+    # same near tie in all of them, so the NUMBER of diverging instances says nothing here)
+    assert_divergences_are_near_ties("slap", _oracle_state(gen, slice(None), P), h, W, out["actions"], ref["actions"],
+                                     use_graph_context=graph_context)
+    same = (out["actions"].cpu() == ref["actions"]).all(1)
+    torch.testing.assert_close(out["reward"].cpu()[same], ref["reward"][same], rtol=RTOL, atol=1e-5)
+    with torch.inference_mode():
+        ev = pol(td, env, actions=ref["actions"].to(dev), hidden=h)
+    ref64 = port.am_rollout("slap", _oracle_state(gen, slice(None), P), h.cpu().double(), {k: v.double() for k, v in W.items()},
+                            actions=ref["actions"], use_graph_context=graph_context, check_solution=False)["log_likelihood"]
+    _assert_fp32_class(ev["log_likelihood"].cpu().double(), ref["log_likelihood"].double(), ref64)
+    torch.testing.assert_close(ev["reward"].cpu(), ref["reward"], rtol=RTOL, atol=1e-5)
