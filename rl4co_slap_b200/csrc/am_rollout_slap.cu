@@ -159,9 +159,11 @@ __device__ __forceinline__ void add_term2(u64 &hi, u64 &lo, u64 q, u64 m1) {
 #ifdef SLAPK_TRACE
 #define SLAPK_TRACE_AT(k) do { if (tid == 0 && blockIdx.x == 0 && it == 1) reinterpret_cast<long long *>(a.logp_all)[t * 8 + (k)] = clock64(); } while (0)
 #define SLAPK_TRACE_INST(k) do { if (tid == 0 && blockIdx.x == 0 && it == 1) reinterpret_cast<long long *>(a.logp_all)[P * 8 + (k)] = clock64(); } while (0)
+#define SLAPK_TRACE_BUILD(k) do { if (tid == 0 && blockIdx.x == 0 && it == 1 && t == 0) reinterpret_cast<long long *>(a.logp_all)[(P + 1) * 8 + (k)] = clock64(); } while (0)
 #else
 #define SLAPK_TRACE_AT(k) do { } while (0)
 #define SLAPK_TRACE_INST(k) do { } while (0)
+#define SLAPK_TRACE_BUILD(k) do { } while (0)
 #endif
 
 constexpr int pow2_at_least(int v) { return v <= 4 ? 4 : v <= 8 ? 8 : 16; }
@@ -347,7 +349,9 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
                 }
                 if (lane == 0) reinterpret_cast<float2 *>(s_z)[warp] = make_float2(zh, zl);
             }
+            SLAPK_TRACE_BUILD(1);
             __syncthreads();
+            SLAPK_TRACE_BUILD(2);
             {
                 u64 ph[2] = {0ull, 0ull}, pl[2] = {0ull, 0ull};
 #pragma unroll
@@ -362,11 +366,13 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
                 *reinterpret_cast<ulonglong2 *>(s_po + warp * E + d0) = make_ulonglong2(ph[0], ph[1]);
                 *reinterpret_cast<ulonglong2 *>(s_po + (kWarps + warp) * E + d0) = make_ulonglong2(pl[0], pl[1]);
             }
+            SLAPK_TRACE_BUILD(3);
             __syncthreads();
+            SLAPK_TRACE_BUILD(4);
             Ohi[0] = Ohi[1] = Olo[0] = Olo[1] = 0ull;
 #pragma unroll
-            for (int w = 0; w < kWarps; ++w) {
-                const ulonglong2 h4 = *reinterpret_cast<const ulonglong2 *>(s_po + w * E + d0);
+            for (int w = 0; w < kWarps; ++w) {      // (splitting these chains in two did not help: the build competes for
+                const ulonglong2 h4 = *reinterpret_cast<const ulonglong2 *>(s_po + w * E + d0);     // issue slots, not latency)
                 const ulonglong2 l4 = *reinterpret_cast<const ulonglong2 *>(s_po + (kWarps + w) * E + d0);
                 add_term2(Ohi[0], Olo[0], h4.x, m1);
                 add_term2(Ohi[1], Olo[1], h4.y, m1);
@@ -375,11 +381,14 @@ am_rollout_slap_kernel(const rl4co_am_rollout_args a) {
             }
             const float2 z2 = reinterpret_cast<const float2 *>(s_z)[hl];
             Zhi = z2.x; Zlo = z2.y; zref = Zhi;
+            SLAPK_TRACE_BUILD(5);
         };
         SLAPK_TRACE_INST(2);
         mbar_wait(bar, par);                        // value table landed in shared memory
         par ^= 1u;
+        SLAPK_TRACE_BUILD(6);
         __syncthreads();                            // scores / noise / given actions visible to every warp
+        SLAPK_TRACE_BUILD(0);
         build_state();
         SLAPK_TRACE_INST(3);
 

@@ -42,7 +42,7 @@ tables = torch.empty(nt, B * N, 128, device=dev)
 gctx = torch.empty(B, 128, device=dev)
 _lib.call("rl4co_am_project", B * N, nt, _lib.ptr(h), _lib.ptr(W), _lib.ptr(tables), stream)
 _lib.call("rl4co_am_graph_context", B, N, _lib.ptr(h), _lib.ptr(Wfixed), _lib.ptr(gctx), stream)
-trace = torch.zeros((P + 1) * 8, dtype=torch.int64, device=dev)
+trace = torch.zeros((P + 2) * 8, dtype=torch.int64, device=dev)
 acts = torch.empty(B, P, dtype=torch.int64, device=dev)
 logp = torch.empty(B, P, device=dev)
 ll, rew = torch.empty(B, device=dev), torch.empty(B, device=dev)
@@ -63,7 +63,7 @@ for _ in range(2):
 torch.cuda.synchronize()
 rb = (steps.cpu().numpy() >> 8)
 print("glimpse rebuilds per instance: mean %.2f  max %d  histogram %s" % (rb.mean(), rb.max(), np.bincount(rb)[:21].tolist()))
-full = trace.cpu().numpy().reshape(P + 1, 8)
+full = trace.cpu().numpy().reshape(P + 2, 8)
 tr = full[:P, :5]
 d = np.diff(tr, axis=1)
 names = ["logits+butterfly", "tanh+warp argmax", "barrier", "winner+update"]
@@ -72,6 +72,9 @@ m = d[1:].mean(0)
 print("per step: " + "  ".join(f"{n} {v:.0f}" for n, v in zip(names, m)), "| step total", (tr[1:, 0] - tr[:-1, 0]).mean())
 print("cycles from step start to next step start:", " ".join(str(int(v)) for v in (tr[1:, 0] - tr[:-1, 0])))
 print("update phase per step:", " ".join(str(int(v)) for v in d[:, 3]))
+w = full[P + 1]
+print(f"first glimpse state: V wait {w[6]-full[P][2]}  barrier {w[0]-w[6]}  exponentials + Z {w[1]-w[0]}  barrier {w[2]-w[1]}  "
+      f"partial numerators {w[3]-w[2]}  barrier {w[4]-w[3]}  combine {w[5]-w[4]}")
 v = full[P]
 print(f"instance: K loads + scores {v[1]-v[0]}  small state {v[2]-v[1]}  V wait + first glimpse {v[3]-v[2]}  decode {v[4]-v[3]}  "
       f"log-probs {v[5]-v[4]}  reward + outputs {v[6]-v[5]}  total {v[6]-v[0]}")
