@@ -250,6 +250,11 @@ int rl4co_am_project_tc(int64_t M, int32_t n_tables, const float *h, const float
  *   y = (act(x W^T + bias) + residual) * scale + shift
  * residual [M,n_out] (must not alias y), scale / shift [n_out]; each may be NULL (0, 1, 0). */
 int rl4co_linear_pack(int32_t n_out, int32_t n_in, const float *W, float *image, rl4co_stream_t stream);
+/* The encoder's init embedding (models/nn/env_embeddings/init.py:51-64 TSP, :111-134 VRP; examples/slap.py:11-47): a Linear
+ * with n_in = 1..8 input features and 128 outputs, y[m][j] = sum_k x[m][k] W[j][k] + bias[j] (k ascending, fp32 FMA).
+ * x [M,n_in], W [128,n_in], bias [128] or NULL, y [M,128], all contiguous fp32. */
+int rl4co_linear_narrow(int64_t M, int32_t n_in, const float *x, const float *W, const float *bias, float *y,
+                        rl4co_stream_t stream);
 int rl4co_linear_tc(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,
                     const float *bias, int32_t relu, float *y, rl4co_stream_t stream);
 int rl4co_linear_tc_ex(int64_t M, int32_t n_out, int32_t n_in, const float *x, const float *image,

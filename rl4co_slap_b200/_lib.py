@@ -84,6 +84,7 @@ _SIGNATURES = {
     "rl4co_am_pack_weights": ([_i32, _p, _p, _p], C.c_int),
     "rl4co_am_project_tc": ([_i64, _i32, _p, _p, _p, _p], C.c_int),
     "rl4co_linear_pack": ([_i32, _i32, _p, _p, _p], C.c_int),
+    "rl4co_linear_narrow": ([_i64, _i32, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_linear_tc": ([_i64, _i32, _i32, _p, _p, _p, _i32, _p, _p], C.c_int),
     "rl4co_linear_tc_ex": ([_i64, _i32, _i32, _p, _p, _p, _i32, _p, _p, _p, _p, _p], C.c_int),
     "rl4co_encoder_attention": ([_i64, _i32, _p, _p, _p], C.c_int),

@@ -211,6 +211,55 @@ extern "C" int rl4co_am_project(int64_t M, int32_t n_tables, const float *h, con
     return 0;
 }
 
+// The init embedding of the encoder: a Linear with 2..8 input features and 128 outputs (nn/env_embeddings/init.py:51-64,
+// 111-134; examples/slap.py:11-47).  A GEMM library runs this K = 2 product as an SGEMM tile kernel at 2.6 TB/s; it is a pure
+// write stream: lane = 4 output columns (weights and bias in registers), a warp writes one 512-byte row per iteration.
+namespace rl4co {
+constexpr int kNarrowMaxIn = 8;
+__global__ void __launch_bounds__(256) linear_narrow_kernel(int64_t M, int n_in, const float *__restrict__ x,
+                                                            const float *__restrict__ W, const float *__restrict__ bias,
+                                                            float *__restrict__ y) {
+    const int lane = threadIdx.x & 31;
+    float w[4][kNarrowMaxIn], b[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        b[c] = bias ? bias[4 * lane + c] : 0.f;
+#pragma unroll
+        for (int k = 0; k < kNarrowMaxIn; ++k) w[c][k] = k < n_in ? W[(size_t)(4 * lane + c) * n_in + k] : 0.f;
+    }
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5), me = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    for (int64_t m = me; m < M; m += warps) {
+        float xv[kNarrowMaxIn];
+#pragma unroll
+        for (int k = 0; k < kNarrowMaxIn; ++k) xv[k] = k < n_in ? __ldg(x + m * n_in + k) : 0.f;
+        float4 o;
+        float *op = &o.x;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float acc = 0.f;                        // ascending k, then the bias: the order of x @ W^T + b
+#pragma unroll
+            for (int k = 0; k < kNarrowMaxIn; ++k)
+                if (k < n_in) acc = fmaf(xv[k], w[c][k], acc);
+            op[c] = acc + b[c];
+        }
+        *reinterpret_cast<float4 *>(y + m * 128 + 4 * lane) = o;
+    }
+}
+}  // namespace rl4co
+
+extern "C" int rl4co_linear_narrow(int64_t M, int32_t n_in, const float *x, const float *W, const float *bias, float *y,
+                                   rl4co_stream_t stream) {
+    RL4CO_REQUIRE(M >= 0 && n_in >= 1 && n_in <= kNarrowMaxIn, "linear_narrow: n_in = %d outside 1..%d", n_in, kNarrowMaxIn);
+    if (M == 0) return 0;
+    RL4CO_REQUIRE(x && W && y, "linear_narrow: null pointer");
+    RL4CO_REQUIRE(((uintptr_t)y & 15) == 0, "linear_narrow: y must be 16-byte aligned");
+    const int64_t want = (M + 7) / 8;
+    const int64_t grid = want < 148 * 8 ? want : 148 * 8;
+    linear_narrow_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(M, n_in, x, W, bias, y);
+    RL4CO_CHECK_LAUNCH("linear_narrow");
+    return 0;
+}
+
 extern "C" int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wfixed,
                                       float *gctx, rl4co_stream_t stream) {
     RL4CO_REQUIRE(B >= 0 && N >= 1, "am_graph_context: bad sizes");

@@ -16,13 +16,29 @@ import torch.nn.functional as F
 
 
 # ---- init embeddings ------------------------------------------------------------------
+def narrow_linear(x: torch.Tensor, lin: nn.Linear) -> torch.Tensor:
+    """``lin(x)`` for the init embeddings (2..8 input features, 128 outputs).  On a CUDA device, outside autograd, the
+    library's write-stream kernel (rl4co_linear_narrow); everywhere else the PyTorch op."""
+    w = lin.weight
+    if not (x.is_cuda and not torch.is_grad_enabled() and w.dtype == torch.float32 and x.dtype == torch.float32
+            and w.shape[0] == 128 and 1 <= w.shape[1] <= 8 and getattr(lin, "tensor_core", True)):
+        return lin(x)
+    from . import _lib
+    x2 = x.reshape(-1, w.shape[1]).contiguous()
+    y = torch.empty(x2.shape[0], 128, dtype=torch.float32, device=x.device)
+    _lib.call("rl4co_linear_narrow", x2.shape[0], w.shape[1], _lib.ptr(x2), _lib.ptr(w.detach().contiguous()),
+              _lib.ptr(lin.bias.detach().contiguous()) if lin.bias is not None else None, _lib.ptr(y),
+              _lib.stream_ptr(x.device))
+    return y.view(*x.shape[:-1], 128)
+
+
 class TSPInitEmbedding(nn.Module):
     def __init__(self, embed_dim: int, linear_bias: bool = True):
         super().__init__()
         self.init_embed = nn.Linear(2, embed_dim, linear_bias)
 
     def forward(self, td):
-        return self.init_embed(td["locs"])
+        return narrow_linear(td["locs"], self.init_embed)
 
 
 class VRPInitEmbedding(nn.Module):
@@ -35,7 +51,7 @@ class VRPInitEmbedding(nn.Module):
         locs = td["locs"]
         depot, cities = locs[:, :1, :], locs[:, 1:, :]
         feats = torch.cat((cities, td["demand"][..., None]), -1)
-        return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
+        return torch.cat((narrow_linear(depot, self.init_embed_depot), narrow_linear(feats, self.init_embed)), -2)
 
 
 class OPInitEmbedding(nn.Module):
@@ -50,7 +66,7 @@ class OPInitEmbedding(nn.Module):
         locs = td["locs"]
         depot, cities = locs[:, :1, :], locs[:, 1:, :]
         feats = torch.cat((cities, td["prize"][..., 1:, None]), -1)
-        return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
+        return torch.cat((narrow_linear(depot, self.init_embed_depot), narrow_linear(feats, self.init_embed)), -2)
 
 
 class PCTSPInitEmbedding(nn.Module):
@@ -65,7 +81,7 @@ class PCTSPInitEmbedding(nn.Module):
         locs = td["locs"]
         depot, cities = locs[:, :1, :], locs[:, 1:, :]
         feats = torch.cat((cities, td["expected_prize"][..., None], td["penalty"][..., 1:, None]), -1)
-        return torch.cat((self.init_embed_depot(depot), self.init_embed(feats)), -2)
+        return torch.cat((narrow_linear(depot, self.init_embed_depot), narrow_linear(feats, self.init_embed)), -2)
 
 
 class SLAPInitEmbedding(nn.Module):
@@ -78,7 +94,7 @@ class SLAPInitEmbedding(nn.Module):
     def forward(self, td):
         locs = td["locs"].to(torch.float32)
         d0 = (locs - locs[:, :1, :]).abs().sum(-1)
-        return self.init_embed(torch.cat((locs, d0[..., None]), -1))
+        return narrow_linear(torch.cat((locs, d0[..., None]), -1), self.init_embed)
 
 
 INIT_EMBEDDINGS = {"tsp": TSPInitEmbedding, "cvrp": VRPInitEmbedding, "sdvrp": VRPInitEmbedding, "slap": SLAPInitEmbedding,

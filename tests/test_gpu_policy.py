@@ -481,6 +481,24 @@ def test_linear_tc_k_chunks_bias_relu(M, n_out, n_in, relu, dev):
     assert ((y.double() - ref).abs() <= bound).all()
 
 
+@pytest.mark.parametrize("M,n_in,bias", ((1, 2, True), (1000, 3, True), (16384 * 100 + 5, 2, True), (777, 4, False), (50, 8, True)))
+def test_linear_narrow_init_embedding(M, n_in, bias, dev):
+    """rl4co_linear_narrow (the encoder's init embedding, 2..8 features -> 128) against fp64 and torch's F.linear"""
+    from rl4co_slap_b200 import _lib
+    torch.manual_seed(M % 97 + n_in)
+    x = torch.rand(M, n_in, device=dev) * 3 - 1
+    lin = torch.nn.Linear(n_in, 128, bias=bias).to(dev)
+    y = torch.full((M, 128), float("nan"), device=dev)
+    _lib.call("rl4co_linear_narrow", M, n_in, _lib.ptr(x), _lib.ptr(lin.weight.detach()),
+              _lib.ptr(lin.bias.detach()) if bias else None, _lib.ptr(y), _lib.stream_ptr(dev))
+    ref = x.double() @ lin.weight.double().t() + (lin.bias.double() if bias else 0)
+    mag = x.double().abs() @ lin.weight.double().abs().t() + (lin.bias.double().abs() if bias else 0)
+    assert ((y.double() - ref).abs() <= 2.5e-7 * mag + 1e-9).all()
+    with torch.inference_mode():
+        torch.testing.assert_close(R.encoder.narrow_linear(x, lin), y, rtol=0, atol=0)        # the module path is this kernel
+        torch.testing.assert_close(y, torch.nn.functional.linear(x, lin.weight, lin.bias), rtol=1e-6, atol=1e-6)
+
+
 def _chi2(counts, probs, n):
     keep = probs * n > 5
     return float((((counts - n * probs) ** 2) / (n * probs).clamp_min(1e-9))[keep].sum()), int(keep.sum())
