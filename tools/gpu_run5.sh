@@ -10,5 +10,5 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 3000 --csv --log-file gpurun_out/r02_e2e_launches_raw.csv python bench.py --steps 1 --warmup 3 --profile-e2e --batch 131072 --no-cpu-baseline --no-side --no-parity > gpurun_out/ncu_e2e.log 2>&1; echo "e2e rc=$?"
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:am_rollout_slap --launch-skip 2 -c 1 -f -o gpurun_out/r02_c5_slap_v2 python tools/profile_side.py c5 > gpurun_out/ncu_c5.log 2>&1; echo "c5 rc=$?"
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:am_project_tc --launch-skip 2 -c 1 -f -o gpurun_out/r02_k3_f16 python tools/profile_side.py k3 5 > gpurun_out/ncu_k3.log 2>&1; echo "k3 rc=$?"
-timeout 300 python tools/trace_slap.py > gpurun_out/r02_slap_trace.txt 2>&1; echo "trace rc=$?"
+python tools/trace_slap.py build > /dev/null 2>&1; timeout 300 python tools/trace_slap.py > gpurun_out/r02_slap_trace.txt 2>&1; echo "trace rc=$?"
 ls -la gpurun_out | tail -14
