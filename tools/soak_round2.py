@@ -1,0 +1,102 @@
+"""Randomised soak of the round-2 kernels (not collected by pytest; run on a GPU box):
+    python tools/soak_round2.py [seconds per part, default 60]
+  k3   - rl4co_am_project_tc / rl4co_linear_tc (FP16 form): random row counts (ragged tiles), 1..8 tables, input magnitudes from
+         1e-6 to 1e5 incl. tiles of zeros and single huge outliers, against fp64;
+  slap - am_rollout_slap.cu against the generic register-file kernel on random warehouse shapes (N = 6..128, P = 2..32), random
+         per-instance hidden states at random scales (collapsed attention included), greedy / sampling / evaluate: evaluate
+         log-likelihoods of the same assignments must agree to the fp32 class of the inputs, rewards to 1e-5.
+Prints one line per case that exceeds its bound and a summary; exit code 1 if any did."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import rl4co_slap_b200 as R
+from rl4co_slap_b200 import _lib
+
+dev = torch.device("cuda:0")
+budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
+bad = 0
+g = torch.Generator(device="cpu").manual_seed(20261105)
+rnd = lambda lo, hi: int(torch.randint(lo, hi + 1, (1,), generator=g))
+
+# ---------------------------------------------------------------- K3 / linear, FP16 form
+t0, n = time.time(), 0
+st = _lib.stream_ptr(dev)
+while time.time() - t0 < budget:
+    M, nt = rnd(1, 70000), rnd(1, 8)
+    mag = 10.0 ** (rnd(-60, 50) / 10.0)
+    x = torch.randn(M, 128, device=dev) * mag
+    kind = rnd(0, 3)
+    if kind == 1 and M > 300:
+        x[128:256] = 0                                          # a whole tile of zeros
+    if kind == 2:
+        x[rnd(0, M - 1), rnd(0, 127)] = mag * 3e4               # one outlier sets the tile's scale
+    if kind == 3:
+        x *= torch.logspace(-6, 0, 128, device=dev)             # columns spanning six decades
+    W = torch.randn(nt * 128, 128, device=dev) * 10.0 ** (rnd(-30, 10) / 10.0)
+    image = torch.empty(int(_lib.load().rl4co_am_weight_image_floats(nt)), device=dev)
+    _lib.call("rl4co_am_pack_weights", nt, _lib.ptr(W), _lib.ptr(image), st)
+    out = torch.full((nt, M, 128), float("nan"), device=dev)
+    _lib.call("rl4co_am_project_tc", M, nt, _lib.ptr(x), _lib.ptr(image), _lib.ptr(out), st)
+    rows = torch.randperm(M, device=dev)[:2048]
+    ref = (x[rows].double() @ W.double().t()).view(-1, nt, 128).permute(1, 0, 2)
+    magn = (x[rows].double().abs() @ W.double().abs().t()).view(-1, nt, 128).permute(1, 0, 2)
+    # 3-term split: <= 8.3e-7 per product (measured over all mantissas); the 24 MMAs of a tile accumulate into the fp32
+    # TMEM accumulator one after the other, each rounding at 2^-23..-24 of the running sum - up to ~2e-6 of a row that one
+    # large product dominates (measured); plus the fp16 floor of entries far below the largest of their tile of x / their
+    # table of W: half an fp16-subnormal ulp, 2^-25 of a scaled value whose largest is >= 2^13, on either operand
+    amax = x.abs().max().double() * W.abs().max().double()
+    err = (out[:, rows].double() - ref).abs()
+    bound = 3.5e-6 * magn + 2 * 128 * 2.0 ** -25 * 2.0 ** -13 * amax * 1.5 + 1e-30
+    if not bool((err <= bound).all()) or not bool(torch.isfinite(out).all()):
+        bad += 1
+        print(f"K3 FAIL M={M} nt={nt} mag={mag:.2e} kind={kind}: worst excess {float((err / bound).max()):.2f}x", flush=True)
+    n += 1
+print(f"k3: {n} random cases, {bad} failures", flush=True)
+
+# ---------------------------------------------------------------- SLAP kernel vs generic kernel
+t0, n, bad_k3 = time.time(), 0, bad
+with torch.inference_mode():
+    while time.time() - t0 < budget:
+        na, nl = rnd(2, 16), rnd(3, 8)
+        N = na * nl
+        P = rnd(2, min(32, N - 1))
+        O, K = rnd(1, 30), rnd(1, 8)
+        B = rnd(1, 900)
+        env = R.SLAPEnv(generator_params={"n_aisles": na, "n_locs": nl, "n_products": P, "max_orders": O,
+                                          "max_products_in_order": K}, device=dev)
+        pol = R.AttentionModelPolicy(env_name="slap", num_encoder_layers=1, feedforward_hidden=128,
+                                     use_graph_context=bool(rnd(0, 3))).to(dev).eval()
+        td = env.reset(env.generator(B).to(dev))
+        h = pol.encoder(td)[0].float()
+        scale = 10.0 ** (rnd(-10, 14) / 10.0)
+        h = ((h + 0.3 * h.std() * torch.randn_like(h)) * scale).contiguous()
+        res = {}
+        for impl in (0, 2):
+            _lib.call("rl4co_set_rollout_impl", impl)
+            torch.manual_seed(n)
+            smp = pol(td, env, decode_type="sampling", hidden=h, return_actions=True)
+            if impl == 0:
+                acts = smp["actions"]
+            res[impl] = (smp, pol(td, env, actions=acts, hidden=h), pol(td, env, decode_type="greedy", hidden=h, return_actions=True))
+        _lib.call("rl4co_set_rollout_impl", 0)
+        a, b = res[0][1], res[2][1]
+        ll_a, ll_b = a["log_likelihood"].double(), b["log_likelihood"].double()
+        # both kernels are fp32 implementations of an ill-conditioned map when attention collapses: scores of size s carry
+        # eps * s of rounding, which the exponential turns into a relative error of the weights
+        smax = float(h.abs().max()) ** 2
+        tol = 1e-5 * ll_b.abs() + 3e-5 + P * 6e-8 * smax * 8
+        ok = bool(((ll_a - ll_b).abs() <= tol).all()) and bool(torch.allclose(a["reward"], b["reward"], rtol=1e-5, atol=1e-5))
+        same_g = (res[0][2]["actions"] == res[2][2]["actions"]).all(1).float().mean().item()
+        same_s = (res[0][0]["actions"] == res[2][0]["actions"]).all(1).float().mean().item()
+        srt = res[0][0]["actions"].sort(1).values
+        valid = bool((srt[:, 1:] != srt[:, :-1]).all()) and bool((res[0][0]["actions"] > 0).all()) and \
+            bool((res[0][0]["actions"] < N).all())
+        if not (ok and valid):
+            bad += 1
+            print(f"SLAP FAIL N={N} P={P} O={O} K={K} B={B} scale={scale:.2f}: ll diff {float((ll_a - ll_b).abs().max()):.3e} "
+                  f"(tol {float(tol.min()):.1e}), valid={valid}, greedy same {same_g:.3f}, sampled same {same_s:.3f}", flush=True)
+        elif same_g < 0.9 and scale < 3:
+            print(f"slap note N={N} P={P} B={B} scale={scale:.2f}: greedy same {same_g:.3f}, sampled same {same_s:.3f}", flush=True)
+        n += 1
+print(f"slap: {n} random cases, {bad - bad_k3} failures", flush=True)
+sys.exit(1 if bad else 0)
