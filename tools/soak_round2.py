@@ -5,6 +5,9 @@
   slap - am_rollout_slap.cu against the generic register-file kernel on random warehouse shapes (N = 6..128, P = 2..32), random
          per-instance hidden states at random scales (collapsed attention included), greedy / sampling / evaluate: evaluate
          log-likelihoods of the same assignments must agree to the fp32 class of the inputs, rewards to 1e-5.
+  linear - rl4co_linear_tc_ex: random widths (K = 128 on FP16 halves, K chunks on TF32), bias / ReLU / skip row / affine, against fp64;
+  multistart - am_rollout_ms_tc.cu against the SIMT kernel: random tsp / cvrp sizes, batch and start counts, greedy tours equal
+         up to near ties with equal log-likelihoods and rewards, sampled tours valid.
 Prints one line per case that exceeds its bound and a summary; exit code 1 if any did."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -99,4 +102,81 @@ with torch.inference_mode():
             print(f"slap note N={N} P={P} B={B} scale={scale:.2f}: greedy same {same_g:.3f}, sampled same {same_s:.3f}", flush=True)
         n += 1
 print(f"slap: {n} random cases, {bad - bad_k3} failures", flush=True)
+
+# ---------------------------------------------------------------- linear layers with epilogues (FP16 K = 128, TF32 K chunks)
+t0, n, bad_prev = time.time(), 0, bad
+while time.time() - t0 < budget:
+    M = rnd(1, 40000)
+    n_out, n_in = 128 * rnd(1, 4), 128 * rnd(1, 4)
+    relu, use_res, use_bn, use_bias = rnd(0, 1), rnd(0, 1), rnd(0, 1), rnd(0, 1)
+    mag = 10.0 ** (rnd(-30, 30) / 10.0)
+    x = torch.randn(M, n_in, device=dev) * mag
+    Wl = torch.randn(n_out, n_in, device=dev) * 0.1
+    bias = torch.randn(n_out, device=dev) * mag if use_bias else None
+    resid = torch.randn(M, n_out, device=dev) * mag if use_res else None
+    sc_, sh_ = (torch.rand(n_out, device=dev) + 0.5, torch.randn(n_out, device=dev) * mag) if use_bn else (None, None)
+    image = torch.empty((n_in // 128) * int(_lib.load().rl4co_am_weight_image_floats(n_out // 128)), device=dev)
+    _lib.call("rl4co_linear_pack", n_out, n_in, _lib.ptr(Wl), _lib.ptr(image), st)
+    y = torch.full((M, n_out), float("nan"), device=dev)
+    _lib.call("rl4co_linear_tc_ex", M, n_out, n_in, _lib.ptr(x), _lib.ptr(image), _lib.ptr(bias), relu, _lib.ptr(resid),
+              _lib.ptr(sc_), _lib.ptr(sh_), _lib.ptr(y), st)
+    rows = torch.randperm(M, device=dev)[:1024]
+    pre = x[rows].double() @ Wl.double().t() + (bias.double() if use_bias else 0)
+    magn = x[rows].double().abs() @ Wl.double().abs().t() + (bias.double().abs() if use_bias else 0)
+    ref = pre.clamp_min(0) if relu else pre
+    if use_res:
+        ref, magn = ref + resid[rows].double(), magn + resid[rows].double().abs()
+    if use_bn:
+        ref, magn = ref * sc_.double() + sh_.double(), magn * sc_.double() + sh_.double().abs()
+    err = (y[rows].double() - ref).abs()
+    bound = (4e-6 if n_in == 128 else 8e-6) * magn + 1e-30     # (TF32 K chunks: 48 accumulations per chunk)
+    if not bool((err <= bound).all()) or not bool(torch.isfinite(y).all()):
+        bad += 1
+        print(f"LINEAR FAIL M={M} {n_in}->{n_out} relu={relu} res={use_res} bn={use_bn} bias={use_bias} mag={mag:.1e}: "
+              f"worst excess {float((err / bound).max()):.2f}x", flush=True)
+    n += 1
+print(f"linear: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- multistart tensor-core kernel vs the SIMT kernel
+t0, n, bad_prev = time.time(), 0, bad
+with torch.inference_mode():
+    while time.time() - t0 < budget:
+        name = ("tsp", "cvrp")[rnd(0, 1)]
+        num_loc = rnd(5, 100)
+        B, S = rnd(1, 160), rnd(1, min(128, num_loc))
+        env = R.get_env(name, generator_params=dict(num_loc=num_loc), device=dev, check_solution=False)
+        pol = R.POMOPolicy(env_name=name, num_encoder_layers=1).to(dev).eval()
+        td = env.reset(env.generator(B).to(dev))
+        h = pol.encoder(td)[0].float().contiguous()
+        out = {}
+        for impl in (0, 2):
+            _lib.call("rl4co_set_rollout_impl", impl)
+            torch.manual_seed(n)
+            out[impl] = (pol(td, env, decode_type="multistart_greedy", num_starts=S, hidden=h, return_actions=True),
+                         pol(td, env, decode_type="multistart_sampling", num_starts=S, hidden=h, return_actions=True))
+        _lib.call("rl4co_set_rollout_impl", 0)
+        ok = True
+        for k in (0, 1):
+            a, b = out[0][k], out[2][k]
+            T = max(a["actions"].shape[1], b["actions"].shape[1])
+            pa = torch.nn.functional.pad(a["actions"], (0, T - a["actions"].shape[1]))
+            pb = torch.nn.functional.pad(b["actions"], (0, T - b["actions"].shape[1]))
+            same = (pa == pb).all(1)
+            if k == 0 and float(same.float().mean()) < 0.9:
+                ok = False
+            if bool(same.any()):
+                ok &= bool(torch.allclose(a["log_likelihood"][same], b["log_likelihood"][same], rtol=1e-5, atol=5e-5))
+                ok &= bool(torch.allclose(a["reward"][same], b["reward"][same], rtol=1e-5, atol=1e-5))
+            # the tensor-core kernel samples by inverse CDF, the SIMT kernel by Gumbel-max: different draws, both must be tours
+            if name == "tsp":
+                srt = a["actions"].sort(1).values
+                ok &= bool((srt == torch.arange(srt.shape[1], device=dev)).all())
+            else:
+                env2 = R.get_env(name, generator_params=dict(num_loc=num_loc), device=dev, check_solution=True)
+                env2.check_solution_validity(R.batchify(td, S), a["actions"])
+        if not ok:
+            bad += 1
+            print(f"MS_TC FAIL {name}{num_loc} B={B} S={S}", flush=True)
+        n += 1
+print(f"multistart: {n} random cases, {bad - bad_prev} failures", flush=True)
 sys.exit(1 if bad else 0)
