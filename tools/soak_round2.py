@@ -8,6 +8,10 @@
   linear - rl4co_linear_tc_ex: random widths (K = 128 on FP16 halves, K chunks on TF32), bias / ReLU / skip row / affine, against fp64;
   multistart - am_rollout_ms_tc.cu against the SIMT kernel: random tsp / cvrp sizes, batch and start counts, greedy tours equal
          up to near ties with equal log-likelihoods and rewards, sampled tours valid.
+  backward - am_backward.cu against autograd through the batched PyTorch pass (log-likelihoods, gradients of the encoder output
+         and of every decoder weight), random tsp / cvrp sizes, single start and multistart;
+  start nodes - multistart with caller-given start nodes (sdvrp, op, cvrp, tsp): every start must be the evaluate-mode episode of
+         its instance with that first action (rewards, per-step log-probs).
 Prints one line per case that exceeds its bound and a summary; exit code 1 if any did."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -179,4 +183,86 @@ with torch.inference_mode():
             print(f"MS_TC FAIL {name}{num_loc} B={B} S={S}", flush=True)
         n += 1
 print(f"multistart: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- backward kernel vs autograd through the PyTorch pass
+from rl4co_slap_b200.training import kernel_backward_supported, kernel_log_likelihood, teacher_forced_log_likelihood
+
+
+def _grads(fn, pol, h, weights):
+    h = h.detach().clone().requires_grad_(True)
+    for p_ in pol.decoder.parameters():
+        p_.grad = None
+    ll = fn(h)
+    (weights * ll).sum().backward()
+    out = {"h": h.grad.detach().clone()}
+    for name_, p_ in pol.decoder.named_parameters():
+        if p_.requires_grad:
+            out[name_] = None if p_.grad is None else p_.grad.detach().clone()
+    return ll.detach(), out
+
+
+t0, n, bad_prev = time.time(), 0, bad
+while time.time() - t0 < budget:
+    name = ("tsp", "cvrp")[rnd(0, 1)]
+    num_loc = rnd(5, 100)
+    S = 0 if rnd(0, 1) else rnd(2, min(12, num_loc))
+    B = rnd(1, 24)
+    pol = R.AttentionModelPolicy(env_name=name, num_encoder_layers=1, use_graph_context=bool(rnd(0, 2))).to(dev)
+    env = R.get_env(name, device=dev, generator_params=dict(num_loc=num_loc))
+    td = env.reset(env.generator(B).to(dev))
+    with torch.no_grad():
+        h0 = pol.encoder(td)[0].float()
+        kw = dict(decode_type="multistart_sampling", num_starts=S) if S else dict(decode_type="sampling")
+        out = pol(td, env, return_actions=True, hidden=h0, **kw)
+    if not kernel_backward_supported(pol, name, h0):
+        continue
+    w_ = torch.randn(out["actions"].shape[0], device=dev)
+    ll_ref, g_ref = _grads(lambda hh: teacher_forced_log_likelihood(pol, td, name, hh, out["actions"], num_starts=S), pol, h0, w_)
+    ll_ker, g_ker = _grads(lambda hh: kernel_log_likelihood(pol, td, name, hh, out["actions"], num_starts=S), pol, h0, w_)
+    ok = bool(torch.allclose(ll_ker, ll_ref, rtol=1e-5, atol=3e-5))
+    worst = ""
+    for key, want in g_ref.items():
+        got = g_ker.get(key)
+        if want is None or float(want.abs().max()) == 0.0:
+            ok &= got is None or float(got.abs().max()) < 1e-5
+            continue
+        e_, s_ = float((got - want).abs().max()), float(want.abs().max())
+        if e_ > 3e-4 * s_:
+            ok, worst = False, f"{key}: {e_:.2e} of {s_:.2e}"
+    if not ok:
+        bad += 1
+        print(f"BACKWARD FAIL {name}{num_loc} B={B} S={S} {worst}", flush=True)
+    n += 1
+print(f"backward: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- sdvrp multistart / given start nodes vs the evaluate path
+t0, n, bad_prev = time.time(), 0, bad
+with torch.inference_mode():
+    while time.time() - t0 < budget:
+        name = ("sdvrp", "op", "cvrp", "tsp")[rnd(0, 3)]
+        num_loc = rnd(6, 60)
+        B, S = rnd(1, 40), rnd(1, min(16, num_loc))
+        env = R.get_env(name, device=dev, generator_params=dict(num_loc=num_loc), check_solution=False)
+        pol = R.AttentionModelPolicy(env_name=name, num_encoder_layers=1).to(dev).eval()
+        td = env.reset(env.generator(B).to(dev))
+        h = pol.encoder(td)[0].float().contiguous()
+        lo = 0 if name == "tsp" else 1
+        if name == "op":                                    # the reference draws them from the feasible nodes
+            feas = td["action_mask"][..., 1:].float()
+            starts = (torch.multinomial(feas, S, replacement=True) + 1).t().reshape(-1)
+        else:
+            starts = torch.randint(lo, num_loc + lo, (S * B,), device=dev)
+        fn = lambda td_, env_, k: starts
+        out = pol(td, env, decode_type="multistart_greedy", num_starts=S, hidden=h, return_actions=True,
+                  return_sum_log_likelihood=False, select_start_nodes_fn=fn)
+        ok = bool((out["actions"][:, 0] == starts).all()) and bool((out["log_likelihood"][:, 0] == 0).all())
+        ev = pol(R.batchify(td, S), env, actions=out["actions"], hidden=R.batchify(h, S), return_sum_log_likelihood=False)
+        ok &= bool(torch.allclose(ev["reward"], out["reward"], rtol=1e-5, atol=1e-5))
+        ok &= bool(torch.allclose(ev["log_likelihood"][:, 1:], out["log_likelihood"][:, 1:], rtol=1e-4, atol=5e-5))
+        if not ok:
+            bad += 1
+            print(f"STARTS FAIL {name}{num_loc} B={B} S={S}: reward diff {float((ev['reward'] - out['reward']).abs().max()):.2e} "
+                  f"logp diff {float((ev['log_likelihood'][:, 1:] - out['log_likelihood'][:, 1:]).abs().max()):.2e}", flush=True)
+        n += 1
+print(f"start nodes: {n} random cases, {bad - bad_prev} failures", flush=True)
 sys.exit(1 if bad else 0)
