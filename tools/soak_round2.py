@@ -12,6 +12,8 @@
          and of every decoder weight), random tsp / cvrp sizes, single start and multistart;
   start nodes - multistart with caller-given start nodes (sdvrp, op, cvrp, tsp): every start must be the evaluate-mode episode of
          its instance with that first action (rewards, per-step log-probs).
+  consistency - all seven environments at random sizes: sampled and greedy rollouts pass the environment's validity check, the
+         fused replay reproduces their reward and the evaluate path their log-likelihood.
 Prints one line per case that exceeds its bound and a summary; exit code 1 if any did."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -21,6 +23,7 @@ from rl4co_slap_b200 import _lib
 
 dev = torch.device("cuda:0")
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
+only = set(sys.argv[2:])                # optional part names: k3 slap linear multistart backward starts consistency
 bad = 0
 g = torch.Generator(device="cpu").manual_seed(20261105)
 rnd = lambda lo, hi: int(torch.randint(lo, hi + 1, (1,), generator=g))
@@ -28,7 +31,7 @@ rnd = lambda lo, hi: int(torch.randint(lo, hi + 1, (1,), generator=g))
 # ---------------------------------------------------------------- K3 / linear, FP16 form
 t0, n = time.time(), 0
 st = _lib.stream_ptr(dev)
-while time.time() - t0 < budget:
+while (not only or "k3" in only) and time.time() - t0 < budget:
     M, nt = rnd(1, 70000), rnd(1, 8)
     mag = 10.0 ** (rnd(-60, 50) / 10.0)
     x = torch.randn(M, 128, device=dev) * mag
@@ -63,7 +66,7 @@ print(f"k3: {n} random cases, {bad} failures", flush=True)
 # ---------------------------------------------------------------- SLAP kernel vs generic kernel
 t0, n, bad_k3 = time.time(), 0, bad
 with torch.inference_mode():
-    while time.time() - t0 < budget:
+    while (not only or "slap" in only) and time.time() - t0 < budget:
         na, nl = rnd(2, 16), rnd(3, 8)
         N = na * nl
         P = rnd(2, min(32, N - 1))
@@ -109,7 +112,7 @@ print(f"slap: {n} random cases, {bad - bad_k3} failures", flush=True)
 
 # ---------------------------------------------------------------- linear layers with epilogues (FP16 K = 128, TF32 K chunks)
 t0, n, bad_prev = time.time(), 0, bad
-while time.time() - t0 < budget:
+while (not only or "linear" in only) and time.time() - t0 < budget:
     M = rnd(1, 40000)
     n_out, n_in = 128 * rnd(1, 4), 128 * rnd(1, 4)
     relu, use_res, use_bn, use_bias = rnd(0, 1), rnd(0, 1), rnd(0, 1), rnd(0, 1)
@@ -144,7 +147,7 @@ print(f"linear: {n} random cases, {bad - bad_prev} failures", flush=True)
 # ---------------------------------------------------------------- multistart tensor-core kernel vs the SIMT kernel
 t0, n, bad_prev = time.time(), 0, bad
 with torch.inference_mode():
-    while time.time() - t0 < budget:
+    while (not only or "multistart" in only) and time.time() - t0 < budget:
         name = ("tsp", "cvrp")[rnd(0, 1)]
         num_loc = rnd(5, 100)
         B, S = rnd(1, 160), rnd(1, min(128, num_loc))
@@ -202,7 +205,7 @@ def _grads(fn, pol, h, weights):
 
 
 t0, n, bad_prev = time.time(), 0, bad
-while time.time() - t0 < budget:
+while (not only or "backward" in only) and time.time() - t0 < budget:
     name = ("tsp", "cvrp")[rnd(0, 1)]
     num_loc = rnd(5, 100)
     S = 0 if rnd(0, 1) else rnd(2, min(12, num_loc))
@@ -238,7 +241,7 @@ print(f"backward: {n} random cases, {bad - bad_prev} failures", flush=True)
 # ---------------------------------------------------------------- sdvrp multistart / given start nodes vs the evaluate path
 t0, n, bad_prev = time.time(), 0, bad
 with torch.inference_mode():
-    while time.time() - t0 < budget:
+    while (not only or "starts" in only) and time.time() - t0 < budget:
         name = ("sdvrp", "op", "cvrp", "tsp")[rnd(0, 3)]
         num_loc = rnd(6, 60)
         B, S = rnd(1, 40), rnd(1, min(16, num_loc))
@@ -265,4 +268,45 @@ with torch.inference_mode():
                   f"logp diff {float((ev['log_likelihood'][:, 1:] - out['log_likelihood'][:, 1:]).abs().max()):.2e}", flush=True)
         n += 1
 print(f"start nodes: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- every env: sampled rollouts are valid and re-evaluate to themselves
+t0, n, bad_prev = time.time(), 0, bad
+with torch.inference_mode():
+    while (not only or "consistency" in only) and time.time() - t0 < budget:
+        name = ("tsp", "cvrp", "sdvrp", "op", "pctsp", "spctsp", "slap")[rnd(0, 6)]
+        if name == "slap":
+            na, nl = rnd(2, 12), rnd(3, 10)
+            num_loc = na * nl
+            env = R.SLAPEnv(generator_params={"n_aisles": na, "n_locs": nl, "n_products": rnd(2, min(30, num_loc - 1))}, device=dev)
+        else:
+            num_loc = rnd(4, 120)
+            env = R.get_env(name, device=dev, generator_params=dict(num_loc=num_loc))
+        B = rnd(1, 300)
+        pol = R.AttentionModelPolicy(env_name=name, num_encoder_layers=1).to(dev).eval()
+        td = env.reset(env.generator(B).to(dev))
+        h = pol.encoder(td)[0].float().contiguous()
+        torch.manual_seed(n)
+        smp = pol(td, env, decode_type="sampling", hidden=h, return_actions=True)
+        grd = pol(td, env, decode_type="greedy", hidden=h, return_actions=True)
+        ok = True
+        try:
+            for o in (smp, grd):
+                if name == "slap":
+                    srt = o["actions"].sort(1).values
+                    assert bool((srt[:, 1:] != srt[:, :-1]).all()) and bool((o["actions"] > 0).all())
+                else:
+                    env.check_solution_validity(td, o["actions"])
+                ev = pol(td, env, actions=o["actions"], hidden=h)
+                assert torch.allclose(ev["reward"], o["reward"], rtol=1e-5, atol=1e-5), "reward"
+                assert torch.allclose(ev["log_likelihood"], o["log_likelihood"], rtol=1e-4, atol=1e-4), \
+                    f"ll {float((ev['log_likelihood'] - o['log_likelihood']).abs().max()):.2e}"
+                _, r = env.replay(td, o["actions"])
+                assert torch.allclose(r, o["reward"], rtol=1e-5, atol=1e-5), "replay reward"
+        except AssertionError as exc:
+            ok = False
+            print(f"CONSISTENCY FAIL {name}{num_loc} B={B}: {str(exc)[:120]}", flush=True)
+        if not ok:
+            bad += 1
+        n += 1
+print(f"consistency: {n} random cases, {bad - bad_prev} failures", flush=True)
 sys.exit(1 if bad else 0)
