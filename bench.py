@@ -112,7 +112,10 @@ def build_policy(device):
     torch.manual_seed(1234)  # the reference's default seed (configs/experiment/routing/am.yaml:41)
     pol = R.AttentionModelPolicy(env_name="tsp", embed_dim=128, num_heads=8, num_encoder_layers=3,
                                  normalization="batch", feedforward_hidden=512)
-    return pol.to(device).eval()
+    pol = pol.to(device).eval()
+    if os.environ.get("RL4CO_BENCH_FIVE_TABLES"):   # A/B hook: project table 4 instead of forming its one row in K2
+        pol.first_context_in_kernel = "never"
+    return pol
 
 
 # ------------------------------------------------------------------------------------------

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define RL4CO_ABI_VERSION 3
+#define RL4CO_ABI_VERSION 4
 
 /* status bits (device int32 word) */
 #define RL4CO_ST_INVALID_TOUR      1   /* tsp/env.py:173, cvrp/env.py:175 */
@@ -291,7 +291,9 @@ int rl4co_am_graph_context(int64_t B, int32_t N, const float *h, const float *Wf
  *   1: glimpse values h.Wv^T
  *   2: folded logit keys h.(Wout^T Wl)^T  (project_out folded: <Wout o, l> = <o, Wout^T l>)
  *   3: (tsp, cvrp) per-node context h.Wctx[:, cur-half]^T
- *   4: (tsp) first-node context h.Wctx[:, first-half]^T
+ *   4: (tsp) first-node context h.Wctx[:, first-half]^T - a trajectory reads ONE row of it (its first node's), so a
+ *      single-start caller may leave table 4 out (n_tables = 4) and pass h / w_first instead (end of the struct): the
+ *      kernel then forms that row itself at step 1, one 128x128 mat-vec per rollout, and the projection writes 20 % less
  */
 typedef struct rl4co_am_rollout_args {
     int32_t env;            /* RL4CO_ENV_* */
@@ -344,6 +346,12 @@ typedef struct rl4co_am_rollout_args {
      * start_nodes[r] instead of s % num_loc (+1) - what a select_start_nodes_fn returned (utils/decoding.py:287-291), e.g.
      * the op branch of utils/ops.py:166-176 that resamples the starts from the feasible nodes.  NULL: the default rule. */
     const int32_t *start_nodes;
+    /* tsp without table 4 (appended, ABI 4): h [B,N,E] = the node embeddings the tables were projected from and
+     * w_first [E][E] = rows 4E..5E of the folded table weights (project_context.weight[:, :E], context.py:123-131; row =
+     * output dim).  Both or neither; with them n_tables may be 4.  The multistart tensor-core kernel reads table 4 for
+     * every start, so multistart callers keep passing five tables. */
+    const float *h;
+    const float *w_first;
 } rl4co_am_rollout_args;
 
 int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_t stream);

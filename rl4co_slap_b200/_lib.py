@@ -53,7 +53,7 @@ class AmRolloutArgs(C.Structure):
         ("actions", _p), ("logp", _p), ("logp_all", _p), ("ll", _p), ("reward", _p),
         ("steps", _p), ("assignment", _p), ("status", _p),
         ("prize", _p), ("max_length", _p), ("penalty", _p), ("prize_required", _p), ("wdyn", _p),
-        ("start_nodes", _p),
+        ("start_nodes", _p), ("h", _p), ("w_first", _p),
     ]
 
 

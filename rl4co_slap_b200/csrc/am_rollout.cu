@@ -241,7 +241,18 @@ am_rollout_kernel(const rl4co_am_rollout_args a, const int n_smem_tab, const int
                         ctx = a.q0[tid];
                     } else {
                         if (!have_first) {
-                            first_ctx = a.tables[((size_t)4 * M + b * (int64_t)N + misc[M_FIRST]) * E + tid];
+                            if (a.w_first) {    // table 4 left out (args h / w_first): its one row, formed here
+                                const float4 *hr = reinterpret_cast<const float4 *>(a.h + (b * (int64_t)N + misc[M_FIRST]) * E);
+                                const float4 *wr = reinterpret_cast<const float4 *>(a.w_first + (size_t)tid * E);
+                                first_ctx = 0.f;
+                                for (int k = 0; k < E / 4; ++k) {
+                                    const float4 x = __ldg(hr + k), w = __ldg(wr + k);
+                                    first_ctx = fmaf(x.x, w.x, first_ctx); first_ctx = fmaf(x.y, w.y, first_ctx);
+                                    first_ctx = fmaf(x.z, w.z, first_ctx); first_ctx = fmaf(x.w, w.w, first_ctx);
+                                }
+                            } else {
+                                first_ctx = a.tables[((size_t)4 * M + b * (int64_t)N + misc[M_FIRST]) * E + tid];
+                            }
                             have_first = true;
                         }
                         float c = Cs ? Cs[(size_t)cur * LD + tid]
@@ -513,7 +524,12 @@ extern "C" int rl4co_am_rollout(const rl4co_am_rollout_args *args, rl4co_stream_
     RL4CO_REQUIRE(a.tables && a.locs && a.actions && a.ll && a.reward, "am_rollout: null tensor");
     RL4CO_REQUIRE(a.temperature > 0.f, "am_rollout: temperature must be > 0");
     RL4CO_REQUIRE(a.mode != RL4CO_MODE_EVALUATE || a.actions_in, "am_rollout: evaluate needs actions_in");
-    const int need_tab = a.env == RL4CO_ENV_TSP ? 5 : (a.env == RL4CO_ENV_SLAP ? 3 : 4);
+    // tsp: table 4 may be left out when the kernel can form its one row itself (h and w_first given)
+    RL4CO_REQUIRE((a.h == nullptr) == (a.w_first == nullptr), "am_rollout: h and w_first come together");
+    RL4CO_REQUIRE(a.w_first == nullptr || a.env == RL4CO_ENV_TSP, "am_rollout: h / w_first are tsp arguments");
+    RL4CO_REQUIRE(a.w_first == nullptr || ((((uintptr_t)a.h) | ((uintptr_t)a.w_first)) & 15) == 0,
+                  "am_rollout: h / w_first must be 16-byte aligned");
+    const int need_tab = a.env == RL4CO_ENV_TSP ? (a.w_first ? 4 : 5) : (a.env == RL4CO_ENV_SLAP ? 3 : 4);
     RL4CO_REQUIRE(a.n_tables >= need_tab, "am_rollout: env needs %d tables, got %d", need_tab, a.n_tables);
     if (a.env == RL4CO_ENV_TSP) RL4CO_REQUIRE(a.q0, "am_rollout: tsp needs q0");
     if (a.env == RL4CO_ENV_CVRP)

@@ -485,7 +485,17 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     const int S = MS ? (a.S > 1 ? a.S : 1) : 1;
     const int64_t W = MS ? a.B * (int64_t)S : a.B;
     constexpr int t_first = MS ? 1 : 0;             // multistart: step 0 is the forced POMO start node
-    if (tid == 0 && (int64_t)blockIdx.x < W) stage_context(MS ? blockIdx.x / S : blockIdx.x, 0);
+    // table 4 left out (a.w_first): the first node's embedding row is needed the moment step 0 ends, so the instance's
+    // block of h goes to L2 one instance ahead like the tables do (51 KB of reads for the 51 KB K3 no longer writes)
+    auto prefetch_h = [&](int64_t b) {
+        const char *src = reinterpret_cast<const char *>(a.h + b * (int64_t)N * E);
+        for (size_t off = 0; off < c_bytes; off += 32768)
+            prefetch_l2(src + off, (unsigned)(c_bytes - off < 32768 ? c_bytes - off : 32768));
+    };
+    if (tid == 0 && (int64_t)blockIdx.x < W) {
+        stage_context(MS ? blockIdx.x / S : blockIdx.x, 0);
+        if (a.w_first) prefetch_h(MS ? blockIdx.x / S : blockIdx.x);
+    }
 
     int it = 0;
     for (int64_t w = blockIdx.x; w < W; w += gridDim.x, ++it) {
@@ -522,7 +532,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
 #endif
         // constant part of the query, pre-scaled: scale * (gctx + extra); extra = step-0 placeholder
         // (context.py:111-121), then the first node's half of the context projection
-        auto set_qb = [&](const float *extra) {
+        auto set_qb_vals = [&](const float (&x)[8]) {
             float v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = 0.f;
@@ -531,14 +541,34 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 const float4 g1 = __ldg(reinterpret_cast<const float4 *>(a.gctx + b * E + dim0) + 1);
                 v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; v[3] = g0.w; v[4] = g1.x; v[5] = g1.y; v[6] = g1.z; v[7] = g1.w;
             }
-            const float4 e0 = __ldg(reinterpret_cast<const float4 *>(extra));
-            const float4 e1 = __ldg(reinterpret_cast<const float4 *>(extra) + 1);
-            v[0] += e0.x; v[1] += e0.y; v[2] += e0.z; v[3] += e0.w; v[4] += e1.x; v[5] += e1.y; v[6] += e1.z; v[7] += e1.w;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] += x[i];
 #pragma unroll
             for (int i = 0; i < 4; ++i) c.qbs2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
         };
+        auto set_qb = [&](const float *extra) {
+            const float4 e0 = __ldg(reinterpret_cast<const float4 *>(extra));
+            const float4 e1 = __ldg(reinterpret_cast<const float4 *>(extra) + 1);
+            const float x[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+            set_qb_vals(x);
+        };
         set_qb(a.q0 + dim0);
-        auto set_first = [&](int node) { set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + node) * E + dim0); };
+        // row `node` of table 4, or - when the caller left that table out - formed here from h and w_first
+        auto set_first = [&](int node) {
+            if (a.w_first) {        // the warp's slice of the glimpse buffer is free between two steps, its compaction
+                                    // scratch before the first compaction
+                float *o16 = reinterpret_cast<float *>(smem + OFF_O) + 16 * warp;
+                first_context_row(a.h + (b * (int64_t)N + node) * E, a.w_first, o16,
+                                  reinterpret_cast<float *>(smem + OFF_SCR) + warp * (kScrSlots * 16), dim0, g);
+                const float4 e0 = *reinterpret_cast<const float4 *>(o16 + 8 * hh);
+                const float4 e1 = *reinterpret_cast<const float4 *>(o16 + 8 * hh + 4);
+                const float x[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                set_qb_vals(x);
+                __syncwarp();
+            } else {
+                set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + node) * E + dim0);
+            }
+        };
 
         TG_TRACE_ROW(T + 2, 1);
         // ------------------------------------------------ small per-instance state -> smem
@@ -564,6 +594,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 for (size_t off = 0; off < c_bytes; off += 32768)
                     prefetch_l2(src + off, (unsigned)(c_bytes - off < 32768 ? c_bytes - off : 32768));
             }
+            if (a.w_first) prefetch_h(nb);
         }
         __syncthreads();
 

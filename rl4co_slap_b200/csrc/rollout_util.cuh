@@ -98,6 +98,73 @@ __device__ __forceinline__ float slap_order_len(const float2 *locs, const int *a
 }
 
 
+// tsp without table 4 (args h / w_first): the first node's half of the step context, project_context.weight[:, :E] . h_first
+// (context.py:123-131), formed in the rollout kernel once the first node is known.  Thread layout of the register-file
+// kernels: a warp owns output dims 16 warp .. 16 warp + 15, this thread dims dim0..dim0+7 of them, and the 16 lanes
+// g = lane & 15 of its half-warp split the 128 inputs, 8 each: inputs 4g..4g+3 and 64+4g..64+4g+3, so that each load
+// instruction of a half-warp covers 256 contiguous bytes of one weight row.  The butterfly leaves the same sum in all 16
+// lanes and lane g == 0 stores it to out16 = 16 floats of shared memory private to the warp (indexed by dim - 16 warp).
+// All 32 lanes must call it; it ends with __syncwarp().
+//
+// Not inlined on purpose: the callers keep ~250 registers live across their decode loop and the 18 loads in flight here
+// would otherwise change that loop's register allocation (spills in the step, seen with ptxas -v); as a call the cost
+// stays on this once-per-rollout path.  The call leaves the function ~56 registers, not enough for 18 x 128-bit loads in
+// one batch (the compiler then splits them into two dependent round trips to L2, ~2.8 k clk per rollout measured), so
+// with `scratch` (4 KB of shared memory private to the warp, free at this point) the weight rows of dims 4..7 travel by
+// cp.async instead and everything is in flight at once.  scratch == nullptr: registers only.
+template <int kUnused = 0>   // a template only so that the header may define a non-inline function
+__device__ __noinline__ void first_context_row(const float *hrow, const float *w_first, float *out16, float *scratch,
+                                               int dim0, int g) {
+    const int lane = threadIdx.x & 31;
+    const float *wr0 = w_first + (size_t)dim0 * 128 + 4 * g;
+    const uint32_t sdst = scratch ? smem_u32(scratch) + lane * 16 : 0u;
+    if (scratch) {
+#pragma unroll
+        for (int i = 4; i < 8; ++i)
+#pragma unroll
+            for (int half = 0; half < 2; ++half)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + ((i - 4) * 2 + half) * 512),
+                             "l"(wr0 + (size_t)i * 128 + 64 * half) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    const float4 h0 = __ldg(reinterpret_cast<const float4 *>(hrow + 4 * g));
+    const float4 h1 = __ldg(reinterpret_cast<const float4 *>(hrow + 64 + 4 * g));
+    float s[8];
+    auto dot8 = [&](const float4 &w0, const float4 &w1) {
+        float v = h0.x * w0.x;
+        v = fmaf(h0.y, w0.y, v); v = fmaf(h0.z, w0.z, v); v = fmaf(h0.w, w0.w, v);
+        v = fmaf(h1.x, w1.x, v); v = fmaf(h1.y, w1.y, v); v = fmaf(h1.z, w1.z, v); v = fmaf(h1.w, w1.w, v);
+        return v;
+    };
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float *wr = wr0 + (size_t)i * 128;
+        s[i] = dot8(__ldg(reinterpret_cast<const float4 *>(wr)), __ldg(reinterpret_cast<const float4 *>(wr + 64)));
+    }
+    if (scratch) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        const float4 *sw = reinterpret_cast<const float4 *>(scratch) + lane;
+#pragma unroll
+        for (int i = 4; i < 8; ++i) s[i] = dot8(sw[((i - 4) * 2) * 32], sw[((i - 4) * 2 + 1) * 32]);
+    } else {
+#pragma unroll
+        for (int i = 4; i < 8; ++i) {
+            const float *wr = wr0 + (size_t)i * 128;
+            s[i] = dot8(__ldg(reinterpret_cast<const float4 *>(wr)), __ldg(reinterpret_cast<const float4 *>(wr + 64)));
+        }
+    }
+#pragma unroll
+    for (int m = 1; m < 16; m <<= 1)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] += __shfl_xor_sync(0xffffffffu, s[i], m);
+    if (g == 0) {
+        float4 *o = reinterpret_cast<float4 *>(out16 + (dim0 & 15));
+        o[0] = make_float4(s[0], s[1], s[2], s[3]);
+        o[1] = make_float4(s[4], s[5], s[6], s[7]);
+    }
+    __syncwarp();
+}
+
 // host-side launchers of the register-file resident single-start kernel (am_rollout_rf.cu)
 int launch_rollout_rf(const rl4co_am_rollout_args &a, cudaStream_t stream);
 bool rollout_rf_supports(const rl4co_am_rollout_args &a);

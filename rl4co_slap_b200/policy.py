@@ -190,6 +190,10 @@ class AttentionModelPolicy(nn.Module):
         self.projection = "tensor"      # "tensor" | "simt": which K3 kernel builds the rollout tables
         self.unused_kwargs = unused_kwargs
         self.last_launches = 0  # rl4co_* kernel launches of the most recent forward()
+        # tsp single start: project 4 tables and let the rollout kernel form table 4's one row ("auto": from 48 nodes on -
+        # the row costs the kernel ~1.6 k clk per rollout, the table costs the projection ~36 clk x SMs per node; "always",
+        # "never")
+        self.first_context_in_kernel = "auto"
         self.profile = None     # set to a list to collect (rollouts, [ev0, ev1, ev2]) per chunk
 
     # ------------------------------------------------------------------------------
@@ -305,6 +309,13 @@ class AttentionModelPolicy(nn.Module):
         W, q0, wcap, Wfixed = self.decoder.folded_weights()
         W_image = self.decoder.weight_image() if self.projection == "tensor" else None
         n_tables = W.shape[0] // 128
+        # tsp, single start: a trajectory reads one row of table 4 (its first node's), so the projection leaves that table
+        # out and the rollout kernel forms the row from h and the table's weight block at step 1 (include/: args h / w_first)
+        w_first = None
+        fck = self.first_context_in_kernel
+        if name == "tsp" and S == 0 and not return_hidden and (fck == "always" or (fck == "auto" and N >= 48)):
+            w_first = W[4 * 128:5 * 128]
+            n_tables = 4
         prof = self.profile  # optional CUDA-event timing of the K3 / K2 launches (bench.py)
         seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if mode == _lib.MODE_SAMPLING else 0
         stream = _lib.stream_ptr(dev)
@@ -374,6 +385,8 @@ class AttentionModelPolicy(nn.Module):
             a.ll, a.reward, a.steps = _lib.ptr(out_ll[sl]), _lib.ptr(out_reward[sl]), _lib.ptr(out_steps[sl])
             a.assignment = _lib.ptr(assign[sl]) if assign is not None else None
             a.start_nodes = _lib.ptr(start_nodes, torch.int32) if start_nodes is not None else None
+            if w_first is not None:
+                a.h, a.w_first = _lib.ptr(h), _lib.ptr(w_first)
             a.status = _lib.ptr(status)
             _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
             launches += 1

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     lib = _lib.load()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.rl4co_abi_version() == 3
+    assert lib.rl4co_abi_version() == 4
 
 
 def test_args_struct_matches_header():

@@ -53,6 +53,10 @@ a.temperature, a.tanh_clipping, a.mask_logits = 1.0, 10.0, 1
 a.tables, a.gctx, a.q0, a.locs = _lib.ptr(tables), _lib.ptr(gctx), _lib.ptr(q0), _lib.ptr(locs)
 a.actions, a.logp, a.logp_all, a.ll, a.reward = _lib.ptr(acts), _lib.ptr(logp), _lib.ptr(trace), _lib.ptr(ll), _lib.ptr(rew)
 a.steps, a.status = _lib.ptr(steps), _lib.ptr(status)
+if os.environ.get("RF_FC"):     # table 4 left out: the kernel forms the first node's context row (ABI 4: h / w_first)
+    w_first = W[512:640]
+    a.n_tables, a.h, a.w_first = 4, _lib.ptr(h), _lib.ptr(w_first)
+    tables[4].fill_(float("nan"))
 for _ in range(2):
     _lib.check(_lib.load().rl4co_am_rollout(a, stream), "rl4co_am_rollout")
 torch.cuda.synchronize()
