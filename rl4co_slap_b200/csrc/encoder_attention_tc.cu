@@ -14,6 +14,8 @@
 //               max, exp2, sum, o += p V_j (V rows as broadcast LDS.128, FFMA2), normalise, store.
 // A CTA walks whole instances (its 8 heads back to back), so the 64-byte column slices it reads share
 // their 128-byte lines through L1 / L2.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "rollout_util.cuh"
 #include "tc_util.cuh"
@@ -565,6 +567,322 @@ encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 
 }  // namespace enctc2
 
+
+// ============================================================================================
+// The two-GEMM kernel with half the tensor-memory traffic (N <= 112).  tcgen05.ld / st move 64 B/clk per SM, and in
+// enctc2 one (instance, head) unit moves 128 lanes x 464 words through that port - the scores read twice (max pass, exp
+// pass), P_hi and P_lo written as TF32 words, O read - i.e. ~3.7 k clk, which is what that kernel takes per unit (its
+// tensor pipe is 21 % active).  Here (a) the score row is read ONCE, into 112 registers, (b) P goes back as FP16 pairs,
+// hi = fp16(p), lo = fp16(p - hi) (22 significant bits), two keys per 32-bit column, scaled by 2^14 so that the residuals
+// of every p that matters are normal fp16 numbers (the scale cancels in O / l), and O = P V is three kind::f16 MMAs per 16
+// keys with V^T staged as fp16 hi / lo images: 128 lanes x 240 words per unit, 21 + 6 MMAs instead of 42 + 6.
+// Q K^T stays 3xTF32, so q and k keep fp32's range.  V goes through fp16: |v| must stay below 65 504 (an encoder whose
+// values get there has diverged), and entries below 2^-14 carry an absolute error of 3e-8 instead of a relative one.
+namespace enctc3 {
+using namespace tcu;
+using enctc::ex2f;
+
+constexpr int H = 8, D = 16, E = 128, NK = 112;         // key columns of the score tile (multiple of 16)
+constexpr int TILE_BYTES = 128 * 128;                   // Q / K operand image (TF32): 128 rows x 128 B (64 B used)
+constexpr int VT_TILE = 16 * 128;                       // V^T k-block (FP16): 16 dims x 64 keys
+constexpr int VT_BYTES = 2 * VT_TILE;                   // 4 KB per image (hi or lo)
+constexpr int QK_STAGE_BYTES = 4 * TILE_BYTES;          // Qhi Qlo Khi Klo = 64 KB, free again once the scores are in TMEM
+constexpr int QK_STAGES = 2;
+constexpr int VT_SLOT_BYTES = 2 * VT_BYTES;             // VThi VTlo = 8 KB, needed until O = P V is complete
+constexpr int VT_SLOTS = 4;
+constexpr int kProducerWarps = 4, kConsumerWarps = 8;
+constexpr int kThreads = (1 + kProducerWarps + kConsumerWarps) * 32;       // 416
+constexpr int SMEM_BYTES = 1024 + QK_STAGES * QK_STAGE_BYTES + VT_SLOTS * VT_SLOT_BYTES + 256;
+constexpr uint32_t kIdescS = make_idesc_tf32(128, NK);
+constexpr uint32_t kIdescO = make_idesc_f16(128, D);
+constexpr int COL_PLO = NK / 2, COL_O = NK, BUF_COLS = 256;    // P_hi [0,56) over the scores, P_lo [56,112), O [112,128)
+constexpr float kPShift = 14.f;                         // P = 2^(s - max + 14): the fp16 residuals stay normal numbers
+
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo32, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 db;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHi)
+        : "memory");
+}
+using enctc2::tmem_ld16;
+__device__ __forceinline__ void tmem_ld32_nw(uint32_t taddr, uint32_t *v) {       // no wait: pair with tcgen05.wait::ld
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld16_nw(uint32_t taddr, uint32_t *v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+// all NK score columns of this thread's lane, one wait
+__device__ __forceinline__ void tmem_ld_row(uint32_t taddr, uint32_t (&v)[NK]) {
+    tmem_ld32_nw(taddr, v);
+    tmem_ld32_nw(taddr + 32, v + 32);
+    tmem_ld32_nw(taddr + 64, v + 64);
+    tmem_ld16_nw(taddr + 96, v + 96);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]),
+                 "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+
+__device__ __forceinline__ uint32_t rn_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
+
+__global__ void __launch_bounds__(kThreads, 1)
+encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, float *__restrict__ out) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char *sVT = smem + QK_STAGES * QK_STAGE_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sVT + VT_SLOTS * VT_SLOT_BYTES);
+    uint64_t *in_full = bars, *s_full = bars + 2, *p_full = bars + 4, *o_full = bars + 6, *buf_free = bars + 8;
+    uint64_t *qk_empty = bars + 10, *vt_free = bars + 12;       // [2], [4]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t n_inst = blockIdx.x < B ? (B - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t n_units = n_inst * H;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&in_full[s], kProducerWarps);     // inputs of a unit staged
+            mbar_init(&s_full[s], 1);                   // scores complete (commit)
+            mbar_init(&p_full[s], 4);                   // P written by the buffer's four consumer warps
+            mbar_init(&o_full[s], 1);                   // O complete (commit)
+            mbar_init(&buf_free[s], 4);                 // O read back: the TMEM buffer may be overwritten
+            mbar_init(&qk_empty[s], 1);                 // Q / K stage read by the score MMAs (commit)
+        }
+        for (int s = 0; s < VT_SLOTS; ++s) mbar_init(&vt_free[s], 1);   // V^T slot read by the P V MMAs (commit)
+        fence_barrier_init();
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================================= MMA issue: QK(i), then PV(i - 1)
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
+        for (int64_t i = 0; i <= n_units; ++i) {
+            if (i < n_units) {
+                const int b = (int)(i & 1);
+                const unsigned ph = (unsigned)((i >> 1) & 1);
+                mbar_wait_bounded(&in_full[b], ph);
+                mbar_wait_bounded(&buf_free[b], ph ^ 1u);
+                tc_fence_after();
+                const uint32_t q_hi = d0 + (uint32_t)((b * QK_STAGE_BYTES) >> 4), q_lo = q_hi + (TILE_BYTES >> 4);
+                const uint32_t k_hi = q_hi + 2 * (TILE_BYTES >> 4), k_lo = q_hi + 3 * (TILE_BYTES >> 4);
+                const uint32_t d = tmem_u + (uint32_t)(b * BUF_COLS);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k8 = 0; k8 < D / 8; ++k8) {
+                        umma_tf32(d, q_lo + 2 * k8, k_hi + 2 * k8, kIdescS, (unsigned)(k8 != 0));
+                        umma_tf32(d, q_hi + 2 * k8, k_lo + 2 * k8, kIdescS, 1u);
+                        umma_tf32(d, q_hi + 2 * k8, k_hi + 2 * k8, kIdescS, 1u);
+                    }
+                    umma_commit(&qk_empty[b]);
+                    umma_commit(&s_full[b]);
+                }
+                __syncwarp();
+            }
+            if (i >= 1) {
+                const int64_t u = i - 1;
+                const int b = (int)(u & 1);
+                mbar_wait_bounded(&p_full[b], (unsigned)((u >> 1) & 1));
+                tc_fence_after();
+                const int vs = (int)(u & 3);
+                const uint32_t vt_hi = d0 + (uint32_t)((QK_STAGES * QK_STAGE_BYTES + vs * VT_SLOT_BYTES) >> 4);
+                const uint32_t vt_lo = vt_hi + (VT_BYTES >> 4);
+                const uint32_t p_hi = tmem_u + (uint32_t)(b * BUF_COLS), p_lo = p_hi + COL_PLO;
+                const uint32_t o = tmem_u + (uint32_t)(b * BUF_COLS + COL_O);
+                if (elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < NK / 16; ++ks) {      // 7 k-steps of 16 keys (8 TMEM columns of fp16 pairs)
+                        const uint32_t voff = (uint32_t)(((ks >> 2) * VT_TILE + (ks & 3) * 32) >> 4);
+                        umma_f16_ts(o, p_lo + 8 * ks, vt_hi + voff, kIdescO, (unsigned)(ks != 0));
+                        umma_f16_ts(o, p_hi + 8 * ks, vt_lo + voff, kIdescO, 1u);
+                        umma_f16_ts(o, p_hi + 8 * ks, vt_hi + voff, kIdescO, 1u);
+                    }
+                    umma_commit(&vt_free[vs]);
+                    umma_commit(&o_full[b]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp <= kProducerWarps) {
+        // ================================================= producers: thread = node row
+        const int row = tid - 32;                               // 0..127
+        const float scale = 0.25f * 1.4426950408889634f;        // 1/sqrt(16) * log2(e), folded into Q
+        const uint32_t r7 = (uint32_t)(row & 7);
+        {                                                       // zero what is never written: pad rows, all of V^T
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            if (row >= N)
+                for (int s = 0; s < QK_STAGES; ++s)
+                    for (int img = 0; img < 4; ++img)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            *reinterpret_cast<uint4 *>(smem + s * QK_STAGE_BYTES + img * TILE_BYTES + swz(row, c)) = z;
+            for (int off = row * 16; off < VT_SLOTS * VT_SLOT_BYTES; off += 128 * 16)
+                *reinterpret_cast<uint4 *>(sVT + off) = z;
+            asm volatile("bar.sync 2, 128;" ::: "memory");      // the four producer warps: zeros before any key write
+        }
+        // V^T element (key j = row, dim d), fp16: k-block j >> 6, row d, 16-byte chunk ((j & 63) >> 3) ^ (d & 7), half j & 7
+        const uint32_t vt_base = (uint32_t)((row >> 6) * VT_TILE + (row & 7) * 2);
+        const uint32_t vt_chunk = (uint32_t)((row & 63) >> 3);
+        for (int64_t i = 0; i < n_units; ++i) {
+            const int st_i = (int)(i & 1), h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            float4 q[4], k[4], v[4];
+            if (row < N) {                                      // loads first: they fly while we wait for the stage
+                const float4 *p = reinterpret_cast<const float4 *>(qkv + (b * N + row) * (3 * E) + h * D);
+                if (h == 0 && i + H < n_units) {                // this row of the CTA's next instance -> L2 (12 lines)
+                    const char *nx = reinterpret_cast<const char *>(qkv + ((b + gridDim.x) * N + row) * (3 * E));
+#pragma unroll
+                    for (int c = 0; c < 12; ++c) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 128 * c));
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { q[c] = __ldg(p + c); k[c] = __ldg(p + E / 4 + c); v[c] = __ldg(p + 2 * E / 4 + c); }
+            }
+            const int vs = (int)(i & 3);
+            mbar_wait_bounded(&qk_empty[st_i], (unsigned)((i >> 1) & 1) ^ 1u);  // scores of unit i - 2 are in TMEM
+            mbar_wait_bounded(&vt_free[vs], (unsigned)((i >> 2) & 1) ^ 1u);     // P V of unit i - 4 is complete
+            if (row < N) {
+                unsigned char *st = smem + st_i * QK_STAGE_BYTES;
+                unsigned char *vt = sVT + vs * VT_SLOT_BYTES;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t off = (uint32_t)row * 128u + (((uint32_t)c ^ r7) << 4);
+                    // hi = x rounded to TF32's 11 significant bits by integer arithmetic (add half an ulp, clear the 13 low
+                    // bits - no overflow check: |x| would have to be within 2^-11 of FLT_MAX), lo = x - hi exactly, of
+                    // which the tensor core reads the top 11 bits: three instructions per value where cvt.rna.tf32 with
+                    // its inf / nan handling costs four and a second conversion for lo (the producers are this kernel's
+                    // critical role)
+                    const float4 a = make_float4(q[c].x * scale, q[c].y * scale, q[c].z * scale, q[c].w * scale);
+                    uint4 hi, lo;
+                    hi.x = rn_tf32(a.x); hi.y = rn_tf32(a.y); hi.z = rn_tf32(a.z); hi.w = rn_tf32(a.w);
+                    lo.x = __float_as_uint(a.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(a.y - __uint_as_float(hi.y));
+                    lo.z = __float_as_uint(a.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(a.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + TILE_BYTES + off) = lo;
+                    const float4 kk = k[c];
+                    hi.x = rn_tf32(kk.x); hi.y = rn_tf32(kk.y); hi.z = rn_tf32(kk.z); hi.w = rn_tf32(kk.w);
+                    lo.x = __float_as_uint(kk.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(kk.y - __uint_as_float(hi.y));
+                    lo.z = __float_as_uint(kk.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(kk.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + 2 * TILE_BYTES + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + 3 * TILE_BYTES + off) = lo;
+                    const float vv[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {               // dim d = 4 c + e of key `row`, transposed
+                        const int d = 4 * c + e;
+                        const uint32_t o2 = vt_base + (uint32_t)d * 128u + ((vt_chunk ^ (uint32_t)(d & 7)) << 4);
+                        const __half vh = __float2half_rn(vv[e]);
+                        *reinterpret_cast<__half *>(vt + o2) = vh;
+                        *reinterpret_cast<__half *>(vt + VT_BYTES + o2) = __float2half_rn(vv[e] - __half2float(vh));
+                    }
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&in_full[st_i]);
+        }
+    } else {
+        // ================================================= consumers: thread = query row = TMEM lane
+        const int cw = warp - (1 + kProducerWarps);             // 0..7
+        const int buf = cw >> 2, quarter = warp & 3;
+        const int row = 32 * quarter + lane;
+        const uint32_t t0 = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)(buf * BUF_COLS);
+        for (int64_t i = buf; i < n_units; i += 2) {
+            const int h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            const unsigned ph = (unsigned)((i >> 1) & 1);
+            mbar_wait_bounded(&s_full[buf], ph);
+            tc_fence_after();
+            // ONE read of the score row (112 registers); columns beyond N (K rows of zeros) -> -inf
+            uint32_t sv[NK];
+            tmem_ld_row(t0, sv);
+#pragma unroll
+            for (int c = 0; c < NK / 16; ++c)
+                if (N < 16 * (c + 1)) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (16 * c + j >= N) sv[16 * c + j] = 0xff800000u;
+                }
+            float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+            for (int j = 0; j < NK; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(sv[j]));
+            const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) - kPShift;
+            float l = 0.f;                                      // P = 2^(s - max + 14) as fp16 pairs hi / lo, in place
+#pragma unroll
+            for (int c = 0; c < NK / 16; ++c) {
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float p0 = ex2f(__uint_as_float(sv[16 * c + 2 * k]) - m);
+                    const float p1 = ex2f(__uint_as_float(sv[16 * c + 2 * k + 1]) - m);
+                    l += p0 + p1;
+                    split_f16x2_trunc(p0, p1, hi[k], lo[k]);    // no F2F conversions: they share the MUFU pipe with ex2
+                }
+                tmem_st8(t0 + 8 * c, hi);
+                tmem_st8(t0 + COL_PLO + 8 * c, lo);
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[buf]);
+            // O = P V arrives from the tensor core; normalise and store this row's 16 outputs
+            mbar_wait_bounded(&o_full[buf], ph);
+            tc_fence_after();
+            uint32_t ov[16];
+            tmem_ld16(t0 + COL_O, ov);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&buf_free[buf]);
+            if (row < N) {
+                const float inv = 1.f / l;
+                float4 *dst = reinterpret_cast<float4 *>(out + (b * N + row) * E + h * D);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    dst[c] = make_float4(__uint_as_float(ov[4 * c]) * inv, __uint_as_float(ov[4 * c + 1]) * inv,
+                                         __uint_as_float(ov[4 * c + 2]) * inv, __uint_as_float(ov[4 * c + 3]) * inv);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace enctc3
+
 int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, int impl, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -574,21 +892,24 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
         if (sm_count <= 0) sm_count = 148;
     }
     const int64_t grid = B < sm_count ? B : sm_count;
-    const bool both = impl == 2 || (impl == 0 && N <= enctc2::NK);     // P V on the tensor cores too
-    if (both && N > enctc2::NK) {
-        set_error("encoder_attention(tc): the two-GEMM kernel needs N <= %d, got %d", enctc2::NK, N);
+    // 0 automatic: both GEMMs on the tensor cores with P as fp16 pairs (enctc3) for N <= 112, else scores only (enctc)
+    const int kind = impl == 0 ? (N <= enctc3::NK ? 3 : 1) : impl;
+    if (kind >= 2 && N > enctc2::NK) {
+        set_error("encoder_attention(tc): the two-GEMM kernels need N <= %d, got %d", enctc2::NK, N);
         return 1;
     }
-    const int smem = both ? enctc2::SMEM_BYTES : enctc::SMEM_BYTES;
-    cudaError_t e = both ? cudaFuncSetAttribute(enctc2::encoder_attention_tc2_kernel,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
-                         : cudaFuncSetAttribute(enctc::encoder_attention_tc_kernel,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int smem = kind == 3 ? enctc3::SMEM_BYTES : (kind == 2 ? enctc2::SMEM_BYTES : enctc::SMEM_BYTES);
+    const void *fn = kind == 3 ? (const void *)enctc3::encoder_attention_tc3_kernel
+                               : (kind == 2 ? (const void *)enctc2::encoder_attention_tc2_kernel
+                                            : (const void *)enctc::encoder_attention_tc_kernel);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) {
         set_error("encoder_attention(tc): cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
         return 2;
     }
-    if (both)
+    if (kind == 3)
+        enctc3::encoder_attention_tc3_kernel<<<(unsigned)grid, enctc3::kThreads, smem, stream>>>(B, N, qkv, out);
+    else if (kind == 2)
         enctc2::encoder_attention_tc2_kernel<<<(unsigned)grid, enctc2::kThreads, smem, stream>>>(B, N, qkv, out);
     else
         enctc::encoder_attention_tc_kernel<<<(unsigned)grid, enctc::kThreads, smem, stream>>>(B, N, qkv, out);
@@ -600,10 +921,10 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
 
 using namespace rl4co;
 
-static int g_attention_impl = 0;    // 0 auto (two-GEMM kernel for N <= 112), 1 Q K^T only, 2 two-GEMM kernel
+static int g_attention_impl = 0;    // 0 auto (enctc3 for N <= 112), 1 Q K^T only, 2 two-GEMM kernel 3xTF32, 3 two-GEMM kernel with fp16 P V
 
 extern "C" int rl4co_set_attention_impl(int32_t impl) {
-    RL4CO_REQUIRE(impl >= 0 && impl <= 2, "set_attention_impl: 0 auto, 1 scores on tensor cores, 2 both GEMMs, got %d", impl);
+    RL4CO_REQUIRE(impl >= 0 && impl <= 3, "set_attention_impl: 0 auto, 1 scores on tensor cores, 2 both GEMMs (TF32), 3 both GEMMs (fp16 P V), got %d", impl);
     g_attention_impl = impl;
     return 0;
 }

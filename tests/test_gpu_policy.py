@@ -436,7 +436,7 @@ def test_encoder_fused_skip_batchnorm_epilogue(name, dev):
 
 @pytest.mark.parametrize("B,N,amp", ((3, 100, 1.0), (7, 5, 1.0), (300, 50, 3.0), (150, 128, 1.0), (500, 101, 2.0), (1, 1, 1.0)))
 def test_encoder_attention_kernels_match_fp64(B, N, amp, dev):
-    """rl4co_encoder_attention_tc (both kernels: Q K^T / Q K^T + P V on tcgen05, 3xTF32) and rl4co_encoder_attention (SIMT) vs an fp64 softmax
+    """rl4co_encoder_attention_tc (the three kernels: Q K^T / Q K^T + P V on tcgen05, 3xTF32 / P V as 3xFP16) and rl4co_encoder_attention (SIMT) vs an fp64 softmax
     attention on the fused Wqkv layout [B, N, 3, 8, 16] (nn/attention.py:81-126, no mask)"""
     from rl4co_slap_b200 import _lib
     torch.manual_seed(B * 131 + N)
@@ -446,6 +446,7 @@ def test_encoder_attention_kernels_match_fp64(B, N, amp, dev):
     variants = [("rl4co_encoder_attention_tc", 1), ("rl4co_encoder_attention", 0)]
     if N <= 112:
         variants.append(("rl4co_encoder_attention_tc", 2))     # P V on the tensor cores too (P in TMEM)
+        variants.append(("rl4co_encoder_attention_tc", 3))     # ... with P and V as fp16 hi / lo pairs (the default)
     try:
         for fn, impl in variants:
             _lib.call("rl4co_set_attention_impl", impl)
