@@ -584,17 +584,21 @@ using enctc::ex2f;
 
 constexpr int H = 8, D = 16, E = 128, NK = 112;         // key columns of the score tile (multiple of 16)
 constexpr int TILE_BYTES = 128 * 128;                   // Q / K operand image (TF32): 128 rows x 128 B (64 B used)
-constexpr int VT_TILE = 16 * 128;                       // V^T k-block (FP16): 16 dims x 64 keys
-constexpr int VT_BYTES = 2 * VT_TILE;                   // 4 KB per image (hi or lo)
+constexpr int V_HALF = 128 * 16;                        // V image (FP16, MN-major, no swizzle): [dim half][key][8 dims = 16 B]
+constexpr int VT_BYTES = 2 * V_HALF;                    // 4 KB per image (hi or lo)
 constexpr int QK_STAGE_BYTES = 4 * TILE_BYTES;          // Qhi Qlo Khi Klo = 64 KB, free again once the scores are in TMEM
 constexpr int QK_STAGES = 2;
-constexpr int VT_SLOT_BYTES = 2 * VT_BYTES;             // VThi VTlo = 8 KB, needed until O = P V is complete
-constexpr int VT_SLOTS = 4;
+constexpr int VT_SLOT_BYTES = 2 * VT_BYTES;             // Vhi Vlo = 8 KB, needed until O = P V is complete
+constexpr int VT_SLOTS = 2;                             // one per TMEM buffer, written by that buffer's consumer group
 constexpr int kProducerWarps = 4, kConsumerWarps = 8;
 constexpr int kThreads = (1 + kProducerWarps + kConsumerWarps) * 32;       // 416
-constexpr int SMEM_BYTES = 1024 + QK_STAGES * QK_STAGE_BYTES + VT_SLOTS * VT_SLOT_BYTES + 256;
+constexpr int V_STAGE_BYTES = 4 * 128 * 16;               // raw V rows of one unit, [16-byte chunk][key]: 8 KB per group
+constexpr int SMEM_BYTES = 1024 + QK_STAGES * QK_STAGE_BYTES + VT_SLOTS * (VT_SLOT_BYTES + V_STAGE_BYTES) + 256;
 constexpr uint32_t kIdescS = make_idesc_tf32(128, NK);
-constexpr uint32_t kIdescO = make_idesc_f16(128, D);
+constexpr uint32_t kIdescO = make_idesc_f16(128, D) | (1u << 16);      // B (= V) is MN-major: a key's dims are contiguous
+// matrix descriptor of V (cute/atom/mma_traits_sm100.hpp, Major-MN, SWIZZLE_NONE: ((1,n),(8,k)):((X,SBO),(1,LBO)) in 16-byte
+// units): 8 keys of a k-group 16 B apart, the next k-group LBO = 128 B on, the other 8 dims SBO = 2048 B on; version 1
+constexpr uint32_t kDescLoV = 8u << 16, kDescHiV = (uint32_t)(V_HALF >> 4) | (1u << 14);
 constexpr int COL_PLO = NK / 2, COL_O = NK, BUF_COLS = 256;    // P_hi [0,56) over the scores, P_lo [56,112), O [112,128)
 constexpr float kPShift = 14.f;                         // P = 2^(s - max + 14): the fp16 residuals stay normal numbers
 
@@ -608,7 +612,7 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
         "setp.ne.b32 p, %4, 0;\n\t"
         "mov.b64 db, {%2, %5};\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %3, p;\n\t"
-        "}\n" ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHi)
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo32), "r"(idesc), "r"(accumulate), "r"(kDescHiV)
         : "memory");
 }
 using enctc2::tmem_ld16;
@@ -652,9 +656,10 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char *sVT = smem + QK_STAGES * QK_STAGE_BYTES;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sVT + VT_SLOTS * VT_SLOT_BYTES);
+    unsigned char *sVraw = sVT + VT_SLOTS * VT_SLOT_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sVraw + VT_SLOTS * V_STAGE_BYTES);
     uint64_t *in_full = bars, *s_full = bars + 2, *p_full = bars + 4, *o_full = bars + 6, *buf_free = bars + 8;
-    uint64_t *qk_empty = bars + 10, *vt_free = bars + 12;       // [2], [4]
+    uint64_t *qk_empty = bars + 10;                             // [2]
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -665,12 +670,11 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
         for (int s = 0; s < 2; ++s) {
             mbar_init(&in_full[s], kProducerWarps);     // inputs of a unit staged
             mbar_init(&s_full[s], 1);                   // scores complete (commit)
-            mbar_init(&p_full[s], 4);                   // P written by the buffer's four consumer warps
+            mbar_init(&p_full[s], 4);                   // P and V^T written by the buffer's four consumer warps
             mbar_init(&o_full[s], 1);                   // O complete (commit)
             mbar_init(&buf_free[s], 4);                 // O read back: the TMEM buffer may be overwritten
             mbar_init(&qk_empty[s], 1);                 // Q / K stage read by the score MMAs (commit)
         }
-        for (int s = 0; s < VT_SLOTS; ++s) mbar_init(&vt_free[s], 1);   // V^T slot read by the P V MMAs (commit)
         fence_barrier_init();
     }
     if (warp == 0) {
@@ -688,6 +692,7 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
         // ================================================= MMA issue: QK(i), then PV(i - 1)
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
         const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
+        const uint32_t dv0 = ((smem_u32(sVT) >> 4) & 0x3FFFu) | kDescLoV;
         for (int64_t i = 0; i <= n_units; ++i) {
             if (i < n_units) {
                 const int b = (int)(i & 1);
@@ -715,50 +720,39 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
                 const int b = (int)(u & 1);
                 mbar_wait_bounded(&p_full[b], (unsigned)((u >> 1) & 1));
                 tc_fence_after();
-                const int vs = (int)(u & 3);
-                const uint32_t vt_hi = d0 + (uint32_t)((QK_STAGES * QK_STAGE_BYTES + vs * VT_SLOT_BYTES) >> 4);
-                const uint32_t vt_lo = vt_hi + (VT_BYTES >> 4);
+                const uint32_t vt_hi = dv0 + (uint32_t)((b * VT_SLOT_BYTES) >> 4), vt_lo = vt_hi + (VT_BYTES >> 4);
                 const uint32_t p_hi = tmem_u + (uint32_t)(b * BUF_COLS), p_lo = p_hi + COL_PLO;
                 const uint32_t o = tmem_u + (uint32_t)(b * BUF_COLS + COL_O);
                 if (elect_one()) {
 #pragma unroll
-                    for (int ks = 0; ks < NK / 16; ++ks) {      // 7 k-steps of 16 keys (8 TMEM columns of fp16 pairs)
-                        const uint32_t voff = (uint32_t)(((ks >> 2) * VT_TILE + (ks & 3) * 32) >> 4);
-                        umma_f16_ts(o, p_lo + 8 * ks, vt_hi + voff, kIdescO, (unsigned)(ks != 0));
-                        umma_f16_ts(o, p_hi + 8 * ks, vt_lo + voff, kIdescO, 1u);
-                        umma_f16_ts(o, p_hi + 8 * ks, vt_hi + voff, kIdescO, 1u);
+                    for (int ks = 0; ks < NK / 16; ++ks) {      // 7 k-steps of 16 keys (8 TMEM columns of fp16 pairs, 256 B of V)
+                        umma_f16_ts(o, p_lo + 8 * ks, vt_hi + 16 * ks, kIdescO, (unsigned)(ks != 0));
+                        umma_f16_ts(o, p_hi + 8 * ks, vt_lo + 16 * ks, kIdescO, 1u);
+                        umma_f16_ts(o, p_hi + 8 * ks, vt_hi + 16 * ks, kIdescO, 1u);
                     }
-                    umma_commit(&vt_free[vs]);
                     umma_commit(&o_full[b]);
                 }
                 __syncwarp();
             }
         }
     } else if (warp <= kProducerWarps) {
-        // ================================================= producers: thread = node row
+        // ================================================= producers: thread = node row; Q and K of one (b, h) per unit
+        // (V goes through the consumers: they have the slack, this role is the kernel's critical one)
         const int row = tid - 32;                               // 0..127
         const float scale = 0.25f * 1.4426950408889634f;        // 1/sqrt(16) * log2(e), folded into Q
         const uint32_t r7 = (uint32_t)(row & 7);
-        {                                                       // zero what is never written: pad rows, all of V^T
+        if (row >= N) {                                         // zero what is never written: the pad rows
             const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-            if (row >= N)
-                for (int s = 0; s < QK_STAGES; ++s)
-                    for (int img = 0; img < 4; ++img)
+            for (int s = 0; s < QK_STAGES; ++s)
+                for (int img = 0; img < 4; ++img)
 #pragma unroll
-                        for (int c = 0; c < 4; ++c)
-                            *reinterpret_cast<uint4 *>(smem + s * QK_STAGE_BYTES + img * TILE_BYTES + swz(row, c)) = z;
-            for (int off = row * 16; off < VT_SLOTS * VT_SLOT_BYTES; off += 128 * 16)
-                *reinterpret_cast<uint4 *>(sVT + off) = z;
-            asm volatile("bar.sync 2, 128;" ::: "memory");      // the four producer warps: zeros before any key write
+                    for (int c = 0; c < 4; ++c)
+                        *reinterpret_cast<uint4 *>(smem + s * QK_STAGE_BYTES + img * TILE_BYTES + swz(row, c)) = z;
         }
-        // V^T element (key j = row, dim d), fp16: k-block j >> 6, row d, 16-byte chunk ((j & 63) >> 3) ^ (d & 7), half j & 7
-        const uint32_t vt_base = (uint32_t)((row >> 6) * VT_TILE + (row & 7) * 2);
-        const uint32_t vt_chunk = (uint32_t)((row & 63) >> 3);
-        for (int64_t i = 0; i < n_units; ++i) {
-            const int st_i = (int)(i & 1), h = (int)(i & 7);
-            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
-            float4 q[4], k[4], v[4];
-            if (row < N) {                                      // loads first: they fly while we wait for the stage
+        auto load = [&](int64_t i, float4 (&q)[4], float4 (&k)[4]) {
+            if (row < N && i < n_units) {
+                const int h = (int)(i & 7);
+                const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
                 const float4 *p = reinterpret_cast<const float4 *>(qkv + (b * N + row) * (3 * E) + h * D);
                 if (h == 0 && i + H < n_units) {                // this row of the CTA's next instance -> L2 (12 lines)
                     const char *nx = reinterpret_cast<const char *>(qkv + ((b + gridDim.x) * N + row) * (3 * E));
@@ -766,22 +760,21 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
                     for (int c = 0; c < 12; ++c) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 128 * c));
                 }
 #pragma unroll
-                for (int c = 0; c < 4; ++c) { q[c] = __ldg(p + c); k[c] = __ldg(p + E / 4 + c); v[c] = __ldg(p + 2 * E / 4 + c); }
+                for (int c = 0; c < 4; ++c) { q[c] = __ldg(p + c); k[c] = __ldg(p + E / 4 + c); }
             }
-            const int vs = (int)(i & 3);
+        };
+        // hi = x rounded to TF32's 11 significant bits by integer arithmetic (add half an ulp, clear the 13 low bits - no
+        // overflow check: |x| would have to be within 2^-11 of FLT_MAX), lo = x - hi exactly, of which the tensor core
+        // reads the top 11 bits: three instructions per value where cvt.rna.tf32 with its inf / nan handling costs four
+        // and a second conversion for lo
+        auto stage = [&](int64_t i, const float4 (&q)[4], const float4 (&k)[4]) {
+            const int st_i = (int)(i & 1);
             mbar_wait_bounded(&qk_empty[st_i], (unsigned)((i >> 1) & 1) ^ 1u);  // scores of unit i - 2 are in TMEM
-            mbar_wait_bounded(&vt_free[vs], (unsigned)((i >> 2) & 1) ^ 1u);     // P V of unit i - 4 is complete
             if (row < N) {
                 unsigned char *st = smem + st_i * QK_STAGE_BYTES;
-                unsigned char *vt = sVT + vs * VT_SLOT_BYTES;
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const uint32_t off = (uint32_t)row * 128u + (((uint32_t)c ^ r7) << 4);
-                    // hi = x rounded to TF32's 11 significant bits by integer arithmetic (add half an ulp, clear the 13 low
-                    // bits - no overflow check: |x| would have to be within 2^-11 of FLT_MAX), lo = x - hi exactly, of
-                    // which the tensor core reads the top 11 bits: three instructions per value where cvt.rna.tf32 with
-                    // its inf / nan handling costs four and a second conversion for lo (the producers are this kernel's
-                    // critical role)
                     const float4 a = make_float4(q[c].x * scale, q[c].y * scale, q[c].z * scale, q[c].w * scale);
                     uint4 hi, lo;
                     hi.x = rn_tf32(a.x); hi.y = rn_tf32(a.y); hi.z = rn_tf32(a.z); hi.w = rn_tf32(a.w);
@@ -795,20 +788,22 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
                     lo.z = __float_as_uint(kk.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(kk.w - __uint_as_float(hi.w));
                     *reinterpret_cast<uint4 *>(st + 2 * TILE_BYTES + off) = hi;
                     *reinterpret_cast<uint4 *>(st + 3 * TILE_BYTES + off) = lo;
-                    const float vv[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {               // dim d = 4 c + e of key `row`, transposed
-                        const int d = 4 * c + e;
-                        const uint32_t o2 = vt_base + (uint32_t)d * 128u + ((vt_chunk ^ (uint32_t)(d & 7)) << 4);
-                        const __half vh = __float2half_rn(vv[e]);
-                        *reinterpret_cast<__half *>(vt + o2) = vh;
-                        *reinterpret_cast<__half *>(vt + VT_BYTES + o2) = __float2half_rn(vv[e] - __half2float(vh));
-                    }
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
             __syncwarp();
             if (lane == 0) mbar_arrive(&in_full[st_i]);
+        };
+        // two register sets: the loads of unit i + 1 are in flight while unit i is converted
+        float4 qa[4], ka[4], qb[4], kb[4];
+        load(0, qa, ka);
+        for (int64_t i = 0; i < n_units; i += 2) {
+            load(i + 1, qb, kb);
+            stage(i, qa, ka);
+            if (i + 1 < n_units) {
+                load(i + 2, qa, ka);
+                stage(i + 1, qb, kb);
+            }
         }
     } else {
         // ================================================= consumers: thread = query row = TMEM lane
@@ -816,10 +811,43 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
         const int buf = cw >> 2, quarter = warp & 3;
         const int row = 32 * quarter + lane;
         const uint32_t t0 = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)(buf * BUF_COLS);
+        // The group stages the V of its own unit (thread = key row; pad keys write zeros) into the slot of its TMEM buffer,
+        // as the MN-major B operand: [dim half][key][8 dims], four 16-byte stores per thread.  The slot is free once the
+        // previous unit's O was seen, and the p_full arrival below publishes it together with P.
+        unsigned char *vimg = sVT + buf * VT_SLOT_BYTES + row * 16;
+        // the raw row travels by cp.async into a staging buffer of the group (no registers held across the softmax, whose
+        // score row needs all of them): issued one unit ahead, right after P is published
+        unsigned char *vraw = sVraw + buf * V_STAGE_BYTES + row * 16;
+        auto fetch_v = [&](int64_t i) {
+            if (row < N && i < n_units) {
+                const float *p = qkv + ((blockIdx.x + (i >> 3) * gridDim.x) * N + row) * (3 * E) + 2 * E + (int)(i & 7) * D;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(vraw + c * 2048)), "l"(p + 4 * c)
+                                 : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        fetch_v(buf);
         for (int64_t i = buf; i < n_units; i += 2) {
             const int h = (int)(i & 7);
             const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
             const unsigned ph = (unsigned)((i >> 1) & 1);
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            {
+                uint32_t vh[8], vl[8];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v4 = row < N ? *reinterpret_cast<const float4 *>(vraw + c * 2048) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    split_f16x2_trunc(v4.x, v4.y, vh[2 * c], vl[2 * c]);
+                    split_f16x2_trunc(v4.z, v4.w, vh[2 * c + 1], vl[2 * c + 1]);
+                }
+                *reinterpret_cast<uint4 *>(vimg) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
+                *reinterpret_cast<uint4 *>(vimg + V_HALF) = make_uint4(vh[4], vh[5], vh[6], vh[7]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES + V_HALF) = make_uint4(vl[4], vl[5], vl[6], vl[7]);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
             mbar_wait_bounded(&s_full[buf], ph);
             tc_fence_after();
             // ONE read of the score row (112 registers); columns beyond N (K rows of zeros) -> -inf
@@ -854,6 +882,7 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[buf]);
+            fetch_v(i + 2);                                     // the group's next unit: in flight during the P V
             // O = P V arrives from the tensor core; normalise and store this row's 16 outputs
             mbar_wait_bounded(&o_full[buf], ph);
             tc_fence_after();
