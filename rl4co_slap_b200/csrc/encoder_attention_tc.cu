@@ -578,6 +578,17 @@ encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 // keys with V^T staged as fp16 hi / lo images: 128 lanes x 240 words per unit, 21 + 6 MMAs instead of 42 + 6.
 // Q K^T stays 3xTF32, so q and k keep fp32's range.  V goes through fp16: |v| must stay below 65 504 (an encoder whose
 // values get there has diverged), and entries below 2^-14 carry an absolute error of 3e-8 instead of a relative one.
+// Roles after that (ncu source-level samples, 16 384 x 100): the four producer warps were the critical role (their
+// round-to-nearest TF32 conversions with inf / nan handling, a 2-byte transposing scatter for V^T, global-load latency
+// exposed once per unit), so the producers now round by integer arithmetic, double-buffer their Q / K loads and prefetch
+// the CTA's next instance to L2, and V is staged by the consumer group that needs it - as an MN-major operand, which takes
+// four 16-byte stores per key row instead of 32 two-byte ones.  1.60 -> 1.50 ms.  Measured and dropped: four score buffers
+// with software-pipelined consumers (softmax(i + 2) before the O of unit i is read: 1.79 ms with 13 warps - 128 registers,
+// the spilled loop state reloads behind the cp.async requests in flight - and 1.70 ms with two producer warps of two rows
+// each, where the producers bound it again); no producer role at all, every worker group staging its own operands (1.9-
+// 2.1 ms: eight warps are two per scheduler, too few to cover their own latencies); 96 of the 112 score columns resident
+// and 16 re-read (1.55 ms).  What limits it is warps per scheduler x registers: the one-pass softmax wants the 112-register
+// row, which caps the CTA at 13 warps.
 namespace enctc3 {
 using namespace tcu;
 using enctc::ex2f;
