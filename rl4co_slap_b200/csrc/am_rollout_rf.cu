@@ -437,7 +437,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                     // first-node half is constant for the rest of the trajectory
                     if (a.w_first) {    // table 4 left out: its one row is formed here (rollout_util.cuh), passed through
                         float *o16 = so + 16 * warp;    // the warp's slice of the glimpse buffer, free between two steps
-                        first_context_row(a.h + (b * (int64_t)N + act) * E, a.w_first, o16, nullptr, dim0, g);
+                        first_context_row(a.h + (b * (int64_t)N + act) * E, a.w_first, o16, nullptr, false, dim0, g);
                         const float4 e0 = *reinterpret_cast<const float4 *>(o16 + 8 * hh);
                         const float4 e1 = *reinterpret_cast<const float4 *>(o16 + 8 * hh + 4);
                         const float x[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};

@@ -487,6 +487,9 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     constexpr int t_first = MS ? 1 : 0;             // multistart: step 0 is the forced POMO start node
     // table 4 left out (a.w_first): the first node's embedding row is needed the moment step 0 ends, so the instance's
     // block of h goes to L2 one instance ahead like the tables do (51 KB of reads for the 51 KB K3 no longer writes)
+    // ... and half of its weight block waits in the warp's compaction scratch (4 KB, dims 4..7 of every thread), which
+    // nothing else uses before the first compaction
+    float *fc_scr = reinterpret_cast<float *>(smem + OFF_SCR) + warp * (kScrSlots * 16);
     auto prefetch_h = [&](int64_t b) {
         const char *src = reinterpret_cast<const char *>(a.h + b * (int64_t)N * E);
         for (size_t off = 0; off < c_bytes; off += 32768)
@@ -558,8 +561,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             if (a.w_first) {        // the warp's slice of the glimpse buffer is free between two steps, its compaction
                                     // scratch before the first compaction
                 float *o16 = reinterpret_cast<float *>(smem + OFF_O) + 16 * warp;
-                first_context_row(a.h + (b * (int64_t)N + node) * E, a.w_first, o16,
-                                  reinterpret_cast<float *>(smem + OFF_SCR) + warp * (kScrSlots * 16), dim0, g);
+                first_context_row(a.h + (b * (int64_t)N + node) * E, a.w_first, o16, fc_scr, true, dim0, g);
                 const float4 e0 = *reinterpret_cast<const float4 *>(o16 + 8 * hh);
                 const float4 e1 = *reinterpret_cast<const float4 *>(o16 + 8 * hh + 4);
                 const float x[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
@@ -580,6 +582,9 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) node_w[4 * lane + k] = 4 * lane + k;
         }
+        // table 4 left out: half of its weight block starts towards the warp's compaction scratch now (free until the first
+        // compaction) and lands during step 0
+        if (a.w_first) first_context_prefetch(a.w_first, fc_scr, dim0, g);
         if (SAMPLING) {                             // Gumbel noise of steps 0..15 (warp w: steps w and w + 8)
             c.seed = a.seed; c.offset = a.offset; c.r = (uint64_t)r;
             gen_noise(c, warp, smem);

@@ -112,21 +112,28 @@ __device__ __forceinline__ float slap_order_len(const float2 *locs, const int *a
 // one batch (the compiler then splits them into two dependent round trips to L2, ~2.8 k clk per rollout measured), so
 // with `scratch` (4 KB of shared memory private to the warp, free at this point) the weight rows of dims 4..7 travel by
 // cp.async instead and everything is in flight at once.  scratch == nullptr: registers only.
+// The weight rows do not depend on the first node, only the h row does: a caller whose scratch is free from the start of
+// the rollout issues first_context_prefetch() there (no registers, the 32 KB land during step 0) and passes
+// prefetched = true, which leaves one L2 round trip for the other half of the rows and the h row at the end of step 0
+// (measured: step 0 of a TSP100 rollout 4.6 k -> 3.7 k clk; 2.3 k with table 4.  Prefetching the other half as well, into
+// unused rows of the kept logits, gained nothing more: what remains is the h row's latency and the mat-vec itself.)
+__device__ __forceinline__ void first_context_prefetch(const float *w_first, float *scratch, int dim0, int g) {
+    const float *wr0 = w_first + (size_t)dim0 * 128 + 4 * g;
+    const uint32_t sdst = smem_u32(scratch) + (threadIdx.x & 31) * 16;
+#pragma unroll
+    for (int i = 4; i < 8; ++i)
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + ((i - 4) * 2 + half) * 512),
+                         "l"(wr0 + (size_t)i * 128 + 64 * half) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
 template <int kUnused = 0>   // a template only so that the header may define a non-inline function
 __device__ __noinline__ void first_context_row(const float *hrow, const float *w_first, float *out16, float *scratch,
-                                               int dim0, int g) {
+                                               bool prefetched, int dim0, int g) {
     const int lane = threadIdx.x & 31;
     const float *wr0 = w_first + (size_t)dim0 * 128 + 4 * g;
-    const uint32_t sdst = scratch ? smem_u32(scratch) + lane * 16 : 0u;
-    if (scratch) {
-#pragma unroll
-        for (int i = 4; i < 8; ++i)
-#pragma unroll
-            for (int half = 0; half < 2; ++half)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst + ((i - 4) * 2 + half) * 512),
-                             "l"(wr0 + (size_t)i * 128 + 64 * half) : "memory");
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
+    if (scratch && !prefetched) first_context_prefetch(w_first, scratch, dim0, g);
     const float4 h0 = __ldg(reinterpret_cast<const float4 *>(hrow + 4 * g));
     const float4 h1 = __ldg(reinterpret_cast<const float4 *>(hrow + 64 + 4 * g));
     float s[8];

@@ -191,7 +191,7 @@ class AttentionModelPolicy(nn.Module):
         self.unused_kwargs = unused_kwargs
         self.last_launches = 0  # rl4co_* kernel launches of the most recent forward()
         # tsp single start: project 4 tables and let the rollout kernel form table 4's one row ("auto": from 48 nodes on -
-        # the row costs the kernel ~1.6 k clk per rollout, the table costs the projection ~36 clk x SMs per node; "always",
+        # the row costs the kernel ~1.4 k clk per rollout, the table costs the projection ~36 clk x SMs per node; "always",
         # "never")
         self.first_context_in_kernel = "auto"
         self.profile = None     # set to a list to collect (rollouts, [ev0, ev1, ev2]) per chunk

@@ -3,6 +3,7 @@
     python tools/profile_side.py c5      SLAP greedy rollout, B = 16 384            (kernel: am_rollout_slap)
     python tools/profile_side.py k3 [nt] K3 projection, 1 638 400 rows x nt tables  (kernel: am_project_tc)
     python tools/profile_side.py c4      CVRP100 POMO multistart sampling, B = 64   (kernel: the multistart rollout)
+    python tools/profile_side.py attention  encoder self-attention, 16 384 x 100 nodes (kernel: encoder_attention_tc3)
 """
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -48,5 +49,12 @@ with torch.inference_mode():
         h = pol.encoder(td)[0]
         for _ in range(reps):
             pol(td, env, decode_type="multistart_sampling", num_starts=100, hidden=h)
+    elif which == "attention":
+        from rl4co_slap_b200 import _lib
+        B, N = 16384, 100
+        qkv = torch.randn(B, N, 384, device=dev)
+        out = torch.empty(B, N, 128, device=dev)
+        for _ in range(3):
+            _lib.call("rl4co_encoder_attention_tc", B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev))
     torch.cuda.synchronize()
 print("done", which)
