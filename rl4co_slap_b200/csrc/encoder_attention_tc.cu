@@ -582,7 +582,9 @@ encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 // round-to-nearest TF32 conversions with inf / nan handling, a 2-byte transposing scatter for V^T, global-load latency
 // exposed once per unit), so the producers now round by integer arithmetic, double-buffer their Q / K loads and prefetch
 // the CTA's next instance to L2, and V is staged by the consumer group that needs it - as an MN-major operand, which takes
-// four 16-byte stores per key row instead of 32 two-byte ones.  1.60 -> 1.50 ms.  Measured and dropped: four score buffers
+// four 16-byte stores per key row instead of 32 two-byte ones.  1.60 -> 1.50 ms, and 1.56 ms with the range scale of V
+// (its exchange among the group's warps: 1.69 ms with a named barrier before the softmax, 1.56 ms posted early and read
+// after the softmax).  Measured and dropped: four score buffers
 // with software-pipelined consumers (softmax(i + 2) before the O of unit i is read: 1.79 ms with 13 warps - 128 registers,
 // the spilled loop state reloads behind the cp.async requests in flight - and 1.70 ms with two producer warps of two rows
 // each, where the producers bound it again); no producer role at all, every worker group staging its own operands (1.9-
@@ -670,8 +672,9 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
     unsigned char *sVraw = sVT + VT_SLOTS * VT_SLOT_BYTES;
     uint64_t *bars = reinterpret_cast<uint64_t *>(sVraw + VT_SLOTS * V_STAGE_BYTES);
     uint64_t *in_full = bars, *s_full = bars + 2, *p_full = bars + 4, *o_full = bars + 6, *buf_free = bars + 8;
-    uint64_t *qk_empty = bars + 10;                             // [2]
+    uint64_t *qk_empty = bars + 10, *v_rng = bars + 12;         // [2] each
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+    uint32_t *s_amax = tmem_slot + 4;                           // [group][unit parity][warp of the group]: V range exchange
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int64_t n_inst = blockIdx.x < B ? (B - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
@@ -685,6 +688,7 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
             mbar_init(&o_full[s], 1);                   // O complete (commit)
             mbar_init(&buf_free[s], 4);                 // O read back: the TMEM buffer may be overwritten
             mbar_init(&qk_empty[s], 1);                 // Q / K stage read by the score MMAs (commit)
+            mbar_init(&v_rng[s], 4);                    // the group's four warps have posted the range of their V rows
         }
         fence_barrier_init();
     }
@@ -845,20 +849,27 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
             const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
             const unsigned ph = (unsigned)((i >> 1) & 1);
             asm volatile("cp.async.wait_group 0;" ::: "memory");
+            // The V tile of the unit is scaled by a power of two so that its largest entry lands in 2^13..2^14 (as the
+            // projection kernel scales its tiles): fp16's range then holds hi AND the residual lo of every entry within 2^-11
+            // of the largest, whatever the magnitude of the values (without it, values below 2^-3 lose bits of lo and an
+            // encoder whose values are all tiny loses them all - found by tools/soak_round2.py).  The group's 128 rows agree
+            // on the scale through shared memory: every warp posts the range of its rows here and the tile is staged after
+            // the softmax, when the four posts have long been made - a barrier at this point costs 0.2 ms per launch.
+            uint32_t *xch = s_amax + (buf * 2 + (int)ph) * 4;
             {
-                uint32_t vh[8], vl[8];
+                float amax = 0.f;
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const float4 v4 = row < N ? *reinterpret_cast<const float4 *>(vraw + c * 2048) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    split_f16x2_trunc(v4.x, v4.y, vh[2 * c], vl[2 * c]);
-                    split_f16x2_trunc(v4.z, v4.w, vh[2 * c + 1], vl[2 * c + 1]);
+                    amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v4.x), fabsf(v4.y))), fmaxf(fabsf(v4.z), fabsf(v4.w)));
                 }
-                *reinterpret_cast<uint4 *>(vimg) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
-                *reinterpret_cast<uint4 *>(vimg + V_HALF) = make_uint4(vh[4], vh[5], vh[6], vh[7]);
-                *reinterpret_cast<uint4 *>(vimg + VT_BYTES) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
-                *reinterpret_cast<uint4 *>(vimg + VT_BYTES + V_HALF) = make_uint4(vl[4], vl[5], vl[6], vl[7]);
+                uint32_t ab = __float_as_uint(amax);
+                asm("redux.sync.max.u32 %0, %1, 0xffffffff;" : "=r"(ab) : "r"(ab));
+                if (lane == 0) {
+                    xch[quarter] = ab;
+                    mbar_arrive(&v_rng[buf]);
+                }
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
             mbar_wait_bounded(&s_full[buf], ph);
             tc_fence_after();
             // ONE read of the score row (112 registers); columns beyond N (K rows of zeros) -> -inf
@@ -889,6 +900,28 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
                 tmem_st8(t0 + 8 * c, hi);
                 tmem_st8(t0 + COL_PLO + 8 * c, lo);
             }
+            float unscale;
+            {                                                   // V as the MN-major fp16 operand, scaled (see above)
+                mbar_wait_bounded(&v_rng[buf], ph);
+                const uint4 all = *reinterpret_cast<const uint4 *>(xch);
+                const uint32_t ab = max(max(all.x, all.y), max(all.z, all.w));
+                int e = (int)(ab >> 23);                        // biased exponent of the largest |v| (nan / inf: 255, they propagate)
+                e = e < 27 ? 27 : e;                            // all-zero or denormal tiles: any scale will do
+                const float vscale = __uint_as_float((uint32_t)(267 - e) << 23);    // 2^(13 - (e - 127))
+                unscale = __uint_as_float((uint32_t)(e - 13) << 23);                // 2^((e - 127) - 13)
+                uint32_t vh[8], vl[8];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v4 = row < N ? *reinterpret_cast<const float4 *>(vraw + c * 2048) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    split_f16x2_trunc(v4.x * vscale, v4.y * vscale, vh[2 * c], vl[2 * c]);
+                    split_f16x2_trunc(v4.z * vscale, v4.w * vscale, vh[2 * c + 1], vl[2 * c + 1]);
+                }
+                *reinterpret_cast<uint4 *>(vimg) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
+                *reinterpret_cast<uint4 *>(vimg + V_HALF) = make_uint4(vh[4], vh[5], vh[6], vh[7]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES + V_HALF) = make_uint4(vl[4], vl[5], vl[6], vl[7]);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic writes -> async proxy (UMMA)
+            }
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             tc_fence_before();
             __syncwarp();
@@ -903,7 +936,7 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
             __syncwarp();
             if (lane == 0) mbar_arrive(&buf_free[buf]);
             if (row < N) {
-                const float inv = 1.f / l;
+                const float inv = unscale / l;
                 float4 *dst = reinterpret_cast<float4 *>(out + (b * N + row) * E + h * D);
 #pragma unroll
                 for (int c = 0; c < 4; ++c)

@@ -14,6 +14,11 @@
          its instance with that first action (rewards, per-step log-probs).
   consistency - all seven environments at random sizes: sampled and greedy rollouts pass the environment's validity check, the
          fused replay reproduces their reward and the evaluate path their log-likelihood.
+  attention - rl4co_encoder_attention_tc (default kernel: both GEMMs on tcgen05, P V as 3 x fp16) against fp64 softmax attention:
+         random batch / node counts (1..112 on that kernel, above it the scores-only kernel), input magnitudes 1e-3..8, rows of
+         zeros, one dominant key.
+  firstctx - tsp with four tables (the kernels form the first node's context row themselves) against five tables: random sizes,
+         greedy tours equal or split at a log-prob gap < 1e-4, evaluate log-likelihoods to 1e-5, on all three kernels.
 Prints one line per case that exceeds its bound and a summary; exit code 1 if any did."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -23,7 +28,7 @@ from rl4co_slap_b200 import _lib
 
 dev = torch.device("cuda:0")
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
-only = set(sys.argv[2:])                # optional part names: k3 slap linear multistart backward starts consistency
+only = set(sys.argv[2:])                # optional part names: k3 slap linear multistart backward starts consistency attention firstctx
 bad = 0
 g = torch.Generator(device="cpu").manual_seed(20261105)
 rnd = lambda lo, hi: int(torch.randint(lo, hi + 1, (1,), generator=g))
@@ -309,4 +314,76 @@ with torch.inference_mode():
             bad += 1
         n += 1
 print(f"consistency: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- encoder attention vs fp64
+t0, n, bad_prev = time.time(), 0, bad
+while (not only or "attention" in only) and time.time() - t0 < budget:
+    B, N = rnd(1, 600), rnd(1, 128)
+    amp = 10.0 ** (rnd(-30, 9) / 10.0)
+    qkv = torch.randn(B, N, 384, device=dev) * amp
+    kind = rnd(0, 3)
+    if kind == 1:
+        qkv[rnd(0, B - 1), rnd(0, N - 1)] = 0                   # a node whose q, k, v are all zero
+    if kind == 2:
+        qkv[:, rnd(0, N - 1), 128:256] *= 4.0                   # one key dominates every row
+    if kind == 3:
+        qkv[..., 256:] *= 10.0 ** (rnd(-30, 20) / 10.0)         # values at another scale than queries / keys
+    q, k, v = qkv.double().view(B, N, 3, 8, 16).permute(2, 0, 3, 1, 4).unbind(0)
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.25, -1) @ v).transpose(1, 2).reshape(B, N, 128)
+    out = torch.full((B, N, 128), float("nan"), device=dev)
+    _lib.call("rl4co_encoder_attention_tc", B, N, _lib.ptr(qkv), _lib.ptr(out), st)
+    # scores carry an absolute error of ~1e-6 |q||k| (3xTF32), i.e. a relative one on the weights: 1e-5 max(1, amp^2) of the
+    # largest value a row can mix, plus the fp16 floor of the values (2^-25 of their magnitude class)
+    vmax = float(v.abs().max())
+    bound = 1e-5 * max(1.0, float(q.abs().max()) * float(k.abs().max()) / 16) * vmax + 1e-7 * vmax + 1e-30
+    err = float((out.double() - ref).abs().max())
+    if not (err <= bound) or not bool(torch.isfinite(out).all()):
+        bad += 1
+        print(f"ATTENTION FAIL B={B} N={N} amp={amp:.3g} kind={kind}: err {err:.3e} bound {bound:.3e}", flush=True)
+    n += 1
+print(f"attention: {n} random cases, {bad - bad_prev} failures", flush=True)
+
+# ---------------------------------------------------------------- tsp: four tables + in-kernel first-node row vs five tables
+t0, n, bad_prev = time.time(), 0, bad
+with torch.inference_mode():
+    while (not only or "firstctx" in only) and time.time() - t0 < budget:
+        num_loc, B = rnd(2, 120), rnd(1, 400)
+        env = R.get_env("tsp", device=dev, generator_params=dict(num_loc=num_loc))
+        pol = R.AttentionModelPolicy(env_name="tsp", num_encoder_layers=1).to(dev).eval()
+        td = env.reset(env.generator(B).to(dev))
+        h = (pol.encoder(td)[0].float() * 10.0 ** (rnd(-10, 5) / 10.0)).contiguous()
+        impl = rnd(0, 2)
+        _lib.call("rl4co_set_rollout_impl", impl)
+        try:
+            res = {}
+            for mode in ("never", "always"):
+                pol.first_context_in_kernel = mode
+                res[mode] = pol(td, env, decode_type="greedy", hidden=h, return_actions=True, return_sum_log_likelihood=False)
+            a5, a4 = res["never"]["actions"], res["always"]["actions"]
+            ok = True
+            diff = (a5 != a4).any(1).nonzero().flatten()
+            if diff.numel():
+                # at the first differing step both paths saw the same state: the two chosen nodes must be a near tie
+                ev5 = pol(td[diff], env, actions=a5[diff], hidden=h[diff], return_sum_log_likelihood=False)["log_likelihood"]
+                ev4 = pol(td[diff], env, actions=a4[diff], hidden=h[diff], return_sum_log_likelihood=False)["log_likelihood"]
+                first = (a5[diff] != a4[diff]).float().argmax(1, keepdim=True)
+                gap = (ev5.gather(1, first) - ev4.gather(1, first)).abs().max()
+                ok &= bool(gap < 1e-4)
+            same = ~(a5 != a4).any(1)
+            ll5, ll4 = res["never"]["log_likelihood"].sum(1), res["always"]["log_likelihood"].sum(1)
+            ok &= bool(torch.allclose(ll4[same], ll5[same], rtol=1e-5, atol=2e-5))
+            ok &= bool(torch.equal(a4.sort(1).values, torch.arange(num_loc, device=dev).expand(B, num_loc)))
+            acts = torch.rand(B, num_loc, device=dev).argsort(1)
+            for mode in ("never", "always"):
+                pol.first_context_in_kernel = mode
+                res[mode] = pol(td, env, actions=acts, hidden=h)["log_likelihood"]
+            ok &= bool(torch.allclose(res["always"], res["never"], rtol=1e-5, atol=2e-5))
+        finally:
+            _lib.call("rl4co_set_rollout_impl", 0)
+        if not ok:
+            bad += 1
+            print(f"FIRSTCTX FAIL tsp{num_loc} B={B} impl={impl}: {int(diff.numel())} tours differ, "
+                  f"evaluate diff {float((res['always'] - res['never']).abs().max()):.2e}", flush=True)
+        n += 1
+print(f"first-node context: {n} random cases, {bad - bad_prev} failures", flush=True)
 sys.exit(1 if bad else 0)
