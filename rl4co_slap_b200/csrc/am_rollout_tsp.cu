@@ -485,20 +485,12 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
     const int S = MS ? (a.S > 1 ? a.S : 1) : 1;
     const int64_t W = MS ? a.B * (int64_t)S : a.B;
     constexpr int t_first = MS ? 1 : 0;             // multistart: step 0 is the forced POMO start node
-    // table 4 left out (a.w_first): the first node's embedding row is needed the moment step 0 ends, so the instance's
-    // block of h goes to L2 one instance ahead like the tables do (51 KB of reads for the 51 KB K3 no longer writes)
-    // ... and half of its weight block waits in the warp's compaction scratch (4 KB, dims 4..7 of every thread), which
-    // nothing else uses before the first compaction
+    // table 4 left out (a.w_first): half of its weight block waits in the warp's compaction scratch (4 KB, dims 4..7 of every
+    // thread), which nothing else uses before the first compaction.  (Sending the instance's block of h to L2 one instance
+    // ahead, so that the first node's row is an L2 hit at the end of step 0, was measured to change nothing - step 0 takes
+    // 3.7 k clk either way - and cost 51 KB of DRAM reads per rollout; not done.)
     float *fc_scr = reinterpret_cast<float *>(smem + OFF_SCR) + warp * (kScrSlots * 16);
-    auto prefetch_h = [&](int64_t b) {
-        const char *src = reinterpret_cast<const char *>(a.h + b * (int64_t)N * E);
-        for (size_t off = 0; off < c_bytes; off += 32768)
-            prefetch_l2(src + off, (unsigned)(c_bytes - off < 32768 ? c_bytes - off : 32768));
-    };
-    if (tid == 0 && (int64_t)blockIdx.x < W) {
-        stage_context(MS ? blockIdx.x / S : blockIdx.x, 0);
-        if (a.w_first) prefetch_h(MS ? blockIdx.x / S : blockIdx.x);
-    }
+    if (tid == 0 && (int64_t)blockIdx.x < W) stage_context(MS ? blockIdx.x / S : blockIdx.x, 0);
 
     int it = 0;
     for (int64_t w = blockIdx.x; w < W; w += gridDim.x, ++it) {
@@ -599,7 +591,6 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                 for (size_t off = 0; off < c_bytes; off += 32768)
                     prefetch_l2(src + off, (unsigned)(c_bytes - off < 32768 ? c_bytes - off : 32768));
             }
-            if (a.w_first) prefetch_h(nb);
         }
         __syncthreads();
 

@@ -15,9 +15,12 @@ TRACE_LIB = os.path.join(ROOT, "tools", "_trace", "librl4co_trace.so")
 ABL = os.environ.get("RF_ABL", "0")          # timing-only ablation bits (csrc/am_rollout_rf.cu)
 if ABL != "0":
     TRACE_LIB = os.path.join(ROOT, "tools", "_trace", f"abl{ABL}", "librl4co_trace.so")
+if os.environ.get("RF_VARIANT"):            # a side build with RF_EXTRA_FLAGS, e.g. RF_VARIANT=nopf RF_EXTRA_FLAGS=-DRL4CO_NO_H_PREFETCH
+    TRACE_LIB = os.path.join(ROOT, "tools", "_trace", os.environ["RF_VARIANT"], "librl4co_trace.so")
 if len(sys.argv) > 1 and sys.argv[1] == "build":
     from rl4co_slap_b200 import build
-    print(build.build(extra_flags=["-DRF_TRACE", f"-DRF_ABL={ABL}"], lib=TRACE_LIB, obj_dir=os.path.dirname(TRACE_LIB)))
+    extra = os.environ.get("RF_EXTRA_FLAGS", "").split()
+    print(build.build(extra_flags=["-DRF_TRACE", f"-DRF_ABL={ABL}"] + extra, lib=TRACE_LIB, obj_dir=os.path.dirname(TRACE_LIB)))
     sys.exit(0)
 
 import numpy as np, torch
