@@ -149,9 +149,9 @@ __device__ __forceinline__ void gen_noise(const Ctx &c, int step, unsigned char 
 // ---------------------------------------------------------------------------------------------
 // decode steps t .. t_stop-1 with MM rows of 16 slots
 // ---------------------------------------------------------------------------------------------
-template <int MM, bool SAMPLING, typename SetQ>
+template <int MM, bool SAMPLING>
 __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const u64 (&V2)[MM][4], const u64 (&L2)[MM][4],
-                                          const int t_stop, unsigned char *smem, SetQ &&set_first) {
+                                          const int t_stop, unsigned char *smem) {
     float *spl = reinterpret_cast<float *>(smem + OFF_PL);
     float *so = reinterpret_cast<float *>(smem + OFF_O);
     float *s_mw = reinterpret_cast<float *>(smem + OFF_MW);
@@ -365,8 +365,7 @@ __device__ __forceinline__ void run_stage(Ctx &c, const u64 (&K2)[MM][4], const 
             if (bit && !(c.alive & bit)) c.status |= RL4CO_ST_INFEASIBLE_ACTION;
             c.alive &= ~bit;
         }
-        if (c.t == 0) set_first(node);              // ctx = Wc [h_first ; h_cur] from step 1 on (context.py:123-131)
-        c.cur = node;
+        c.cur = node;                               // (step 0: the caller sets the first node's context half, below)
         TG_TRACE_AT(7);
         ++c.t;
         c.x_addr += 128 * 4;
@@ -636,9 +635,20 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
         };
         // ================================================== decode, in stages of fewer and fewer rows
         // after t steps N - t nodes are unvisited: 4 rows hold them from t = N - 64 on, 2 rows from t = N - 32
+        // ctx = Wc [h_first ; h_cur] from step 1 on (context.py:123-131): the stage that holds step 0 is entered twice, for
+        // step 0 and for the rest, and the first node's half is set in between - OUTSIDE the step loop.  With table 4 left
+        // out that is a call and 18 loads; inside the loop body they changed its register allocation and cost every step
+        // (K2 509 -> 533 ms per 2^20 rollouts even when the branch was never taken).
+        auto with_first = [&](auto &&run, int stop) {
+#pragma unroll 1
+            for (int pass = (c.t == 0 && stop > 0) ? 0 : 1; pass < 2; ++pass) {
+                run(pass == 0 ? 1 : stop);
+                if (pass == 0) set_first(c.cur);
+            }
+        };
         if (M0 > 4) {
             const int stop = N - 64 < t_end ? N - 64 : t_end;
-            run_stage<M0, SAMPLING>(c, K2, V2, L2, stop, smem, set_first);
+            with_first([&](int t_stop) { run_stage<M0, SAMPLING>(c, K2, V2, L2, t_stop, smem); }, stop);
         }
         if (M0 > 4 ? c.t < t_end : true) {
             u64 K4[4][4], V4[4][4], L4[4][4];
@@ -653,7 +663,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
             if (M0 >= 4) {
                 const int stop = N - 32 < t_end ? N - 32 : t_end;
                 if (RL4CO_TSPG_FUSED_ROWS >= 4) fill_rows(c.t);
-                run_stage<4, SAMPLING>(c, K4, V4, L4, stop, smem, set_first);
+                with_first([&](int t_stop) { run_stage<4, SAMPLING>(c, K4, V4, L4, t_stop, smem); }, stop);
             }
             if (c.t < t_end) {
                 u64 Ka[2][4], Va[2][4], La[2][4];
@@ -666,7 +676,7 @@ am_rollout_tsp_greedy_kernel(const rl4co_am_rollout_args a) {
                         for (int i = 0; i < 4; ++i) { Ka[j][i] = K2[j < M0 ? j : 0][i]; Va[j][i] = V2[j < M0 ? j : 0][i]; La[j][i] = L2[j < M0 ? j : 0][i]; }
                 }
                 if (RL4CO_TSPG_FUSED_ROWS < 4 || M0 < 4) fill_rows(c.t);
-                run_stage<2, SAMPLING>(c, Ka, Va, La, t_end, smem, set_first);
+                with_first([&](int t_stop) { run_stage<2, SAMPLING>(c, Ka, Va, La, t_stop, smem); }, t_end);
             }
         }
 
