@@ -348,8 +348,10 @@ typedef struct rl4co_am_rollout_args {
     const int32_t *start_nodes;
     /* tsp without table 4 (appended, ABI 4): h [B,N,E] = the node embeddings the tables were projected from and
      * w_first [E][E] = rows 4E..5E of the folded table weights (project_context.weight[:, :E], context.py:123-131; row =
-     * output dim).  Both or neither; with them n_tables may be 4.  The multistart tensor-core kernel reads table 4 for
-     * every start, so multistart callers keep passing five tables. */
+     * output dim).  Both or neither; with them n_tables may be 4.  Taken by the compaction kernel (greedy / sampling, N <= 112,
+     * standard logit post-processing), which is where it pays, and by the shared-memory kernel; the register-file kernel
+     * is skipped for such calls.  The multistart tensor-core kernel reads table 4 for every start, so multistart callers
+     * keep passing five tables. */
     const float *h;
     const float *w_first;
 } rl4co_am_rollout_args;

@@ -256,7 +256,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
         load_tables();
         // constant part of the query, pre-scaled: qbs = scale * (gctx [+ step-0 placeholder])
         u64 qbs2[4];
-        auto set_qb_vals = [&](const float (&x)[8]) {
+        auto set_qb = [&](const float *extra) {      // extra: 8 floats at this thread's dims, or null
             float v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = 0.f;
@@ -265,19 +265,13 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 const float4 g1 = __ldg(reinterpret_cast<const float4 *>(a.gctx + b * E + dim0) + 1);
                 v[0] = g0.x; v[1] = g0.y; v[2] = g0.z; v[3] = g0.w; v[4] = g1.x; v[5] = g1.y; v[6] = g1.z; v[7] = g1.w;
             }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] += x[i];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) qbs2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
-        };
-        auto set_qb = [&](const float *extra) {      // extra: 8 floats at this thread's dims, or null
-            float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (extra) {
                 const float4 e0 = __ldg(reinterpret_cast<const float4 *>(extra));
                 const float4 e1 = __ldg(reinterpret_cast<const float4 *>(extra) + 1);
-                x[0] = e0.x; x[1] = e0.y; x[2] = e0.z; x[3] = e0.w; x[4] = e1.x; x[5] = e1.y; x[6] = e1.z; x[7] = e1.w;
+                v[0] += e0.x; v[1] += e0.y; v[2] += e0.z; v[3] += e0.w; v[4] += e1.x; v[5] += e1.y; v[6] += e1.z; v[7] += e1.w;
             }
-            set_qb_vals(x);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) qbs2[i] = pack2(v[2 * i] * kScoreScale, v[2 * i + 1] * kScoreScale);
         };
         // ------------------------------------------------ small per-instance state -> smem
         __syncthreads();                            // previous instance's epilogue is done with smem
@@ -435,17 +429,7 @@ am_rollout_rf_kernel(const rl4co_am_rollout_args a, const int n_parts) {
                 if (t == 0) {
                     // from step 1 on: ctx = Wc [h_first ; h_cur] (context.py:123-131); the
                     // first-node half is constant for the rest of the trajectory
-                    if (a.w_first) {    // table 4 left out: its one row is formed here (rollout_util.cuh), passed through
-                        float *o16 = so + 16 * warp;    // the warp's slice of the glimpse buffer, free between two steps
-                        first_context_row(a.h + (b * (int64_t)N + act) * E, a.w_first, o16, nullptr, false, dim0, g);
-                        const float4 e0 = *reinterpret_cast<const float4 *>(o16 + 8 * hh);
-                        const float4 e1 = *reinterpret_cast<const float4 *>(o16 + 8 * hh + 4);
-                        const float x[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
-                        set_qb_vals(x);
-                        __syncwarp();
-                    } else {
-                        set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + act) * E + dim0);
-                    }
+                    set_qb(a.tables + ((size_t)4 * Mrows + b * (int64_t)N + act) * E + dim0);
                     use_c = true;
                 }
             } else if (ENV == RL4CO_ENV_CVRP) {         // cvrp/env.py:73-105,137-149
@@ -956,6 +940,7 @@ bool rollout_rf_supports(const rl4co_am_rollout_args &a) {
     if (a.logp_all != nullptr) return false;
 #endif
     if (a.N > 128) return false;
+    if (a.w_first != nullptr) return false;     // tsp without table 4: the compaction kernel or the shared-memory kernel
     if (a.multistart && a.env == RL4CO_ENV_SLAP) return false;
     return rf::make_layout(a.N, a.T, a.env != RL4CO_ENV_SLAP, a.env == RL4CO_ENV_SDVRP).total <= (size_t)227 * 1024;
 }

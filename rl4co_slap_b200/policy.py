@@ -313,7 +313,11 @@ class AttentionModelPolicy(nn.Module):
         # out and the rollout kernel forms the row from h and the table's weight block at step 1 (include/: args h / w_first)
         w_first = None
         fck = self.first_context_in_kernel
-        if name == "tsp" and S == 0 and not return_hidden and (fck == "always" or (fck == "auto" and N >= 48)):
+        # "auto": where the compaction kernel (am_rollout_tsp.cu) will run - the register-file kernel does not take h / w_first
+        # and the shared-memory kernel is the slow fallback
+        auto = (fck == "auto" and 48 <= N <= 112 and mode != _lib.MODE_EVALUATE and not store_all_logp
+                and tanh_clipping > 0 and temperature == 1.0 and mask_logits)
+        if name == "tsp" and S == 0 and not return_hidden and (fck == "always" or auto):
             w_first = W[4 * 128:5 * 128]
             n_tables = 4
         prof = self.profile  # optional CUDA-event timing of the K3 / K2 launches (bench.py)

@@ -1,8 +1,9 @@
 """tsp without table 4: the rollout kernels form the first node's context row themselves (args h / w_first, ABI 4).
 
 The row is project_context.weight[:, :E] . h_first (nn/env_embeddings/context.py:123-131); K3 used to write it for every
-node although a trajectory reads one.  Checked on all three single-start kernels (compaction / register file / shared
-memory), in all three decode modes, against the five-table path of the same kernels and against the oracle in fp64.
+node although a trajectory reads one.  Checked under all three kernel selections (the compaction kernel and the shared-memory
+kernel form the row; with the compaction kernel switched off the call skips the register-file kernel, which does not take
+h / w_first), in all three decode modes, against the five-table path and against the oracle in fp64.
 Tolerances: the suite's 1e-5 relative on the log-likelihood (+2e-5 absolute, the fp32 noise floor of a 100-step sum);
 tours of the two paths may split only at verified near ties of the oracle's log-probs.
 """
