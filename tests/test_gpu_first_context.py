@@ -78,9 +78,11 @@ def test_greedy_tours_split_only_at_near_ties(impl):
     torch.testing.assert_close(four["log_likelihood"][same], five["log_likelihood"][same], rtol=RTOL, atol=2e-5)
 
 
-@pytest.mark.parametrize("impl", ["auto", "rf"])
+@pytest.mark.parametrize("impl", ["auto", "smem"])
 def test_sampling_same_noise_same_tours(impl):
-    """Same Philox seed -> same Gumbel noise: the two paths draw the same tours except at near ties of logit + noise."""
+    """Same Philox seed -> same noise: the two paths draw the same tours except at near ties.  (Not with the "rf" selection:
+    there the five-table call samples on the register-file kernel and the four-table call on the shared-memory kernel, which
+    draw differently.)"""
     dev = torch.device("cuda:0")
     B, N = 1024, 50
     pol, env, td, h = _setup(B, N, dev, seed=11)

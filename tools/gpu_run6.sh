@@ -17,3 +17,6 @@ python tools/trace_slap.py build > /dev/null 2>&1; timeout 300 python tools/trac
 python tools/trace_rollout.py build > /dev/null 2>&1; timeout 300 python tools/trace_rollout.py > gpurun_out/r02_tsp_trace_5tables.txt 2>&1; RF_FC=1 timeout 300 python tools/trace_rollout.py > gpurun_out/r02_tsp_trace_4tables.txt 2>&1; echo "tsp trace rc=$?"
 timeout 300 python tools/check_attention_tc.py > gpurun_out/r02_attention_check.txt 2>&1; echo "attention check rc=$?"
 ls -la gpurun_out | tail -20
+# same-box reference: the tree before the four-table path and enctc3 (commit 565e2ee unpacked and built under tools/_exp/old_tree by
+#   git archive 565e2ee | tar -x -C tools/_exp/old_tree; (cd tools/_exp/old_tree; python -m rl4co_slap_b200.build) ), if present
+if [ -d tools/_exp/old_tree ]; then (cd tools/_exp/old_tree && timeout 900 python bench.py --no-side --no-parity > /root/repo/gpurun_out/r02_bench6_prev_tree.log 2>/dev/null; echo "prev tree bench rc=$?"); fi
