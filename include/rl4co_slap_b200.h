@@ -269,8 +269,9 @@ int rl4co_encoder_attention(int64_t B, int32_t N, const float *qkv, float *out, 
  * softmax and P V stay fp32 on the CUDA cores.  The kernel the encoder uses; the one above is the SIMT cross-check. */
 int rl4co_encoder_attention_tc(int64_t B, int32_t N, const float *qkv, float *out, rl4co_stream_t stream);
 /* Kernel behind rl4co_encoder_attention_tc: 0 = auto (N <= 112: P V on the tensor cores as well, P kept in TMEM as fp16
- * hi / lo pairs, V as a range-scaled fp16 operand - kernel 3; above that kernel 1), 1 = scores only, 2 = both GEMMs as
- * 3xTF32, 3 = both GEMMs with the fp16 P V (2 and 3: error for N > 112).  Process-wide; for cross-checks and timing. */
+ * hi / lo pairs, V as a range-scaled fp16 operand, four consumer groups - kernel 4; above that kernel 1), 1 = scores only,
+ * 2 = both GEMMs as 3xTF32, 3 = both GEMMs with the fp16 P V and a one-pass softmax, 4 = the same with a two-pass softmax and
+ * four units in flight (2-4: error for N > 112).  Process-wide; for cross-checks and timing. */
 int rl4co_set_attention_impl(int32_t impl);
 
 /* Graph context: gctx[b] = Wfixed . mean_n h[b,n,:]  (am/decoder.py:225-228). */

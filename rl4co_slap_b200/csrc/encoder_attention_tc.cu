@@ -956,6 +956,319 @@ encoder_attention_tc3_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 
 }  // namespace enctc3
 
+
+// ============================================================================================
+// enctc3 with FOUR consumer groups (21 warps) and the two-pass, rolled softmax of enctc2: what limited enctc3 was warps per
+// scheduler x registers - its one-pass softmax holds the 112-register score row, which caps the CTA at 13 warps.  Here the
+// consumers read the row twice in 16-column chunks (~50 registers), so 16 consumer warps fit (80 registers per thread) and
+// four units are in flight instead of two.  P goes back IN PLACE per chunk: the 16 score columns of chunk c become 8 columns
+// of fp16 hi pairs and 8 columns of lo pairs, so a buffer is 112 + 16 (O) = 128 columns and four of them fill the tensor
+// memory.  Everything else as enctc3: 3xTF32 scores, kind::f16 P V, V as an MN-major range-scaled operand staged by the group.
+namespace enctc4 {
+using namespace tcu;
+using enctc::ex2f;
+using enctc2::tmem_ld16;
+using enctc3::tmem_st8;
+using enctc3::umma_f16_ts;
+using enctc3::rn_tf32;
+
+constexpr int H = 8, D = 16, E = 128, NK = 112;
+constexpr int kGroups = 4;                              // consumer groups = TMEM buffers = V slots = units in flight
+constexpr int TILE_BYTES = 128 * 128;
+constexpr int V_HALF = 128 * 16, VT_BYTES = 2 * V_HALF, VT_SLOT_BYTES = 2 * VT_BYTES, V_STAGE_BYTES = 4 * 128 * 16;
+constexpr int QK_STAGE_BYTES = 4 * TILE_BYTES, QK_STAGES = 2;
+constexpr int kProducerWarps = 4, kConsumerWarps = 4 * kGroups;
+constexpr int kThreads = (1 + kProducerWarps + kConsumerWarps) * 32;       // 672
+constexpr int SMEM_BYTES = 1024 + QK_STAGES * QK_STAGE_BYTES + kGroups * (VT_SLOT_BYTES + V_STAGE_BYTES) + 512;
+constexpr uint32_t kIdescS = make_idesc_tf32(128, NK);
+constexpr uint32_t kIdescO = make_idesc_f16(128, D) | (1u << 16);
+constexpr int BUF_COLS = 128, COL_O = NK;
+constexpr float kPShift = 14.f;
+
+__global__ void __launch_bounds__(kThreads, 1)
+encoder_attention_tc4_kernel(int64_t B, int N, const float *__restrict__ qkv, float *__restrict__ out) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char *sVT = smem + QK_STAGES * QK_STAGE_BYTES;
+    unsigned char *sVraw = sVT + kGroups * VT_SLOT_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sVraw + kGroups * V_STAGE_BYTES);
+    uint64_t *in_full = bars, *qk_empty = bars + 2;             // [2] each
+    uint64_t *s_full = bars + 4, *p_full = bars + 8, *o_full = bars + 12, *buf_free = bars + 16, *v_rng = bars + 20;   // [kGroups] each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 24);
+    uint32_t *s_amax = tmem_slot + 4;                           // [group][unit parity][warp of the group]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t n_inst = blockIdx.x < B ? (B - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t n_units = n_inst * H;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&in_full[s], kProducerWarps);
+            mbar_init(&qk_empty[s], 1);
+        }
+        for (int s = 0; s < kGroups; ++s) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&p_full[s], 4);
+            mbar_init(&o_full[s], 1);
+            mbar_init(&buf_free[s], 4);
+            mbar_init(&v_rng[s], 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================================= MMA issue: QK(i), then PV(i - 2)
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
+        const uint32_t dv0 = ((smem_u32(sVT) >> 4) & 0x3FFFu) | enctc3::kDescLoV;
+        for (int64_t i = 0; i < n_units + 2; ++i) {
+            if (i < n_units) {
+                const int st = (int)(i & 1), x = (int)(i & (kGroups - 1));
+                mbar_wait_bounded(&in_full[st], (unsigned)((i >> 1) & 1));
+                mbar_wait_bounded(&buf_free[x], (unsigned)((i / kGroups) & 1) ^ 1u);
+                tc_fence_after();
+                const uint32_t q_hi = d0 + (uint32_t)((st * QK_STAGE_BYTES) >> 4), q_lo = q_hi + (TILE_BYTES >> 4);
+                const uint32_t k_hi = q_hi + 2 * (TILE_BYTES >> 4), k_lo = q_hi + 3 * (TILE_BYTES >> 4);
+                const uint32_t d = tmem_u + (uint32_t)(x * BUF_COLS);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k8 = 0; k8 < D / 8; ++k8) {
+                        umma_tf32(d, q_lo + 2 * k8, k_hi + 2 * k8, kIdescS, (unsigned)(k8 != 0));
+                        umma_tf32(d, q_hi + 2 * k8, k_lo + 2 * k8, kIdescS, 1u);
+                        umma_tf32(d, q_hi + 2 * k8, k_hi + 2 * k8, kIdescS, 1u);
+                    }
+                    umma_commit(&qk_empty[st]);
+                    umma_commit(&s_full[x]);
+                }
+                __syncwarp();
+            }
+            if (i >= 2) {
+                const int64_t u = i - 2;
+                const int x = (int)(u & (kGroups - 1));
+                mbar_wait_bounded(&p_full[x], (unsigned)((u / kGroups) & 1));
+                tc_fence_after();
+                const uint32_t vt_hi = dv0 + (uint32_t)((x * VT_SLOT_BYTES) >> 4), vt_lo = vt_hi + (VT_BYTES >> 4);
+                const uint32_t pb = tmem_u + (uint32_t)(x * BUF_COLS);
+                const uint32_t o = pb + COL_O;
+                if (elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < NK / 16; ++ks) {      // chunk ks: hi pairs in columns 16 ks .. + 7, lo pairs in + 8 .. + 15
+                        umma_f16_ts(o, pb + 16 * ks + 8, vt_hi + 16 * ks, kIdescO, (unsigned)(ks != 0));
+                        umma_f16_ts(o, pb + 16 * ks, vt_lo + 16 * ks, kIdescO, 1u);
+                        umma_f16_ts(o, pb + 16 * ks, vt_hi + 16 * ks, kIdescO, 1u);
+                    }
+                    umma_commit(&o_full[x]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp <= kProducerWarps) {
+        // ================================================= producers: thread = node row; Q and K of one (b, h) per unit
+        const int row = tid - 32;
+        const float scale = 0.25f * 1.4426950408889634f;
+        if (row >= N) {
+            const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+            for (int s = 0; s < QK_STAGES; ++s)
+                for (int img = 0; img < 4; ++img)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        *reinterpret_cast<uint4 *>(smem + s * QK_STAGE_BYTES + img * TILE_BYTES + swz(row, c)) = z;
+        }
+        for (int64_t i = 0; i < n_units; ++i) {
+            const int st_i = (int)(i & 1), h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            float4 q[4], k[4];
+            if (row < N) {                                      // loads first: they fly while we wait for the stage
+                const float4 *p = reinterpret_cast<const float4 *>(qkv + (b * N + row) * (3 * E) + h * D);
+                if (h == 0 && i + H < n_units) {                // this row of the CTA's next instance -> L2 (12 lines)
+                    const char *nx = reinterpret_cast<const char *>(qkv + ((b + gridDim.x) * N + row) * (3 * E));
+#pragma unroll
+                    for (int c = 0; c < 12; ++c) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + 128 * c));
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { q[c] = __ldg(p + c); k[c] = __ldg(p + E / 4 + c); }
+            }
+            mbar_wait_bounded(&qk_empty[st_i], (unsigned)((i >> 1) & 1) ^ 1u);
+            if (row < N) {
+                unsigned char *st = smem + st_i * QK_STAGE_BYTES;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t off = swz(row, c);
+                    const float4 a = make_float4(q[c].x * scale, q[c].y * scale, q[c].z * scale, q[c].w * scale);
+                    uint4 hi, lo;
+                    hi.x = rn_tf32(a.x); hi.y = rn_tf32(a.y); hi.z = rn_tf32(a.z); hi.w = rn_tf32(a.w);
+                    lo.x = __float_as_uint(a.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(a.y - __uint_as_float(hi.y));
+                    lo.z = __float_as_uint(a.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(a.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + TILE_BYTES + off) = lo;
+                    const float4 kk = k[c];
+                    hi.x = rn_tf32(kk.x); hi.y = rn_tf32(kk.y); hi.z = rn_tf32(kk.z); hi.w = rn_tf32(kk.w);
+                    lo.x = __float_as_uint(kk.x - __uint_as_float(hi.x)); lo.y = __float_as_uint(kk.y - __uint_as_float(hi.y));
+                    lo.z = __float_as_uint(kk.z - __uint_as_float(hi.z)); lo.w = __float_as_uint(kk.w - __uint_as_float(hi.w));
+                    *reinterpret_cast<uint4 *>(st + 2 * TILE_BYTES + off) = hi;
+                    *reinterpret_cast<uint4 *>(st + 3 * TILE_BYTES + off) = lo;
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&in_full[st_i]);
+        }
+    } else {
+        // ================================================= consumers: thread = query row = TMEM lane; group g: units g, g + 4, ...
+        const int cw = warp - (1 + kProducerWarps);             // 0..15
+        const int grp = cw >> 2, quarter = warp & 3;
+        const int row = 32 * quarter + lane;
+        const uint32_t t0 = tmem_base + ((uint32_t)(32 * quarter) << 16) + (uint32_t)(grp * BUF_COLS);
+        const int n_full = N >> 4, tail = N & 15;
+        unsigned char *vimg = sVT + grp * VT_SLOT_BYTES + row * 16;
+        unsigned char *vraw = sVraw + grp * V_STAGE_BYTES + row * 16;
+        auto fetch_v = [&](int64_t i) {
+            if (row < N && i < n_units) {
+                const float *p = qkv + ((blockIdx.x + (i >> 3) * gridDim.x) * N + row) * (3 * E) + 2 * E + (int)(i & 7) * D;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(vraw + c * 2048)), "l"(p + 4 * c)
+                                 : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        fetch_v(grp);
+        for (int64_t i = grp; i < n_units; i += kGroups) {
+            const int h = (int)(i & 7);
+            const int64_t b = blockIdx.x + (i >> 3) * gridDim.x;
+            const unsigned ph = (unsigned)((i / kGroups) & 1);
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            uint32_t *xch = s_amax + (grp * 2 + (int)ph) * 4;
+            {                                                   // post the range of this warp's V rows (see enctc3)
+                float amax = 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v4 = row < N ? *reinterpret_cast<const float4 *>(vraw + c * 2048) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    amax = fmaxf(fmaxf(amax, fmaxf(fabsf(v4.x), fabsf(v4.y))), fmaxf(fabsf(v4.z), fabsf(v4.w)));
+                }
+                uint32_t ab = __float_as_uint(amax);
+                asm("redux.sync.max.u32 %0, %1, 0xffffffff;" : "=r"(ab) : "r"(ab));
+                if (lane == 0) {
+                    xch[quarter] = ab;
+                    mbar_arrive(&v_rng[grp]);
+                }
+            }
+            mbar_wait_bounded(&s_full[grp], ph);
+            tc_fence_after();
+            uint32_t sv[16];
+            float m = -INFINITY;                                // pass 1: row maximum over the N real keys
+#pragma unroll 1
+            for (int c = 0; c < n_full; ++c) {
+                tmem_ld16(t0 + c * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) m = fmaxf(m, __uint_as_float(sv[j]));
+            }
+            if (tail) {
+                tmem_ld16(t0 + n_full * 16, sv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (j < tail) m = fmaxf(m, __uint_as_float(sv[j]));
+            }
+            m -= kPShift;
+            float l = 0.f;                                      // pass 2: P = 2^(s - max + 14) as fp16 pairs, in place per chunk
+            uint32_t hi[8], lo[8];
+#pragma unroll 1
+            for (int c = 0; c < n_full; ++c) {
+                tmem_ld16(t0 + c * 16, sv);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float p0 = ex2f(__uint_as_float(sv[2 * k]) - m), p1 = ex2f(__uint_as_float(sv[2 * k + 1]) - m);
+                    l += p0 + p1;
+                    split_f16x2_trunc(p0, p1, hi[k], lo[k]);
+                }
+                tmem_st8(t0 + c * 16, hi);
+                tmem_st8(t0 + c * 16 + 8, lo);
+            }
+            int c_next = n_full;
+            if (tail) {
+                tmem_ld16(t0 + n_full * 16, sv);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float p0 = 2 * k < tail ? ex2f(__uint_as_float(sv[2 * k]) - m) : 0.f;
+                    const float p1 = 2 * k + 1 < tail ? ex2f(__uint_as_float(sv[2 * k + 1]) - m) : 0.f;
+                    l += p0 + p1;
+                    split_f16x2_trunc(p0, p1, hi[k], lo[k]);
+                }
+                tmem_st8(t0 + n_full * 16, hi);
+                tmem_st8(t0 + n_full * 16 + 8, lo);
+                c_next = n_full + 1;
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) hi[k] = 0u;
+#pragma unroll 1
+            for (int c = c_next; c < NK / 16; ++c) {            // key columns beyond N: P = 0
+                tmem_st8(t0 + c * 16, hi);
+                tmem_st8(t0 + c * 16 + 8, hi);
+            }
+            float unscale;
+            {                                                   // V as the MN-major fp16 operand, range-scaled (see enctc3)
+                mbar_wait_bounded(&v_rng[grp], ph);
+                const uint4 all = *reinterpret_cast<const uint4 *>(xch);
+                const uint32_t ab = max(max(all.x, all.y), max(all.z, all.w));
+                int e = (int)(ab >> 23);
+                e = e < 27 ? 27 : e;
+                const float vscale = __uint_as_float((uint32_t)(267 - e) << 23);
+                unscale = __uint_as_float((uint32_t)(e - 13) << 23);
+                uint32_t vh[8], vl[8];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v4 = row < N ? *reinterpret_cast<const float4 *>(vraw + c * 2048) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    split_f16x2_trunc(v4.x * vscale, v4.y * vscale, vh[2 * c], vl[2 * c]);
+                    split_f16x2_trunc(v4.z * vscale, v4.w * vscale, vh[2 * c + 1], vl[2 * c + 1]);
+                }
+                *reinterpret_cast<uint4 *>(vimg) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
+                *reinterpret_cast<uint4 *>(vimg + V_HALF) = make_uint4(vh[4], vh[5], vh[6], vh[7]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
+                *reinterpret_cast<uint4 *>(vimg + VT_BYTES + V_HALF) = make_uint4(vl[4], vl[5], vl[6], vl[7]);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[grp]);
+            fetch_v(i + kGroups);
+            mbar_wait_bounded(&o_full[grp], ph);
+            tc_fence_after();
+            tmem_ld16(t0 + COL_O, sv);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&buf_free[grp]);
+            if (row < N) {
+                const float inv = unscale / l;
+                float4 *dst = reinterpret_cast<float4 *>(out + (b * N + row) * E + h * D);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    dst[c] = make_float4(__uint_as_float(sv[4 * c]) * inv, __uint_as_float(sv[4 * c + 1]) * inv,
+                                         __uint_as_float(sv[4 * c + 2]) * inv, __uint_as_float(sv[4 * c + 3]) * inv);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace enctc4
+
 int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, int impl, cudaStream_t stream) {
     static int sm_count = 0;
     if (sm_count == 0) {
@@ -965,14 +1278,15 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
         if (sm_count <= 0) sm_count = 148;
     }
     const int64_t grid = B < sm_count ? B : sm_count;
-    // 0 automatic: both GEMMs on the tensor cores with P as fp16 pairs (enctc3) for N <= 112, else scores only (enctc)
-    const int kind = impl == 0 ? (N <= enctc3::NK ? 3 : 1) : impl;
+    // 0 automatic: both GEMMs on the tensor cores with P as fp16 pairs and four consumer groups (enctc4) for N <= 112, else
+    // scores only (enctc)
+    const int kind = impl == 0 ? (N <= enctc4::NK ? 4 : 1) : impl;
     if (kind >= 2 && N > enctc2::NK) {
         set_error("encoder_attention(tc): the two-GEMM kernels need N <= %d, got %d", enctc2::NK, N);
         return 1;
     }
-    const int smem = kind == 3 ? enctc3::SMEM_BYTES : (kind == 2 ? enctc2::SMEM_BYTES : enctc::SMEM_BYTES);
-    const void *fn = kind == 3 ? (const void *)enctc3::encoder_attention_tc3_kernel
+    const int smem = kind == 4 ? enctc4::SMEM_BYTES : kind == 3 ? enctc3::SMEM_BYTES : (kind == 2 ? enctc2::SMEM_BYTES : enctc::SMEM_BYTES);
+    const void *fn = kind == 4 ? (const void *)enctc4::encoder_attention_tc4_kernel : kind == 3 ? (const void *)enctc3::encoder_attention_tc3_kernel
                                : (kind == 2 ? (const void *)enctc2::encoder_attention_tc2_kernel
                                             : (const void *)enctc::encoder_attention_tc_kernel);
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -980,7 +1294,9 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
         set_error("encoder_attention(tc): cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
         return 2;
     }
-    if (kind == 3)
+    if (kind == 4)
+        enctc4::encoder_attention_tc4_kernel<<<(unsigned)grid, enctc4::kThreads, smem, stream>>>(B, N, qkv, out);
+    else if (kind == 3)
         enctc3::encoder_attention_tc3_kernel<<<(unsigned)grid, enctc3::kThreads, smem, stream>>>(B, N, qkv, out);
     else if (kind == 2)
         enctc2::encoder_attention_tc2_kernel<<<(unsigned)grid, enctc2::kThreads, smem, stream>>>(B, N, qkv, out);
@@ -994,10 +1310,10 @@ int launch_encoder_attention_tc(int64_t B, int N, const float *qkv, float *out, 
 
 using namespace rl4co;
 
-static int g_attention_impl = 0;    // 0 auto (enctc3 for N <= 112), 1 Q K^T only, 2 two-GEMM kernel 3xTF32, 3 two-GEMM kernel with fp16 P V
+static int g_attention_impl = 0;    // 0 auto (enctc4 for N <= 112), 1 Q K^T only, 2 two-GEMM kernel 3xTF32, 3 / 4 two-GEMM kernels with fp16 P V
 
 extern "C" int rl4co_set_attention_impl(int32_t impl) {
-    RL4CO_REQUIRE(impl >= 0 && impl <= 3, "set_attention_impl: 0 auto, 1 scores on tensor cores, 2 both GEMMs (TF32), 3 both GEMMs (fp16 P V), got %d", impl);
+    RL4CO_REQUIRE(impl >= 0 && impl <= 4, "set_attention_impl: 0 auto, 1 scores on tensor cores, 2 both GEMMs (TF32), 3 / 4 both GEMMs (fp16 P V; 4: four consumer groups), got %d", impl);
     g_attention_impl = impl;
     return 0;
 }

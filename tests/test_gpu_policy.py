@@ -446,7 +446,8 @@ def test_encoder_attention_kernels_match_fp64(B, N, amp, dev):
     variants = [("rl4co_encoder_attention_tc", 1), ("rl4co_encoder_attention", 0)]
     if N <= 112:
         variants.append(("rl4co_encoder_attention_tc", 2))     # P V on the tensor cores too (P in TMEM)
-        variants.append(("rl4co_encoder_attention_tc", 3))     # ... with P and V as fp16 hi / lo pairs (the default)
+        variants.append(("rl4co_encoder_attention_tc", 3))     # ... with P and V as fp16 hi / lo pairs
+        variants.append(("rl4co_encoder_attention_tc", 4))     # ... and four consumer groups (the default)
     try:
         for fn, impl in variants:
             _lib.call("rl4co_set_attention_impl", impl)

@@ -26,7 +26,7 @@ for B, N, amp in ((3, 100, 1.0), (7, 5, 1.0), (300, 50, 3.0), (150, 128, 1.0), (
     r = ref64(qkv, B, N)
     _lib.call("rl4co_set_attention_impl", 1)
     tc = run("rl4co_encoder_attention_tc", B, N, qkv)
-    e2 = e3 = float("nan")
+    e2 = e3 = e4 = float("nan")
     if N <= 112:
         _lib.call("rl4co_set_attention_impl", 2)
         tc2 = run("rl4co_encoder_attention_tc", B, N, qkv)
@@ -34,13 +34,16 @@ for B, N, amp in ((3, 100, 1.0), (7, 5, 1.0), (300, 50, 3.0), (150, 128, 1.0), (
         _lib.call("rl4co_set_attention_impl", 3)
         tc3 = run("rl4co_encoder_attention_tc", B, N, qkv)
         e3 = (tc3.double() - r).abs().max().item()
+        _lib.call("rl4co_set_attention_impl", 4)
+        tc4 = run("rl4co_encoder_attention_tc", B, N, qkv)
+        e4 = (tc4.double() - r).abs().max().item()
     si = run("rl4co_encoder_attention", B, N, qkv)
     s = r.abs().max().item()
-    print(f"B={B} N={N} amp={amp}: max|ref| {s:.3f}  err tc(QK) {(tc.double()-r).abs().max().item():.3e}  err tc(QK+PV) {e2:.3e}  err tc(QK + fp16 PV) {e3:.3e}  err simt {(si.double()-r).abs().max().item():.3e}", flush=True)
+    print(f"B={B} N={N} amp={amp}: max|ref| {s:.3f}  err tc(QK) {(tc.double()-r).abs().max().item():.3e}  err tc(QK+PV) {e2:.3e}  err tc(QK + fp16 PV) {e3:.3e} / 4 groups {e4:.3e}  err simt {(si.double()-r).abs().max().item():.3e}", flush=True)
 B, N = 16384, 100
 qkv = torch.randn(B, N, 384, device=dev)
 out = torch.empty(B, N, 128, device=dev)
-for name, impl in (("rl4co_encoder_attention_tc", 3), ("rl4co_encoder_attention_tc", 2), ("rl4co_encoder_attention_tc", 1), ("rl4co_encoder_attention", 0)):
+for name, impl in (("rl4co_encoder_attention_tc", 4), ("rl4co_encoder_attention_tc", 3), ("rl4co_encoder_attention_tc", 2), ("rl4co_encoder_attention_tc", 1), ("rl4co_encoder_attention", 0)):
     _lib.call("rl4co_set_attention_impl", impl)
     t = timed(lambda: _lib.call(name, B, N, _lib.ptr(qkv), _lib.ptr(out), _lib.stream_ptr(dev)))
     print(f"{name} impl {impl}: {t:.3f} ms per {B} x {N}", flush=True)
