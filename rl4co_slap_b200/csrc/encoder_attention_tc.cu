@@ -591,6 +591,7 @@ encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 // 2.1 ms: eight warps are two per scheduler, too few to cover their own latencies); 96 of the 112 score columns resident
 // and 16 re-read (1.55 ms).  What limits it is warps per scheduler x registers: the one-pass softmax wants the 112-register
 // row, which caps the CTA at 13 warps.
+// -> enctc4 below (the default): the two-pass rolled softmax at 72 registers, four consumer groups, 1.34 ms.
 namespace enctc3 {
 using namespace tcu;
 using enctc::ex2f;
