@@ -591,7 +591,7 @@ encoder_attention_tc2_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
 // 2.1 ms: eight warps are two per scheduler, too few to cover their own latencies); 96 of the 112 score columns resident
 // and 16 re-read (1.55 ms).  What limits it is warps per scheduler x registers: the one-pass softmax wants the 112-register
 // row, which caps the CTA at 13 warps.
-// -> enctc4 below (the default): the two-pass rolled softmax at 72 registers, four consumer groups, 1.34 ms.
+// -> enctc4 below (the default): the two-pass rolled softmax at 72 registers, four consumer groups, 1.30 ms.
 namespace enctc3 {
 using namespace tcu;
 using enctc::ex2f;
@@ -985,6 +985,15 @@ constexpr uint32_t kIdescS = make_idesc_tf32(128, NK);
 constexpr uint32_t kIdescO = make_idesc_f16(128, D) | (1u << 16);
 constexpr int BUF_COLS = 128, COL_O = NK;
 constexpr float kPShift = 14.f;
+#ifndef ENC4_LAG
+#define ENC4_LAG 1                                      // the MMA warp issues P V of unit i - ENC4_LAG after Q K^T of unit i
+                                                        // (measured per 16 384 x 100: lag 1 1.30 ms, 2 1.34, 3 1.37; unrolling
+                                                        // the chunk loop by 2 / 4: 1.32 / 1.51 ms)
+#endif
+#ifndef ENC4_UNROLL
+#define ENC4_UNROLL 1
+#endif
+constexpr int kChunkUnroll = ENC4_UNROLL;
 
 __global__ void __launch_bounds__(kThreads, 1)
 encoder_attention_tc4_kernel(int64_t B, int N, const float *__restrict__ qkv, float *__restrict__ out) {
@@ -1028,11 +1037,11 @@ encoder_attention_tc4_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ================================================= MMA issue: QK(i), then PV(i - 2)
+        // ================================================= MMA issue: QK(i), then PV(i - ENC4_LAG)
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
         const uint32_t d0 = (uint32_t)smem_desc(smem_u32(smem));
         const uint32_t dv0 = ((smem_u32(sVT) >> 4) & 0x3FFFu) | enctc3::kDescLoV;
-        for (int64_t i = 0; i < n_units + 2; ++i) {
+        for (int64_t i = 0; i < n_units + ENC4_LAG; ++i) {
             if (i < n_units) {
                 const int st = (int)(i & 1), x = (int)(i & (kGroups - 1));
                 mbar_wait_bounded(&in_full[st], (unsigned)((i >> 1) & 1));
@@ -1053,8 +1062,8 @@ encoder_attention_tc4_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
                 }
                 __syncwarp();
             }
-            if (i >= 2) {
-                const int64_t u = i - 2;
+            if (i >= ENC4_LAG) {
+                const int64_t u = i - ENC4_LAG;
                 const int x = (int)(u & (kGroups - 1));
                 mbar_wait_bounded(&p_full[x], (unsigned)((u / kGroups) & 1));
                 tc_fence_after();
@@ -1183,7 +1192,7 @@ encoder_attention_tc4_kernel(int64_t B, int N, const float *__restrict__ qkv, fl
             m -= kPShift;
             float l = 0.f;                                      // pass 2: P = 2^(s - max + 14) as fp16 pairs, in place per chunk
             uint32_t hi[8], lo[8];
-#pragma unroll 1
+#pragma unroll kChunkUnroll
             for (int c = 0; c < n_full; ++c) {
                 tmem_ld16(t0 + c * 16, sv);
 #pragma unroll
